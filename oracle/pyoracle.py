@@ -1,0 +1,204 @@
+"""TEST INFRASTRUCTURE ONLY: ctypes bindings for the oracles.
+
+ * `RefScene`  - oracle/_ref/libpsref*.so, the reference's own SIMD polygonizer compiled from
+                 /root/reference by oracle/Makefile (unmodified, or capacity-widened variants).
+ * `COracle`   - oracle/libps_oracle.so, the plain-C restatement (oracle/ps_oracle.c).
+
+Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs may import this.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+
+
+def _p(a, t):
+    return a.ctypes.data_as(C.POINTER(t))
+
+
+class _RefDesc(C.Structure):
+    _fields_ = [
+        ("n_prims", C.c_int32), ("n_ops", C.c_int32), ("n_mats", C.c_int32),
+        ("prim_type", C.POINTER(C.c_int32)),
+        ("prim_pos", C.POINTER(C.c_float)), ("prim_dir", C.POINTER(C.c_float)),
+        ("prim_res", C.POINTER(C.c_float)), ("prim_color", C.POINTER(C.c_float)),
+        ("prim_mat", C.POINTER(C.c_int32)),
+        ("op_type", C.POINTER(C.c_int32)), ("op_left", C.POINTER(C.c_int32)),
+        ("op_right", C.POINTER(C.c_int32)), ("op_kind", C.POINTER(C.c_int32)),
+        ("op_res", C.POINTER(C.c_float)),
+        ("mats_bwd", C.POINTER(C.c_float)), ("mats_fwd", C.POINTER(C.c_float)),
+    ]
+
+
+def ref_lib_path(n_nodes: int = 128) -> str:
+    if n_nodes <= 128:
+        name = "libpsref.so"
+    elif n_nodes <= 1024:
+        name = "libpsref_w1k.so"
+    else:
+        name = "libpsref_w16k.so"
+    return os.path.join(HERE, "_ref", name)
+
+
+def ref_available(n_nodes: int = 128) -> bool:
+    return os.path.exists(ref_lib_path(n_nodes))
+
+
+_libs = {}
+
+
+def _load_ref(path):
+    if path in _libs:
+        return _libs[path]
+    lib = C.CDLL(path)
+    lib.psref_scene_create.restype = C.c_void_p
+    lib.psref_scene_create.argtypes = [C.POINTER(_RefDesc)]
+    lib.psref_scene_destroy.argtypes = [C.c_void_p]
+    lib.psref_prepare_bboxes.argtypes = [C.c_void_p, C.c_float]
+    lib.psref_get_bbox.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
+    lib.psref_set_bbox.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
+    lib.psref_get_prim_boxes.argtypes = [C.c_void_p, C.c_void_p]
+    lib.psref_get_op_boxes.argtypes = [C.c_void_p, C.c_void_p]
+    lib.psref_pad_op_boxes.argtypes = [C.c_void_p, C.c_float]
+    lib.psref_count_mpus.restype = C.c_uint32
+    lib.psref_count_mpus.argtypes = [C.c_void_p, C.c_float]
+    lib.psref_field.argtypes = [C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p]
+    lib.psref_field_color_normal.argtypes = [C.c_void_p, C.c_int64] + [C.c_void_p] * 4
+    lib.psref_polygonize.argtypes = [C.c_void_p, C.c_float, C.c_void_p]
+    lib.psref_mpu_info.argtypes = [C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p]
+    lib.psref_mpu_copy.argtypes = [C.c_void_p, C.c_uint32] + [C.c_void_p] * 4
+    lib.psref_mesh_concat.argtypes = [C.c_void_p] + [C.c_void_p] * 4
+    lib.psref_polygonize_stream.argtypes = [C.c_void_p, C.c_float, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]
+    lib.psref_stream_counts.restype = C.c_int64
+    lib.psref_stream_counts.argtypes = [C.c_void_p, C.c_void_p]
+    lib.psref_stream_copy.argtypes = [C.c_void_p] + [C.c_void_p] * 6
+    lib.psref_set_threads.argtypes = [C.c_int]
+    lib.psref_build_info.argtypes = [C.c_void_p]
+    _libs[path] = lib
+    return lib
+
+
+class RefScene:
+    """A scene held by the reference's own SOA structs (PS_Polygonizer.h:96-172)."""
+
+    def __init__(self, soa: dict, lib_path: str | None = None):
+        n = max(soa["n_prims"], soa["n_ops"])
+        self.lib = _load_ref(lib_path or ref_lib_path(n))
+        self._keep = {k: np.ascontiguousarray(v) for k, v in soa.items() if isinstance(v, np.ndarray)}
+        k = self._keep
+        d = _RefDesc(soa["n_prims"], soa["n_ops"], soa["n_mats"],
+                     _p(k["prim_type"], C.c_int32), _p(k["prim_pos"], C.c_float), _p(k["prim_dir"], C.c_float),
+                     _p(k["prim_res"], C.c_float), _p(k["prim_color"], C.c_float), _p(k["prim_mat"], C.c_int32),
+                     _p(k["op_type"], C.c_int32), _p(k["op_left"], C.c_int32), _p(k["op_right"], C.c_int32),
+                     _p(k["op_kind"], C.c_int32), _p(k["op_res"], C.c_float),
+                     _p(k["mats_bwd"], C.c_float), _p(k["mats_fwd"], C.c_float))
+        self.h = self.lib.psref_scene_create(C.byref(d))
+        if not self.h:
+            raise RuntimeError("psref_scene_create failed (capacity or node type)")
+        self.n_prims, self.n_ops = soa["n_prims"], soa["n_ops"]
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            self.lib.psref_scene_destroy(self.h)
+            self.h = None
+
+    def build_info(self):
+        out = np.zeros(16, np.int64)
+        self.lib.psref_build_info(out.ctypes.data)
+        return dict(max_tree_nodes=int(out[0]), max_mpu_count=int(out[1]), sizeof_mpu=int(out[2]),
+                    sizeof_polympus=int(out[3]), simd_flen=int(out[4]), grid_dim=int(out[5]),
+                    sizeof_prims=int(out[6]), sizeof_ops=int(out[7]), sizeof_primmats=int(out[8]),
+                    sizeof_boxmats=int(out[9]))
+
+    def set_threads(self, n):
+        self.lib.psref_set_threads(int(n))
+
+    def prepare_bboxes(self, cellsize):
+        return self.lib.psref_prepare_bboxes(self.h, float(cellsize))
+
+    def bbox(self):
+        lo, hi = np.zeros(3, np.float32), np.zeros(3, np.float32)
+        self.lib.psref_get_bbox(self.h, lo.ctypes.data, hi.ctypes.data)
+        return lo, hi
+
+    def set_bbox(self, lo, hi):
+        lo, hi = np.ascontiguousarray(lo, np.float32), np.ascontiguousarray(hi, np.float32)
+        self.lib.psref_set_bbox(self.h, lo.ctypes.data, hi.ctypes.data)
+
+    def prim_boxes(self):
+        out = np.zeros((self.n_prims, 6), np.float32)
+        self.lib.psref_get_prim_boxes(self.h, out.ctypes.data)
+        return out
+
+    def op_boxes(self):
+        out = np.zeros((max(self.n_ops, 1), 6), np.float32)
+        self.lib.psref_get_op_boxes(self.h, out.ctypes.data)
+        return out[:self.n_ops]
+
+    def pad_op_boxes(self, pad):
+        self.lib.psref_pad_op_boxes(self.h, float(pad))
+
+    def count_mpus(self, cellsize):
+        return int(self.lib.psref_count_mpus(self.h, float(cellsize)))
+
+    def field(self, xyz):
+        xyz = np.ascontiguousarray(xyz, np.float32).reshape(-1, 3)
+        out = np.zeros(len(xyz), np.float32)
+        self.lib.psref_field(self.h, len(xyz), xyz.ctypes.data, out.ctypes.data)
+        return out
+
+    def field_color_normal(self, xyz):
+        xyz = np.ascontiguousarray(xyz, np.float32).reshape(-1, 3)
+        n = len(xyz)
+        f, col, nrm = np.zeros(n, np.float32), np.zeros((n, 3), np.float32), np.zeros((n, 3), np.float32)
+        self.lib.psref_field_color_normal(self.h, n, xyz.ctypes.data, f.ctypes.data, col.ctypes.data, nrm.ctypes.data)
+        return f, col, nrm
+
+    def polygonize(self, cellsize):
+        """Whole-grid reference Polygonize. Returns (ret, stats dict)."""
+        st = np.zeros(8, np.int64)
+        ret = self.lib.psref_polygonize(self.h, float(cellsize), st.ctypes.data)
+        return ret, dict(mpus=int(st[0]), crossed=int(st[1]), vertices=int(st[2]), triangles=int(st[3]),
+                         simd_evals=int(st[4]))
+
+    def mpu(self, idx):
+        info, lo = np.zeros(3, np.int32), np.zeros(3, np.float32)
+        self.lib.psref_mpu_info(self.h, idx, info.ctypes.data, lo.ctypes.data)
+        nv, nt = int(info[0]), int(info[1])
+        pos, nrm, col = (np.zeros((nv, 3), np.float32) for _ in range(3))
+        tri = np.zeros((nt, 3), np.uint16)
+        if nv or nt:
+            self.lib.psref_mpu_copy(self.h, idx, pos.ctypes.data, nrm.ctypes.data, col.ctypes.data, tri.ctypes.data)
+        return dict(lo=lo, nv=nv, nt=nt, field_evals=int(info[2]), pos=pos, nrm=nrm, col=col, tri=tri)
+
+    def mesh(self, stats):
+        nv, nt = stats["vertices"], stats["triangles"]
+        pos, nrm, col = (np.zeros((nv, 3), np.float32) for _ in range(3))
+        tri = np.zeros((nt, 3), np.uint32)
+        self.lib.psref_mesh_concat(self.h, pos.ctypes.data, nrm.ctypes.data, col.ctypes.data, tri.ctypes.data)
+        return pos, nrm, col, tri
+
+    def polygonize_stream(self, cellsize, b0=None, e0=None, keep_mesh=False):
+        st = np.zeros(8, np.int64)
+        b = np.ascontiguousarray(b0, np.int32) if b0 is not None else None
+        e = np.ascontiguousarray(e0, np.int32) if e0 is not None else None
+        ret = self.lib.psref_polygonize_stream(self.h, float(cellsize), b.ctypes.data if b is not None else None,
+                                               e.ctypes.data if e is not None else None, int(keep_mesh), st.ctypes.data)
+        stats = dict(mpus=int(st[0]), crossed=int(st[1]), vertices=int(st[2]), triangles=int(st[3]),
+                     simd_evals=int(st[4]), lattice=(int(st[5]), int(st[6]), int(st[7])))
+        if not keep_mesh:
+            return ret, stats
+        c = np.zeros(3, np.int64)
+        self.lib.psref_stream_counts(self.h, c.ctypes.data)
+        nv, nt, nm = int(c[0]), int(c[1]), int(c[2])
+        pos, nrm, col = (np.zeros((nv, 3), np.float32) for _ in range(3))
+        tri = np.zeros((nt, 3), np.uint32)
+        midx, mcnt = np.zeros((nm, 3), np.int32), np.zeros((nm, 2), np.uint32)
+        self.lib.psref_stream_copy(self.h, pos.ctypes.data, nrm.ctypes.data, col.ctypes.data, tri.ctypes.data,
+                                   midx.ctypes.data, mcnt.ctypes.data)
+        stats.update(pos=pos, nrm=nrm, col=col, tri=tri, mpu_idx=midx, mpu_counts=mcnt)
+        return ret, stats
