@@ -202,3 +202,235 @@ class RefScene:
                                    midx.ctypes.data, mcnt.ctypes.data)
         stats.update(pos=pos, nrm=nrm, col=col, tri=tri, mpu_idx=midx, mpu_counts=mcnt)
         return ret, stats
+
+
+# ----------------------------------------------------------------------------------------------
+# plain-C restatement (oracle/ps_oracle.c)
+# ----------------------------------------------------------------------------------------------
+class _SoaDesc(_RefDesc):
+    pass
+
+
+class _Tree(C.Structure):
+    _fields_ = [
+        ("n_nodes", C.c_int32), ("root", C.c_int32),
+        ("type", C.POINTER(C.c_int32)), ("first_child", C.POINTER(C.c_int32)),
+        ("n_children", C.POINTER(C.c_int32)), ("child", C.POINTER(C.c_int32)),
+        ("pos", C.POINTER(C.c_float)), ("dir", C.POINTER(C.c_float)), ("res", C.POINTER(C.c_float)),
+        ("color", C.POINTER(C.c_float)), ("xform", C.POINTER(C.c_float)), ("has_xform", C.POINTER(C.c_uint8)),
+    ]
+
+
+def make_tree_struct(flat: dict):
+    """psgpu_tree (include/psgpu_types.h) over the arrays of blobtree.flatten(); returns (struct, keepalive)."""
+    k = {n: np.ascontiguousarray(v) for n, v in flat.items() if isinstance(v, np.ndarray)}
+    t = _Tree(flat["n_nodes"], flat["root"], _p(k["type"], C.c_int32), _p(k["first_child"], C.c_int32),
+              _p(k["n_children"], C.c_int32), _p(k["child"], C.c_int32), _p(k["pos"], C.c_float),
+              _p(k["dir"], C.c_float), _p(k["res"], C.c_float), _p(k["color"], C.c_float),
+              _p(k["xform"], C.c_float), _p(k["has_xform"], C.c_uint8))
+    return t, k
+
+
+def oracle_lib_path():
+    return os.path.join(HERE, "libps_oracle.so")
+
+
+_olib = None
+
+
+def _load_oracle():
+    global _olib
+    if _olib is not None:
+        return _olib
+    lib = C.CDLL(oracle_lib_path())
+    vp = C.c_void_p
+    lib.pso_simd_create.restype = vp
+    lib.pso_simd_create.argtypes = [C.POINTER(_RefDesc)]
+    lib.pso_simd_destroy.argtypes = [vp]
+    lib.pso_simd_prepare_bboxes.argtypes = [vp, C.c_float]
+    lib.pso_simd_get_bbox.argtypes = [vp, vp, vp]
+    lib.pso_simd_set_bbox.argtypes = [vp, vp, vp]
+    lib.pso_simd_get_prim_boxes.argtypes = [vp, vp]
+    lib.pso_simd_get_op_boxes.argtypes = [vp, vp]
+    lib.pso_simd_pad_op_boxes.argtypes = [vp, C.c_float]
+    lib.pso_count_mpus.restype = C.c_uint32
+    lib.pso_count_mpus.argtypes = [C.c_float, vp, vp]
+    lib.pso_simd_field.argtypes = [vp, C.c_int64, vp, vp]
+    lib.pso_simd_field_color_normal.argtypes = [vp, C.c_int64, vp, vp, vp, vp]
+    lib.pso_simd_mpu_cache.argtypes = [vp, C.c_float, vp, vp, vp]
+    lib.pso_simd_polygonize.argtypes = [vp, C.c_float, C.c_int, vp, vp, C.c_int, vp]
+    lib.pso_simd_result_counts.argtypes = [vp, vp]
+    lib.pso_simd_result_copy.argtypes = [vp] * 7
+    lib.pso_scalar_create.restype = vp
+    lib.pso_scalar_create.argtypes = [C.POINTER(_Tree)]
+    lib.pso_scalar_destroy.argtypes = [vp]
+    lib.pso_scalar_field.argtypes = [vp, C.c_int64, vp, vp]
+    lib.pso_scalar_field_color_normal.argtypes = [vp, C.c_int64, vp, vp, vp, vp]
+    lib.pso_scalar_newton.argtypes = [vp, C.c_int64, vp, vp, vp, vp, C.c_float, C.c_int, vp, vp, vp]
+    lib.pso_scalar_mpu_cache.argtypes = [vp, vp, C.c_float, vp, vp, vp]
+    lib.pso_scalar_polygonize.argtypes = [vp, vp, vp, C.c_float, C.c_int, vp, vp, C.c_int, vp]
+    lib.pso_scalar_result_counts.argtypes = [vp, vp]
+    lib.pso_scalar_result_copy.argtypes = [vp] * 7
+    _olib = lib
+    return lib
+
+
+def _stats(st):
+    return dict(mpus=int(st[0]), crossed=int(st[1]), vertices=int(st[2]), triangles=int(st[3]),
+                simd_evals=int(st[4]), lattice=(int(st[5]), int(st[6]), int(st[7])), over_capacity=int(st[8]))
+
+
+def _fetch_mesh(count_fn, copy_fn, h, stats):
+    c = np.zeros(3, np.int64)
+    count_fn(h, c.ctypes.data)
+    nv, nt, nm = int(c[0]), int(c[1]), int(c[2])
+    pos, nrm, col = (np.zeros((nv, 3), np.float32) for _ in range(3))
+    tri = np.zeros((nt, 3), np.uint32)
+    midx, mcnt = np.zeros((nm, 3), np.int32), np.zeros((nm, 2), np.uint32)
+    copy_fn(h, pos.ctypes.data, nrm.ctypes.data, col.ctypes.data, tri.ctypes.data, midx.ctypes.data, mcnt.ctypes.data)
+    stats.update(pos=pos, nrm=nrm, col=col, tri=tri, mpu_idx=midx, mpu_counts=mcnt)
+
+
+class SimdOracle:
+    """PS_SimdPoly semantics restated in C (binary SOA input, like RefScene)."""
+
+    def __init__(self, soa: dict):
+        self.lib = _load_oracle()
+        self._keep = {k: np.ascontiguousarray(v) for k, v in soa.items() if isinstance(v, np.ndarray)}
+        k = self._keep
+        d = _RefDesc(soa["n_prims"], soa["n_ops"], soa["n_mats"],
+                     _p(k["prim_type"], C.c_int32), _p(k["prim_pos"], C.c_float), _p(k["prim_dir"], C.c_float),
+                     _p(k["prim_res"], C.c_float), _p(k["prim_color"], C.c_float), _p(k["prim_mat"], C.c_int32),
+                     _p(k["op_type"], C.c_int32), _p(k["op_left"], C.c_int32), _p(k["op_right"], C.c_int32),
+                     _p(k["op_kind"], C.c_int32), _p(k["op_res"], C.c_float),
+                     _p(k["mats_bwd"], C.c_float), _p(k["mats_fwd"], C.c_float))
+        self.h = self.lib.pso_simd_create(C.byref(d))
+        if not self.h:
+            raise RuntimeError("pso_simd_create failed")
+        self.n_prims, self.n_ops = soa["n_prims"], soa["n_ops"]
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            self.lib.pso_simd_destroy(self.h)
+            self.h = None
+
+    def prepare_bboxes(self, cellsize):
+        return self.lib.pso_simd_prepare_bboxes(self.h, float(cellsize))
+
+    def bbox(self):
+        lo, hi = np.zeros(3, np.float32), np.zeros(3, np.float32)
+        self.lib.pso_simd_get_bbox(self.h, lo.ctypes.data, hi.ctypes.data)
+        return lo, hi
+
+    def set_bbox(self, lo, hi):
+        lo, hi = np.ascontiguousarray(lo, np.float32), np.ascontiguousarray(hi, np.float32)
+        self.lib.pso_simd_set_bbox(self.h, lo.ctypes.data, hi.ctypes.data)
+
+    def prim_boxes(self):
+        out = np.zeros((self.n_prims, 6), np.float32)
+        self.lib.pso_simd_get_prim_boxes(self.h, out.ctypes.data)
+        return out
+
+    def op_boxes(self):
+        out = np.zeros((max(self.n_ops, 1), 6), np.float32)
+        self.lib.pso_simd_get_op_boxes(self.h, out.ctypes.data)
+        return out[:self.n_ops]
+
+    def pad_op_boxes(self, pad):
+        self.lib.pso_simd_pad_op_boxes(self.h, float(pad))
+
+    def count_mpus(self, cellsize):
+        lo, hi = self.bbox()
+        return int(self.lib.pso_count_mpus(float(cellsize), lo.ctypes.data, hi.ctypes.data))
+
+    def field(self, xyz):
+        xyz = np.ascontiguousarray(xyz, np.float32).reshape(-1, 3)
+        out = np.zeros(len(xyz), np.float32)
+        self.lib.pso_simd_field(self.h, len(xyz), xyz.ctypes.data, out.ctypes.data)
+        return out
+
+    def field_color_normal(self, xyz):
+        xyz = np.ascontiguousarray(xyz, np.float32).reshape(-1, 3)
+        n = len(xyz)
+        f, col, nrm = np.zeros(n, np.float32), np.zeros((n, 3), np.float32), np.zeros((n, 3), np.float32)
+        self.lib.pso_simd_field_color_normal(self.h, n, xyz.ctypes.data, f.ctypes.data, col.ctypes.data, nrm.ctypes.data)
+        return f, col, nrm
+
+    def mpu_cache(self, cellsize, ijk):
+        ijk = np.ascontiguousarray(ijk, np.int32)
+        fv, cs = np.zeros(512, np.float32), np.zeros(343, np.uint8)
+        self.lib.pso_simd_mpu_cache(self.h, float(cellsize), ijk.ctypes.data, fv.ctypes.data, cs.ctypes.data)
+        return fv, cs
+
+    def polygonize(self, cellsize, nthreads=0, b0=None, e0=None, keep_mesh=True):
+        st = np.zeros(16, np.int64)
+        b = np.ascontiguousarray(b0, np.int32) if b0 is not None else None
+        e = np.ascontiguousarray(e0, np.int32) if e0 is not None else None
+        ret = self.lib.pso_simd_polygonize(self.h, float(cellsize), int(nthreads or os.cpu_count() or 1),
+                                           b.ctypes.data if b is not None else None,
+                                           e.ctypes.data if e is not None else None, int(keep_mesh), st.ctypes.data)
+        stats = _stats(st)
+        if keep_mesh:
+            _fetch_mesh(self.lib.pso_simd_result_counts, self.lib.pso_simd_result_copy, self.h, stats)
+        return ret, stats
+
+
+class ScalarOracle:
+    """Scalar-twin semantics (COMPACTBLOBTREE / CParsipOptimized) restated in C; n-ary flat tree input."""
+
+    def __init__(self, flat: dict):
+        self.lib = _load_oracle()
+        t, self._keep = make_tree_struct(flat)
+        self.h = self.lib.pso_scalar_create(C.byref(t))
+        if not self.h:
+            raise RuntimeError("pso_scalar_create failed")
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            self.lib.pso_scalar_destroy(self.h)
+            self.h = None
+
+    def field(self, xyz):
+        xyz = np.ascontiguousarray(xyz, np.float32).reshape(-1, 3)
+        out = np.zeros(len(xyz), np.float32)
+        self.lib.pso_scalar_field(self.h, len(xyz), xyz.ctypes.data, out.ctypes.data)
+        return out
+
+    def field_color_normal(self, xyz):
+        xyz = np.ascontiguousarray(xyz, np.float32).reshape(-1, 3)
+        n = len(xyz)
+        f, col, nrm = np.zeros(n, np.float32), np.zeros((n, 3), np.float32), np.zeros((n, 3), np.float32)
+        self.lib.pso_scalar_field_color_normal(self.h, n, xyz.ctypes.data, f.ctypes.data, col.ctypes.data, nrm.ctypes.data)
+        return f, col, nrm
+
+    def newton(self, p1, p2, f1, f2, iso=0.5, iterations=8):
+        p1 = np.ascontiguousarray(p1, np.float32).reshape(-1, 3)
+        p2 = np.ascontiguousarray(p2, np.float32).reshape(-1, 3)
+        f1 = np.ascontiguousarray(f1, np.float32)
+        f2 = np.ascontiguousarray(f2, np.float32)
+        n = len(p1)
+        root, fr, ev = np.zeros((n, 3), np.float32), np.zeros(n, np.float32), np.zeros(n, np.int32)
+        self.lib.pso_scalar_newton(self.h, n, p1.ctypes.data, p2.ctypes.data, f1.ctypes.data, f2.ctypes.data,
+                                   float(iso), int(iterations), root.ctypes.data, fr.ctypes.data, ev.ctypes.data)
+        return root, fr, ev
+
+    def mpu_cache(self, lo, cellsize, ijk):
+        lo = np.ascontiguousarray(lo, np.float32)
+        ijk = np.ascontiguousarray(ijk, np.int32)
+        fv, cs = np.zeros(512, np.float32), np.zeros(343, np.uint8)
+        self.lib.pso_scalar_mpu_cache(self.h, lo.ctypes.data, float(cellsize), ijk.ctypes.data, fv.ctypes.data, cs.ctypes.data)
+        return fv, cs
+
+    def polygonize(self, lo, hi, cellsize, nthreads=0, b0=None, e0=None, keep_mesh=True):
+        lo, hi = np.ascontiguousarray(lo, np.float32), np.ascontiguousarray(hi, np.float32)
+        st = np.zeros(16, np.int64)
+        b = np.ascontiguousarray(b0, np.int32) if b0 is not None else None
+        e = np.ascontiguousarray(e0, np.int32) if e0 is not None else None
+        ret = self.lib.pso_scalar_polygonize(self.h, lo.ctypes.data, hi.ctypes.data, float(cellsize),
+                                             int(nthreads or os.cpu_count() or 1),
+                                             b.ctypes.data if b is not None else None,
+                                             e.ctypes.data if e is not None else None, int(keep_mesh), st.ctypes.data)
+        stats = _stats(st)
+        if keep_mesh:
+            _fetch_mesh(self.lib.pso_scalar_result_counts, self.lib.pso_scalar_result_copy, self.h, stats)
+        return ret, stats
