@@ -1,0 +1,142 @@
+/* psgpu.h - C ABI of the B200-native polygonizer (libpsgpu.so).
+ *
+ * Drop-in boundary for Parsip's parallel polygonization path. The C++ facade in
+ * include/PS_SimdPolyCompat.h (same names/structs as the reference's PS::SIMDPOLY, see
+ * INTEGRATION.md) forwards to these entry points; nothing in the signatures is a C++ or torch type.
+ *
+ * Reference interfaces replaced (all under /root/reference/Parsip100):
+ *   psgpu_linearize          <- SimdPoly::linearizeBlobTree        ParsipHaptics/include/PS_HighPerformanceRender.cpp:42-371
+ *                               COMPACTBLOBTREE::convert           ParsipHaptics/include/CompactBlobTree.cpp:25-408
+ *   psgpu_prepare_bboxes     <- PrepareBBoxes                      PS_SimdPoly/include/PS_Polygonizer.cpp:55-309
+ *   psgpu_count_mpus         <- CountMPUNeeded                     PS_SimdPoly/include/PS_Polygonizer.cpp:388-412
+ *   psgpu_polygonize         <- Polygonize / CParsipOptimized::run PS_SimdPoly/include/PS_Polygonizer.cpp:315-385,
+ *                                                                  ParsipHaptics/include/CPolyParsipOptimized.cpp:392-410
+ *   psgpu_field_eval         <- FieldComputer::fieldValue          PS_SimdPoly/include/PS_Polygonizer.cpp:1184-1376
+ *                               COMPACTBLOBTREE::fieldvalue        ParsipHaptics/include/CompactBlobTree.cpp:476-487
+ *   psgpu_field_color_normal <- FieldComputer::fieldValueAndColor + normal   PS_Polygonizer.cpp:1378-1622
+ *   psgpu_get_stats          <- PrintThreadResults / MPUSTATS      PS_SimdPoly/include/PS_Polygonizer.cpp:414-428
+ *
+ * Conventions: every function returns an int status (PSGPU_SUCCESS == 1, errors negative, the
+ * reference's RET_* values where one exists, PS_Polygonizer.h:47-50). No exceptions cross the ABI.
+ * One context per host thread; calls on a context are serialised by the caller. There is no CPU
+ * fallback: without a CUDA device psgpu_create fails with PSGPU_ERROR_NO_DEVICE.
+ */
+#ifndef PSGPU_H
+#define PSGPU_H
+#include <stddef.h>
+#include <stdint.h>
+#include "psgpu_types.h"
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct psgpu_ctx psgpu_ctx;
+typedef struct psgpu_program psgpu_program; /* host-side linearized BlobTree */
+
+/* which reference polygonizer's semantics to reproduce (SURVEY.md "two CPU polygonizers") */
+#define PSGPU_SEM_SIMD 0   /* PS_SimdPoly: infinite lines, fast_pow Ricci, warps pass-through, f >= iso, SIMD colour rule */
+#define PSGPU_SEM_SCALAR 1 /* CompactBlobTree: clamped segments, true Ricci, warps, f > iso, normalised colours (canonical) */
+
+#define PSGPU_ROOT_FOURSAMPLE 0 /* PS_Polygonizer.cpp:703-762: t = 0,1/3,2/3,1, bracket, lerp */
+#define PSGPU_ROOT_NEWTON_REF 1 /* CompactBlobTree.cpp:1581-1622: shrink-wrap Newton, <= 8 iterations */
+#define PSGPU_ROOT_BISECT 2     /* bracketed secant/bisection on the edge, re-evaluating the field (native default) */
+
+#define PSGPU_COORD_MPU_LOCAL 0 /* corner = (lo + I*side) + i*cellsize, the reference's expressions */
+#define PSGPU_COORD_GLOBAL 1    /* corner = lo + (7I+i)*cellsize: identical across MPUs, slabs and GPUs */
+
+#define PSGPU_OUT_INDEXED 0 /* one indexed mesh, vertices deduplicated by global edge id */
+#define PSGPU_OUT_MPU 1     /* per-MPU meshes in the reference's vertex/triangle order (PolyMPUs content) */
+
+#define PSGPU_CULL_NONE 0     /* every MPU evaluates the whole program (brute-force cross-check) */
+#define PSGPU_CULL_SUPPORT 1  /* per-MPU pruned lists: primitives whose support misses the MPU are dropped */
+#define PSGPU_CULL_INTERVAL 2 /* + MPUs whose field interval excludes the iso value are skipped (default) */
+
+#define PSGPU_LIN_REASSOCIATE 1 /* flatten blend-in-blend chains (changes summation order by a few ulp) */
+
+typedef struct psgpu_params {
+    float cellsize;
+    float bbox_lo[3], bbox_hi[3]; /* grid domain; the MPU lattice is laid out from bbox_lo like PS_Polygonizer.cpp:328-371 */
+    float iso;                    /* 0 = default ISO_VALUE 0.5 */
+    int32_t root_mode;
+    int32_t root_iterations; /* 0 = default (8 Newton / 10 bisect) */
+    int32_t coord_mode;
+    int32_t output;
+    int32_t cull;
+    int32_t z_begin, z_end; /* MPU-layer slab [z_begin, z_end); z_end <= 0 = whole lattice (multi-GPU sharding) */
+    int32_t want_colors, want_normals; /* 0 skips the colour walk / gradient samples; buffers stay unwritten */
+    int32_t collect_stats;             /* 1: also run the op-count kernel that fills prim_evals / algorithmic_flops */
+} psgpu_params;
+
+/* Result mesh. In PSGPU_OUT_INDEXED tri[] indexes pos[] directly; in PSGPU_OUT_MPU indices are
+ * MPU-local and mpu_* describe the slices (MPUs in lattice order, x outer, z inner). Pointers refer
+ * to context-owned DEVICE memory valid until the next psgpu_polygonize / psgpu_destroy. */
+typedef struct psgpu_mesh {
+    int64_t n_vertices, n_triangles;
+    const float* pos; /* 3*n_vertices */
+    const float* nrm;
+    const float* col;
+    const uint32_t* tri; /* 3*n_triangles */
+    int64_t n_mpus_out;         /* PSGPU_OUT_MPU: MPUs that produced triangles */
+    const int32_t* mpu_ijk;     /* 3*n_mpus_out lattice index */
+    const uint32_t* mpu_vbase;  /* n_mpus_out+1 */
+    const uint32_t* mpu_tbase;  /* n_mpus_out+1 */
+    int32_t lattice[3];
+    int32_t over_capacity;      /* PSGPU_OUT_MPU: MPUs exceeding the reference's 512 vertex/triangle capacity */
+} psgpu_mesh;
+
+typedef struct psgpu_stats {
+    int64_t mpus_total;       /* lattice size (slab) */
+    int64_t mpus_evaluated;   /* MPUs whose 512 corners were evaluated */
+    int64_t mpus_crossed;     /* MPUs that produced triangles */
+    int64_t field_evals;      /* point evaluations of the (pruned) tree: corners + root/gradient samples */
+    int64_t prim_evals;       /* primitive instructions executed, summed over points (grid phase) */
+    int64_t algorithmic_flops;/* SURVEY 8(d) op counts x executions, grid phase */
+    int64_t program_quads;    /* size of the full program */
+    int64_t pruned_quads;     /* total size of all per-MPU pruned programs */
+    float ms_cull, ms_field, ms_scan, ms_emit, ms_total; /* CUDA-event times of the last polygonize */
+    int64_t gpu_launches;     /* kernels launched by the last polygonize */
+} psgpu_stats;
+
+/* ---- context ---- */
+int psgpu_create(int device, psgpu_ctx** out);
+int psgpu_destroy(psgpu_ctx* ctx);
+const char* psgpu_last_error(const psgpu_ctx* ctx);
+int psgpu_device_count(void);
+
+/* ---- host side: linearizer and bounding boxes (no GPU needed) ---- */
+/* Flattens an n-ary BlobTree into the postfix instruction + parameter stream.
+ * Errors: PSGPU_PARAM_ERROR (empty tree), PSGPU_ERROR_UNSUPPORTED_NODE, PSGPU_NOT_ENOUGH_MEM (stack depth). */
+int psgpu_linearize(const psgpu_tree* tree, int semantics, int flags, psgpu_program** out);
+int psgpu_program_free(psgpu_program* p);
+/* info[0] quads, [1] primitives, [2] max value-stack depth, [3] max point-stack depth, [4] instructions */
+int psgpu_program_info(const psgpu_program* p, int64_t* info5);
+int psgpu_program_copy(const psgpu_program* p, uint32_t* quads_out /* 4 words per quad */);
+/* Grid-domain box of the tree the way PrepareBBoxes computes it (iso distance 0.4542 + 0.05 padding). */
+int psgpu_prepare_bboxes(const psgpu_tree* tree, float cellsize, float* lo3, float* hi3);
+uint32_t psgpu_count_mpus(float cellsize, const float* lo3, const float* hi3);
+
+/* ---- device side ---- */
+int psgpu_upload_program(psgpu_ctx* ctx, const psgpu_program* p);
+/* Runs cull -> field -> scan -> emit. The mesh stays on the device (see psgpu_mesh). */
+int psgpu_polygonize(psgpu_ctx* ctx, const psgpu_params* params, psgpu_mesh* out);
+/* Same, then copies the mesh into caller-provided HOST buffers (capacity in vertices / triangles;
+ * PSGPU_NOT_ENOUGH_MEM if too small, with the needed sizes in out). NULL buffers are skipped. */
+int psgpu_polygonize_host(psgpu_ctx* ctx, const psgpu_params* params, psgpu_mesh* out, float* pos, float* nrm,
+                          float* col, uint32_t* tri, int64_t cap_vertices, int64_t cap_triangles);
+/* Copies the last device mesh (and the PSGPU_OUT_MPU tables) to host buffers. */
+int psgpu_mesh_download(psgpu_ctx* ctx, float* pos, float* nrm, float* col, uint32_t* tri, int32_t* mpu_ijk,
+                        uint32_t* mpu_vbase, uint32_t* mpu_tbase);
+/* Parity hooks: field (and colour / normal) at arbitrary HOST points with the full, unculled program. */
+int psgpu_field_eval(psgpu_ctx* ctx, const float* xyz, int64_t n, float* f_out);
+int psgpu_field_color_normal(psgpu_ctx* ctx, const float* xyz, int64_t n, float* f, float* col, float* nrm);
+/* Field cache (fv[i*8 + j*64 + k]) and cube cases (cell i*49 + j*7 + k) of one MPU, for parity tests. */
+int psgpu_mpu_cache(psgpu_ctx* ctx, const psgpu_params* params, const int32_t* ijk, float* fv512, uint8_t* case343);
+int psgpu_get_stats(const psgpu_ctx* ctx, psgpu_stats* out);
+/* FP32 FMA-chain microbenchmark (dependent-free FFMA streams on every SM); returns measured TFLOP/s. */
+int psgpu_measure_fp32_peak(psgpu_ctx* ctx, float* tflops_out, float* sm_clock_mhz_out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,273 @@
+"""ctypes binding of libpsgpu.so (include/psgpu.h). Thin: arrays in, arrays out, status codes raised."""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+import numpy as np
+
+SEM_SIMD, SEM_SCALAR = 0, 1
+ROOT_FOURSAMPLE, ROOT_NEWTON_REF, ROOT_BISECT = 0, 1, 2
+COORD_MPU_LOCAL, COORD_GLOBAL = 0, 1
+OUT_INDEXED, OUT_MPU = 0, 1
+CULL_NONE, CULL_SUPPORT, CULL_INTERVAL = 0, 1, 2
+LIN_REASSOCIATE = 1
+
+SUCCESS = 1
+ERRORS = {-1: "PARAM_ERROR", -2: "NOT_ENOUGH_MEM", -3: "INVALID_BVH", -4: "UNSUPPORTED_NODE", -5: "CUDA", -6: "NO_DEVICE"}
+
+# every symbol include/psgpu.h declares (tests/test_abi.py checks the library exports them all)
+EXPORTS = [
+    "psgpu_create", "psgpu_destroy", "psgpu_last_error", "psgpu_device_count", "psgpu_linearize", "psgpu_program_free",
+    "psgpu_program_info", "psgpu_program_copy", "psgpu_prepare_bboxes", "psgpu_count_mpus", "psgpu_upload_program",
+    "psgpu_polygonize", "psgpu_polygonize_host", "psgpu_mesh_download", "psgpu_field_eval", "psgpu_field_color_normal",
+    "psgpu_mpu_cache", "psgpu_get_stats", "psgpu_measure_fp32_peak",
+]
+
+
+class PsGpuError(RuntimeError):
+    def __init__(self, code, what=""):
+        self.code = code
+        super().__init__("psgpu error %s (%d) %s" % (ERRORS.get(code, "?"), code, what))
+
+
+class _Tree(C.Structure):
+    _fields_ = [
+        ("n_nodes", C.c_int32), ("root", C.c_int32),
+        ("type", C.POINTER(C.c_int32)), ("first_child", C.POINTER(C.c_int32)),
+        ("n_children", C.POINTER(C.c_int32)), ("child", C.POINTER(C.c_int32)),
+        ("pos", C.POINTER(C.c_float)), ("dir", C.POINTER(C.c_float)), ("res", C.POINTER(C.c_float)),
+        ("color", C.POINTER(C.c_float)), ("xform", C.POINTER(C.c_float)), ("has_xform", C.POINTER(C.c_uint8)),
+    ]
+
+
+class Params(C.Structure):
+    _fields_ = [
+        ("cellsize", C.c_float), ("bbox_lo", C.c_float * 3), ("bbox_hi", C.c_float * 3), ("iso", C.c_float),
+        ("root_mode", C.c_int32), ("root_iterations", C.c_int32), ("coord_mode", C.c_int32), ("output", C.c_int32),
+        ("cull", C.c_int32), ("z_begin", C.c_int32), ("z_end", C.c_int32), ("want_colors", C.c_int32),
+        ("want_normals", C.c_int32), ("collect_stats", C.c_int32),
+    ]
+
+    @classmethod
+    def make(cls, cellsize, lo, hi, root_mode=ROOT_BISECT, coord_mode=COORD_GLOBAL, output=OUT_INDEXED, cull=CULL_INTERVAL,
+             z_begin=0, z_end=0, want_colors=1, want_normals=1, collect_stats=0, root_iterations=0, iso=0.0):
+        p = cls()
+        p.cellsize = float(cellsize)
+        for a in range(3):
+            p.bbox_lo[a] = float(lo[a])
+            p.bbox_hi[a] = float(hi[a])
+        p.iso = iso
+        p.root_mode, p.root_iterations, p.coord_mode, p.output, p.cull = root_mode, root_iterations, coord_mode, output, cull
+        p.z_begin, p.z_end, p.want_colors, p.want_normals, p.collect_stats = z_begin, z_end, want_colors, want_normals, collect_stats
+        return p
+
+
+class _Mesh(C.Structure):
+    _fields_ = [
+        ("n_vertices", C.c_int64), ("n_triangles", C.c_int64),
+        ("pos", C.c_void_p), ("nrm", C.c_void_p), ("col", C.c_void_p), ("tri", C.c_void_p),
+        ("n_mpus_out", C.c_int64), ("mpu_ijk", C.c_void_p), ("mpu_vbase", C.c_void_p), ("mpu_tbase", C.c_void_p),
+        ("lattice", C.c_int32 * 3), ("over_capacity", C.c_int32),
+    ]
+
+
+class _Stats(C.Structure):
+    _fields_ = [
+        ("mpus_total", C.c_int64), ("mpus_evaluated", C.c_int64), ("mpus_crossed", C.c_int64), ("field_evals", C.c_int64),
+        ("prim_evals", C.c_int64), ("algorithmic_flops", C.c_int64), ("program_quads", C.c_int64), ("pruned_quads", C.c_int64),
+        ("ms_cull", C.c_float), ("ms_field", C.c_float), ("ms_scan", C.c_float), ("ms_emit", C.c_float), ("ms_total", C.c_float),
+        ("gpu_launches", C.c_int64),
+    ]
+
+
+def lib_path() -> str:
+    return os.path.join(os.path.dirname(os.path.abspath(__file__)), "libpsgpu.so")
+
+
+_lib = None
+
+
+def load_library():
+    """Loads libpsgpu.so; raises (never falls back) if it has not been built."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    path = lib_path()
+    if not os.path.exists(path):
+        raise PsGpuError(-6, "libpsgpu.so is not built: run `python -c 'import __graft_entry__ as g; g.build()'` (there is no CPU fallback)")
+    lib = C.CDLL(path)
+    vp = C.c_void_p
+    lib.psgpu_create.argtypes = [C.c_int, C.POINTER(vp)]
+    lib.psgpu_destroy.argtypes = [vp]
+    lib.psgpu_last_error.restype = C.c_char_p
+    lib.psgpu_last_error.argtypes = [vp]
+    lib.psgpu_linearize.argtypes = [C.POINTER(_Tree), C.c_int, C.c_int, C.POINTER(vp)]
+    lib.psgpu_program_free.argtypes = [vp]
+    lib.psgpu_program_info.argtypes = [vp, vp]
+    lib.psgpu_program_copy.argtypes = [vp, vp]
+    lib.psgpu_prepare_bboxes.argtypes = [C.POINTER(_Tree), C.c_float, vp, vp]
+    lib.psgpu_count_mpus.restype = C.c_uint32
+    lib.psgpu_count_mpus.argtypes = [C.c_float, vp, vp]
+    lib.psgpu_lattice_dims.argtypes = [C.c_float, vp, vp, vp]
+    lib.psgpu_upload_program.argtypes = [vp, vp]
+    lib.psgpu_polygonize.argtypes = [vp, C.POINTER(Params), C.POINTER(_Mesh)]
+    lib.psgpu_polygonize_host.argtypes = [vp, C.POINTER(Params), C.POINTER(_Mesh), vp, vp, vp, vp, C.c_int64, C.c_int64]
+    lib.psgpu_mesh_download.argtypes = [vp] * 8
+    lib.psgpu_field_eval.argtypes = [vp, vp, C.c_int64, vp]
+    lib.psgpu_field_color_normal.argtypes = [vp, vp, C.c_int64, vp, vp, vp]
+    lib.psgpu_mpu_cache.argtypes = [vp, C.POINTER(Params), vp, vp, vp]
+    lib.psgpu_get_stats.argtypes = [vp, C.POINTER(_Stats)]
+    lib.psgpu_measure_fp32_peak.argtypes = [vp, vp, vp]
+    _lib = lib
+    return lib
+
+
+def _tree_struct(flat: dict):
+    k = {n: np.ascontiguousarray(v) for n, v in flat.items() if isinstance(v, np.ndarray)}
+
+    def p(a, t):
+        return a.ctypes.data_as(C.POINTER(t))
+
+    t = _Tree(flat["n_nodes"], flat["root"], p(k["type"], C.c_int32), p(k["first_child"], C.c_int32), p(k["n_children"], C.c_int32),
+              p(k["child"], C.c_int32), p(k["pos"], C.c_float), p(k["dir"], C.c_float), p(k["res"], C.c_float),
+              p(k["color"], C.c_float), p(k["xform"], C.c_float), p(k["has_xform"], C.c_uint8))
+    return t, k
+
+
+class Program:
+    """A linearized BlobTree (host side)."""
+
+    def __init__(self, handle, lib):
+        self.h, self.lib = handle, lib
+        info = np.zeros(5, np.int64)
+        lib.psgpu_program_info(self.h, info.ctypes.data)
+        self.n_quads, self.n_prims, self.max_value_stack, self.max_point_stack, self.n_instr = (int(v) for v in info)
+
+    def quads(self) -> np.ndarray:
+        out = np.zeros((self.n_quads, 4), np.uint32)
+        self.lib.psgpu_program_copy(self.h, out.ctypes.data)
+        return out
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            self.lib.psgpu_program_free(self.h)
+            self.h = None
+
+
+def linearize(flat: dict, semantics: int = SEM_SCALAR, flags: int = LIN_REASSOCIATE) -> Program:
+    lib = load_library()
+    t, keep = _tree_struct(flat)
+    h = C.c_void_p()
+    rc = lib.psgpu_linearize(C.byref(t), semantics, flags, C.byref(h))
+    if rc != SUCCESS:
+        raise PsGpuError(rc, "psgpu_linearize")
+    return Program(h, lib)
+
+
+def prepare_bboxes(flat: dict, cellsize: float = 0.14):
+    lib = load_library()
+    t, keep = _tree_struct(flat)
+    lo, hi = np.zeros(3, np.float32), np.zeros(3, np.float32)
+    rc = lib.psgpu_prepare_bboxes(C.byref(t), float(cellsize), lo.ctypes.data, hi.ctypes.data)
+    if rc != SUCCESS:
+        raise PsGpuError(rc, "psgpu_prepare_bboxes")
+    return lo, hi
+
+
+def count_mpus(cellsize, lo, hi) -> int:
+    lib = load_library()
+    lo, hi = np.ascontiguousarray(lo, np.float32), np.ascontiguousarray(hi, np.float32)
+    return int(lib.psgpu_count_mpus(float(cellsize), lo.ctypes.data, hi.ctypes.data))
+
+
+def lattice_dims(cellsize, lo, hi):
+    lib = load_library()
+    lo, hi = np.ascontiguousarray(lo, np.float32), np.ascontiguousarray(hi, np.float32)
+    nm = np.zeros(3, np.int32)
+    lib.psgpu_lattice_dims(float(cellsize), lo.ctypes.data, hi.ctypes.data, nm.ctypes.data)
+    return tuple(int(v) for v in nm)
+
+
+class Context:
+    """One GPU context (psgpu_ctx). Not thread-safe, like the reference's Polygonize."""
+
+    def __init__(self, device: int = 0):
+        self.lib = load_library()
+        self.h = C.c_void_p()
+        rc = self.lib.psgpu_create(int(device), C.byref(self.h))
+        if rc != SUCCESS:
+            self.h = None
+            raise PsGpuError(rc, "psgpu_create: no usable CUDA device (there is no CPU fallback)")
+        self.device = device
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.lib.psgpu_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        self.close()
+
+    def _check(self, rc, what):
+        if rc != SUCCESS:
+            raise PsGpuError(rc, "%s: %s" % (what, self.lib.psgpu_last_error(self.h).decode()))
+
+    def upload(self, program: Program):
+        self._check(self.lib.psgpu_upload_program(self.h, program.h), "psgpu_upload_program")
+
+    def field(self, xyz) -> np.ndarray:
+        xyz = np.ascontiguousarray(xyz, np.float32).reshape(-1, 3)
+        out = np.zeros(len(xyz), np.float32)
+        self._check(self.lib.psgpu_field_eval(self.h, xyz.ctypes.data, len(xyz), out.ctypes.data), "psgpu_field_eval")
+        return out
+
+    def field_color_normal(self, xyz):
+        xyz = np.ascontiguousarray(xyz, np.float32).reshape(-1, 3)
+        n = len(xyz)
+        f, col, nrm = np.zeros(n, np.float32), np.zeros((n, 3), np.float32), np.zeros((n, 3), np.float32)
+        self._check(self.lib.psgpu_field_color_normal(self.h, xyz.ctypes.data, n, f.ctypes.data, col.ctypes.data, nrm.ctypes.data),
+                    "psgpu_field_color_normal")
+        return f, col, nrm
+
+    def mpu_cache(self, params: Params, ijk):
+        ijk = np.ascontiguousarray(ijk, np.int32)
+        fv, cs = np.zeros(512, np.float32), np.zeros(343, np.uint8)
+        self._check(self.lib.psgpu_mpu_cache(self.h, C.byref(params), ijk.ctypes.data, fv.ctypes.data, cs.ctypes.data), "psgpu_mpu_cache")
+        return fv, cs
+
+    def polygonize(self, params: Params, download: bool = True, allow_over_capacity: bool = False) -> dict:
+        """cull -> field -> scan -> emit on the device; optionally copies the mesh to numpy arrays."""
+        m = _Mesh()
+        rc = self.lib.psgpu_polygonize(self.h, C.byref(params), C.byref(m))
+        if rc != SUCCESS and not (allow_over_capacity and rc == -2 and m.over_capacity > 0):
+            self._check(rc, "psgpu_polygonize")
+        out = dict(n_vertices=int(m.n_vertices), n_triangles=int(m.n_triangles), n_mpus_out=int(m.n_mpus_out),
+                   lattice=tuple(m.lattice), over_capacity=int(m.over_capacity))
+        if download:
+            nv, nt, nm = out["n_vertices"], out["n_triangles"], out["n_mpus_out"]
+            pos, nrm, col = (np.zeros((nv, 3), np.float32) for _ in range(3))
+            tri = np.zeros((nt, 3), np.uint32)
+            ijk, vb, tb = np.zeros((nm, 3), np.int32), np.zeros(nm + 1, np.uint32), np.zeros(nm + 1, np.uint32)
+            self._check(self.lib.psgpu_mesh_download(self.h, pos.ctypes.data, nrm.ctypes.data, col.ctypes.data, tri.ctypes.data,
+                                                     ijk.ctypes.data, vb.ctypes.data, tb.ctypes.data), "psgpu_mesh_download")
+            out.update(pos=pos, nrm=nrm, col=col, tri=tri, mpu_ijk=ijk, mpu_vbase=vb, mpu_tbase=tb)
+        return out
+
+    def polygonize_host(self, params: Params, pos, nrm, col, tri) -> dict:
+        """The reference-facing call with HOST buffers (device -> host copies inside)."""
+        m = _Mesh()
+        rc = self.lib.psgpu_polygonize_host(self.h, C.byref(params), C.byref(m), pos.ctypes.data, nrm.ctypes.data, col.ctypes.data,
+                                            tri.ctypes.data, pos.shape[0], tri.shape[0])
+        self._check(rc, "psgpu_polygonize_host")
+        return dict(n_vertices=int(m.n_vertices), n_triangles=int(m.n_triangles), lattice=tuple(m.lattice))
+
+    def stats(self) -> dict:
+        s = _Stats()
+        self.lib.psgpu_get_stats(self.h, C.byref(s))
+        return {f: getattr(s, f) for f, _ in _Stats._fields_}
+
+    def fp32_peak(self):
+        t, mhz = C.c_float(), C.c_float()
+        self._check(self.lib.psgpu_measure_fp32_peak(self.h, C.byref(t), C.byref(mhz)), "psgpu_measure_fp32_peak")
+        return float(t.value), float(mhz.value)

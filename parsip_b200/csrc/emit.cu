@@ -1,0 +1,345 @@
+// Marching-cubes mesh emission (north-star subsystem 4): one CTA per surface-crossing MPU. The MPU's field
+// cache (2 KB) and pruned instruction list come back in through TMA bulk copies; cells are re-classified from
+// the cache, every crossing edge this MPU owns gets its root (4-sample + lerp / reference Newton / bracketed
+// secant, all re-evaluating the field), a forward-difference normal and a colour, and triangles are written
+// with GLOBAL vertex indices: a vertex's index is (MPU's vertex base) + (rank of its edge bit in the MPU's
+// crossing-edge mask), so neighbouring MPUs resolve shared edges with one popcount and no hashing - the
+// deterministic replacement for the reference's per-MPU EDGETABLE (PS_Polygonizer.h:211-222, cpp:832-916).
+//
+// Reference: process_cells_simd phases 2-4 (PS_SimdPoly/include/PS_Polygonizer.cpp:612-829),
+// doMarchingCubes + ComputeRootNewtonRaphsonVEC4 (ParsipHaptics/include/CPolyParsipOptimized.cpp:187-327,
+// CompactBlobTree.cpp:1581-1622). PSGPU_OUT_MPU reproduces the reference's per-MPU vertex/triangle ORDER
+// (first-use order of the sequential i,j,k cell loop) with a prefix sum instead of a serial loop.
+#include "device_util.cuh"
+#include "interp.cuh"
+#include "kernels.h"
+#include "mc_tables.h"
+
+namespace psgpu {
+
+namespace {
+
+constexpr int kThreads = 128;
+constexpr uint32_t kMaxProgCapQuads = 1024;
+
+__device__ const int8_t g_triTable[256 * 16] = PS_MC_TRITABLE_INIT;
+__constant__ uint8_t c_corner1[12] = PS_MC_CORNER1_INIT;
+__constant__ uint8_t c_edgeAxis[12] = PS_MC_EDGEAXIS_INIT;
+__constant__ uint8_t c_nTriE[256] = PS_MC_NTRI_INIT;
+
+struct __align__(16) EmitSmem {
+    uint64_t bar;
+    float fv[512];
+    uint32_t insideW[16];
+    uint32_t edgeW[48];
+    uint16_t edgeP[48];
+    uint16_t edgeVid[1536];  // PSGPU_OUT_MPU: reference-order local vertex id per edge bit
+    int8_t tri[256 * 16];
+    uint8_t cellCase[344];
+    uint32_t warpSum[4];
+    int next;
+};
+
+__device__ __forceinline__ uint32_t inside_bit(const EmitSmem& S, int idx) { return (S.insideW[idx >> 5] >> (idx & 31)) & 1u; }
+
+// exclusive block scan of one value per thread (128 threads); returns the exclusive prefix, total in `total`
+__device__ __forceinline__ uint32_t block_excl_scan(EmitSmem& S, uint32_t v, uint32_t& total) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    uint32_t inc = v;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const uint32_t a = __shfl_up_sync(0xffffffffu, inc, o);
+        if (lane >= o) inc += a;
+    }
+    __syncthreads();
+    if (lane == 31) S.warpSum[warp] = inc;
+    __syncthreads();
+    uint32_t off = 0;
+#pragma unroll
+    for (int w = 0; w < 4; w++) { if (w < warp) off += S.warpSum[w]; }
+    total = S.warpSum[0] + S.warpSum[1] + S.warpSum[2] + S.warpSum[3];
+    return inc - v + off;
+}
+
+struct EdgePos { float e1[3]; float e2a; int axis; };
+
+__device__ __forceinline__ EdgePos edge_endpoints(const GridParams& G, const Region& r, int ci, int cj, int ck, int axis) {
+    EdgePos E;
+    E.axis = axis;
+    E.e1[0] = corner_coord(G, 0, r.x, ci); E.e1[1] = corner_coord(G, 1, r.y, cj); E.e1[2] = corner_coord(G, 2, r.z, ck);
+    if (G.coordMode == PSGPU_COORD_MPU_LOCAL) E.e2a = __fadd_rn(E.e1[axis], G.cellsize);  // PS_Polygonizer.cpp:722-724
+    else E.e2a = corner_coord(G, axis, axis == 0 ? r.x : (axis == 1 ? r.y : r.z), (axis == 0 ? ci : (axis == 1 ? cj : ck)) + 1);
+    return E;
+}
+
+// PS_Polygonizer.cpp:728-762: samples at t = 0, 1/3, 2/3, 1 in one 4-wide evaluation, first lane whose
+// inside flag differs from lane 0 brackets the root, linear interpolation inside that sub-interval.
+__device__ void root_foursample(const GridParams& G, const float4* prog, const EdgePos& E, float (&p)[3]) {
+    float X[4], Y[4], Z[4], F[4];
+    const float d = __fsub_rn(E.e2a, E.e1[E.axis]);
+#pragma unroll
+    for (int l = 0; l < 4; l++) {
+        const float res = __fmul_rn((float)l, 1.0f / 3.0f);
+        const float moved = __fadd_rn(E.e1[E.axis], __fmul_rn(d, res));
+        X[l] = (E.axis == 0) ? moved : E.e1[0];
+        Y[l] = (E.axis == 1) ? moved : E.e1[1];
+        Z[l] = (E.axis == 2) ? moved : E.e1[2];
+    }
+    eval_program<4, false>(prog, X, Y, Z, F, nullptr, nullptr, G.sem);
+    const bool state = is_inside(G, F[0]);
+    // first lane whose flag differs from lane 0, else the last one (cpp:748-755)
+    const int interval = (is_inside(G, F[1]) != state) ? 1 : ((is_inside(G, F[2]) != state) ? 2 : 3);
+    float fa = F[0], fb = F[1], xa = X[0], xb = X[1], ya = Y[0], yb = Y[1], za = Z[0], zb = Z[1];
+    if (interval == 2) { fa = F[1]; fb = F[2]; xa = X[1]; xb = X[2]; ya = Y[1]; yb = Y[2]; za = Z[1]; zb = Z[2]; }
+    if (interval == 3) { fa = F[2]; fb = F[3]; xa = X[2]; xb = X[3]; ya = Y[2]; yb = Y[3]; za = Z[2]; zb = Z[3]; }
+    const float scale = __fdiv_rn(__fsub_rn(G.iso, fa), __fsub_rn(fb, fa));
+    p[0] = __fadd_rn(xa, __fmul_rn(scale, __fsub_rn(xb, xa)));
+    p[1] = __fadd_rn(ya, __fmul_rn(scale, __fsub_rn(yb, ya)));
+    p[2] = __fadd_rn(za, __fmul_rn(scale, __fsub_rn(zb, za)));
+}
+
+// Bracketed false position (Illinois) along the edge, re-evaluating the field; the bracket is guaranteed
+// because both endpoints are lattice corners whose cached values were produced by this same program.
+__device__ void root_bisect(const GridParams& G, const float4* prog, const EdgePos& E, float f1, float f2, int iters, float (&p)[3]) {
+    float ta = 0.f, tb = 1.f, fa = f1 - G.iso, fb = f2 - G.iso;
+    const float d = E.e2a - E.e1[E.axis];
+    float t = 0.5f;
+    int side = 0;
+    for (int it = 0; it < iters; it++) {
+        const float den = fa - fb;
+        t = (den != 0.f) ? ta + (tb - ta) * (fa / den) : 0.5f * (ta + tb);
+        if (!(t > ta && t < tb)) t = 0.5f * (ta + tb);
+        float X[1] = {E.e1[0]}, Y[1] = {E.e1[1]}, Z[1] = {E.e1[2]}, F[1];
+        const float moved = fmaf(t, d, E.e1[E.axis]);
+        if (E.axis == 0) X[0] = moved; else if (E.axis == 1) Y[0] = moved; else Z[0] = moved;
+        eval_program<1, false>(prog, X, Y, Z, F, nullptr, nullptr, G.sem);
+        const float ft = F[0] - G.iso;
+        if (fabsf(ft) < 1e-6f) break;
+        if ((ft < 0.f) == (fa < 0.f)) { ta = t; fa = ft; if (side == -1) fb *= 0.5f; side = -1; }
+        else { tb = t; fb = ft; if (side == 1) fa *= 0.5f; side = 1; }
+    }
+    p[0] = E.e1[0]; p[1] = E.e1[1]; p[2] = E.e1[2];
+    p[E.axis] = fmaf(t, d, E.e1[E.axis]);
+}
+
+// ComputeRootNewtonRaphsonVEC4 (CompactBlobTree.cpp:1581-1622) incl. the fp^2 damping of its vec4 dot
+__device__ void root_newton_ref(const GridParams& G, const float4* prog, const EdgePos& E, float f1, float f2, int iters, float (&p)[3]) {
+    float x[3] = {E.e1[0], E.e1[1], E.e1[2]};
+    if (!(fabsf(f1 - G.iso) < fabsf(f2 - G.iso))) x[E.axis] = E.e2a;
+    const float eps = PS_FIELDVALUE_EPSILON, inv = 1.0f / PS_FIELDVALUE_EPSILON;
+    for (int it = 0; it < iters; it++) {
+        float X[4] = {x[0], x[0] + eps, x[0], x[0]}, Y[4] = {x[1], x[1], x[1] + eps, x[1]}, Z[4] = {x[2], x[2], x[2], x[2] + eps}, F[4];
+        eval_program<4, false>(prog, X, Y, Z, F, nullptr, nullptr, G.sem);
+        const float fp = F[0];
+        const float gx = (F[1] - fp) * inv, gy = (F[2] - fp) * inv, gz = (F[3] - fp) * inv;
+        const float dd = G.iso - fp;
+        const float g = 1.0f / (gx * gx + gy * gy + gz * gz + fp * fp);
+        x[0] = x[0] + (dd * gx) * g; x[1] = x[1] + (dd * gy) * g; x[2] = x[2] + (dd * gz) * g;
+        float X1[1] = {x[0]}, Y1[1] = {x[1]}, Z1[1] = {x[2]}, F1[1];
+        eval_program<1, false>(prog, X1, Y1, Z1, F1, nullptr, nullptr, G.sem);
+        if (fabsf(F1[0] - G.iso) < eps) break;
+    }
+    p[0] = x[0]; p[1] = x[1]; p[2] = x[2];
+}
+
+__global__ void __launch_bounds__(kThreads) emit_kernel(GridParams G, const Region* __restrict__ cands, const float4* __restrict__ pool,
+                                                        const float* __restrict__ colorTab, FieldOutputs fo, MeshOutputs mo,
+                                                        const int32_t* __restrict__ candOfMpu, int nMixed, uint32_t capQuads) {
+    extern __shared__ __align__(16) unsigned char smemRaw[];
+    EmitSmem& S = *reinterpret_cast<EmitSmem*>(smemRaw);
+    float4* progBuf = reinterpret_cast<float4*>(smemRaw + sizeof(EmitSmem));
+    const int t = threadIdx.x;
+    for (int i = t; i < 256 * 16; i += kThreads) S.tri[i] = g_triTable[i];
+    if (t == 0) { mbar_init(&S.bar, 1); fence_mbar_init(); }
+    __syncthreads();
+    uint32_t phase = 0;
+    const bool perMpu = (G.output == PSGPU_OUT_MPU);
+    const int ny = G.hi[1] - G.lo[1], nz = G.hi[2] - G.lo[2];
+
+    int m = blockIdx.x;
+    while (m < nMixed) {
+        const uint32_t cand = fo.mixedList[m];
+        const Region r = cands[cand];
+        const bool staged = r.len <= capQuads;
+        if (t == 0) {
+            S.next = (int)atomicAdd(&fo.counters[3], 1u) + (int)gridDim.x;
+            fence_proxy_async();
+            mbar_expect_tx(&S.bar, 2048u + (staged ? r.len * 16u : 0u));
+            tma_load_bulk(S.fv, fo.fv + (size_t)cand * 128, 2048u, &S.bar);
+            if (staged) tma_load_bulk(progBuf, pool + r.off, r.len * 16u, &S.bar);
+        }
+        if (t < 16) S.insideW[t] = 0u;
+        if (t < 48) { S.edgeW[t] = fo.edgeMask[(size_t)cand * 48 + t]; S.edgeP[t] = fo.edgePrefix[(size_t)cand * 48 + t]; }
+        const uint32_t vbase = mo.vbase[cand], tbase = mo.tbase[cand];
+        const uint32_t nV = fo.vcount[cand];
+        mbar_wait(&S.bar, phase);
+        phase ^= 1u;
+        __syncthreads();
+        const float4* prog = staged ? progBuf : pool + r.off;
+        {
+            const float4 f4 = reinterpret_cast<const float4*>(S.fv)[t];
+            const uint32_t in4 = (is_inside(G, f4.x) ? 1u : 0u) | (is_inside(G, f4.y) ? 2u : 0u) | (is_inside(G, f4.z) ? 4u : 0u) |
+                                 (is_inside(G, f4.w) ? 8u : 0u);
+            atomicOr(&S.insideW[t >> 3], in4 << ((t & 7) * 4));
+        }
+        __syncthreads();
+        for (int c = t; c < 343; c += kThreads) {
+            const int cx = c / 49, cy = (c / 7) % 7, cz = c % 7;
+            uint32_t cfg = 0;
+#pragma unroll
+            for (int b = 0; b < 8; b++) cfg |= inside_bit(S, (cx + ((b >> 2) & 1)) * 8 + (cy + ((b >> 1) & 1)) * 64 + (cz + (b & 1))) << b;
+            S.cellCase[c] = (uint8_t)cfg;
+        }
+        __syncthreads();
+
+        if (perMpu) {
+            // reference vertex order: a vertex is created by the first cell (i outer, k inner) whose table row
+            // names its edge, in row order (PS_Polygonizer.cpp:647-808). The first cell of edge (corner c, axis a)
+            // is c with the two non-axis coordinates decremented (clipped at 0).
+            uint32_t carry = 0;
+            for (int round = 0; round < 3; round++) {
+                const int c = round * kThreads + t;
+                uint32_t nNew = 0;
+                uint32_t newMask = 0;  // row positions that create a vertex
+                if (c < 343) {
+                    const int cx = c / 49, cy = (c / 7) % 7, cz = c % 7;
+                    const int8_t* row = &S.tri[S.cellCase[c] * 16];
+                    uint32_t seen = 0;
+                    for (int k = 0; k < 16; k++) {
+                        const int e = row[k];
+                        if (e < 0) break;
+                        if (seen & (1u << e)) continue;
+                        seen |= 1u << e;
+                        const int c1 = c_corner1[e], ax = c_edgeAxis[e];
+                        const int sx = cx + ((c1 >> 2) & 1), sy = cy + ((c1 >> 1) & 1), sz = cz + (c1 & 1);
+                        const bool fx = (ax == 0) || (sx == cx + 1) || (sx == 0), fy = (ax == 1) || (sy == cy + 1) || (sy == 0),
+                                   fz = (ax == 2) || (sz == cz + 1) || (sz == 0);
+                        if (fx && fy && fz) { newMask |= 1u << k; nNew++; }
+                    }
+                }
+                uint32_t total;
+                const uint32_t ex = block_excl_scan(S, nNew, total) + carry;
+                carry += total;
+                if (c < 343 && nNew) {
+                    const int cx = c / 49, cy = (c / 7) % 7, cz = c % 7;
+                    const int8_t* row = &S.tri[S.cellCase[c] * 16];
+                    uint32_t id = ex;
+                    for (int k = 0; k < 16; k++) {
+                        if (!(newMask >> k)) break;
+                        if (!((newMask >> k) & 1u)) continue;
+                        const int e = row[k];
+                        const int c1 = c_corner1[e], ax = c_edgeAxis[e];
+                        const int sx = cx + ((c1 >> 2) & 1), sy = cy + ((c1 >> 1) & 1), sz = cz + (c1 & 1);
+                        S.edgeVid[(sx * 8 + sy * 64 + sz) * 3 + ax] = (uint16_t)id;
+                        id++;
+                    }
+                }
+            }
+            __syncthreads();
+        }
+
+        // ---- vertices: rank -> edge bit -> root, normal, colour
+        for (uint32_t rk = t; rk < nV; rk += kThreads) {
+            int lo = 0, hi = 47;  // last word whose exclusive prefix <= rk
+            while (lo < hi) {
+                const int mid = (lo + hi + 1) >> 1;
+                if (S.edgeP[mid] <= rk) lo = mid; else hi = mid - 1;
+            }
+            const int bit = __fns(S.edgeW[lo], 0, (int)(rk - S.edgeP[lo]) + 1);
+            const int e = lo * 32 + bit;
+            const int corner = e / 3, axis = e - corner * 3;
+            const int ck = corner & 7, ci = (corner >> 3) & 7, cj = corner >> 6;
+            const EdgePos E = edge_endpoints(G, r, ci, cj, ck, axis);
+            const float f1 = S.fv[corner], f2 = S.fv[corner + (axis == 0 ? 8 : (axis == 1 ? 64 : 1))];
+            float p[3];
+            if (G.rootMode == PSGPU_ROOT_FOURSAMPLE) root_foursample(G, prog, E, p);
+            else if (G.rootMode == PSGPU_ROOT_NEWTON_REF) root_newton_ref(G, prog, E, f1, f2, G.rootIters, p);
+            else root_bisect(G, prog, E, f1, f2, G.rootIters, p);
+            const size_t vo = (size_t)(vbase + (perMpu ? (uint32_t)S.edgeVid[e] : rk)) * 3;
+            mo.pos[vo] = p[0]; mo.pos[vo + 1] = p[1]; mo.pos[vo + 2] = p[2];
+            if (G.wantColors || G.wantNormals) {
+                const float dl = PS_NORMAL_DELTA;
+                float X[4] = {p[0], p[0] + dl, p[0], p[0]}, Y[4] = {p[1], p[1], p[1] + dl, p[1]}, Z[4] = {p[2], p[2], p[2], p[2] + dl};
+                float F[4], rgb[3];
+                eval_program<4, true>(prog, X, Y, Z, F, rgb, colorTab, G.sem);
+                const float dinv = -1.0f / dl;
+                float nx = (F[1] - F[0]) * dinv, nyv = (F[2] - F[0]) * dinv, nzv = (F[3] - F[0]) * dinv;
+                const float l2 = nx * nx + nyv * nyv + nzv * nzv;
+                if (l2 > 0.f) { const float il = rsqrtf(l2); nx *= il; nyv *= il; nzv *= il; }
+                else if (G.sem == PSGPU_SEM_SCALAR) { nx = nyv = nzv = 1.0f; }  // normalizeXYZ, PS_Vector.h:1072-1086
+                mo.nrm[vo] = nx; mo.nrm[vo + 1] = nyv; mo.nrm[vo + 2] = nzv;
+                mo.col[vo] = rgb[0]; mo.col[vo + 1] = rgb[1]; mo.col[vo + 2] = rgb[2];
+            }
+        }
+
+        // ---- triangles in cell order
+        uint32_t carryT = 0;
+        for (int round = 0; round < 3; round++) {
+            const int c = round * kThreads + t;
+            const uint32_t cfg = (c < 343) ? S.cellCase[c] : 0u;
+            const uint32_t nTri = c_nTriE[cfg];
+            uint32_t total;
+            const uint32_t ex = block_excl_scan(S, nTri, total) + carryT;
+            carryT += total;
+            if (nTri) {
+                const int cx = c / 49, cy = (c / 7) % 7, cz = c % 7;
+                const int8_t* row = &S.tri[cfg * 16];
+                for (uint32_t k = 0; k < nTri * 3; k++) {
+                    const int e = row[k];
+                    const int c1 = c_corner1[e], ax = c_edgeAxis[e];
+                    int sx = cx + ((c1 >> 2) & 1), sy = cy + ((c1 >> 1) & 1), sz = cz + (c1 & 1);
+                    uint32_t vid;
+                    if (perMpu) vid = S.edgeVid[(sx * 8 + sy * 64 + sz) * 3 + ax];
+                    else {
+                        const int dI = (sx == 7 && ax != 0 && r.x != G.hi[0] - 1) ? 1 : 0;
+                        const int dJ = (sy == 7 && ax != 1 && r.y != G.hi[1] - 1) ? 1 : 0;
+                        const int dK = (sz == 7 && ax != 2 && r.z != G.hi[2] - 1) ? 1 : 0;
+                        if ((dI | dJ | dK) == 0) {
+                            const int eb = (sx * 8 + sy * 64 + sz) * 3 + ax;
+                            vid = vbase + S.edgeP[eb >> 5] + __popc(S.edgeW[eb >> 5] & ((1u << (eb & 31)) - 1u));
+                        } else {
+                            sx -= 7 * dI; sy -= 7 * dJ; sz -= 7 * dK;
+                            const int32_t nc = candOfMpu[((size_t)(r.x + dI - G.lo[0]) * ny + (r.y + dJ - G.lo[1])) * nz + (r.z + dK - G.lo[2])];
+                            const int eb = (sx * 8 + sy * 64 + sz) * 3 + ax;
+                            const uint32_t w = fo.edgeMask[(size_t)nc * 48 + (eb >> 5)];
+                            vid = mo.vbase[nc] + fo.edgePrefix[(size_t)nc * 48 + (eb >> 5)] + __popc(w & ((1u << (eb & 31)) - 1u));
+                        }
+                    }
+                    mo.tri[(size_t)(tbase + ex) * 3 + k] = vid;
+                }
+            }
+        }
+        if (perMpu && t == 0 && mo.mixedIdx) {
+            const uint32_t mi = mo.mixedIdx[cand];
+            mo.mpuIjk[mi * 3] = r.x; mo.mpuIjk[mi * 3 + 1] = r.y; mo.mpuIjk[mi * 3 + 2] = r.z;
+            mo.mpuVbase[mi] = vbase; mo.mpuTbase[mi] = tbase;
+        }
+        __syncthreads();
+        m = S.next;
+        __syncthreads();
+    }
+}
+
+}  // namespace
+
+void launch_emit_kernel(const GridParams& G, const Region* cands, const float4* pool, const float* colorTab, const FieldOutputs& fo,
+                        const MeshOutputs& mo, const int32_t* candOfMpu, int nMixed, uint32_t maxProgQuads, int numSMs, cudaStream_t st) {
+    if (nMixed <= 0) return;
+    uint32_t cap = maxProgQuads < 8 ? 8 : maxProgQuads;
+    if (cap > kMaxProgCapQuads) cap = kMaxProgCapQuads;
+    cap = (cap + 7u) & ~7u;
+    const int smem = (int)(sizeof(EmitSmem) + cap * 16u);
+    static int configured = -1;
+    if (smem > configured) {
+        cudaFuncSetAttribute(emit_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+        configured = smem;
+    }
+    int perSM = 0;
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSM, emit_kernel, kThreads, smem);
+    if (perSM < 1) perSM = 1;
+    int grid = numSMs * perSM;
+    if (grid > nMixed) grid = nMixed;
+    emit_kernel<<<grid, kThreads, smem, st>>>(G, cands, pool, colorTab, fo, mo, candOfMpu, nMixed, cap);
+}
+
+}  // namespace psgpu

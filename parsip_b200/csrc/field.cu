@@ -1,0 +1,325 @@
+// Field-evaluation kernel (north-star subsystem 3) and the point-sampling parity hooks.
+//
+// One CTA of 128 threads evaluates the 8x8x8 corner lattice of an MPU: the MPU's pruned instruction list is
+// staged into shared memory by a TMA bulk copy (cp.async.bulk + mbarrier, double-buffered so the next MPU's
+// list lands while this one is evaluated), every thread interprets it for 4 consecutive-z corners, and the
+// field cache leaves as one coalesced float4 per thread. The same pass classifies the MPU (mixed signs?),
+// marks the crossing edges it owns and counts its triangles, so the mesh kernel knows its output offsets.
+//
+// Reference: CMPUProcessor::process_cells_simd phases 0-2 (PS_SimdPoly/include/PS_Polygonizer.cpp:483-701) and
+// CSIMDMPURunBody::doMarchingCubes' cache + classify (ParsipHaptics/include/CPolyParsipOptimized.cpp:187-244).
+#include "device_util.cuh"
+#include "interp.cuh"
+#include "kernels.h"
+#include "mc_tables.h"
+
+namespace psgpu {
+
+__constant__ uint8_t c_nTri[256] = PS_MC_NTRI_INIT;
+
+namespace {
+
+constexpr int kThreads = 128;
+constexpr uint32_t kMaxProgCapQuads = 1024;  // 16 KB per staging buffer; longer lists are read from global
+
+struct __align__(16) FieldSmemHeader {
+    uint64_t bar[2];
+    float fv[512];
+    uint32_t insideW[16];
+    uint32_t edgeW[48];
+    uint32_t warpSum[8];
+    int next;
+    int flags;
+};
+
+__global__ void __launch_bounds__(kThreads) field_kernel(GridParams G, const Region* __restrict__ cands, int nCand,
+                                                         const float4* __restrict__ pool, FieldOutputs out, uint32_t capQuads) {
+    extern __shared__ __align__(16) unsigned char smemRaw[];
+    FieldSmemHeader& S = *reinterpret_cast<FieldSmemHeader*>(smemRaw);
+    float4* progBuf = reinterpret_cast<float4*>(smemRaw + sizeof(FieldSmemHeader));
+    const int t = threadIdx.x;
+    const int lane = t & 31;
+
+    if (t == 0) {
+        mbar_init(&S.bar[0], 1);
+        mbar_init(&S.bar[1], 1);
+        fence_mbar_init();
+    }
+    __syncthreads();
+
+    int item = blockIdx.x;  // first item is static, the rest come from the work counter
+    int stage = 0;
+    uint32_t phase[2] = {0u, 0u};
+    if (t == 0 && item < nCand) {
+        const Region r = cands[item];
+        if (r.len <= capQuads) {
+            mbar_expect_tx(&S.bar[0], r.len * 16u);
+            tma_load_bulk(progBuf, pool + r.off, r.len * 16u, &S.bar[0]);
+        }
+    }
+    while (item < nCand) {
+        // fetch and prefetch the next work item
+        if (t == 0) {
+            const int nxt = (int)atomicAdd(&out.counters[0], 1u) + (int)gridDim.x;
+            S.next = nxt;
+            if (nxt < nCand) {
+                const Region rn = cands[nxt];
+                if (rn.len <= capQuads) {
+                    fence_proxy_async();
+                    mbar_expect_tx(&S.bar[stage ^ 1], rn.len * 16u);
+                    tma_load_bulk(progBuf + (size_t)(stage ^ 1) * capQuads, pool + rn.off, rn.len * 16u, &S.bar[stage ^ 1]);
+                }
+            }
+        }
+        if (t < 16) S.insideW[t] = 0u;
+        if (t < 48) S.edgeW[t] = 0u;
+        const Region r = cands[item];
+        const float4* prog;
+        if (r.len <= capQuads) {
+            mbar_wait(&S.bar[stage], phase[stage]);
+            phase[stage] ^= 1u;
+            prog = progBuf + (size_t)stage * capQuads;
+        } else {
+            prog = pool + r.off;
+        }
+
+        // ---- evaluate 4 corners: (i, j, 4*kh .. 4*kh+3)
+        const int kh = t & 1, ci = (t >> 1) & 7, cj = t >> 4;
+        float X[4], Y[4], Z[4], F[4];
+        {
+            const float x = corner_coord(G, 0, r.x, ci), y = corner_coord(G, 1, r.y, cj);
+#pragma unroll
+            for (int n = 0; n < 4; n++) { X[n] = x; Y[n] = y; Z[n] = corner_coord(G, 2, r.z, 4 * kh + n); }
+        }
+        eval_program<4, false>(prog, X, Y, Z, F, nullptr, nullptr, G.sem);
+        reinterpret_cast<float4*>(S.fv)[t] = make_float4(F[0], F[1], F[2], F[3]);
+        uint32_t in4 = 0;
+#pragma unroll
+        for (int n = 0; n < 4; n++) in4 |= (is_inside(G, F[n]) ? 1u : 0u) << n;
+        // early discard like PS_Polygonizer.cpp:602-609: all corners inside or all outside
+        const int anyIn = __syncthreads_or(in4 != 0u);
+        const int anyOut = __syncthreads_or(in4 != 0xFu);
+        uint32_t nV = 0, nT = 0;
+        if (anyIn && anyOut) {
+            atomicOr(&S.insideW[t >> 3], in4 << ((t & 7) * 4));
+            __syncthreads();
+            // ---- crossing edges this MPU owns: 12 bits per thread (4 corners x 3 axes)
+            const bool lastX = (r.x == G.hi[0] - 1), lastY = (r.y == G.hi[1] - 1), lastZ = (r.z == G.hi[2] - 1);
+            const bool perMpu = (G.output == PSGPU_OUT_MPU);
+            uint32_t bits12 = 0;
+#pragma unroll
+            for (int n = 0; n < 4; n++) {
+                const int ck = 4 * kh + n;
+                const int idx = 4 * t + n;
+                const bool me = (in4 >> n) & 1u;
+                const bool ownX = perMpu || ci < 7 || lastX, ownY = perMpu || cj < 7 || lastY, ownZ = perMpu || ck < 7 || lastZ;
+                if (ci < 7 && ownY && ownZ) { const int nb = idx + 8; if (((S.insideW[nb >> 5] >> (nb & 31)) & 1u) != (uint32_t)me) bits12 |= 1u << (n * 3 + 0); }
+                if (cj < 7 && ownX && ownZ) { const int nb = idx + 64; if (((S.insideW[nb >> 5] >> (nb & 31)) & 1u) != (uint32_t)me) bits12 |= 1u << (n * 3 + 1); }
+                if (ck < 7 && ownX && ownY) { const int nb = idx + 1; if (((S.insideW[nb >> 5] >> (nb & 31)) & 1u) != (uint32_t)me) bits12 |= 1u << (n * 3 + 2); }
+            }
+            if (bits12) {
+                const int e0 = 12 * t;
+                atomicOr(&S.edgeW[e0 >> 5], bits12 << (e0 & 31));
+                if ((e0 & 31) > 20) atomicOr(&S.edgeW[(e0 >> 5) + 1], bits12 >> (32 - (e0 & 31)));
+            }
+            // ---- triangles
+            uint32_t myT = 0;
+            for (int c = t; c < 343; c += kThreads) {
+                const int cx = c / 49, cy = (c / 7) % 7, cz = c % 7;
+                uint32_t cfg = 0;
+#pragma unroll
+                for (int b = 0; b < 8; b++) {
+                    const int idx = (cx + ((b >> 2) & 1)) * 8 + (cy + ((b >> 1) & 1)) * 64 + (cz + (b & 1));
+                    cfg |= ((S.insideW[idx >> 5] >> (idx & 31)) & 1u) << b;
+                }
+                myT += c_nTri[cfg];
+            }
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) myT += __shfl_xor_sync(0xffffffffu, myT, o);
+            if (lane == 0) S.warpSum[t >> 5] = myT;
+            __syncthreads();
+            nT = S.warpSum[0] + S.warpSum[1] + S.warpSum[2] + S.warpSum[3];
+            // ---- exclusive popcount prefix over the 48 edge words (warp 0)
+            if (t < 32) {
+                const uint32_t w0 = S.edgeW[t], w1 = (t < 16) ? S.edgeW[32 + t] : 0u;
+                uint32_t p0 = __popc(w0), p1 = __popc(w1);
+                uint32_t s0 = p0, s1 = p1;
+#pragma unroll
+                for (int o = 1; o < 32; o <<= 1) {
+                    const uint32_t a = __shfl_up_sync(0xffffffffu, s0, o), b = __shfl_up_sync(0xffffffffu, s1, o);
+                    if (lane >= o) { s0 += a; s1 += b; }
+                }
+                const uint32_t tot0 = __shfl_sync(0xffffffffu, s0, 31), tot1 = __shfl_sync(0xffffffffu, s1, 15);
+                out.edgeMask[(size_t)item * 48 + t] = w0;
+                out.edgePrefix[(size_t)item * 48 + t] = (uint16_t)(s0 - p0);
+                if (t < 16) {
+                    out.edgeMask[(size_t)item * 48 + 32 + t] = w1;
+                    out.edgePrefix[(size_t)item * 48 + 32 + t] = (uint16_t)(tot0 + s1 - p1);
+                }
+                if (t == 0) S.warpSum[4] = tot0 + tot1;
+            }
+            __syncthreads();
+            nV = S.warpSum[4];
+            if (nT > 0 && !G.forceFv) out.fv[(size_t)item * 128 + t] = reinterpret_cast<float4*>(S.fv)[t];
+        }
+        if (G.forceFv) out.fv[(size_t)item * 128 + t] = reinterpret_cast<float4*>(S.fv)[t];
+        if (t == 0) {
+            out.vcount[item] = (nT > 0) ? nV : 0u;
+            out.tcount[item] = nT;
+            if (nT > 0) {
+                const uint32_t slot = atomicAdd(&out.counters[1], 1u);
+                out.mixedList[slot] = (uint32_t)item;
+                if (G.output == PSGPU_OUT_MPU && (nV > 512u || nT > 512u)) atomicAdd(&out.counters[2], 1u);
+            }
+        }
+        __syncthreads();
+        item = S.next;
+        stage ^= 1;
+        __syncthreads();
+    }
+}
+
+// ---- parity hooks: the full program at arbitrary points ------------------------------------------------
+__global__ void __launch_bounds__(128) points_field_kernel(const float4* __restrict__ prog, const float* __restrict__ xyz, int64_t n,
+                                                           float* __restrict__ f, int sem) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t j = i < n ? i : n - 1;
+    float X[1] = {xyz[j * 3]}, Y[1] = {xyz[j * 3 + 1]}, Z[1] = {xyz[j * 3 + 2]}, F[1];
+    eval_program<1, false>(prog, X, Y, Z, F, nullptr, nullptr, sem);
+    if (i < n) f[i] = F[0];
+}
+
+// field + colour at p and the forward-difference normal with NORMAL_DELTA (PS_Polygonizer.cpp:764-782, 1598-1622)
+__global__ void __launch_bounds__(128) points_fcn_kernel(const float4* __restrict__ prog, const float* __restrict__ colorTab,
+                                                         const float* __restrict__ xyz, int64_t n, float* __restrict__ f,
+                                                         float* __restrict__ col, float* __restrict__ nrm, int sem) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t j = i < n ? i : n - 1;
+    const float px = xyz[j * 3], py = xyz[j * 3 + 1], pz = xyz[j * 3 + 2];
+    float X[4] = {px, px + PS_NORMAL_DELTA, px, px}, Y[4] = {py, py, py + PS_NORMAL_DELTA, py}, Z[4] = {pz, pz, pz, pz + PS_NORMAL_DELTA};
+    float F[4], rgb[3];
+    eval_program<4, true>(prog, X, Y, Z, F, rgb, colorTab, sem);
+    if (i < n) {
+        const float dinv = -1.0f / PS_NORMAL_DELTA;
+        float nx = (F[1] - F[0]) * dinv, ny = (F[2] - F[0]) * dinv, nz = (F[3] - F[0]) * dinv;
+        const float l2 = nx * nx + ny * ny + nz * nz;
+        if (l2 > 0.f) { const float inv = rsqrtf(l2); nx *= inv; ny *= inv; nz *= inv; }
+        f[i] = F[0];
+        col[i * 3] = rgb[0]; col[i * 3 + 1] = rgb[1]; col[i * 3 + 2] = rgb[2];
+        nrm[i * 3] = nx; nrm[i * 3 + 1] = ny; nrm[i * 3 + 2] = nz;
+    }
+}
+
+// exact SURVEY 8(d) bookkeeping over the final per-MPU programs: acc[0] += 512 * flops, acc[1] += 512 * prims,
+// acc[2] += quads, acc[3] += 512 (corner evaluations)
+__global__ void program_stats_kernel(const Region* __restrict__ cands, int nCand, const float4* __restrict__ pool,
+                                     unsigned long long* __restrict__ acc) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    unsigned long long fl = 0, pr = 0, qd = 0, ev = 0;
+    if (i < nCand) {
+        const Region r = cands[i];
+        const float4* p = pool + r.off;
+        for (uint32_t pc = 0;;) {
+            const uint32_t hdr = __float_as_uint(p[pc].x);
+            if (PS_HDR_OPC(hdr) == OPC_END) break;
+            fl += (unsigned long long)ps_algorithmic_flops(hdr);
+            if (PS_HDR_OPC(hdr) < OPC_FIRST_NONPRIM) pr++;
+            pc += ps_instr_quads(hdr);
+        }
+        qd = r.len; ev = 512;
+        fl *= 512; pr *= 512;
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        fl += __shfl_xor_sync(0xffffffffu, fl, o); pr += __shfl_xor_sync(0xffffffffu, pr, o);
+        qd += __shfl_xor_sync(0xffffffffu, qd, o); ev += __shfl_xor_sync(0xffffffffu, ev, o);
+    }
+    if ((threadIdx.x & 31) == 0 && ev) { atomicAdd(&acc[0], fl); atomicAdd(&acc[1], pr); atomicAdd(&acc[2], qd); atomicAdd(&acc[3], ev); }
+}
+
+// FP32 FMA-chain microbenchmark: 8 independent FFMA chains per thread, 2048 threads per SM
+__global__ void __launch_bounds__(256) fp32_peak_kernel(float* out, int iters, float a, float b) {
+    float v[8];
+#pragma unroll
+    for (int i = 0; i < 8; i++) v[i] = (float)(threadIdx.x + i);
+    for (int it = 0; it < iters; it++) {
+#pragma unroll
+        for (int u = 0; u < 8; u++) {
+#pragma unroll
+            for (int i = 0; i < 8; i++) v[i] = fmaf(v[i], a, b);
+        }
+    }
+    float s = 0;
+#pragma unroll
+    for (int i = 0; i < 8; i++) s += v[i];
+    if (s == 12345.678f) out[0] = s;
+}
+
+}  // namespace
+
+int field_kernel_smem_bytes(uint32_t maxProgQuads, uint32_t* capQuads) {
+    uint32_t cap = maxProgQuads < 8 ? 8 : maxProgQuads;
+    if (cap > kMaxProgCapQuads) cap = kMaxProgCapQuads;
+    cap = (cap + 7u) & ~7u;
+    *capQuads = cap;
+    return (int)(sizeof(FieldSmemHeader) + 2u * cap * 16u);
+}
+
+void launch_field_kernel(const GridParams& G, const Region* cands, int nCand, const float4* pool, const FieldOutputs& out, uint32_t maxProgQuads,
+                         int numSMs, cudaStream_t st) {
+    if (nCand <= 0) return;
+    uint32_t cap;
+    const int smem = field_kernel_smem_bytes(maxProgQuads, &cap);
+    static int configured = -1;
+    if (smem > configured) {
+        cudaFuncSetAttribute(field_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+        configured = smem;
+    }
+    int perSM = 0;
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSM, field_kernel, kThreads, smem);
+    if (perSM < 1) perSM = 1;
+    int grid = numSMs * perSM;  // persistent CTAs: a whole number of waves on 148 SMs
+    if (grid > nCand) grid = nCand;
+    field_kernel<<<grid, kThreads, smem, st>>>(G, cands, nCand, pool, out, cap);
+}
+
+void launch_points_field(const float4* prog, const float* xyz, int64_t n, float* f, int sem, cudaStream_t st) {
+    if (n <= 0) return;
+    points_field_kernel<<<(unsigned)((n + 127) / 128), 128, 0, st>>>(prog, xyz, n, f, sem);
+}
+
+void launch_points_field_color_normal(const float4* prog, const float* colorTab, const float* xyz, int64_t n, float* f, float* col, float* nrm,
+                                      int sem, cudaStream_t st) {
+    if (n <= 0) return;
+    points_fcn_kernel<<<(unsigned)((n + 127) / 128), 128, 0, st>>>(prog, colorTab, xyz, n, f, col, nrm, sem);
+}
+
+void launch_program_stats(const Region* cands, int nCand, const float4* pool, const uint32_t*, unsigned long long* acc, cudaStream_t st) {
+    if (nCand <= 0) return;
+    program_stats_kernel<<<(nCand + 127) / 128, 128, 0, st>>>(cands, nCand, pool, acc);
+}
+
+float run_fp32_peak(int numSMs, cudaStream_t st, float* ms_out) {
+    float* d = nullptr;
+    cudaMalloc(&d, 4);
+    const int iters = 4096, blocks = numSMs * 8;
+    cudaEvent_t e0, e1;
+    cudaEventCreate(&e0); cudaEventCreate(&e1);
+    float best = 1e30f;
+    for (int rep = 0; rep < 5; rep++) {
+        cudaEventRecord(e0, st);
+        fp32_peak_kernel<<<blocks, 256, 0, st>>>(d, iters, 1.0000001f, 1e-9f);
+        cudaEventRecord(e1, st);
+        cudaEventSynchronize(e1);
+        float ms = 0;
+        cudaEventElapsedTime(&ms, e0, e1);
+        if (rep > 0 && ms < best) best = ms;
+    }
+    cudaEventDestroy(e0); cudaEventDestroy(e1);
+    cudaFree(d);
+    if (ms_out) *ms_out = best;
+    const double flops = 2.0 * 64.0 * iters * 256.0 * blocks;
+    return (float)(flops / (best * 1e-3) / 1e12);
+}
+
+}  // namespace psgpu

@@ -1,0 +1,382 @@
+// Device-side interpreter of the postfix quad stream (program.h): evaluates the BlobTree field (and
+// optionally the colour) at N points per thread. Every thread of a CTA walks the SAME instruction list, so
+// the opcode switch is warp-uniform and parameter reads are shared-memory / L1 broadcasts; register
+// blocking over N points amortises the decode.
+//
+// Restates FieldComputer::fieldValue / computePrimitiveField / fieldValueAndColor
+// (PS_SimdPoly/include/PS_Polygonizer.cpp:934-1551) and COMPACTBLOBTREE::fieldvalueOp / fieldvaluePrim /
+// baseColorOp / warp* (ParsipHaptics/include/CompactBlobTree.cpp:677-1092, 1124-1294, 1315-1536) as a
+// stack machine instead of an explicit-stack tree walk / recursion.
+#ifndef PSGPU_INTERP_CUH
+#define PSGPU_INTERP_CUH
+#include <cuda_runtime.h>
+#include "../../include/psgpu.h"
+#include "program.h"
+
+namespace psgpu {
+
+__device__ __forceinline__ float wyvill(float d2) {
+    // max(0, (1-d^2)^3): PS_Polygonizer.h:397-407 (== ComputeWyvillFieldValueSquare for d^2 < 1)
+    const float t = 1.0f - d2;
+    return fmaxf(t * t * t, 0.0f);
+}
+
+// fast_pow of PS_SIMDVecN.h:122-128 with an exact reciprocal
+__device__ __forceinline__ float ricci_simd(float base, float e) { return base / (base + (e - e * base)); }
+
+template <int N>
+__device__ __forceinline__ void xform_points(const float4* q, const float (&x)[N], const float (&y)[N], const float (&z)[N],
+                                             float (&ox)[N], float (&oy)[N], float (&oz)[N]) {
+    const float4 r0 = q[0], r1 = q[1], r2 = q[2];
+#pragma unroll
+    for (int n = 0; n < N; n++) {
+        ox[n] = fmaf(r0.x, x[n], fmaf(r0.y, y[n], fmaf(r0.z, z[n], r0.w)));
+        oy[n] = fmaf(r1.x, x[n], fmaf(r1.y, y[n], fmaf(r1.z, z[n], r1.w)));
+        oz[n] = fmaf(r2.x, x[n], fmaf(r2.y, y[n], fmaf(r2.z, z[n], r2.w)));
+    }
+}
+
+// Squared skeleton distance of one primitive at N points. q0 = header quad, q = following quads.
+// (Also used by the culling pass, whose bounds rest on these being distances to a set, i.e. 1-Lipschitz.)
+template <int N>
+__device__ __forceinline__ void prim_d2(uint32_t opc, const float4 q0, const float4* __restrict__ q,
+                                           const float (&x)[N], const float (&y)[N], const float (&z)[N], float (&d2o)[N]) {
+    switch (opc) {
+    case OPC_POINT: {
+#pragma unroll
+        for (int n = 0; n < N; n++) {
+            const float dx = q0.y - x[n], dy = q0.z - y[n], dz = q0.w - z[n];
+            d2o[n] = fmaf(dx, dx, fmaf(dy, dy, dz * dz));
+        }
+    } break;
+    case OPC_SEGMENT: {  // clamped to the segment: PS_GeometryFuncs.cpp:156-179
+        const float4 d = q[0];
+#pragma unroll
+        for (int n = 0; n < N; n++) {
+            const float vx = x[n] - q0.y, vy = y[n] - q0.z, vz = z[n] - q0.w;
+            const float t = __saturatef(fmaf(vx, d.x, fmaf(vy, d.y, vz * d.z)) * d.w);
+            const float rx = fmaf(-t, d.x, vx), ry = fmaf(-t, d.y, vy), rz = fmaf(-t, d.z, vz);
+            d2o[n] = fmaf(rx, rx, fmaf(ry, ry, rz * rz));
+        }
+    } break;
+    case OPC_LINE_INF: {  // PS_Polygonizer.cpp:984-1011: projection not clamped
+        const float4 d = q[0];
+#pragma unroll
+        for (int n = 0; n < N; n++) {
+            const float vx = x[n] - q0.y, vy = y[n] - q0.z, vz = z[n] - q0.w;
+            const float t = fmaf(vx, d.x, fmaf(vy, d.y, vz * d.z)) / d.w;
+            const float rx = fmaf(-t, d.x, vx), ry = fmaf(-t, d.y, vy), rz = fmaf(-t, d.z, vz);
+            d2o[n] = fmaf(rx, rx, fmaf(ry, ry, rz * rz));
+        }
+    } break;
+    case OPC_CYLINDER: {  // PS_Polygonizer.cpp:1012-1039 == CompactBlobTree.cpp:915-930
+        const float4 d = q[0];
+        const float height = q[1].x;
+#pragma unroll
+        for (int n = 0; n < N; n++) {
+            const float vx = x[n] - q0.y, vy = y[n] - q0.z, vz = z[n] - q0.w;
+            float yy = fmaf(vx, d.x, fmaf(vy, d.y, vz * d.z));
+            const float r2 = fmaf(vx, vx, fmaf(vy, vy, vz * vz)) - yy * yy;
+            const float xx = fmaxf(sqrtf(fmaxf(r2, 0.0f)) - d.w, 0.0f);
+            yy = (yy > 0.0f) ? fmaxf(yy - height, 0.0f) : yy;
+            d2o[n] = fmaf(xx, xx, yy * yy);
+        }
+    } break;
+    case OPC_CUBE: {  // PS_Polygonizer.cpp:1059-1097: per-axis overshoot beyond +-side
+        const float side = q[0].x;
+#pragma unroll
+        for (int n = 0; n < N; n++) {
+            const float ex = fmaxf(fabsf(x[n] - q0.y) - side, 0.0f);
+            const float ey = fmaxf(fabsf(y[n] - q0.z) - side, 0.0f);
+            const float ez = fmaxf(fabsf(z[n] - q0.w) - side, 0.0f);
+            d2o[n] = fmaf(ex, ex, fmaf(ey, ey, ez * ez));
+        }
+    } break;
+    case OPC_DISC: {  // PS_Polygonizer.cpp:1099-1132 / CompactBlobTree.cpp:996-1017, exact rsqrt (Q7)
+        const float4 nr = q[0];
+#pragma unroll
+        for (int n = 0; n < N; n++) {
+            const float vx = x[n] - q0.y, vy = y[n] - q0.z, vz = z[n] - q0.w;
+            const float nd = fmaf(nr.x, vx, fmaf(nr.y, vy, nr.z * vz));
+            const float ux = fmaf(-nr.x, nd, vx), uy = fmaf(-nr.y, nd, vy), uz = fmaf(-nr.z, nd, vz);
+            const float u2 = fmaf(ux, ux, fmaf(uy, uy, uz * uz));
+            float d2;
+            if (nr.w * nr.w >= u2) d2 = fabsf(fmaf(vx, vx, fmaf(vy, vy, vz * vz)) - u2);
+            else {
+                const float s = nr.w * rsqrtf(u2);
+                const float wx = fmaf(s, ux, -vx), wy = fmaf(s, uy, -vy), wz = fmaf(s, uz, -vz);
+                d2 = fmaf(wx, wx, fmaf(wy, wy, wz * wz));
+            }
+            d2o[n] = d2;
+        }
+    } break;
+    case OPC_RING: {  // PS_Polygonizer.cpp:1134-1173 / CompactBlobTree.cpp:1019-1040
+        const float4 nr = q[0];
+#pragma unroll
+        for (int n = 0; n < N; n++) {
+            const float vx = x[n] - q0.y, vy = y[n] - q0.z, vz = z[n] - q0.w;
+            const float nd = fmaf(nr.x, vx, fmaf(nr.y, vy, nr.z * vz));
+            const float ux = fmaf(-nr.x, nd, vx), uy = fmaf(-nr.y, nd, vy), uz = fmaf(-nr.z, nd, vz);
+            const float u2 = fmaf(ux, ux, fmaf(uy, uy, uz * uz));
+            float d2;
+            if (u2 == 0.0f) d2 = fmaf(nr.w, nr.w, fmaf(vx, vx, fmaf(vy, vy, vz * vz)));
+            else {
+                const float s = nr.w * rsqrtf(u2);
+                const float wx = fmaf(s, ux, -vx), wy = fmaf(s, uy, -vy), wz = fmaf(s, uz, -vz);
+                d2 = fmaf(wx, wx, fmaf(wy, wy, wz * wz));
+            }
+            d2o[n] = d2;
+        }
+    } break;
+    default: {  // OPC_NULLPRIM
+#pragma unroll
+        for (int n = 0; n < N; n++) d2o[n] = 4.0f;  // field 0
+    } break;
+    }
+}
+
+template <int N>
+__device__ __forceinline__ void prim_field(uint32_t opc, const float4 q0, const float4* __restrict__ q,
+                                           const float (&x)[N], const float (&y)[N], const float (&z)[N], float (&f)[N]) {
+    float d2[N];
+    prim_d2<N>(opc, q0, q, x, y, z, d2);
+#pragma unroll
+    for (int n = 0; n < N; n++) f[n] = wyvill(d2[n]);
+}
+
+__device__ __forceinline__ float combine_val(uint32_t cmb, float top, float v) {
+    switch (cmb) {
+    case CMB_ADD: return top + v;
+    case CMB_MAX: return fmaxf(top, v);
+    case CMB_MIN: return fminf(top, v);
+    case CMB_DIF: return fminf(top, 1.0f - v);
+    default: return top * (1.0f - v);  // CMB_SDIF
+    }
+}
+
+// colour of `top (cmb) v` for point 0; (tf, tc) = stack top before the combine, (vf, vc) = incoming value.
+// taux = running min used by the scalar twin's (smooth) difference colour pick.
+__device__ __forceinline__ void combine_color(int sem, uint32_t cmb, float tf, float (&tc)[3], float& taux, float vf,
+                                              const float (&vc)[3], float result) {
+    if (sem == PSGPU_SEM_SIMD) {
+        float wl, wr;
+        if (cmb == CMB_ADD) {  // PS_Polygonizer.cpp:1475-1487: two*(half+f)-one, unnormalised
+            wl = __fsub_rn(__fmul_rn(2.0f, __fadd_rn(0.5f, tf)), 1.0f);
+            wr = __fsub_rn(__fmul_rn(2.0f, __fadd_rn(0.5f, vf)), 1.0f);
+        } else if (cmb == CMB_MAX || cmb == CMB_MIN) {  // :1489-1500
+            wl = (result - tf == 0.0f) ? 1.0f : 0.0f;
+            wr = (result - vf == 0.0f) ? 1.0f : 0.0f;
+        } else {  // :1502-1512
+            wl = (tf == result) ? 1.0f : 0.0f;
+            wr = (1.0f - vf == result) ? 1.0f : 0.0f;
+        }
+#pragma unroll
+        for (int a = 0; a < 3; a++) tc[a] = __fadd_rn(__fmul_rn(wl, tc[a]), __fmul_rn(wr, vc[a]));
+    } else {  // CompactBlobTree.cpp:1186-1260, kept normalised per entry (association-invariant)
+        if (cmb == CMB_ADD) {
+            const float s = tf + vf;
+            if (s != 0.0f) {
+                const float inv = 1.0f / s;
+#pragma unroll
+                for (int a = 0; a < 3; a++) tc[a] = (tf * tc[a] + vf * vc[a]) * inv;
+            }
+        } else if (cmb == CMB_MAX) {
+            if (vf > tf) { tc[0] = vc[0]; tc[1] = vc[1]; tc[2] = vc[2]; }
+        } else if (cmb == CMB_MIN) {
+            if (vf < tf) { tc[0] = vc[0]; tc[1] = vc[1]; tc[2] = vc[2]; }
+        } else {
+            const float cf = 1.0f - vf;
+            if (cf < taux) { taux = cf; tc[0] = vc[0]; tc[1] = vc[1]; tc[2] = vc[2]; }
+        }
+    }
+}
+
+// Evaluates the program at N points. COLOR also produces the colour at point 0.
+// `prog` may point to shared or global memory (generic address).
+template <int N, bool COLOR>
+__device__ void eval_program(const float4* __restrict__ prog, const float (&X)[N], const float (&Y)[N], const float (&Z)[N],
+                             float (&F)[N], float* rgb, const float* __restrict__ colorTab, int sem) {
+    float x[N], y[N], z[N];
+    float top[N];
+    float vs[PS_MAX_VALUE_STACK][N];
+    float pstk[PS_MAX_POINT_STACK][3][N];
+    float cstk[COLOR ? PS_MAX_VALUE_STACK : 1][5];
+    float tc[3] = {0.f, 0.f, 0.f};
+    float taux = 0.f;
+    int sp = 0, psp = 0;
+#pragma unroll
+    for (int n = 0; n < N; n++) { x[n] = X[n]; y[n] = Y[n]; z[n] = Z[n]; top[n] = 0.0f; }
+    int pc = 0;
+    bool first = true;
+    for (;;) {
+        const float4 q0 = prog[pc];
+        const uint32_t hdr = __float_as_uint(q0.x);
+        const uint32_t opc = PS_HDR_OPC(hdr);
+        if (opc == OPC_END) break;
+        if (opc < OPC_FIRST_NONPRIM) {
+            const uint32_t cmb = PS_HDR_CMB(hdr);
+            const int nq = ps_base_quads(opc);
+            float f[N];
+            if (PS_HDR_XF(hdr)) {
+                float lx[N], ly[N], lz[N];
+                xform_points<N>(prog + pc + nq, x, y, z, lx, ly, lz);
+                prim_field<N>(opc, q0, prog + pc + 1, lx, ly, lz, f);
+                pc += nq + 3;
+            } else {
+                prim_field<N>(opc, q0, prog + pc + 1, x, y, z, f);
+                pc += nq;
+            }
+            float pcol[3];
+            if (COLOR) {
+                const uint32_t id = PS_HDR_PRIM(hdr);
+                pcol[0] = colorTab[id * 3]; pcol[1] = colorTab[id * 3 + 1]; pcol[2] = colorTab[id * 3 + 2];
+            }
+            if (cmb == CMB_PUSH) {
+                if (!first) {
+#pragma unroll
+                    for (int n = 0; n < N; n++) vs[sp][n] = top[n];
+                    if (COLOR) { cstk[sp][0] = tc[0]; cstk[sp][1] = tc[1]; cstk[sp][2] = tc[2]; cstk[sp][3] = taux; }
+                    sp++;
+                }
+                first = false;
+#pragma unroll
+                for (int n = 0; n < N; n++) top[n] = f[n];
+                if (COLOR) { tc[0] = pcol[0]; tc[1] = pcol[1]; tc[2] = pcol[2]; taux = f[0]; }
+            } else {
+                if (COLOR) {
+                    const float r0 = combine_val(cmb, top[0], f[0]);
+                    combine_color(sem, cmb, top[0], tc, taux, f[0], pcol, r0);
+                }
+#pragma unroll
+                for (int n = 0; n < N; n++) top[n] = combine_val(cmb, top[n], f[n]);
+            }
+            continue;
+        }
+        switch (opc) {
+        case OPC_COMBINE: {
+            const uint32_t cmb = PS_HDR_CMB(hdr);
+            sp--;
+            if (COLOR) {
+                float vc[3] = {tc[0], tc[1], tc[2]};
+                const float vf = top[0];
+                tc[0] = cstk[sp][0]; tc[1] = cstk[sp][1]; tc[2] = cstk[sp][2]; taux = cstk[sp][3];
+                const float tf = vs[sp][0];
+                const float r0 = combine_val(cmb, tf, vf);
+                combine_color(sem, cmb, tf, tc, taux, vf, vc, r0);
+            }
+#pragma unroll
+            for (int n = 0; n < N; n++) top[n] = combine_val(cmb, vs[sp][n], top[n]);
+            pc += 1;
+        } break;
+        case OPC_POW: {
+#pragma unroll
+            for (int n = 0; n < N; n++) top[n] = powf(top[n], q0.y);
+            pc += 1;
+        } break;
+        case OPC_RICCI_SIMD: {
+            sp--;
+            if (COLOR) {
+                float vc[3] = {tc[0], tc[1], tc[2]};
+                const float vf = top[0];
+                tc[0] = cstk[sp][0]; tc[1] = cstk[sp][1]; tc[2] = cstk[sp][2]; taux = cstk[sp][3];
+                combine_color(sem, CMB_ADD, vs[sp][0], tc, taux, vf, vc, 0.0f);
+            }
+#pragma unroll
+            for (int n = 0; n < N; n++) top[n] = ricci_simd(vs[sp][n] + top[n], q0.y);
+            pc += 1;
+        } break;
+        case OPC_CLAMP1: {
+#pragma unroll
+            for (int n = 0; n < N; n++) top[n] = fminf(top[n], 1.0f);
+            pc += 1;
+        } break;
+        case OPC_DIF0: {
+#pragma unroll
+            for (int n = 0; n < N; n++) top[n] = fminf(0.0f, 1.0f - top[n]);
+            pc += 1;
+        } break;
+        case OPC_POPPOINT: {
+            psp--;
+#pragma unroll
+            for (int n = 0; n < N; n++) { x[n] = pstk[psp][0][n]; y[n] = pstk[psp][1][n]; z[n] = pstk[psp][2][n]; }
+            pc += 1;
+        } break;
+        default: {  // warps and operator affine: push the point, transform it
+#pragma unroll
+            for (int n = 0; n < N; n++) { pstk[psp][0][n] = x[n]; pstk[psp][1][n] = y[n]; pstk[psp][2][n] = z[n]; }
+            psp++;
+            if (opc == OPC_AFFINE) {
+                float ox[N], oy[N], oz[N];
+                xform_points<N>(prog + pc + 1, x, y, z, ox, oy, oz);
+#pragma unroll
+                for (int n = 0; n < N; n++) { x[n] = ox[n]; y[n] = oy[n]; z[n] = oz[n]; }
+                pc += 4;
+            } else if (opc == OPC_TWIST) {  // CompactBlobTree.cpp:1355-1385
+                const float k = q0.y;
+                const int axis = (int)q0.z;
+#pragma unroll
+                for (int n = 0; n < N; n++) {
+                    float s, c;
+                    if (axis == 0) {
+                        sincosf(x[n] * k, &s, &c);
+                        const float ny = y[n] * c - z[n] * s, nz = y[n] * s + z[n] * c;
+                        y[n] = ny; z[n] = nz;
+                    } else if (axis == 1) {
+                        sincosf(y[n] * k, &s, &c);
+                        const float nx = x[n] * c - z[n] * s, nz = x[n] * s + z[n] * c;
+                        x[n] = nx; z[n] = nz;
+                    } else {
+                        sincosf(z[n] * k, &s, &c);
+                        const float nx = x[n] * c - y[n] * s, ny = x[n] * s + y[n] * c;
+                        x[n] = nx; y[n] = ny;
+                    }
+                }
+                pc += 1;
+            } else if (opc == OPC_TAPER) {  // CompactBlobTree.cpp:1387-1462 (incl. the taperAlongZ axis mix-up)
+                const float k = q0.y;
+                const int along = (int)q0.z, taper = (int)q0.w;
+#pragma unroll
+                for (int n = 0; n < N; n++) {
+                    const float a = (along == 0) ? x[n] : ((along == 1) ? y[n] : z[n]);
+                    const float s = 1.0f + a * k;
+                    if (along == 0) { if (taper == 2) z[n] *= s; else y[n] *= s; }
+                    else if (along == 1) { if (taper == 2) z[n] *= s; else x[n] *= s; }
+                    else { if (taper == 2) y[n] *= s; else x[n] *= s; }
+                }
+                pc += 1;
+            } else if (opc == OPC_BEND) {  // CompactBlobTree.cpp:1315-1353 (Barr bend in y/z)
+                const float k = q0.y, y0 = q0.z, left = q0.w;
+                const float4 q1 = prog[pc + 1];
+                const float right = q1.x, kd = q1.y;
+#pragma unroll
+                for (int n = 0; n < N; n++) {
+                    const float yh = fminf(fmaxf(y[n], left), right);
+                    float s, c;
+                    sincosf(k * (yh - y0), &s, &c);
+                    const float dy = y[n] - yh, zz = z[n] - kd;
+                    const float ny = -s * zz + y0 + c * dy;
+                    const float nz = c * zz + kd + s * dy;
+                    y[n] = ny; z[n] = nz;
+                }
+                pc += 2;
+            } else {  // OPC_SHEAR, CompactBlobTree.cpp:1464-1536
+                const float k = q0.y;
+                const int along = (int)q0.z, dep = (int)q0.w;
+#pragma unroll
+                for (int n = 0; n < N; n++) {
+                    if (along == 1) y[n] += k * ((dep == 2) ? z[n] : x[n]);
+                    else if (along == 2) z[n] += k * ((dep == 1) ? y[n] : x[n]);
+                    else x[n] += k * ((dep == 2) ? z[n] : y[n]);
+                }
+                pc += 1;
+            }
+        } break;
+        }
+    }
+#pragma unroll
+    for (int n = 0; n < N; n++) F[n] = top[n];
+    if (COLOR) { rgb[0] = tc[0]; rgb[1] = tc[1]; rgb[2] = tc[2]; }
+}
+
+}  // namespace psgpu
+#endif

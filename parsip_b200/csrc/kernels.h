@@ -1,0 +1,84 @@
+// Launch wrappers and POD parameter blocks shared by context.cu and the kernel translation units.
+#ifndef PSGPU_KERNELS_H
+#define PSGPU_KERNELS_H
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include "../../include/psgpu.h"
+#include "program.h"
+
+namespace psgpu {
+
+// A region of the MPU lattice (coordinates in units of the level's region size; for the last level = MPU
+// lattice index) with its pruned program in the pool.
+struct Region {
+    int32_t x, y, z;
+    uint32_t off, len;  // quads
+};
+
+struct CullLevel {
+    int childSize;       // MPUs per child-region edge
+    int lo[3], hi[3];    // slab bounds in MPUs (absolute lattice indices)
+    float gridLo[3];
+    float mpuSide;
+    int cullMode;
+    float iso;
+};
+
+struct GridParams {
+    float gridLo[3];
+    float cellsize;
+    float mpuSide;       // cellsize * 7 as a float product (PS_Polygonizer.cpp:329)
+    int lo[3], hi[3];    // slab bounds in MPUs
+    int dims[3];         // full lattice
+    int coordMode, sem, output, rootMode, rootIters;
+    int insideGE;        // 1: inside = f >= iso (SIMD path), 0: f > iso (scalar twin)
+    int wantColors, wantNormals;
+    int forceFv;         // parity hook: write the field cache of every candidate
+    float iso;
+};
+
+// per-candidate outputs of the field kernel
+struct FieldOutputs {
+    float4* fv;            // [cand][128] field cache, fv[i*8 + j*64 + k] layout
+    uint32_t* vcount;      // [cand]
+    uint32_t* tcount;      // [cand]
+    uint32_t* edgeMask;    // [cand][48] crossing-edge bits, bit e = (i*8 + j*64 + k)*3 + axis
+    uint16_t* edgePrefix;  // [cand][48] exclusive popcount prefix
+    uint32_t* mixedList;   // candidates with triangles (arrival order)
+    uint32_t* counters;    // [0] work counter, [1] mixed count, [2] over-capacity MPUs, [3] emit work counter
+};
+
+struct MeshOutputs {
+    float* pos; float* nrm; float* col; uint32_t* tri;
+    const uint32_t* vbase;   // [cand] exclusive scan of vcount
+    const uint32_t* tbase;   // [cand]
+    const uint32_t* mixedIdx;  // [cand] rank among mixed candidates (PSGPU_OUT_MPU tables), may be null
+    int32_t* mpuIjk; uint32_t* mpuVbase; uint32_t* mpuTbase;
+};
+
+// cull.cu
+void launch_all_mpus(const CullLevel& L, Region* out, uint32_t fullLen, int32_t* candOfMpu, int n, cudaStream_t st);
+void launch_prune_count(const CullLevel& L, const Region* parents, int nParents, const float4* pool, uint32_t* childLen, cudaStream_t st);
+void launch_flags(const uint32_t* len, uint32_t* flag, int n, cudaStream_t st);
+void launch_prune_emit(const CullLevel& L, const Region* parents, int nParents, const float4* pool, const uint32_t* childLen,
+                       const uint32_t* childOff, const uint32_t* childIdx, float4* outPool, uint32_t outBase, Region* children,
+                       int32_t* candOfMpu, uint32_t* maxLen, cudaStream_t st);
+size_t scan_temp_bytes(int n);
+void exclusive_scan_u32(void* temp, size_t tempBytes, const uint32_t* in, uint32_t* out, int n, cudaStream_t st);
+
+// field.cu
+int field_kernel_smem_bytes(uint32_t maxProgQuads, uint32_t* progCapQuads);
+void launch_field_kernel(const GridParams& G, const Region* cands, int nCand, const float4* pool, const FieldOutputs& out, uint32_t maxProgQuads,
+                         int numSMs, cudaStream_t st);
+void launch_points_field(const float4* prog, const float* xyz, int64_t n, float* f, int sem, cudaStream_t st);
+void launch_points_field_color_normal(const float4* prog, const float* colorTab, const float* xyz, int64_t n, float* f, float* col, float* nrm,
+                                      int sem, cudaStream_t st);
+void launch_program_stats(const Region* cands, int nCand, const float4* pool, const uint32_t* tcount, unsigned long long* acc, cudaStream_t st);
+float run_fp32_peak(int numSMs, cudaStream_t st, float* ms_out);
+
+// emit.cu
+void launch_emit_kernel(const GridParams& G, const Region* cands, const float4* pool, const float* colorTab, const FieldOutputs& fo,
+                        const MeshOutputs& mo, const int32_t* candOfMpu, int nMixed, uint32_t maxProgQuads, int numSMs, cudaStream_t st);
+
+}  // namespace psgpu
+#endif
