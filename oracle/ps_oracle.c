@@ -185,10 +185,10 @@ static float wyvill_iso_distance(float fv) {
     return fast_sqrt(1.0f - powf(fv, oneThird));
 }
 
-/* mat4Transform of a point, SP/PS_MATRIX4.h (row-major 4x4, w = 1) */
+/* mat4Transform of a point, SP/PS_MATRIX4.h:199-209: e[col][row] storage, translation in e[3][0..2] */
 static void mat4_transform(const float* m, const float* v, float* out) {
     float r[3];
-    for (int a = 0; a < 3; a++) r[a] = m[a * 4 + 0] * v[0] + m[a * 4 + 1] * v[1] + m[a * 4 + 2] * v[2] + m[a * 4 + 3];
+    for (int a = 0; a < 3; a++) r[a] = (m[0 * 4 + a] * v[0] + m[1 * 4 + a] * v[1] + m[2 * 4 + a] * v[2]) + m[3 * 4 + a];
     out[0] = r[0]; out[1] = r[1]; out[2] = r[2];
 }
 

@@ -5,7 +5,7 @@ package holds its ctypes binding (`api`), a host-side BlobTree description (`blo
 scene generators of SURVEY.md section 8(d) (`scenes`). There is no CPU fallback: every compute entry point
 raises if the CUDA extension is missing or no GPU is present.
 """
-from . import blobtree, scenes  # noqa: F401
+from . import blobtree, scenes, sharding  # noqa: F401
 from .api import (  # noqa: F401
     PsGpuError, Context, Program, Params, linearize, prepare_bboxes, count_mpus, lattice_dims, lib_path, load_library,
     SEM_SIMD, SEM_SCALAR, ROOT_FOURSAMPLE, ROOT_NEWTON_REF, ROOT_BISECT, COORD_MPU_LOCAL, COORD_GLOBAL,

@@ -247,7 +247,8 @@ def to_binary_soa(root: Node) -> dict:
             mats.append(p.xform)
             m4 = np.eye(4, dtype=np.float64)
             m4[:3, :] = p.xform
-            fwd.append(np.linalg.inv(m4).astype(np.float32))
+            # forward 4x4 in the memory order mat4Transform reads (e[col][row], translation in e[3][0..2], PS_MATRIX4.h:199-209)
+            fwd.append(np.ascontiguousarray(np.linalg.inv(m4).T).astype(np.float32))
     d["n_mats"] = len(mats)
     d["mats_bwd"] = np.stack(mats).reshape(-1, 12).astype(np.float32)
     d["mats_fwd"] = np.stack(fwd).reshape(-1, 16).astype(np.float32)

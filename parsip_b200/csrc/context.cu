@@ -60,6 +60,8 @@ struct psgpu_ctx {
     DevBuf pos, nrm, col, tri, mpuIjk, mpuVbase, mpuTbase;
     DevBuf ptsIn, ptsF, ptsCol, ptsNrm;
     uint32_t* hostScalars = nullptr;  // pinned readback
+    void* hostStage = nullptr;        // pinned upload staging (program + colours)
+    size_t hostStageCap = 0;
     cudaEvent_t ev[6];
     psgpu_mesh last{};
     psgpu_stats stats{};
@@ -110,6 +112,7 @@ extern "C" int psgpu_destroy(psgpu_ctx* ctx) {
     for (DevBuf* b : all) b->release();
     for (auto& e : ctx->ev) cudaEventDestroy(e);
     if (ctx->hostScalars) cudaFreeHost(ctx->hostScalars);
+    if (ctx->hostStage) cudaFreeHost(ctx->hostStage);
     cudaStreamDestroy(ctx->stream);
     delete ctx;
     return PSGPU_SUCCESS;
@@ -121,10 +124,19 @@ extern "C" int psgpu_upload_program(psgpu_ctx* ctx, const psgpu_program* p) {
     if (!ctx || !p || p->words.empty()) return PSGPU_PARAM_ERROR;
     CK(cudaSetDevice(ctx->device));
     const size_t bytes = p->words.size() * 4;
+    const size_t cbytes = p->colors.size() * 4;
+    if (bytes + cbytes > ctx->hostStageCap) {  // host -> device copies go through pinned memory
+        if (ctx->hostStage) cudaFreeHost(ctx->hostStage);
+        ctx->hostStage = nullptr;
+        ctx->hostStageCap = (bytes + cbytes) * 2;
+        CK(cudaMallocHost(&ctx->hostStage, ctx->hostStageCap));
+    }
+    memcpy(ctx->hostStage, p->words.data(), bytes);
+    if (cbytes) memcpy((char*)ctx->hostStage + bytes, p->colors.data(), cbytes);
     CK(ctx->pool.reserve(std::max(bytes * 4, (size_t)64 << 20)));
-    CK(cudaMemcpyAsync(ctx->pool.p, p->words.data(), bytes, cudaMemcpyHostToDevice, ctx->stream));
-    CK(ctx->colors.reserve(std::max(p->colors.size() * 4, (size_t)256)));
-    if (!p->colors.empty()) CK(cudaMemcpyAsync(ctx->colors.p, p->colors.data(), p->colors.size() * 4, cudaMemcpyHostToDevice, ctx->stream));
+    CK(cudaMemcpyAsync(ctx->pool.p, ctx->hostStage, bytes, cudaMemcpyHostToDevice, ctx->stream));
+    CK(ctx->colors.reserve(std::max(cbytes, (size_t)256)));
+    if (cbytes) CK(cudaMemcpyAsync(ctx->colors.p, (char*)ctx->hostStage + bytes, cbytes, cudaMemcpyHostToDevice, ctx->stream));
     CK(cudaStreamSynchronize(ctx->stream));
     ctx->progQuads = (uint32_t)(p->words.size() / 4);
     ctx->nPrims = p->nPrims;

@@ -11,300 +11,12 @@
 // the field over the region exclude the iso value (no surface can cross it).
 #include <cub/device/device_scan.cuh>
 
-#include "interp.cuh"
+#include "cull_walk.cuh"
 #include "kernels.h"
 
 namespace psgpu {
 
 namespace {
-
-struct Box3 { float lo[3], hi[3]; };
-
-__device__ __forceinline__ void imul(float alo, float ahi, float blo, float bhi, float& lo, float& hi) {
-    const float p0 = alo * blo, p1 = alo * bhi, p2 = ahi * blo, p3 = ahi * bhi;
-    lo = fminf(fminf(p0, p1), fminf(p2, p3));
-    hi = fmaxf(fmaxf(p0, p1), fmaxf(p2, p3));
-}
-
-// range of cos and sin over [t0, t1]
-__device__ void trig_range(float t0, float t1, float& cmin, float& cmax, float& smin, float& smax) {
-    const float TWO_PI = 6.2831853f, PI = 3.14159265f;
-    if (!(t1 - t0 < TWO_PI)) { cmin = smin = -1.f; cmax = smax = 1.f; return; }
-    float s0, c0, s1, c1;
-    sincosf(t0, &s0, &c0); sincosf(t1, &s1, &c1);
-    cmin = fminf(c0, c1); cmax = fmaxf(c0, c1); smin = fminf(s0, s1); smax = fmaxf(s0, s1);
-    // extremum at phase + 2*pi*n inside [t0, t1]  <=>  floor((t1-phase)/2pi) > floor((t0-phase)/2pi) or exact hit
-    auto has = [&](float phase) { return floorf((t1 - phase) / TWO_PI) != floorf((t0 - phase) / TWO_PI) || fmodf(t0 - phase, TWO_PI) == 0.f; };
-    if (has(0.f)) cmax = 1.f;
-    if (has(PI)) cmin = -1.f;
-    if (has(0.5f * PI)) smax = 1.f;
-    if (has(1.5f * PI)) smin = -1.f;
-    const float e = 1e-5f;
-    cmin = fmaxf(cmin - e, -1.f); cmax = fminf(cmax + e, 1.f); smin = fmaxf(smin - e, -1.f); smax = fminf(smax + e, 1.f);
-}
-
-__device__ __forceinline__ void pad_box(Box3& b) {
-#pragma unroll
-    for (int a = 0; a < 3; a++) {
-        const float e = 1e-5f * (fabsf(b.lo[a]) + fabsf(b.hi[a])) + 1e-6f;
-        b.lo[a] -= e; b.hi[a] += e;
-    }
-}
-
-// conservative image of a box under a warp / operator affine (interval arithmetic), SURVEY 7.3 item 4b
-__device__ void warp_box(uint32_t opc, const float4 q0, const float4* __restrict__ q, Box3& b) {
-    Box3 o = b;
-    if (opc == OPC_AFFINE) {
-        const float4 r[3] = {q[0], q[1], q[2]};
-        float c[3], h[3];
-#pragma unroll
-        for (int a = 0; a < 3; a++) { c[a] = 0.5f * (b.lo[a] + b.hi[a]); h[a] = 0.5f * (b.hi[a] - b.lo[a]); }
-#pragma unroll
-        for (int a = 0; a < 3; a++) {
-            const float cc = r[a].x * c[0] + r[a].y * c[1] + r[a].z * c[2] + r[a].w;
-            const float hh = fabsf(r[a].x) * h[0] + fabsf(r[a].y) * h[1] + fabsf(r[a].z) * h[2];
-            o.lo[a] = cc - hh; o.hi[a] = cc + hh;
-        }
-    } else if (opc == OPC_TWIST) {
-        const float k = q0.y;
-        const int ax = (int)q0.z;
-        const int u = (ax == 0) ? 1 : 0, v = (ax == 2) ? 1 : 2;
-        const float t0 = fminf(b.lo[ax] * k, b.hi[ax] * k), t1 = fmaxf(b.lo[ax] * k, b.hi[ax] * k);
-        float cmin, cmax, smin, smax;
-        trig_range(t0, t1, cmin, cmax, smin, smax);
-        float a0, a1, b0, b1;
-        imul(b.lo[u], b.hi[u], cmin, cmax, a0, a1); imul(b.lo[v], b.hi[v], smin, smax, b0, b1);
-        o.lo[u] = a0 - b1; o.hi[u] = a1 - b0;
-        imul(b.lo[u], b.hi[u], smin, smax, a0, a1); imul(b.lo[v], b.hi[v], cmin, cmax, b0, b1);
-        o.lo[v] = a0 + b0; o.hi[v] = a1 + b1;
-    } else if (opc == OPC_TAPER) {
-        const float k = q0.y;
-        const int al = (int)q0.z, tp = (int)q0.w;
-        int tgt;
-        if (al == 0) tgt = (tp == 2) ? 2 : 1; else if (al == 1) tgt = (tp == 2) ? 2 : 0; else tgt = (tp == 2) ? 1 : 0;
-        const float s0 = 1.0f + fminf(b.lo[al] * k, b.hi[al] * k), s1 = 1.0f + fmaxf(b.lo[al] * k, b.hi[al] * k);
-        imul(b.lo[tgt], b.hi[tgt], s0, s1, o.lo[tgt], o.hi[tgt]);
-    } else if (opc == OPC_BEND) {
-        const float k = q0.y, y0 = q0.z, left = q0.w, right = q[0].x, kd = q[0].y;
-        const float yh0 = fminf(fmaxf(b.lo[1], left), right), yh1 = fminf(fmaxf(b.hi[1], left), right);
-        const float ta = k * (yh0 - y0), tb = k * (yh1 - y0);
-        float cmin, cmax, smin, smax;
-        trig_range(fminf(ta, tb), fmaxf(ta, tb), cmin, cmax, smin, smax);
-        const float dy0 = fminf(b.lo[1] - left, 0.f), dy1 = fmaxf(b.hi[1] - right, 0.f);
-        const float z0 = b.lo[2] - kd, z1 = b.hi[2] - kd;
-        float a0, a1, b0, b1;
-        imul(smin, smax, z0, z1, a0, a1); imul(cmin, cmax, dy0, dy1, b0, b1);
-        o.lo[1] = -a1 + y0 + b0; o.hi[1] = -a0 + y0 + b1;
-        imul(cmin, cmax, z0, z1, a0, a1); imul(smin, smax, dy0, dy1, b0, b1);
-        o.lo[2] = a0 + kd + b0; o.hi[2] = a1 + kd + b1;
-    } else {  // OPC_SHEAR
-        const float k = q0.y;
-        const int al = (int)q0.z, dp = (int)q0.w;
-        int tgt, src;
-        if (al == 1) { tgt = 1; src = (dp == 2) ? 2 : 0; } else if (al == 2) { tgt = 2; src = (dp == 1) ? 1 : 0; } else { tgt = 0; src = (dp == 2) ? 2 : 1; }
-        o.lo[tgt] = b.lo[tgt] + fminf(k * b.lo[src], k * b.hi[src]);
-        o.hi[tgt] = b.hi[tgt] + fmaxf(k * b.lo[src], k * b.hi[src]);
-    }
-    pad_box(o);
-    b = o;
-}
-
-// [lo, hi] bound of one primitive's field over the ball around the box; returns true if identically zero.
-__device__ bool prim_bound(uint32_t hdr, const float4 q0, const float4* __restrict__ q, const Box3& b, float& flo, float& fhi) {
-    const uint32_t opc = PS_HDR_OPC(hdr);
-    if (opc == OPC_NULLPRIM) { flo = fhi = 0.f; return true; }
-    float c[1][3], r;
-    {
-        const float hx = 0.5f * (b.hi[0] - b.lo[0]), hy = 0.5f * (b.hi[1] - b.lo[1]), hz = 0.5f * (b.hi[2] - b.lo[2]);
-        c[0][0] = 0.5f * (b.lo[0] + b.hi[0]); c[0][1] = 0.5f * (b.lo[1] + b.hi[1]); c[0][2] = 0.5f * (b.lo[2] + b.hi[2]);
-        r = sqrtf(hx * hx + hy * hy + hz * hz);
-    }
-    float x[1] = {c[0][0]}, y[1] = {c[0][1]}, z[1] = {c[0][2]};
-    const int nq = ps_base_quads(opc);
-    if (PS_HDR_XF(hdr)) {
-        const float4* m = q + (nq - 1);
-        float ox[1], oy[1], oz[1];
-        xform_points<1>(m, x, y, z, ox, oy, oz);
-        x[0] = ox[0]; y[0] = oy[0]; z[0] = oz[0];
-        float fro = 0.f;
-#pragma unroll
-        for (int a = 0; a < 3; a++) fro += m[a].x * m[a].x + m[a].y * m[a].y + m[a].z * m[a].z;
-        r *= sqrtf(fro) * 1.00001f;
-    }
-    float d2[1];
-    prim_d2<1>(opc, q0, q, x, y, z, d2);
-    if (!(d2[0] == d2[0])) { flo = 0.f; fhi = 1.f; return false; }  // NaN: keep, unknown
-    const float d = sqrtf(d2[0]);
-    const float eps = 4e-6f * (fabsf(x[0]) + fabsf(y[0]) + fabsf(z[0]) + 1.0f) + 1e-5f * r + 1e-5f * d;
-    const float dmin = fmaxf(d - r - eps, 0.f), dmax = d + r + eps;
-    if (dmin >= 1.0f) { flo = fhi = 0.f; return true; }
-    fhi = fminf(wyvill(dmin * dmin) * 1.00001f + 1e-7f, 1.0f);
-    flo = fmaxf(wyvill(dmax * dmax) * 0.99999f - 1e-7f, 0.f);
-    return false;
-}
-
-__device__ __forceinline__ void bound_combine(uint32_t cmb, float& lo, float& hi, float vlo, float vhi) {
-    switch (cmb) {
-    case CMB_ADD: lo += vlo; hi += vhi; break;
-    case CMB_MAX: lo = fmaxf(lo, vlo); hi = fmaxf(hi, vhi); break;
-    case CMB_MIN: lo = fminf(lo, vlo); hi = fminf(hi, vhi); break;
-    case CMB_DIF: lo = fminf(lo, 1.0f - vhi); hi = fminf(hi, 1.0f - vlo); break;
-    default: {
-        float a, b;
-        imul(lo, hi, 1.0f - vhi, 1.0f - vlo, a, b);
-        lo = a; hi = b;
-    } break;
-    }
-    const float e = 2e-6f * (fabsf(lo) + fabsf(hi)) + 1e-7f;
-    lo -= e; hi += e;
-}
-
-// Prunes src against `box`. EMIT = false only measures. Returns the pruned length in quads including the
-// END quad, or 0 if the region needs no evaluation.
-template <bool EMIT>
-__device__ uint32_t prune_walk(const float4* __restrict__ src, const Box3& region, int cullMode, float iso, float4* __restrict__ dst) {
-    float blo[PS_MAX_VALUE_STACK], bhi[PS_MAX_VALUE_STACK];
-    uint32_t bstart[PS_MAX_VALUE_STACK];
-    bool bzero[PS_MAX_VALUE_STACK];
-    Box3 wbox[PS_MAX_POINT_STACK];
-    uint32_t wstart[PS_MAX_POINT_STACK];
-    int sp = -1, wsp = 0;
-    uint32_t emit = 0;
-    Box3 box = region;
-    auto put = [&](float4 v) { if (EMIT) dst[emit] = v; emit++; };
-    auto hdrquad = [&](uint32_t h) { return make_float4(__uint_as_float(h), 0.f, 0.f, 0.f); };
-    for (uint32_t pc = 0;;) {
-        const float4 q0 = src[pc];
-        const uint32_t hdr = __float_as_uint(q0.x);
-        const uint32_t opc = PS_HDR_OPC(hdr);
-        if (opc == OPC_END) break;
-        const int nq = ps_instr_quads(hdr);
-        auto copy = [&](uint32_t newHdr) {
-            put(make_float4(__uint_as_float(newHdr), q0.y, q0.z, q0.w));
-            for (int i = 1; i < nq; i++) put(src[pc + i]);
-        };
-        if (opc < OPC_FIRST_NONPRIM) {
-            const uint32_t cmb = PS_HDR_CMB(hdr);
-            float flo, fhi;
-            const bool pz = prim_bound(hdr, q0, src + pc + 1, box, flo, fhi);
-            if (cmb == CMB_PUSH) {
-                sp++;
-                bstart[sp] = emit; bzero[sp] = pz; blo[sp] = flo; bhi[sp] = fhi;
-                if (!pz) copy(hdr);
-            } else if (bzero[sp]) {
-                if (!pz && (cmb == CMB_ADD || cmb == CMB_MAX)) {  // 0 + f, max(0, f): the primitive becomes the entry
-                    copy((hdr & ~(15u << 6)) | (CMB_PUSH << 6));
-                    bzero[sp] = false; blo[sp] = flo; bhi[sp] = fhi;
-                }  // min(0,f) = 0, min(0,1-f) = 0 (f <= 1), 0*(1-f) = 0: stays zero
-            } else if (pz) {
-                if (cmb == CMB_MAX) {
-                    if (blo[sp] < 0.f) { put(hdrquad(PS_HDR(OPC_NULLPRIM, CMB_MAX, 0, 0))); blo[sp] = fmaxf(blo[sp], 0.f); }
-                } else if (cmb == CMB_MIN) {
-                    if (blo[sp] >= 0.f) { emit = bstart[sp]; bzero[sp] = true; blo[sp] = bhi[sp] = 0.f; }
-                    else { put(hdrquad(PS_HDR(OPC_NULLPRIM, CMB_MIN, 0, 0))); bhi[sp] = fminf(bhi[sp], 0.f); }
-                } else if (cmb == CMB_DIF) {  // min(top, 1 - 0)
-                    if (bhi[sp] > 1.0f) { put(hdrquad(PS_HDR(OPC_CLAMP1, 0, 0, 0))); bhi[sp] = 1.0f; blo[sp] = fminf(blo[sp], 1.0f); }
-                }  // top + 0, top * (1 - 0): nothing
-            } else {
-                copy(hdr);
-                bound_combine(cmb, blo[sp], bhi[sp], flo, fhi);
-            }
-            pc += nq;
-            continue;
-        }
-        switch (opc) {
-        case OPC_COMBINE: {
-            const uint32_t cmb = PS_HDR_CMB(hdr);
-            const int v = sp, t = sp - 1;
-            sp--;
-            if (bzero[t] && bzero[v]) {
-                // nothing was emitted for either
-            } else if (bzero[t]) {  // 0 (cmb) V; V's code starts at bstart[t]
-                if (cmb == CMB_ADD) { bzero[t] = false; blo[t] = blo[v]; bhi[t] = bhi[v]; }
-                else if (cmb == CMB_MAX) {
-                    bzero[t] = false; blo[t] = blo[v]; bhi[t] = bhi[v];
-                    if (blo[v] < 0.f) { put(hdrquad(PS_HDR(OPC_NULLPRIM, CMB_MAX, 0, 0))); blo[t] = 0.f; bhi[t] = fmaxf(bhi[v], 0.f); }
-                } else if (cmb == CMB_MIN) {
-                    if (blo[v] >= 0.f) emit = bstart[t];
-                    else { put(hdrquad(PS_HDR(OPC_NULLPRIM, CMB_MIN, 0, 0))); bzero[t] = false; blo[t] = fminf(blo[v], 0.f); bhi[t] = 0.f; }
-                } else if (cmb == CMB_DIF) {  // min(0, 1 - V)
-                    if (bhi[v] <= 1.0f) emit = bstart[t];
-                    else { put(hdrquad(PS_HDR(OPC_DIF0, 0, 0, 0))); bzero[t] = false; blo[t] = fminf(0.f, 1.0f - bhi[v]) - 1e-6f; bhi[t] = 0.f; }
-                } else emit = bstart[t];  // 0 * (1 - V)
-            } else if (bzero[v]) {  // T (cmb) 0
-                if (cmb == CMB_MAX) {
-                    if (blo[t] < 0.f) { put(hdrquad(PS_HDR(OPC_NULLPRIM, CMB_MAX, 0, 0))); blo[t] = 0.f; bhi[t] = fmaxf(bhi[t], 0.f); }
-                } else if (cmb == CMB_MIN) {
-                    if (blo[t] >= 0.f) { emit = bstart[t]; bzero[t] = true; blo[t] = bhi[t] = 0.f; }
-                    else { put(hdrquad(PS_HDR(OPC_NULLPRIM, CMB_MIN, 0, 0))); bhi[t] = fminf(bhi[t], 0.f); }
-                } else if (cmb == CMB_DIF) {
-                    if (bhi[t] > 1.0f) { put(hdrquad(PS_HDR(OPC_CLAMP1, 0, 0, 0))); bhi[t] = 1.0f; blo[t] = fminf(blo[t], 1.0f); }
-                }
-            } else {
-                copy(hdr);
-                bound_combine(cmb, blo[t], bhi[t], blo[v], bhi[v]);
-            }
-        } break;
-        case OPC_POW: {
-            if (!bzero[sp]) {
-                copy(hdr);
-                const float e = q0.y;
-                const float a = powf(fmaxf(blo[sp], 0.f), e), b = powf(fmaxf(bhi[sp], 0.f), e);
-                blo[sp] = fminf(a, b) * 0.9999f - 1e-7f; bhi[sp] = fmaxf(a, b) * 1.0001f + 1e-7f;
-                if (!(blo[sp] == blo[sp]) || !(bhi[sp] == bhi[sp])) { blo[sp] = -3.0e38f; bhi[sp] = 3.0e38f; }
-            }
-        } break;
-        case OPC_RICCI_SIMD: {
-            const int v = sp, t = sp - 1;
-            sp--;
-            if (bzero[t] && bzero[v]) {
-                // fast_pow(0) = 0
-            } else {
-                if (bzero[t] || bzero[v]) put(hdrquad(PS_HDR(OPC_NULLPRIM, CMB_PUSH, 0, 0)));  // materialise the zero operand
-                copy(hdr);
-                const float e = q0.y;
-                const float b0 = (bzero[t] ? 0.f : blo[t]) + (bzero[v] ? 0.f : blo[v]);
-                const float b1 = (bzero[t] ? 0.f : bhi[t]) + (bzero[v] ? 0.f : bhi[v]);
-                const float a = ricci_simd(b0, e), b = ricci_simd(b1, e);
-                bzero[t] = false;
-                blo[t] = fminf(a, b) - 1e-5f * fabsf(a) - 1e-6f; bhi[t] = fmaxf(a, b) + 1e-5f * fabsf(b) + 1e-6f;
-                if (!(e > 0.f) || !(blo[t] == blo[t]) || !(bhi[t] == bhi[t]) || b0 < 0.f) { blo[t] = -3.0e38f; bhi[t] = 3.0e38f; }
-            }
-        } break;
-        case OPC_CLAMP1: {
-            if (!bzero[sp]) { copy(hdr); bhi[sp] = fminf(bhi[sp], 1.0f); blo[sp] = fminf(blo[sp], 1.0f); }
-        } break;
-        case OPC_DIF0: {
-            if (!bzero[sp]) {
-                copy(hdr);
-                const float a = fminf(0.f, 1.0f - bhi[sp]) - 1e-6f, b = fminf(0.f, 1.0f - blo[sp]);
-                blo[sp] = a; bhi[sp] = b;
-            }
-        } break;
-        case OPC_POPPOINT: {
-            wsp--;
-            box = wbox[wsp];
-            if (bzero[sp]) emit = wstart[wsp];
-            else copy(hdr);
-            bstart[sp] = wstart[wsp];
-        } break;
-        default: {  // warps, operator affine
-            wbox[wsp] = box;
-            wstart[wsp] = emit;
-            wsp++;
-            copy(hdr);
-            warp_box(opc, q0, src + pc + 1, box);
-        } break;
-        }
-        pc += nq;
-    }
-    if (sp < 0 || bzero[0]) return 0;
-    if (cullMode >= PSGPU_CULL_INTERVAL) {
-        if (bhi[0] < iso - 1e-4f || blo[0] > iso + 1e-4f) return 0;
-    }
-    put(make_float4(__uint_as_float(PS_HDR(OPC_END, 0, 0, 0)), 0.f, 0.f, 0.f));
-    return emit;
-}
 
 __device__ __forceinline__ bool child_region(const CullLevel& L, const Region& parent, int c, int (&coord)[3], Box3& box) {
     coord[0] = parent.x * 4 + (c & 3); coord[1] = parent.y * 4 + ((c >> 2) & 3); coord[2] = parent.z * 4 + (c >> 4);

@@ -28,8 +28,8 @@ __constant__ uint8_t c_edgeAxis[12] = PS_MC_EDGEAXIS_INIT;
 __constant__ uint8_t c_nTriE[256] = PS_MC_NTRI_INIT;
 
 struct __align__(16) EmitSmem {
+    float fv[512];  // TMA destination: 16-byte aligned (first member)
     uint64_t bar;
-    float fv[512];
     uint32_t insideW[16];
     uint32_t edgeW[48];
     uint16_t edgeP[48];

@@ -23,8 +23,8 @@ constexpr int kThreads = 128;
 constexpr uint32_t kMaxProgCapQuads = 1024;  // 16 KB per staging buffer; longer lists are read from global
 
 struct __align__(16) FieldSmemHeader {
-    uint64_t bar[2];
     float fv[512];
+    uint64_t bar[2];
     uint32_t insideW[16];
     uint32_t edgeW[48];
     uint32_t warpSum[8];

@@ -9,7 +9,9 @@
 // stack machine instead of an explicit-stack tree walk / recursion.
 #ifndef PSGPU_INTERP_CUH
 #define PSGPU_INTERP_CUH
+#ifndef PSGPU_HOST_EMULATION
 #include <cuda_runtime.h>
+#endif
 #include "../../include/psgpu.h"
 #include "program.h"
 

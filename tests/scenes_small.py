@@ -1,0 +1,76 @@
+"""Small seeded scenes used by both the CPU and GPU tests (sized so the oracles finish in seconds)."""
+import numpy as np
+
+from parsip_b200 import blobtree as bt, scenes
+
+
+def s1():
+    """BASELINE configs[0]: 10 point/line primitives, union of two blends (runs on the UNMODIFIED reference)."""
+    return scenes.small()
+
+
+def blob(n=60, extent=3.5, seed=7, group=6):
+    return scenes.blobs(n, extent, seed, group=group)
+
+
+def csg_simd(seed=11):
+    """point / cylinder / cube / disc / ring under every operator the SIMD evaluator implements; no lines (Q1), no Ricci (Q6)."""
+    rs = np.random.RandomState(seed)
+    P = lambda: rs.uniform(0.4, 2.6, 3).astype(np.float32)
+    col = lambda: rs.uniform(0, 1, 3)
+    a = bt.Blend(bt.Point(P(), col()), bt.Cylinder(P(), rs.normal(size=3), 0.2, 0.6, col()))
+    b = bt.Union(bt.Cube(P(), 0.25, col()), bt.Point(P(), col()))
+    c = bt.Intersect(bt.Blend(bt.Point([1.5, 1.5, 1.5], col()), bt.Point([1.8, 1.5, 1.5], col())), bt.Cube([1.6, 1.5, 1.5], 0.5, col()))
+    d = bt.Dif(bt.Blend(bt.Point([0.8, 2.2, 0.9], col()), bt.Point([1.1, 2.2, 0.9], col())), bt.Point([0.95, 2.3, 1.0], col()))
+    e = bt.SmoothDif(bt.Cylinder([2.2, 0.8, 2.0], [0, 1, 0], 0.25, 0.8, col()), bt.Point([2.2, 1.2, 2.1], col()))
+    return bt.Union(bt.Union(a, b), bt.Union(c, bt.Union(d, e)))
+
+
+def discs_rings(seed=13):
+    rs = np.random.RandomState(seed)
+    P = lambda: rs.uniform(0.5, 2.5, 3).astype(np.float32)
+    col = lambda: rs.uniform(0, 1, 3)
+    return bt.Union(bt.Blend(bt.Disc(P(), rs.normal(size=3), 0.3, col()), bt.Ring(P(), rs.normal(size=3), 0.45, col())),
+                    bt.Blend(bt.Ring(P(), rs.normal(size=3), 0.35, col()), bt.Point(P(), col())))
+
+
+def with_xforms(seed=17):
+    """primitives carrying a backward 3x4 matrix (rotation + non-uniform scale + translation)."""
+    rs = np.random.RandomState(seed)
+
+    def M():
+        q, _ = np.linalg.qr(rs.normal(size=(3, 3)))
+        s = np.diag(rs.uniform(0.7, 1.4, 3))
+        m = np.zeros((3, 4), np.float32)
+        m[:, :3] = (q @ s).astype(np.float32)
+        m[:, 3] = rs.uniform(-0.3, 0.3, 3)
+        return m
+    col = lambda: rs.uniform(0, 1, 3)
+    P = lambda: rs.uniform(0.6, 2.0, 3).astype(np.float32)
+    return bt.Union(bt.Blend(bt.Point(P(), col(), M()), bt.Cylinder(P(), rs.normal(size=3), 0.15, 0.5, col(), M())),
+                    bt.Blend(bt.Cube(P(), 0.2, col(), M()), bt.Point(P(), col())))
+
+
+def csgwarp_small():
+    return scenes.csgwarp(n_groups=3, extent=5.0, seed=3)
+
+
+def ricci():
+    return bt.Ricci(2.5, bt.Point([1.0, 1.0, 1.0], (1, 0, 0)), bt.Point([1.5, 1.0, 1.0], (0, 1, 0)), bt.Line([1.0, 1.4, 1.0], [1.6, 1.5, 1.1], (0, 0, 1)))
+
+
+SIMD_SCENES = {"s1": s1, "blob": blob, "csg": csg_simd, "discs_rings": discs_rings, "xforms": with_xforms}
+SCALAR_SCENES = {"s1": s1, "blob": blob, "csg": csg_simd, "discs_rings": discs_rings, "xforms": with_xforms, "csgwarp": csgwarp_small, "ricci": ricci}
+
+
+def simd_oracle(root, pad_op_boxes=True):
+    """(binary tree, SOA arrays, SimdOracle with boxes prepared). pad_op_boxes neutralises the reference's depth>3
+    operator-box prune (boxes padded by 0.504 although the Wyvill support is 1.0)."""
+    from oracle.pyoracle import SimdOracle
+    b = bt.binarize(root)
+    soa = bt.to_binary_soa(b)
+    o = SimdOracle(soa)
+    o.prepare_bboxes(0.05)
+    if pad_op_boxes:
+        o.pad_op_boxes(1.0e6)  # infinite lines (Q1) reach beyond any finite box
+    return b, soa, o

@@ -12,6 +12,7 @@ root = bt.binarize(scenes.small())
 soa = bt.to_binary_soa(root)
 orc = SimdOracle(soa)
 orc.prepare_bboxes(0.05)
+orc.pad_op_boxes(1.0e6)  # neutralise the reference op-box prune
 lo, hi = orc.bbox()
 cs = scenes.cellsize_for(lo, hi, 128)
 prog = ps.linearize(bt.flatten(root), ps.SEM_SIMD, 0)
@@ -37,10 +38,10 @@ print("oracle nv", ref["vertices"], "nt", ref["triangles"], "crossed", ref["cros
 order = np.lexsort((m["mpu_ijk"][:, 2], m["mpu_ijk"][:, 1], m["mpu_ijk"][:, 0]))
 ro = ref["mpu_idx"]
 print("mpu sets equal:", np.array_equal(m["mpu_ijk"][order], ro))
-vb_ref = np.concatenate([[0], np.cumsum(ref["mpu_counts"][:, 0])]); tb_ref = np.concatenate([[0], np.cumsum(ref["mpu_counts"][:, 1])])
+vb_ref = np.concatenate([[0], np.cumsum(ref["mpu_counts"][:, 0].astype(np.int64))]).astype(np.int64); tb_ref = np.concatenate([[0], np.cumsum(ref["mpu_counts"][:, 1].astype(np.int64))]).astype(np.int64)
 maxd = 0.0; badc = 0; tri_bad = 0
 for q, r in enumerate(order):
-    v0, v1, t0, t1 = m["mpu_vbase"][r], m["mpu_vbase"][r + 1], m["mpu_tbase"][r], m["mpu_tbase"][r + 1]
+    v0, v1, t0, t1 = int(m["mpu_vbase"][r]), int(m["mpu_vbase"][r + 1]), int(m["mpu_tbase"][r]), int(m["mpu_tbase"][r + 1])
     if v1 - v0 != ref["mpu_counts"][q, 0] or t1 - t0 != ref["mpu_counts"][q, 1]:
         badc += 1; continue
     pg, pr = m["pos"][v0:v1], ref["pos"][vb_ref[q]:vb_ref[q + 1]]
