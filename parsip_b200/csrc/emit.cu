@@ -74,6 +74,7 @@ __device__ __forceinline__ EdgePos edge_endpoints(const GridParams& G, const Reg
 
 // PS_Polygonizer.cpp:728-762: samples at t = 0, 1/3, 2/3, 1 in one 4-wide evaluation, first lane whose
 // inside flag differs from lane 0 brackets the root, linear interpolation inside that sub-interval.
+template <bool STRICT>
 __device__ void root_foursample(const GridParams& G, const float4* prog, const EdgePos& E, float (&p)[3]) {
     float X[4], Y[4], Z[4], F[4];
     const float d = __fsub_rn(E.e2a, E.e1[E.axis]);
@@ -85,7 +86,7 @@ __device__ void root_foursample(const GridParams& G, const float4* prog, const E
         Y[l] = (E.axis == 1) ? moved : E.e1[1];
         Z[l] = (E.axis == 2) ? moved : E.e1[2];
     }
-    eval_program<4, false>(prog, X, Y, Z, F, nullptr, nullptr, G.sem);
+    eval_program<4, false, STRICT>(prog, X, Y, Z, F, nullptr, nullptr, G.sem);
     const bool state = is_inside(G, F[0]);
     // first lane whose flag differs from lane 0, else the last one (cpp:748-755)
     const int interval = (is_inside(G, F[1]) != state) ? 1 : ((is_inside(G, F[2]) != state) ? 2 : 3);
@@ -100,6 +101,7 @@ __device__ void root_foursample(const GridParams& G, const float4* prog, const E
 
 // Bracketed false position (Illinois) along the edge, re-evaluating the field; the bracket is guaranteed
 // because both endpoints are lattice corners whose cached values were produced by this same program.
+template <bool STRICT>
 __device__ void root_bisect(const GridParams& G, const float4* prog, const EdgePos& E, float f1, float f2, int iters, float (&p)[3]) {
     float ta = 0.f, tb = 1.f, fa = f1 - G.iso, fb = f2 - G.iso;
     const float d = E.e2a - E.e1[E.axis];
@@ -112,7 +114,7 @@ __device__ void root_bisect(const GridParams& G, const float4* prog, const EdgeP
         float X[1] = {E.e1[0]}, Y[1] = {E.e1[1]}, Z[1] = {E.e1[2]}, F[1];
         const float moved = fmaf(t, d, E.e1[E.axis]);
         if (E.axis == 0) X[0] = moved; else if (E.axis == 1) Y[0] = moved; else Z[0] = moved;
-        eval_program<1, false>(prog, X, Y, Z, F, nullptr, nullptr, G.sem);
+        eval_program<1, false, STRICT>(prog, X, Y, Z, F, nullptr, nullptr, G.sem);
         const float ft = F[0] - G.iso;
         if (fabsf(ft) < 1e-6f) break;
         if ((ft < 0.f) == (fa < 0.f)) { ta = t; fa = ft; if (side == -1) fb *= 0.5f; side = -1; }
@@ -123,25 +125,27 @@ __device__ void root_bisect(const GridParams& G, const float4* prog, const EdgeP
 }
 
 // ComputeRootNewtonRaphsonVEC4 (CompactBlobTree.cpp:1581-1622) incl. the fp^2 damping of its vec4 dot
+template <bool STRICT>
 __device__ void root_newton_ref(const GridParams& G, const float4* prog, const EdgePos& E, float f1, float f2, int iters, float (&p)[3]) {
     float x[3] = {E.e1[0], E.e1[1], E.e1[2]};
     if (!(fabsf(f1 - G.iso) < fabsf(f2 - G.iso))) x[E.axis] = E.e2a;
     const float eps = PS_FIELDVALUE_EPSILON, inv = 1.0f / PS_FIELDVALUE_EPSILON;
     for (int it = 0; it < iters; it++) {
         float X[4] = {x[0], x[0] + eps, x[0], x[0]}, Y[4] = {x[1], x[1], x[1] + eps, x[1]}, Z[4] = {x[2], x[2], x[2], x[2] + eps}, F[4];
-        eval_program<4, false>(prog, X, Y, Z, F, nullptr, nullptr, G.sem);
+        eval_program<4, false, STRICT>(prog, X, Y, Z, F, nullptr, nullptr, G.sem);
         const float fp = F[0];
         const float gx = (F[1] - fp) * inv, gy = (F[2] - fp) * inv, gz = (F[3] - fp) * inv;
         const float dd = G.iso - fp;
         const float g = 1.0f / (gx * gx + gy * gy + gz * gz + fp * fp);
         x[0] = x[0] + (dd * gx) * g; x[1] = x[1] + (dd * gy) * g; x[2] = x[2] + (dd * gz) * g;
         float X1[1] = {x[0]}, Y1[1] = {x[1]}, Z1[1] = {x[2]}, F1[1];
-        eval_program<1, false>(prog, X1, Y1, Z1, F1, nullptr, nullptr, G.sem);
+        eval_program<1, false, STRICT>(prog, X1, Y1, Z1, F1, nullptr, nullptr, G.sem);
         if (fabsf(F1[0] - G.iso) < eps) break;
     }
     p[0] = x[0]; p[1] = x[1]; p[2] = x[2];
 }
 
+template <bool STRICT>
 __global__ void __launch_bounds__(kThreads) emit_kernel(GridParams G, const Region* __restrict__ cands, const float4* __restrict__ pool,
                                                         const float* __restrict__ colorTab, FieldOutputs fo, MeshOutputs mo,
                                                         const int32_t* __restrict__ candOfMpu, int nMixed, uint32_t capQuads) {
@@ -252,16 +256,16 @@ __global__ void __launch_bounds__(kThreads) emit_kernel(GridParams G, const Regi
             const EdgePos E = edge_endpoints(G, r, ci, cj, ck, axis);
             const float f1 = S.fv[corner], f2 = S.fv[corner + (axis == 0 ? 8 : (axis == 1 ? 64 : 1))];
             float p[3];
-            if (G.rootMode == PSGPU_ROOT_FOURSAMPLE) root_foursample(G, prog, E, p);
-            else if (G.rootMode == PSGPU_ROOT_NEWTON_REF) root_newton_ref(G, prog, E, f1, f2, G.rootIters, p);
-            else root_bisect(G, prog, E, f1, f2, G.rootIters, p);
+            if (G.rootMode == PSGPU_ROOT_FOURSAMPLE) root_foursample<STRICT>(G, prog, E, p);
+            else if (G.rootMode == PSGPU_ROOT_NEWTON_REF) root_newton_ref<STRICT>(G, prog, E, f1, f2, G.rootIters, p);
+            else root_bisect<STRICT>(G, prog, E, f1, f2, G.rootIters, p);
             const size_t vo = (size_t)(vbase + (perMpu ? (uint32_t)S.edgeVid[e] : rk)) * 3;
             mo.pos[vo] = p[0]; mo.pos[vo + 1] = p[1]; mo.pos[vo + 2] = p[2];
             if (G.wantColors || G.wantNormals) {
                 const float dl = PS_NORMAL_DELTA;
                 float X[4] = {p[0], p[0] + dl, p[0], p[0]}, Y[4] = {p[1], p[1], p[1] + dl, p[1]}, Z[4] = {p[2], p[2], p[2], p[2] + dl};
                 float F[4], rgb[3];
-                eval_program<4, true>(prog, X, Y, Z, F, rgb, colorTab, G.sem);
+                eval_program<4, true, STRICT>(prog, X, Y, Z, F, rgb, colorTab, G.sem);
                 const float dinv = -1.0f / dl;
                 float nx = (F[1] - F[0]) * dinv, nyv = (F[2] - F[0]) * dinv, nzv = (F[3] - F[0]) * dinv;
                 const float l2 = nx * nx + nyv * nyv + nzv * nzv;
@@ -329,17 +333,21 @@ void launch_emit_kernel(const GridParams& G, const Region* cands, const float4* 
     if (cap > kMaxProgCapQuads) cap = kMaxProgCapQuads;
     cap = (cap + 7u) & ~7u;
     const int smem = (int)(sizeof(EmitSmem) + cap * 16u);
-    static int configured = -1;
-    if (smem > configured) {
-        cudaFuncSetAttribute(emit_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
-        configured = smem;
+    const bool strict = (G.sem == PSGPU_SEM_SIMD);
+    static int configured[2] = {-1, -1};
+    if (smem > configured[strict]) {
+        if (strict) cudaFuncSetAttribute(emit_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+        else cudaFuncSetAttribute(emit_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+        configured[strict] = smem;
     }
     int perSM = 0;
-    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSM, emit_kernel, kThreads, smem);
+    if (strict) cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSM, emit_kernel<true>, kThreads, smem);
+    else cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSM, emit_kernel<false>, kThreads, smem);
     if (perSM < 1) perSM = 1;
     int grid = numSMs * perSM;
     if (grid > nMixed) grid = nMixed;
-    emit_kernel<<<grid, kThreads, smem, st>>>(G, cands, pool, colorTab, fo, mo, candOfMpu, nMixed, cap);
+    if (strict) emit_kernel<true><<<grid, kThreads, smem, st>>>(G, cands, pool, colorTab, fo, mo, candOfMpu, nMixed, cap);
+    else emit_kernel<false><<<grid, kThreads, smem, st>>>(G, cands, pool, colorTab, fo, mo, candOfMpu, nMixed, cap);
 }
 
 }  // namespace psgpu

@@ -32,6 +32,7 @@ struct __align__(16) FieldSmemHeader {
     int flags;
 };
 
+template <bool STRICT>
 __global__ void __launch_bounds__(kThreads) field_kernel(GridParams G, const Region* __restrict__ cands, int nCand,
                                                          const float4* __restrict__ pool, FieldOutputs out, uint32_t capQuads) {
     extern __shared__ __align__(16) unsigned char smemRaw[];
@@ -91,7 +92,7 @@ __global__ void __launch_bounds__(kThreads) field_kernel(GridParams G, const Reg
 #pragma unroll
             for (int n = 0; n < 4; n++) { X[n] = x; Y[n] = y; Z[n] = corner_coord(G, 2, r.z, 4 * kh + n); }
         }
-        eval_program<4, false>(prog, X, Y, Z, F, nullptr, nullptr, G.sem);
+        eval_program<4, false, STRICT>(prog, X, Y, Z, F, nullptr, nullptr, G.sem);
         reinterpret_cast<float4*>(S.fv)[t] = make_float4(F[0], F[1], F[2], F[3]);
         uint32_t in4 = 0;
 #pragma unroll
@@ -180,16 +181,18 @@ __global__ void __launch_bounds__(kThreads) field_kernel(GridParams G, const Reg
 }
 
 // ---- parity hooks: the full program at arbitrary points ------------------------------------------------
+template <bool STRICT>
 __global__ void __launch_bounds__(128) points_field_kernel(const float4* __restrict__ prog, const float* __restrict__ xyz, int64_t n,
                                                            float* __restrict__ f, int sem) {
     const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     const int64_t j = i < n ? i : n - 1;
     float X[1] = {xyz[j * 3]}, Y[1] = {xyz[j * 3 + 1]}, Z[1] = {xyz[j * 3 + 2]}, F[1];
-    eval_program<1, false>(prog, X, Y, Z, F, nullptr, nullptr, sem);
+    eval_program<1, false, STRICT>(prog, X, Y, Z, F, nullptr, nullptr, sem);
     if (i < n) f[i] = F[0];
 }
 
 // field + colour at p and the forward-difference normal with NORMAL_DELTA (PS_Polygonizer.cpp:764-782, 1598-1622)
+template <bool STRICT>
 __global__ void __launch_bounds__(128) points_fcn_kernel(const float4* __restrict__ prog, const float* __restrict__ colorTab,
                                                          const float* __restrict__ xyz, int64_t n, float* __restrict__ f,
                                                          float* __restrict__ col, float* __restrict__ nrm, int sem) {
@@ -198,7 +201,7 @@ __global__ void __launch_bounds__(128) points_fcn_kernel(const float4* __restric
     const float px = xyz[j * 3], py = xyz[j * 3 + 1], pz = xyz[j * 3 + 2];
     float X[4] = {px, px + PS_NORMAL_DELTA, px, px}, Y[4] = {py, py, py + PS_NORMAL_DELTA, py}, Z[4] = {pz, pz, pz, pz + PS_NORMAL_DELTA};
     float F[4], rgb[3];
-    eval_program<4, true>(prog, X, Y, Z, F, rgb, colorTab, sem);
+    eval_program<4, true, STRICT>(prog, X, Y, Z, F, rgb, colorTab, sem);
     if (i < n) {
         const float dinv = -1.0f / PS_NORMAL_DELTA;
         float nx = (F[1] - F[0]) * dinv, ny = (F[2] - F[0]) * dinv, nz = (F[3] - F[0]) * dinv;
@@ -270,28 +273,34 @@ void launch_field_kernel(const GridParams& G, const Region* cands, int nCand, co
     if (nCand <= 0) return;
     uint32_t cap;
     const int smem = field_kernel_smem_bytes(maxProgQuads, &cap);
-    static int configured = -1;
-    if (smem > configured) {
-        cudaFuncSetAttribute(field_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
-        configured = smem;
+    const bool strict = (G.sem == PSGPU_SEM_SIMD);
+    static int configured[2] = {-1, -1};
+    if (smem > configured[strict]) {
+        if (strict) cudaFuncSetAttribute(field_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+        else cudaFuncSetAttribute(field_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+        configured[strict] = smem;
     }
     int perSM = 0;
-    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSM, field_kernel, kThreads, smem);
+    if (strict) cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSM, field_kernel<true>, kThreads, smem);
+    else cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSM, field_kernel<false>, kThreads, smem);
     if (perSM < 1) perSM = 1;
     int grid = numSMs * perSM;  // persistent CTAs: a whole number of waves on 148 SMs
     if (grid > nCand) grid = nCand;
-    field_kernel<<<grid, kThreads, smem, st>>>(G, cands, nCand, pool, out, cap);
+    if (strict) field_kernel<true><<<grid, kThreads, smem, st>>>(G, cands, nCand, pool, out, cap);
+    else field_kernel<false><<<grid, kThreads, smem, st>>>(G, cands, nCand, pool, out, cap);
 }
 
 void launch_points_field(const float4* prog, const float* xyz, int64_t n, float* f, int sem, cudaStream_t st) {
     if (n <= 0) return;
-    points_field_kernel<<<(unsigned)((n + 127) / 128), 128, 0, st>>>(prog, xyz, n, f, sem);
+    if (sem == PSGPU_SEM_SIMD) points_field_kernel<true><<<(unsigned)((n + 127) / 128), 128, 0, st>>>(prog, xyz, n, f, sem);
+    else points_field_kernel<false><<<(unsigned)((n + 127) / 128), 128, 0, st>>>(prog, xyz, n, f, sem);
 }
 
 void launch_points_field_color_normal(const float4* prog, const float* colorTab, const float* xyz, int64_t n, float* f, float* col, float* nrm,
                                       int sem, cudaStream_t st) {
     if (n <= 0) return;
-    points_fcn_kernel<<<(unsigned)((n + 127) / 128), 128, 0, st>>>(prog, colorTab, xyz, n, f, col, nrm, sem);
+    if (sem == PSGPU_SEM_SIMD) points_fcn_kernel<true><<<(unsigned)((n + 127) / 128), 128, 0, st>>>(prog, colorTab, xyz, n, f, col, nrm, sem);
+    else points_fcn_kernel<false><<<(unsigned)((n + 127) / 128), 128, 0, st>>>(prog, colorTab, xyz, n, f, col, nrm, sem);
 }
 
 void launch_program_stats(const Region* cands, int nCand, const float4* pool, const uint32_t*, unsigned long long* acc, cudaStream_t st) {

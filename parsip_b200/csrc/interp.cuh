@@ -23,13 +23,49 @@ __device__ __forceinline__ float wyvill(float d2) {
     return fmaxf(t * t * t, 0.0f);
 }
 
+// ---- STRICT arithmetic: the reference's SSE code has no FMA and a fixed association order, so the PS_SimdPoly
+// compat semantics (PSGPU_SEM_SIMD) evaluate every expression with separately rounded mul/add in exactly the order of
+// PS_Polygonizer.cpp:934-1179 (the __f*_rn intrinsics are never contracted by nvcc). Field values, cube cases and
+// 4-sample roots then come out BIT-IDENTICAL to the reference build instead of within an FMA-rounding tolerance that
+// (1-d^2)^3 amplifies near f -> 0. The native semantics keep the fused forms.
+#define PS_ADD __fadd_rn
+#define PS_SUB __fsub_rn
+#define PS_MUL __fmul_rn
+#define PS_DIV __fdiv_rn
+__device__ __forceinline__ float ps_sqrt_rn(float x) {
+#ifdef PSGPU_HOST_EMULATION
+    return sqrtf(x);
+#else
+    return __fsqrt_rn(x);
+#endif
+}
+// _mm_max_ps(a, b) = a > b ? a : b (returns b when either is NaN); _mm_min_ps likewise
+__device__ __forceinline__ float sse_max(float a, float b) { return a > b ? a : b; }
+__device__ __forceinline__ float sse_min(float a, float b) { return a < b ? a : b; }
+__device__ __forceinline__ float dot3_strict(float ax, float ay, float az, float bx, float by, float bz) {
+    return PS_ADD(PS_ADD(PS_MUL(ax, bx), PS_MUL(ay, by)), PS_MUL(az, bz));
+}
+__device__ __forceinline__ float wyvill_strict(float d2) {
+    const float r1 = PS_SUB(1.0f, d2);
+    return sse_max(0.0f, PS_MUL(PS_MUL(r1, r1), r1));
+}
+
 // fast_pow of PS_SIMDVecN.h:122-128 with an exact reciprocal
 __device__ __forceinline__ float ricci_simd(float base, float e) { return base / (base + (e - e * base)); }
 
-template <int N>
+template <int N, bool STRICT = false>
 __device__ __forceinline__ void xform_points(const float4* q, const float (&x)[N], const float (&y)[N], const float (&z)[N],
                                              float (&ox)[N], float (&oy)[N], float (&oz)[N]) {
     const float4 r0 = q[0], r1 = q[1], r2 = q[2];
+    if (STRICT) {  // PS_Polygonizer.cpp:951-969: ((m0*x + m1*y) + m2*z) + m3
+#pragma unroll
+        for (int n = 0; n < N; n++) {
+            ox[n] = PS_ADD(dot3_strict(r0.x, r0.y, r0.z, x[n], y[n], z[n]), r0.w);
+            oy[n] = PS_ADD(dot3_strict(r1.x, r1.y, r1.z, x[n], y[n], z[n]), r1.w);
+            oz[n] = PS_ADD(dot3_strict(r2.x, r2.y, r2.z, x[n], y[n], z[n]), r2.w);
+        }
+        return;
+    }
 #pragma unroll
     for (int n = 0; n < N; n++) {
         ox[n] = fmaf(r0.x, x[n], fmaf(r0.y, y[n], fmaf(r0.z, z[n], r0.w)));
@@ -137,13 +173,105 @@ __device__ __forceinline__ void prim_d2(uint32_t opc, const float4 q0, const flo
     }
 }
 
+// The same squared distances in the reference's exact operation order (PS_Polygonizer.cpp:975-1173, SSE, no FMA; see the
+// STRICT note above). Only the opcodes the PS_SimdPoly semantics can produce have a strict form; the rest fall through.
+// The mask-blend expressions (mask*A + (1-mask)*B) are kept because 0*NaN / 0*inf propagate in the reference too.
 template <int N>
+__device__ __forceinline__ void prim_d2_strict(uint32_t opc, const float4 q0, const float4* __restrict__ q,
+                                               const float (&x)[N], const float (&y)[N], const float (&z)[N], float (&d2o)[N]) {
+    switch (opc) {
+    case OPC_POINT: {  // :975-983
+#pragma unroll
+        for (int n = 0; n < N; n++) {
+            const float dx = PS_SUB(q0.y, x[n]), dy = PS_SUB(q0.z, y[n]), dz = PS_SUB(q0.w, z[n]);
+            d2o[n] = dot3_strict(dx, dy, dz, dx, dy, dz);
+        }
+    } break;
+    case OPC_LINE_INF: {  // :984-1011
+        const float4 d = q[0];
+#pragma unroll
+        for (int n = 0; n < N; n++) {
+            float dx = PS_SUB(x[n], q0.y), dy = PS_SUB(y[n], q0.z), dz = PS_SUB(z[n], q0.w);
+            const float delta = PS_DIV(dot3_strict(dx, dy, dz, d.x, d.y, d.z), d.w);
+            dx = PS_SUB(x[n], PS_ADD(q0.y, PS_MUL(delta, d.x)));
+            dy = PS_SUB(y[n], PS_ADD(q0.z, PS_MUL(delta, d.y)));
+            dz = PS_SUB(z[n], PS_ADD(q0.w, PS_MUL(delta, d.z)));
+            d2o[n] = dot3_strict(dx, dy, dz, dx, dy, dz);
+        }
+    } break;
+    case OPC_CYLINDER: {  // :1012-1039
+        const float4 d = q[0];
+        const float height = q[1].x;
+#pragma unroll
+        for (int n = 0; n < N; n++) {
+            const float px = PS_SUB(x[n], q0.y), py = PS_SUB(y[n], q0.z), pz = PS_SUB(z[n], q0.w);
+            float yy = dot3_strict(px, py, pz, d.x, d.y, d.z);
+            const float xx = sse_max(0.0f, PS_SUB(ps_sqrt_rn(PS_SUB(dot3_strict(px, py, pz, px, py, pz), PS_MUL(yy, yy))), d.w));
+            const float mask = (yy > 0.0f) ? 1.0f : 0.0f;
+            yy = PS_ADD(PS_MUL(mask, sse_max(0.0f, PS_SUB(yy, height))), PS_MUL(PS_SUB(1.0f, mask), yy));
+            d2o[n] = PS_ADD(PS_MUL(xx, xx), PS_MUL(yy, yy));
+        }
+    } break;
+    case OPC_CUBE: {  // :1059-1097
+        const float side = q[0].x, minusSide = PS_MUL(-1.0f, side);
+#pragma unroll
+        for (int n = 0; n < N; n++) {
+            const float dif[3] = {PS_SUB(x[n], q0.y), PS_SUB(y[n], q0.z), PS_SUB(z[n], q0.w)};
+            float acc = 0.0f;
+#pragma unroll
+            for (int a = 0; a < 3; a++) {
+                const float mm = (minusSide > dif[a]) ? 1.0f : 0.0f, mp = (dif[a] > side) ? 1.0f : 0.0f;
+                const float delta = PS_ADD(PS_MUL(PS_ADD(dif[a], side), mm), PS_MUL(PS_SUB(dif[a], side), mp));
+                acc = (a == 0) ? PS_MUL(delta, delta) : PS_ADD(acc, PS_MUL(delta, delta));
+            }
+            d2o[n] = acc;
+        }
+    } break;
+    case OPC_DISC:  // :1099-1132 (SimdRSqrt evaluated exactly)
+    case OPC_RING: {  // :1134-1173
+        const float4 nr = q[0];
+        const float radius = nr.w;
+#pragma unroll
+        for (int n = 0; n < N; n++) {
+            const float dX = PS_SUB(x[n], q0.y), dY = PS_SUB(y[n], q0.z), dZ = PS_SUB(z[n], q0.w);
+            float dot = dot3_strict(nr.x, nr.y, nr.z, dX, dY, dZ);
+            float dirX = PS_SUB(dX, PS_MUL(nr.x, dot)), dirY = PS_SUB(dY, PS_MUL(nr.y, dot)), dirZ = PS_SUB(dZ, PS_MUL(nr.z, dot));
+            dot = dot3_strict(dirX, dirY, dirZ, dirX, dirY, dirZ);
+            const float rs = PS_DIV(1.0f, ps_sqrt_rn(dot));
+            dirX = PS_MUL(dirX, rs); dirY = PS_MUL(dirY, rs); dirZ = PS_MUL(dirZ, rs);
+            const float nX = PS_SUB(PS_MUL(radius, dirX), dX), nY = PS_SUB(PS_MUL(radius, dirY), dY), nZ = PS_SUB(PS_MUL(radius, dirZ), dZ);
+            const float far2 = dot3_strict(nX, nY, nZ, nX, nY, nZ);
+            const float dd = dot3_strict(dX, dY, dZ, dX, dY, dZ);
+            if (opc == OPC_DISC) {
+                const float mask = (PS_MUL(radius, radius) >= dot) ? 1.0f : 0.0f;
+                d2o[n] = PS_ADD(PS_MUL(mask, PS_SUB(dd, dot)), PS_MUL(PS_SUB(1.0f, mask), far2));
+            } else {
+                const float mask = (dot == 0.0f) ? 1.0f : 0.0f;
+                // radius*radius + dX*dX + dY*dY + dZ*dZ, left to right
+                const float on = PS_ADD(PS_ADD(PS_ADD(PS_MUL(radius, radius), PS_MUL(dX, dX)), PS_MUL(dY, dY)), PS_MUL(dZ, dZ));
+                d2o[n] = PS_ADD(PS_MUL(mask, on), PS_MUL(PS_SUB(1.0f, mask), far2));
+            }
+        }
+    } break;
+    default:
+        prim_d2<N>(opc, q0, q, x, y, z, d2o);
+        break;
+    }
+}
+
+template <int N, bool STRICT = false>
 __device__ __forceinline__ void prim_field(uint32_t opc, const float4 q0, const float4* __restrict__ q,
                                            const float (&x)[N], const float (&y)[N], const float (&z)[N], float (&f)[N]) {
     float d2[N];
-    prim_d2<N>(opc, q0, q, x, y, z, d2);
+    if (STRICT) {
+        prim_d2_strict<N>(opc, q0, q, x, y, z, d2);
 #pragma unroll
-    for (int n = 0; n < N; n++) f[n] = wyvill(d2[n]);
+        for (int n = 0; n < N; n++) f[n] = wyvill_strict(d2[n]);
+    } else {
+        prim_d2<N>(opc, q0, q, x, y, z, d2);
+#pragma unroll
+        for (int n = 0; n < N; n++) f[n] = wyvill(d2[n]);
+    }
 }
 
 __device__ __forceinline__ float combine_val(uint32_t cmb, float top, float v) {
@@ -195,7 +323,7 @@ __device__ __forceinline__ void combine_color(int sem, uint32_t cmb, float tf, f
 
 // Evaluates the program at N points. COLOR also produces the colour at point 0.
 // `prog` may point to shared or global memory (generic address).
-template <int N, bool COLOR>
+template <int N, bool COLOR, bool STRICT = false>
 __device__ void eval_program(const float4* __restrict__ prog, const float (&X)[N], const float (&Y)[N], const float (&Z)[N],
                              float (&F)[N], float* rgb, const float* __restrict__ colorTab, int sem) {
     float x[N], y[N], z[N];
@@ -221,11 +349,11 @@ __device__ void eval_program(const float4* __restrict__ prog, const float (&X)[N
             float f[N];
             if (PS_HDR_XF(hdr)) {
                 float lx[N], ly[N], lz[N];
-                xform_points<N>(prog + pc + nq, x, y, z, lx, ly, lz);
-                prim_field<N>(opc, q0, prog + pc + 1, lx, ly, lz, f);
+                xform_points<N, STRICT>(prog + pc + nq, x, y, z, lx, ly, lz);
+                prim_field<N, STRICT>(opc, q0, prog + pc + 1, lx, ly, lz, f);
                 pc += nq + 3;
             } else {
-                prim_field<N>(opc, q0, prog + pc + 1, x, y, z, f);
+                prim_field<N, STRICT>(opc, q0, prog + pc + 1, x, y, z, f);
                 pc += nq;
             }
             float pcol[3];

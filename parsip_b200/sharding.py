@@ -55,9 +55,9 @@ def exchange_counts(n_vertices: int, n_triangles: int, device=None):
 
     world, rank = dist.get_world_size(), dist.get_rank()
     mine = torch.tensor([int(n_vertices), int(n_triangles)], dtype=torch.int64, device=device)
-    allc = torch.empty((world, 2), dtype=torch.int64, device=device)
+    allc = torch.empty(world * 2, dtype=torch.int64, device=device)  # flat: gloo insists on a 1-D concatenation
     dist.all_gather_into_tensor(allc, mine)
-    counts: List[Tuple[int, int]] = [(int(a), int(b)) for a, b in allc.cpu().tolist()]
+    counts: List[Tuple[int, int]] = [(int(a), int(b)) for a, b in allc.view(world, 2).cpu().tolist()]
     return offsets_from_counts(counts, rank)
 
 

@@ -14,7 +14,8 @@ void hostemu_field(const float* quads, const float* xyz, int64_t n, float* f, in
     const float4* prog = reinterpret_cast<const float4*>(quads);
     for (int64_t i = 0; i < n; i++) {
         float X[1] = {xyz[i * 3]}, Y[1] = {xyz[i * 3 + 1]}, Z[1] = {xyz[i * 3 + 2]}, F[1];
-        eval_program<1, false>(prog, X, Y, Z, F, nullptr, nullptr, sem);
+        if (sem == PSGPU_SEM_SIMD) eval_program<1, false, true>(prog, X, Y, Z, F, nullptr, nullptr, sem);
+        else eval_program<1, false, false>(prog, X, Y, Z, F, nullptr, nullptr, sem);
         f[i] = F[0];
     }
 }
@@ -23,7 +24,8 @@ void hostemu_field_color(const float* quads, const float* colorTab, const float*
     const float4* prog = reinterpret_cast<const float4*>(quads);
     for (int64_t i = 0; i < n; i++) {
         float X[1] = {xyz[i * 3]}, Y[1] = {xyz[i * 3 + 1]}, Z[1] = {xyz[i * 3 + 2]}, F[1];
-        eval_program<1, true>(prog, X, Y, Z, F, col + i * 3, colorTab, sem);
+        if (sem == PSGPU_SEM_SIMD) eval_program<1, true, true>(prog, X, Y, Z, F, col + i * 3, colorTab, sem);
+        else eval_program<1, true, false>(prog, X, Y, Z, F, col + i * 3, colorTab, sem);
         f[i] = F[0];
     }
 }

@@ -1,0 +1,87 @@
+"""CPU checks of the per-MPU pruning walk (parsip_b200/csrc/cull_walk.cuh compiled for the host): culling must be
+EXACT - the pruned program evaluates to bit-identical floats inside its region, dropped regions hold no surface
+("cull on/off must give bit-identical fields")."""
+import numpy as np
+import pytest
+
+import hostemu_binding as emu
+import scenes_small
+from parsip_b200 import blobtree as bt
+import parsip_b200 as ps
+
+ISO = 0.5
+
+
+def _regions(lo, hi, rs, n, side):
+    c = rs.uniform(lo, hi, (n, 3)).astype(np.float32)
+    return c, (c + np.float32(side)).astype(np.float32)
+
+
+@pytest.mark.parametrize("name", sorted(scenes_small.SCALAR_SCENES))
+@pytest.mark.parametrize("side", [0.14, 0.56])
+def test_pruned_program_is_bit_identical_inside_its_region(name, side):
+    root = scenes_small.SCALAR_SCENES[name]()
+    prog = ps.linearize(bt.flatten(root), ps.SEM_SCALAR, ps.LIN_REASSOCIATE)
+    quads = prog.quads()
+    lo, hi = ps.prepare_bboxes(bt.flatten(bt.binarize(root)))
+    rs = np.random.RandomState(5)
+    blo, bhi = _regions(lo - 0.5, hi + 0.2, rs, 150, side)
+    kept = dropped_support = dropped_interval = shorter = 0
+    for a, b in zip(blo, bhi):
+        pts = rs.uniform(a, b, (64, 3)).astype(np.float32)
+        # the 8 corners too: the lattice evaluates exactly there
+        corners = np.array([[x, y, z] for x in (a[0], b[0]) for y in (a[1], b[1]) for z in (a[2], b[2])], np.float32)
+        pts = np.concatenate([pts, corners])
+        full = emu.field(quads, pts, ps.SEM_SCALAR)
+        sup = emu.prune(quads, a, b, ps.CULL_SUPPORT, ISO)
+        if sup is None:
+            dropped_support += 1
+            assert (full == 0.0).all(), "support cull dropped a region with a non-zero field"
+        else:
+            kept += 1
+            shorter += int(len(sup) < len(quads))
+            f = emu.field(sup, pts, ps.SEM_SCALAR)
+            assert np.array_equal(f.view(np.uint32), full.view(np.uint32)), "pruned program changed the field"
+        itv = emu.prune(quads, a, b, ps.CULL_INTERVAL, ISO)
+        if itv is None:
+            dropped_interval += 1
+            inside = full > ISO
+            assert inside.all() or (~inside).all(), "interval cull dropped a region the surface crosses"
+        else:
+            assert sup is not None and np.array_equal(itv, sup)
+    assert kept > 0 and dropped_interval >= dropped_support
+    if name in ("blob", "csgwarp"):
+        assert shorter > 0  # the pruning does shorten programs
+
+
+def test_simd_semantics_programs_prune_exactly_too():
+    root = bt.binarize(scenes_small.blob())
+    prog = ps.linearize(bt.flatten(root), ps.SEM_SIMD, 0)
+    quads = prog.quads()
+    lo, hi = ps.prepare_bboxes(bt.flatten(root))
+    rs = np.random.RandomState(9)
+    blo, bhi = _regions(lo, hi, rs, 100, 0.2)
+    for a, b in zip(blo, bhi):
+        pts = rs.uniform(a, b, (48, 3)).astype(np.float32)
+        full = emu.field(quads, pts, ps.SEM_SIMD)
+        pr = emu.prune(quads, a, b, ps.CULL_SUPPORT, ISO)
+        if pr is None:
+            assert (full == 0.0).all()
+        else:
+            assert np.array_equal(emu.field(pr, pts, ps.SEM_SIMD).view(np.uint32), full.view(np.uint32))
+
+
+def test_zero_folding_rules_of_difference():
+    """difference min(L, 1 - 0) must become min(L, 1), not L (blend sums exceed 1)."""
+    L = bt.Blend(bt.Point([0, 0, 0]), bt.Point([0.05, 0, 0]), bt.Point([0, 0.05, 0]))
+    tree = bt.Dif(L, bt.Point([5, 5, 5]))  # subtrahend is identically 0 near the origin
+    quads = ps.linearize(bt.flatten(tree), ps.SEM_SCALAR, ps.LIN_REASSOCIATE).quads()
+    a, b = np.float32([-0.1, -0.1, -0.1]), np.float32([0.1, 0.1, 0.1])
+    pts = np.random.RandomState(1).uniform(a, b, (200, 3)).astype(np.float32)
+    full = emu.field(quads, pts, ps.SEM_SCALAR)
+    assert full.max() == 1.0  # the clamp is active here
+    pr = emu.prune(quads, a, b, ps.CULL_SUPPORT, ISO)
+    assert pr is not None and (pr[-2, 0] & 63) == 19  # the subtrahend is replaced by OPC_CLAMP1
+    assert np.array_equal(emu.field(pr, pts, ps.SEM_SCALAR), full)
+    # all-inside region: the interval cull may drop it (no surface), the support cull must not
+    assert emu.prune(quads, a, b, ps.CULL_INTERVAL, ISO) is None
