@@ -112,6 +112,8 @@ int psgpu_program_free(psgpu_program* p);
 /* info[0] quads, [1] primitives, [2] max value-stack depth, [3] max point-stack depth, [4] instructions */
 int psgpu_program_info(const psgpu_program* p, int64_t* info5);
 int psgpu_program_copy(const psgpu_program* p, uint32_t* quads_out /* 4 words per quad */);
+/* diffuse colour table, 3 floats per primitive id (the id in each primitive's header word) */
+int psgpu_program_colors(const psgpu_program* p, float* rgb_out /* 3 * primitives */);
 /* Grid-domain box of the tree the way PrepareBBoxes computes it (iso distance 0.4542 + 0.05 padding). */
 int psgpu_prepare_bboxes(const psgpu_tree* tree, float cellsize, float* lo3, float* hi3);
 uint32_t psgpu_count_mpus(float cellsize, const float* lo3, const float* hi3);

@@ -19,7 +19,7 @@ ERRORS = {-1: "PARAM_ERROR", -2: "NOT_ENOUGH_MEM", -3: "INVALID_BVH", -4: "UNSUP
 # every symbol include/psgpu.h declares (tests/test_abi.py checks the library exports them all)
 EXPORTS = [
     "psgpu_create", "psgpu_destroy", "psgpu_last_error", "psgpu_device_count", "psgpu_linearize", "psgpu_program_free",
-    "psgpu_program_info", "psgpu_program_copy", "psgpu_prepare_bboxes", "psgpu_count_mpus", "psgpu_upload_program",
+    "psgpu_program_info", "psgpu_program_copy", "psgpu_program_colors", "psgpu_prepare_bboxes", "psgpu_count_mpus", "psgpu_upload_program",
     "psgpu_polygonize", "psgpu_polygonize_host", "psgpu_mesh_download", "psgpu_field_eval", "psgpu_field_color_normal",
     "psgpu_mpu_cache", "psgpu_get_stats", "psgpu_measure_fp32_peak",
 ]
@@ -106,6 +106,7 @@ def load_library():
     lib.psgpu_program_free.argtypes = [vp]
     lib.psgpu_program_info.argtypes = [vp, vp]
     lib.psgpu_program_copy.argtypes = [vp, vp]
+    lib.psgpu_program_colors.argtypes = [vp, vp]
     lib.psgpu_prepare_bboxes.argtypes = [C.POINTER(_Tree), C.c_float, vp, vp]
     lib.psgpu_count_mpus.restype = C.c_uint32
     lib.psgpu_count_mpus.argtypes = [C.c_float, vp, vp]
@@ -148,6 +149,11 @@ class Program:
         out = np.zeros((self.n_quads, 4), np.uint32)
         self.lib.psgpu_program_copy(self.h, out.ctypes.data)
         return out
+
+    def colors(self) -> np.ndarray:
+        out = np.zeros((max(self.n_prims, 1), 3), np.float32)
+        self.lib.psgpu_program_colors(self.h, out.ctypes.data)
+        return out[:self.n_prims]
 
     def __del__(self):
         if getattr(self, "h", None):

@@ -170,14 +170,14 @@ int fill_grid(psgpu_ctx* ctx, const psgpu_params* P, GridParams& G) {
 }
 
 // Hierarchical pruning; leaves ctx->cands / ctx->nCand (device) and returns the longest candidate program.
-int run_cull(psgpu_ctx* ctx, const GridParams& G, int cullMode, uint32_t& maxLen, uint32_t& poolUsed, int& launches) {
+int run_cull(psgpu_ctx* ctx, const GridParams& G, int cullMode, bool colorExact, uint32_t& maxLen, uint32_t& poolUsed, int& launches) {
     cudaStream_t st = ctx->stream;
     const int nx = G.hi[0] - G.lo[0], ny = G.hi[1] - G.lo[1], nz = G.hi[2] - G.lo[2];
     const size_t nMpu = (size_t)nx * ny * nz;
     CK(ctx->candOfMpu.reserve(nMpu * 4));
     CullLevel L;
     for (int a = 0; a < 3; a++) { L.lo[a] = G.lo[a]; L.hi[a] = G.hi[a]; L.gridLo[a] = G.gridLo[a]; }
-    L.mpuSide = G.mpuSide; L.cullMode = cullMode; L.iso = G.iso; L.childSize = 1;
+    L.mpuSide = G.mpuSide; L.cullMode = cullMode; L.iso = G.iso; L.childSize = 1; L.colorExact = colorExact ? 1 : 0;
     poolUsed = ctx->progQuads;
     if (cullMode == PSGPU_CULL_NONE) {
         if (nMpu > (size_t)1 << 30) { ctx->err = "lattice too large"; return PSGPU_NOT_ENOUGH_MEM; }
@@ -272,7 +272,7 @@ int polygonize_impl(psgpu_ctx* ctx, const psgpu_params* P, psgpu_mesh* out, bool
     S.program_quads = ctx->progQuads;
     CK(cudaEventRecord(ctx->ev[0], st));
     uint32_t maxLen = 0, poolUsed = 0;
-    rc = run_cull(ctx, G, P->cull, maxLen, poolUsed, launches);
+    rc = run_cull(ctx, G, P->cull, ctx->semantics == PSGPU_SEM_SIMD && P->want_colors, maxLen, poolUsed, launches);
     if (rc != PSGPU_SUCCESS) return rc;
     CK(cudaEventRecord(ctx->ev[1], st));
     const int nCand = ctx->nCand;

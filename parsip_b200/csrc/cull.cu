@@ -48,7 +48,7 @@ __global__ void __launch_bounds__(128) prune_count_kernel(CullLevel L, const Reg
     Box3 box;
     uint32_t len = 0;
     if (child_region(L, parent, tid & 63, coord, box))
-        len = prune_walk<false>(pool + parent.off, box, L.cullMode, L.iso, nullptr);
+        len = prune_walk<false>(pool + parent.off, box, L.cullMode, L.iso, nullptr, L.colorExact != 0);
     childLen[tid] = len;
 }
 
@@ -66,7 +66,7 @@ __global__ void __launch_bounds__(128) prune_emit_kernel(CullLevel L, const Regi
     Box3 box;
     child_region(L, parent, tid & 63, coord, box);
     const uint32_t off = outBase + childOff[tid];
-    prune_walk<true>(pool + parent.off, box, L.cullMode, L.iso, outPool + off);
+    prune_walk<true>(pool + parent.off, box, L.cullMode, L.iso, outPool + off, L.colorExact != 0);
     const uint32_t idx = childIdx[tid];
     Region r;
     r.x = coord[0]; r.y = coord[1]; r.z = coord[2]; r.off = off; r.len = len;

@@ -150,8 +150,10 @@ __device__ __forceinline__ void bound_combine(uint32_t cmb, float& lo, float& hi
 
 // Prunes src against `box`. EMIT = false only measures. Returns the pruned length in quads including the
 // END quad, or 0 if the region needs no evaluation.
+// colorExact (PS_SimdPoly semantics): a blend that loses an all-zero operand leaves an OPC_CSCALE marker, see program.h.
 template <bool EMIT>
-__device__ uint32_t prune_walk(const float4* __restrict__ src, const Box3& region, int cullMode, float iso, float4* __restrict__ dst) {
+__device__ uint32_t prune_walk(const float4* __restrict__ src, const Box3& region, int cullMode, float iso, float4* __restrict__ dst,
+                               bool colorExact = false) {
     float blo[PS_MAX_VALUE_STACK], bhi[PS_MAX_VALUE_STACK];
     uint32_t bstart[PS_MAX_VALUE_STACK];
     bool bzero[PS_MAX_VALUE_STACK];
@@ -162,6 +164,17 @@ __device__ uint32_t prune_walk(const float4* __restrict__ src, const Box3& regio
     Box3 box = region;
     auto put = [&](float4 v) { if (EMIT) dst[emit] = v; emit++; };
     auto hdrquad = [&](uint32_t h) { return make_float4(__uint_as_float(h), 0.f, 0.f, 0.f); };
+    uint32_t lastScale = 0xFFFFFFFFu, scaleCount = 0;  // position of the trailing OPC_CSCALE quad, if emit == lastScale + 1
+    auto rewind = [&](uint32_t pos) {
+        emit = pos;
+        if (lastScale != 0xFFFFFFFFu && lastScale >= emit) lastScale = 0xFFFFFFFFu;
+    };
+    auto cscale = [&](uint32_t n) {
+        if (!colorExact || n == 0) return;
+        if (lastScale + 1 == emit) scaleCount += n;
+        else { lastScale = emit; scaleCount = n; emit++; }
+        if (EMIT) dst[lastScale] = make_float4(__uint_as_float(PS_HDR(OPC_CSCALE, 0, 0, 0)), __uint_as_float(scaleCount), 0.f, 0.f);
+    };
     for (uint32_t pc = 0;;) {
         const float4 q0 = src[pc];
         const uint32_t hdr = __float_as_uint(q0.x);
@@ -184,16 +197,17 @@ __device__ uint32_t prune_walk(const float4* __restrict__ src, const Box3& regio
                 if (!pz && (cmb == CMB_ADD || cmb == CMB_MAX)) {  // 0 + f, max(0, f): the primitive becomes the entry
                     copy((hdr & ~(15u << 6)) | (CMB_PUSH << 6));
                     bzero[sp] = false; blo[sp] = flo; bhi[sp] = fhi;
+                    if (cmb == CMB_ADD) cscale(1);
                 }  // min(0,f) = 0, min(0,1-f) = 0 (f <= 1), 0*(1-f) = 0: stays zero
             } else if (pz) {
                 if (cmb == CMB_MAX) {
                     if (blo[sp] < 0.f) { put(hdrquad(PS_HDR(OPC_NULLPRIM, CMB_MAX, 0, 0))); blo[sp] = fmaxf(blo[sp], 0.f); }
                 } else if (cmb == CMB_MIN) {
-                    if (blo[sp] >= 0.f) { emit = bstart[sp]; bzero[sp] = true; blo[sp] = bhi[sp] = 0.f; }
+                    if (blo[sp] >= 0.f) { rewind(bstart[sp]); bzero[sp] = true; blo[sp] = bhi[sp] = 0.f; }
                     else { put(hdrquad(PS_HDR(OPC_NULLPRIM, CMB_MIN, 0, 0))); bhi[sp] = fminf(bhi[sp], 0.f); }
                 } else if (cmb == CMB_DIF) {  // min(top, 1 - 0)
                     if (bhi[sp] > 1.0f) { put(hdrquad(PS_HDR(OPC_CLAMP1, 0, 0, 0))); bhi[sp] = 1.0f; blo[sp] = fminf(blo[sp], 1.0f); }
-                }  // top + 0, top * (1 - 0): nothing
+                } else if (cmb == CMB_ADD) cscale(1);  // top + 0 (top * (1 - 0): nothing)
             } else {
                 copy(hdr);
                 bound_combine(cmb, blo[sp], bhi[sp], flo, fhi);
@@ -209,30 +223,33 @@ __device__ uint32_t prune_walk(const float4* __restrict__ src, const Box3& regio
             if (bzero[t] && bzero[v]) {
                 // nothing was emitted for either
             } else if (bzero[t]) {  // 0 (cmb) V; V's code starts at bstart[t]
-                if (cmb == CMB_ADD) { bzero[t] = false; blo[t] = blo[v]; bhi[t] = bhi[v]; }
+                if (cmb == CMB_ADD) { bzero[t] = false; blo[t] = blo[v]; bhi[t] = bhi[v]; cscale(1); }
                 else if (cmb == CMB_MAX) {
                     bzero[t] = false; blo[t] = blo[v]; bhi[t] = bhi[v];
                     if (blo[v] < 0.f) { put(hdrquad(PS_HDR(OPC_NULLPRIM, CMB_MAX, 0, 0))); blo[t] = 0.f; bhi[t] = fmaxf(bhi[v], 0.f); }
                 } else if (cmb == CMB_MIN) {
-                    if (blo[v] >= 0.f) emit = bstart[t];
+                    if (blo[v] >= 0.f) rewind(bstart[t]);
                     else { put(hdrquad(PS_HDR(OPC_NULLPRIM, CMB_MIN, 0, 0))); bzero[t] = false; blo[t] = fminf(blo[v], 0.f); bhi[t] = 0.f; }
                 } else if (cmb == CMB_DIF) {  // min(0, 1 - V)
-                    if (bhi[v] <= 1.0f) emit = bstart[t];
+                    if (bhi[v] <= 1.0f) rewind(bstart[t]);
                     else { put(hdrquad(PS_HDR(OPC_DIF0, 0, 0, 0))); bzero[t] = false; blo[t] = fminf(0.f, 1.0f - bhi[v]) - 1e-6f; bhi[t] = 0.f; }
-                } else emit = bstart[t];  // 0 * (1 - V)
+                } else rewind(bstart[t]);  // 0 * (1 - V)
             } else if (bzero[v]) {  // T (cmb) 0
                 if (cmb == CMB_MAX) {
                     if (blo[t] < 0.f) { put(hdrquad(PS_HDR(OPC_NULLPRIM, CMB_MAX, 0, 0))); blo[t] = 0.f; bhi[t] = fmaxf(bhi[t], 0.f); }
                 } else if (cmb == CMB_MIN) {
-                    if (blo[t] >= 0.f) { emit = bstart[t]; bzero[t] = true; blo[t] = bhi[t] = 0.f; }
+                    if (blo[t] >= 0.f) { rewind(bstart[t]); bzero[t] = true; blo[t] = bhi[t] = 0.f; }
                     else { put(hdrquad(PS_HDR(OPC_NULLPRIM, CMB_MIN, 0, 0))); bhi[t] = fminf(bhi[t], 0.f); }
                 } else if (cmb == CMB_DIF) {
                     if (bhi[t] > 1.0f) { put(hdrquad(PS_HDR(OPC_CLAMP1, 0, 0, 0))); bhi[t] = 1.0f; blo[t] = fminf(blo[t], 1.0f); }
-                }
+                } else if (cmb == CMB_ADD) cscale(1);
             } else {
                 copy(hdr);
                 bound_combine(cmb, blo[t], bhi[t], blo[v], bhi[v]);
             }
+        } break;
+        case OPC_CSCALE: {
+            if (!bzero[sp]) cscale(__float_as_uint(q0.y));
         } break;
         case OPC_POW: {
             if (!bzero[sp]) {
@@ -273,7 +290,7 @@ __device__ uint32_t prune_walk(const float4* __restrict__ src, const Box3& regio
         case OPC_POPPOINT: {
             wsp--;
             box = wbox[wsp];
-            if (bzero[sp]) emit = wstart[wsp];
+            if (bzero[sp]) rewind(wstart[wsp]);
             else copy(hdr);
             bstart[sp] = wstart[wsp];
         } break;

@@ -415,6 +415,16 @@ __device__ void eval_program(const float4* __restrict__ prog, const float (&X)[N
             for (int n = 0; n < N; n++) top[n] = ricci_simd(vs[sp][n] + top[n], q0.y);
             pc += 1;
         } break;
+        case OPC_CSCALE: {
+            if (COLOR) {
+                const float w = __fsub_rn(__fmul_rn(2.0f, __fadd_rn(0.5f, top[0])), 1.0f);
+                const uint32_t cnt = __float_as_uint(q0.y);
+                for (uint32_t k = 0; k < cnt; k++) {
+                    tc[0] = __fmul_rn(w, tc[0]); tc[1] = __fmul_rn(w, tc[1]); tc[2] = __fmul_rn(w, tc[2]);
+                }
+            }
+            pc += 1;
+        } break;
         case OPC_CLAMP1: {
 #pragma unroll
             for (int n = 0; n < N; n++) top[n] = fminf(top[n], 1.0f);

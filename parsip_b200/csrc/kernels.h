@@ -22,6 +22,7 @@ struct CullLevel {
     float mpuSide;
     int cullMode;
     float iso;
+    int colorExact;      // PS_SimdPoly semantics with colours wanted: blends keep OPC_CSCALE markers (program.h)
 };
 
 struct GridParams {

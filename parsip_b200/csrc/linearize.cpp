@@ -245,6 +245,12 @@ extern "C" int psgpu_program_copy(const psgpu_program* p, uint32_t* out) {
     return PSGPU_SUCCESS;
 }
 
+extern "C" int psgpu_program_colors(const psgpu_program* p, float* out) {
+    if (!p || !out) return PSGPU_PARAM_ERROR;
+    memcpy(out, p->colors.data(), p->colors.size() * 4);
+    return PSGPU_SUCCESS;
+}
+
 // ---------------------------------------------------------------------------------------------------
 // bounding boxes
 // ---------------------------------------------------------------------------------------------------

@@ -38,6 +38,9 @@ enum PsOpcode : uint32_t {
     OPC_RICCI_SIMD = 18, // {h, e}         v = pop; top = fast_pow(top + v, e)   (PS_SIMDVecN.h:122-128, Q6)
     OPC_CLAMP1 = 19,     // {h}            top = min(top, 1)          (difference with an all-zero subtrahend, Q16)
     OPC_DIF0 = 20,       // {h}            top = min(0, 1 - top)      (difference with an all-zero minuend)
+    OPC_CSCALE = 21,     // {h, n}         colour *= (2*(0.5+top)-1), n times; field untouched. Left by the culling pass where a
+                         //                blend lost an all-zero operand: the PS_SimdPoly colour rule 2*f_L*c_L + 2*f_R*c_R is
+                         //                unnormalised (PS_Polygonizer.cpp:1475-1487), so the surviving operand's colour keeps its weight
     OPC_TWIST = 24,      // {h, k, axis}                 push point; warp
     OPC_TAPER = 25,      // {h, k, along, taper}
     OPC_BEND = 26,       // {h, k, y0, left}{right, 1/k, 0, 0}

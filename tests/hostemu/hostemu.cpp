@@ -31,13 +31,14 @@ void hostemu_field_color(const float* quads, const float* colorTab, const float*
 }
 
 // prunes the program against the box; returns the pruned length in quads (0 = region needs no evaluation)
-uint32_t hostemu_prune(const float* quads, const float* lo3, const float* hi3, int cullMode, float iso, float* out, uint32_t outCapQuads) {
+uint32_t hostemu_prune(const float* quads, const float* lo3, const float* hi3, int cullMode, float iso, float* out, uint32_t outCapQuads,
+                       int colorExact) {
     const float4* prog = reinterpret_cast<const float4*>(quads);
     Box3 b;
     for (int a = 0; a < 3; a++) { b.lo[a] = lo3[a]; b.hi[a] = hi3[a]; }
-    const uint32_t len = prune_walk<false>(prog, b, cullMode, iso, nullptr);
+    const uint32_t len = prune_walk<false>(prog, b, cullMode, iso, nullptr, colorExact != 0);
     if (len == 0 || len > outCapQuads || !out) return len;
-    prune_walk<true>(prog, b, cullMode, iso, reinterpret_cast<float4*>(out));
+    prune_walk<true>(prog, b, cullMode, iso, reinterpret_cast<float4*>(out), colorExact != 0);
     return len;
 }
 

@@ -17,7 +17,7 @@ def lib():
         l.hostemu_field.argtypes = [vp, vp, C.c_int64, vp, C.c_int]
         l.hostemu_field_color.argtypes = [vp, vp, vp, C.c_int64, vp, vp, C.c_int]
         l.hostemu_prune.restype = C.c_uint32
-        l.hostemu_prune.argtypes = [vp, vp, vp, C.c_int, C.c_float, vp, C.c_uint32]
+        l.hostemu_prune.argtypes = [vp, vp, vp, C.c_int, C.c_float, vp, C.c_uint32, C.c_int]
         _lib = l
     return _lib
 
@@ -39,13 +39,13 @@ def field_color(quads, colors, xyz, sem):
     return f, col
 
 
-def prune(quads, lo, hi, cull_mode: int, iso: float = 0.5):
+def prune(quads, lo, hi, cull_mode: int, iso: float = 0.5, color_exact: bool = False):
     """Returns the pruned program (n,4) uint32, or None when the region needs no evaluation."""
     quads = np.ascontiguousarray(quads, np.uint32)
     lo, hi = np.ascontiguousarray(lo, np.float32), np.ascontiguousarray(hi, np.float32)
     cap = len(quads) + 64
     out = np.zeros((cap, 4), np.uint32)
-    n = lib().hostemu_prune(quads.ctypes.data, lo.ctypes.data, hi.ctypes.data, cull_mode, iso, out.ctypes.data, cap)
+    n = lib().hostemu_prune(quads.ctypes.data, lo.ctypes.data, hi.ctypes.data, cull_mode, iso, out.ctypes.data, cap, int(color_exact))
     if n == 0:
         return None
     assert n <= cap

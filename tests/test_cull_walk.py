@@ -85,3 +85,28 @@ def test_zero_folding_rules_of_difference():
     assert np.array_equal(emu.field(pr, pts, ps.SEM_SCALAR), full)
     # all-inside region: the interval cull may drop it (no surface), the support cull must not
     assert emu.prune(quads, a, b, ps.CULL_INTERVAL, ISO) is None
+
+
+def test_simd_colour_rule_survives_pruning():
+    """The PS_SimdPoly blend colour 2*f_L*c_L + 2*f_R*c_R is unnormalised (PS_Polygonizer.cpp:1475-1487): dropping an
+    all-zero operand must keep the survivor's weight (OPC_CSCALE markers), or mesh colours would depend on the culling."""
+    root = bt.binarize(scenes_small.blob())
+    prog = ps.linearize(bt.flatten(root), ps.SEM_SIMD, 0)
+    quads, colors = prog.quads(), prog.colors()
+    lo, hi = ps.prepare_bboxes(bt.flatten(root))
+    rs = np.random.RandomState(21)
+    blo, bhi = _regions(lo, hi, rs, 200, 0.15)
+    checked = marked = 0
+    for a, b in zip(blo, bhi):
+        pts = rs.uniform(a, b, (32, 3)).astype(np.float32)
+        full_f, full_c = emu.field_color(quads, colors, pts, ps.SEM_SIMD)
+        pr = emu.prune(quads, a, b, ps.CULL_SUPPORT, ISO, color_exact=True)
+        if pr is None:
+            continue
+        marked += int(((pr[:, 0] & 63) == 21).any())
+        f, c = emu.field_color(pr, colors, pts, ps.SEM_SIMD)
+        assert np.array_equal(f.view(np.uint32), full_f.view(np.uint32))
+        on = full_f > 0  # where the field is exactly 0 the reference's tie rule adds up colours of zero operands: never a vertex
+        assert np.array_equal(c[on].view(np.uint32), full_c[on].view(np.uint32))
+        checked += int(on.sum())
+    assert checked > 1000 and marked > 0

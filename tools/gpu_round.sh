@@ -1,8 +1,15 @@
 #!/bin/bash
-# Development aid: one GPU-box session = quick shake-out, gpu tests, bench, launch list. Outputs under gpurun_out/.
+# Development aid: one GPU-box session = gpu tests, bench, ncu launch list + one full capture. Outputs under gpurun_out/.
 mkdir -p gpurun_out
 nvidia-smi --query-gpu=name,clocks.sm,clocks.max.sm,memory.total --format=csv > gpurun_out/smi.txt 2>&1
-timeout 300 python tools/gpu_quick.py > gpurun_out/quick.log 2>&1; echo "quick rc=$?" >> gpurun_out/quick.log
-timeout 900 python -m pytest tests -m gpu -x -q > gpurun_out/pytest_gpu.log 2>&1; echo "pytest rc=$?" >> gpurun_out/pytest_gpu.log
+timeout 1200 python -m pytest tests -m gpu -x -q > gpurun_out/pytest_gpu.log 2>&1; echo "pytest rc=$?" >> gpurun_out/pytest_gpu.log
+tail -30 gpurun_out/pytest_gpu.log
 timeout 600 python bench.py --steps 5 --warmup 3 > gpurun_out/bench.log 2> gpurun_out/bench.err; echo "bench rc=$?" >> gpurun_out/bench.err
-tail -5 gpurun_out/quick.log; tail -3 gpurun_out/pytest_gpu.log; tail -c 3000 gpurun_out/bench.log; tail -5 gpurun_out/bench.err
+tail -c 2500 gpurun_out/bench.log; tail -5 gpurun_out/bench.err
+if [ "$1" = "ncu" ]; then
+  timeout 300 python tools/prof_step.py > gpurun_out/plain.log 2>&1 &&
+  timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 200 --csv --log-file gpurun_out/launches.csv python tools/prof_step.py > gpurun_out/ncu_list.log 2>&1
+  timeout 300 python tools/prof_step.py > gpurun_out/plain2.log 2>&1 &&
+  timeout 1200 ncu --set full --clock-control none --import-source on -k regex:'field_kernel|emit_kernel|prune_' -s 10 -c 8 -o gpurun_out/prof -f python tools/prof_step.py > gpurun_out/ncu_full.log 2>&1
+  tail -3 gpurun_out/ncu_list.log gpurun_out/ncu_full.log; cat gpurun_out/plain.log
+fi

@@ -1,0 +1,27 @@
+"""Profiling target (development aid): the N=1 bench workload (blob1k@512^3, BASELINE configs[1]), 1 warm-up + 2 steps,
+no CPU legs - short enough to sit under ncu. `--native` runs the canonical semantics instead of the PS_SimdPoly compat ones."""
+import os, sys
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import parsip_b200 as ps
+from parsip_b200 import blobtree as bt, scenes
+
+native = "--native" in sys.argv
+cells = 512
+for a in sys.argv[1:]:
+    if a.startswith("--cells="):
+        cells = int(a.split("=")[1])
+root = scenes.blob1k()
+flat_bin = bt.flatten(bt.binarize(root))
+lo, hi = ps.prepare_bboxes(flat_bin)
+cs = scenes.cellsize_for(lo, hi, cells)
+ctx = ps.Context(0)
+if native:
+    ctx.upload(ps.linearize(bt.flatten(root), ps.SEM_SCALAR, ps.LIN_REASSOCIATE))
+    prm = ps.Params.make(cs, lo, hi)
+else:
+    ctx.upload(ps.linearize(flat_bin, ps.SEM_SIMD, 0))
+    prm = ps.Params.make(cs, lo, hi, root_mode=ps.ROOT_FOURSAMPLE)
+for i in range(3):
+    m = ctx.polygonize(prm, download=False)
+    st = ctx.stats()
+    print({k: (round(v, 3) if isinstance(v, float) else v) for k, v in st.items()}, m["n_vertices"], m["n_triangles"])
