@@ -59,7 +59,7 @@ typedef struct psgpu_params {
     float bbox_lo[3], bbox_hi[3]; /* grid domain; the MPU lattice is laid out from bbox_lo like PS_Polygonizer.cpp:328-371 */
     float iso;                    /* 0 = default ISO_VALUE 0.5 */
     int32_t root_mode;
-    int32_t root_iterations; /* 0 = default (8 Newton / 10 bisect) */
+    int32_t root_iterations; /* 0 = default (8 Newton / 16 bisect) */
     int32_t coord_mode;
     int32_t output;
     int32_t cull;
@@ -134,6 +134,14 @@ int psgpu_field_eval(psgpu_ctx* ctx, const float* xyz, int64_t n, float* f_out);
 int psgpu_field_color_normal(psgpu_ctx* ctx, const float* xyz, int64_t n, float* f, float* col, float* nrm);
 /* Field cache (fv[i*8 + j*64 + k]) and cube cases (cell i*49 + j*7 + k) of one MPU, for parity tests. */
 int psgpu_mpu_cache(psgpu_ctx* ctx, const psgpu_params* params, const int32_t* ijk, float* fv512, uint8_t* case343);
+/* Parity hook: runs cull + field for `params` and returns the lattice index and the 512-value field cache of EVERY evaluated
+ * MPU, each computed with that MPU's own pruned program (compare with psgpu_mpu_cache = full program). n_out = MPUs evaluated;
+ * nothing is copied if cap_mpus is too small. */
+int psgpu_mpu_caches_culled(psgpu_ctx* ctx, const psgpu_params* params, int32_t* ijk_out, float* fv_out, int64_t cap_mpus, int64_t* n_out);
+/* Parity hook for the culling pass: prunes the uploaded program against the box [lo, hi] on the device (one thread of the
+ * same prune_walk the cull kernels run). len_out = pruned length in quads, 0 = region needs no evaluation. */
+int psgpu_prune_region(psgpu_ctx* ctx, const float* lo3, const float* hi3, int cull, float iso, int color_exact, uint32_t* quads_out,
+                       uint32_t cap_quads, uint32_t* len_out);
 int psgpu_get_stats(const psgpu_ctx* ctx, psgpu_stats* out);
 /* FP32 FMA-chain microbenchmark (dependent-free FFMA streams on every SM); returns measured TFLOP/s. */
 int psgpu_measure_fp32_peak(psgpu_ctx* ctx, float* tflops_out, float* sm_clock_mhz_out);

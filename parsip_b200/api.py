@@ -21,7 +21,7 @@ EXPORTS = [
     "psgpu_create", "psgpu_destroy", "psgpu_last_error", "psgpu_device_count", "psgpu_linearize", "psgpu_program_free",
     "psgpu_program_info", "psgpu_program_copy", "psgpu_program_colors", "psgpu_prepare_bboxes", "psgpu_count_mpus", "psgpu_upload_program",
     "psgpu_polygonize", "psgpu_polygonize_host", "psgpu_mesh_download", "psgpu_field_eval", "psgpu_field_color_normal",
-    "psgpu_mpu_cache", "psgpu_get_stats", "psgpu_measure_fp32_peak",
+    "psgpu_mpu_cache", "psgpu_mpu_caches_culled", "psgpu_prune_region", "psgpu_get_stats", "psgpu_measure_fp32_peak",
 ]
 
 
@@ -118,6 +118,8 @@ def load_library():
     lib.psgpu_field_eval.argtypes = [vp, vp, C.c_int64, vp]
     lib.psgpu_field_color_normal.argtypes = [vp, vp, C.c_int64, vp, vp, vp]
     lib.psgpu_mpu_cache.argtypes = [vp, C.POINTER(Params), vp, vp, vp]
+    lib.psgpu_mpu_caches_culled.argtypes = [vp, C.POINTER(Params), vp, vp, C.c_int64, vp]
+    lib.psgpu_prune_region.argtypes = [vp, vp, vp, C.c_int, C.c_float, C.c_int, vp, C.c_uint32, vp]
     lib.psgpu_get_stats.argtypes = [vp, C.POINTER(_Stats)]
     lib.psgpu_measure_fp32_peak.argtypes = [vp, vp, vp]
     _lib = lib
@@ -241,6 +243,23 @@ class Context:
         fv, cs = np.zeros(512, np.float32), np.zeros(343, np.uint8)
         self._check(self.lib.psgpu_mpu_cache(self.h, C.byref(params), ijk.ctypes.data, fv.ctypes.data, cs.ctypes.data), "psgpu_mpu_cache")
         return fv, cs
+
+    def mpu_caches_culled(self, params: Params):
+        """(ijk (n,3), fv (n,512)) of every MPU the culled pipeline evaluates, each with its own pruned program."""
+        n = C.c_int64()
+        self._check(self.lib.psgpu_mpu_caches_culled(self.h, C.byref(params), None, None, 0, C.byref(n)), "psgpu_mpu_caches_culled")
+        ijk, fv = np.zeros((max(n.value, 1), 3), np.int32), np.zeros((max(n.value, 1), 512), np.float32)
+        self._check(self.lib.psgpu_mpu_caches_culled(self.h, C.byref(params), ijk.ctypes.data, fv.ctypes.data, n.value, C.byref(n)),
+                    "psgpu_mpu_caches_culled")
+        return ijk[:n.value], fv[:n.value]
+
+    def prune_region(self, lo, hi, cull: int, iso: float = 0.5, color_exact: bool = False, cap: int = 1 << 16):
+        """Device-side prune of the uploaded program against a box; returns the pruned quads or None (nothing to evaluate)."""
+        lo, hi = np.ascontiguousarray(lo, np.float32), np.ascontiguousarray(hi, np.float32)
+        out, n = np.zeros((cap, 4), np.uint32), C.c_uint32()
+        self._check(self.lib.psgpu_prune_region(self.h, lo.ctypes.data, hi.ctypes.data, cull, iso, int(color_exact), out.ctypes.data, cap,
+                                                C.byref(n)), "psgpu_prune_region")
+        return None if n.value == 0 else out[:n.value].copy()
 
     def polygonize(self, params: Params, download: bool = True, allow_over_capacity: bool = False) -> dict:
         """cull -> field -> scan -> emit on the device; optionally copies the mesh to numpy arrays."""

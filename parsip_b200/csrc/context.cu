@@ -7,6 +7,7 @@
 #include <algorithm>
 #include <cmath>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <string>
 #include <vector>
@@ -161,7 +162,7 @@ int fill_grid(psgpu_ctx* ctx, const psgpu_params* P, GridParams& G) {
     G.cellsize = P->cellsize;
     G.mpuSide = P->cellsize * (float)PS_CELLS_PER_MPU;
     G.coordMode = P->coord_mode; G.sem = ctx->semantics; G.output = P->output; G.rootMode = P->root_mode;
-    G.rootIters = P->root_iterations > 0 ? P->root_iterations : (P->root_mode == PSGPU_ROOT_NEWTON_REF ? 8 : 10);
+    G.rootIters = P->root_iterations > 0 ? P->root_iterations : (P->root_mode == PSGPU_ROOT_NEWTON_REF ? 8 : 16);
     G.insideGE = (ctx->semantics == PSGPU_SEM_SIMD) ? 1 : 0;
     G.wantColors = P->want_colors; G.wantNormals = P->want_normals;
     G.forceFv = 0;
@@ -195,6 +196,11 @@ int run_cull(psgpu_ctx* ctx, const GridParams& G, int cullMode, bool colorExact,
     if (maxDim > 64) sizes = {16, 4, 1};
     else if (maxDim > 4) sizes = {4, 1};
     else sizes = {1};
+    if (const char* ov = getenv("PSGPU_CULL_LEVELS")) {  // tuning / debugging aid: "16,4,1", "4,1" or "1"
+        std::vector<int> o;
+        for (const char* c = ov; *c;) { o.push_back(atoi(c)); while (*c && *c != ',') c++; if (*c == ',') c++; }
+        if (!o.empty() && o.back() == 1) sizes = o;
+    }
     // top-level parents: regions of 4 * sizes[0] MPUs carrying the full program
     std::vector<Region> top;
     {
@@ -474,6 +480,52 @@ extern "C" int psgpu_mpu_cache(psgpu_ctx* ctx, const psgpu_params* params, const
             if (in) cfg |= 1 << b;
         }
         case343[i * 49 + j * 7 + k] = (uint8_t)cfg;
+    }
+    return PSGPU_SUCCESS;
+}
+
+extern "C" int psgpu_mpu_caches_culled(psgpu_ctx* ctx, const psgpu_params* params, int32_t* ijk_out, float* fv_out, int64_t cap_mpus, int64_t* n_out) {
+    if (!ctx || !params || !n_out) return PSGPU_PARAM_ERROR;
+    int rc = polygonize_impl(ctx, params, nullptr, true);
+    if (rc != PSGPU_SUCCESS && rc != PSGPU_NOT_ENOUGH_MEM) return rc;
+    *n_out = ctx->nCand;
+    if (ctx->nCand > cap_mpus || !ijk_out || !fv_out) return PSGPU_SUCCESS;
+    std::vector<psgpu::Region> regs((size_t)ctx->nCand);
+    if (ctx->nCand > 0) {
+        CK(cudaMemcpyAsync(regs.data(), ctx->cands, regs.size() * sizeof(psgpu::Region), cudaMemcpyDeviceToHost, ctx->stream));
+        CK(cudaMemcpyAsync(fv_out, ctx->fv.p, (size_t)ctx->nCand * 2048, cudaMemcpyDeviceToHost, ctx->stream));
+        CK(cudaStreamSynchronize(ctx->stream));
+    }
+    for (int i = 0; i < ctx->nCand; i++) { ijk_out[i * 3] = regs[i].x; ijk_out[i * 3 + 1] = regs[i].y; ijk_out[i * 3 + 2] = regs[i].z; }
+    return PSGPU_SUCCESS;
+}
+
+// debugging aid (not in psgpu.h): pruned program of candidate `idx` of the last polygonize
+extern "C" int psgpu_debug_candidate_program(psgpu_ctx* ctx, int idx, uint32_t* quads_out, uint32_t cap, uint32_t* len_out) {
+    if (!ctx || idx < 0 || idx >= ctx->nCand) return PSGPU_PARAM_ERROR;
+    psgpu::Region r;
+    CK(cudaMemcpy(&r, ctx->cands + idx, sizeof(r), cudaMemcpyDeviceToHost));
+    *len_out = r.len;
+    if (r.len <= cap) CK(cudaMemcpy(quads_out, ctx->pool.as<float4>() + r.off, (size_t)r.len * 16, cudaMemcpyDeviceToHost));
+    return PSGPU_SUCCESS;
+}
+
+extern "C" int psgpu_prune_region(psgpu_ctx* ctx, const float* lo3, const float* hi3, int cull, float iso, int color_exact, uint32_t* quads_out,
+                                  uint32_t cap_quads, uint32_t* len_out) {
+    if (!ctx || !lo3 || !hi3 || !quads_out || !len_out || ctx->progQuads == 0) return PSGPU_PARAM_ERROR;
+    CK(cudaSetDevice(ctx->device));
+    cudaStream_t st = ctx->stream;
+    CK(ctx->ptsIn.reserve((size_t)cap_quads * 16 + 16));
+    CK(ctx->scalars.reserve(64));
+    psgpu::launch_prune_one(ctx->pool.as<float4>(), lo3, hi3, cull, iso > 0.f ? iso : PS_ISO_VALUE, color_exact, ctx->ptsIn.as<float4>(), cap_quads,
+                            ctx->scalars.as<uint32_t>(), st);
+    CK(cudaMemcpyAsync(&ctx->hostScalars[10], ctx->scalars.p, 4, cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
+    CK(cudaGetLastError());
+    *len_out = ctx->hostScalars[10];
+    if (*len_out > 0 && *len_out <= cap_quads) {
+        CK(cudaMemcpyAsync(quads_out, ctx->ptsIn.p, (size_t)*len_out * 16, cudaMemcpyDeviceToHost, st));
+        CK(cudaStreamSynchronize(st));
     }
     return PSGPU_SUCCESS;
 }

@@ -66,7 +66,7 @@ __global__ void __launch_bounds__(128) prune_emit_kernel(CullLevel L, const Regi
     Box3 box;
     child_region(L, parent, tid & 63, coord, box);
     const uint32_t off = outBase + childOff[tid];
-    prune_walk<true>(pool + parent.off, box, L.cullMode, L.iso, outPool + off, L.colorExact != 0);
+    prune_walk<true>(pool + parent.off, box, L.cullMode, L.iso, outPool + off, L.colorExact != 0, len);
     const uint32_t idx = childIdx[tid];
     Region r;
     r.x = coord[0]; r.y = coord[1]; r.z = coord[2]; r.off = off; r.len = len;
@@ -96,7 +96,22 @@ __global__ void all_mpus_kernel(CullLevel L, Region* __restrict__ out, uint32_t 
     candOfMpu[i] = i;
 }
 
+// parity hook: one thread prunes the full program against an arbitrary box (psgpu_prune_region)
+__global__ void prune_one_kernel(const float4* __restrict__ prog, Box3 box, int cullMode, float iso, int colorExact, float4* __restrict__ out,
+                                 uint32_t cap, uint32_t* __restrict__ lenOut) {
+    const uint32_t len = prune_walk<false>(prog, box, cullMode, iso, nullptr, colorExact != 0);
+    *lenOut = len;
+    if (len > 0 && len <= cap) prune_walk<true>(prog, box, cullMode, iso, out, colorExact != 0, len);
+}
+
 }  // namespace
+
+void launch_prune_one(const float4* prog, const float* lo, const float* hi, int cullMode, float iso, int colorExact, float4* out, uint32_t cap,
+                      uint32_t* lenOut, cudaStream_t st) {
+    Box3 b;
+    for (int a = 0; a < 3; a++) { b.lo[a] = lo[a]; b.hi[a] = hi[a]; }
+    prune_one_kernel<<<1, 1, 0, st>>>(prog, b, cullMode, iso, colorExact, out, cap, lenOut);
+}
 
 void launch_all_mpus(const CullLevel& L, Region* out, uint32_t fullLen, int32_t* candOfMpu, int n, cudaStream_t st) {
     all_mpus_kernel<<<(n + 255) / 256, 256, 0, st>>>(L, out, fullLen, candOfMpu, n);

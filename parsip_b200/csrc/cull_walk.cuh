@@ -134,7 +134,7 @@ __device__ bool prim_bound(uint32_t hdr, const float4 q0, const float4* __restri
 
 __device__ __forceinline__ void bound_combine(uint32_t cmb, float& lo, float& hi, float vlo, float vhi) {
     switch (cmb) {
-    case CMB_ADD: lo += vlo; hi += vhi; break;
+    case CMB_ADD: case CMB_RADD: lo += vlo; hi += vhi; break;
     case CMB_MAX: lo = fmaxf(lo, vlo); hi = fmaxf(hi, vhi); break;
     case CMB_MIN: lo = fminf(lo, vlo); hi = fminf(hi, vhi); break;
     case CMB_DIF: lo = fminf(lo, 1.0f - vhi); hi = fminf(hi, 1.0f - vlo); break;
@@ -151,9 +151,13 @@ __device__ __forceinline__ void bound_combine(uint32_t cmb, float& lo, float& hi
 // Prunes src against `box`. EMIT = false only measures. Returns the pruned length in quads including the
 // END quad, or 0 if the region needs no evaluation.
 // colorExact (PS_SimdPoly semantics): a blend that loses an all-zero operand leaves an OPC_CSCALE marker, see program.h.
+// `limit` (EMIT only) = the length the measuring pass returned: the walk writes TENTATIVE code that a later zero-fold may
+// rewind (intersection with 0, all-zero warp bracket, ...), and such code can run past the final length - into the slot of
+// the next region's program in the pool, which another thread is writing. Nothing at or beyond `limit` survives, so it is
+// simply not stored.
 template <bool EMIT>
 __device__ uint32_t prune_walk(const float4* __restrict__ src, const Box3& region, int cullMode, float iso, float4* __restrict__ dst,
-                               bool colorExact = false) {
+                               bool colorExact = false, uint32_t limit = 0xFFFFFFFFu) {
     float blo[PS_MAX_VALUE_STACK], bhi[PS_MAX_VALUE_STACK];
     uint32_t bstart[PS_MAX_VALUE_STACK];
     bool bzero[PS_MAX_VALUE_STACK];
@@ -162,7 +166,7 @@ __device__ uint32_t prune_walk(const float4* __restrict__ src, const Box3& regio
     int sp = -1, wsp = 0;
     uint32_t emit = 0;
     Box3 box = region;
-    auto put = [&](float4 v) { if (EMIT) dst[emit] = v; emit++; };
+    auto put = [&](float4 v) { if (EMIT && emit < limit) dst[emit] = v; emit++; };
     auto hdrquad = [&](uint32_t h) { return make_float4(__uint_as_float(h), 0.f, 0.f, 0.f); };
     uint32_t lastScale = 0xFFFFFFFFu, scaleCount = 0;  // position of the trailing OPC_CSCALE quad, if emit == lastScale + 1
     auto rewind = [&](uint32_t pos) {
@@ -173,7 +177,7 @@ __device__ uint32_t prune_walk(const float4* __restrict__ src, const Box3& regio
         if (!colorExact || n == 0) return;
         if (lastScale + 1 == emit) scaleCount += n;
         else { lastScale = emit; scaleCount = n; emit++; }
-        if (EMIT) dst[lastScale] = make_float4(__uint_as_float(PS_HDR(OPC_CSCALE, 0, 0, 0)), __uint_as_float(scaleCount), 0.f, 0.f);
+        if (EMIT && lastScale < limit) dst[lastScale] = make_float4(__uint_as_float(PS_HDR(OPC_CSCALE, 0, 0, 0)), __uint_as_float(scaleCount), 0.f, 0.f);
     };
     for (uint32_t pc = 0;;) {
         const float4 q0 = src[pc];
@@ -217,7 +221,8 @@ __device__ uint32_t prune_walk(const float4* __restrict__ src, const Box3& regio
         }
         switch (opc) {
         case OPC_COMBINE: {
-            const uint32_t cmb = PS_HDR_CMB(hdr);
+            const uint32_t cmbRaw = PS_HDR_CMB(hdr);
+            const uint32_t cmb = (cmbRaw == CMB_RADD) ? (uint32_t)CMB_ADD : cmbRaw;  // same zero-folding as a blend
             const int v = sp, t = sp - 1;
             sp--;
             if (bzero[t] && bzero[v]) {

@@ -107,9 +107,10 @@ __device__ void root_bisect(const GridParams& G, const float4* prog, const EdgeP
     const float d = E.e2a - E.e1[E.axis];
     float t = 0.5f;
     int side = 0;
+    bool bisect = false;  // forced when the last step failed to halve the bracket (creases of CSG fields, flat tails)
     for (int it = 0; it < iters; it++) {
-        const float den = fa - fb;
-        t = (den != 0.f) ? ta + (tb - ta) * (fa / den) : 0.5f * (ta + tb);
+        const float den = fa - fb, w0 = tb - ta;
+        t = (!bisect && den != 0.f) ? ta + w0 * (fa / den) : 0.5f * (ta + tb);
         if (!(t > ta && t < tb)) t = 0.5f * (ta + tb);
         float X[1] = {E.e1[0]}, Y[1] = {E.e1[1]}, Z[1] = {E.e1[2]}, F[1];
         const float moved = fmaf(t, d, E.e1[E.axis]);
@@ -119,6 +120,8 @@ __device__ void root_bisect(const GridParams& G, const float4* prog, const EdgeP
         if (fabsf(ft) < 1e-6f) break;
         if ((ft < 0.f) == (fa < 0.f)) { ta = t; fa = ft; if (side == -1) fb *= 0.5f; side = -1; }
         else { tb = t; fb = ft; if (side == 1) fa *= 0.5f; side = 1; }
+        bisect = (tb - ta) > 0.5f * w0;
+        if (tb - ta < 1e-6f) break;
     }
     p[0] = E.e1[0]; p[1] = E.e1[1]; p[2] = E.e1[2];
     p[E.axis] = fmaf(t, d, E.e1[E.axis]);

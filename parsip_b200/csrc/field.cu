@@ -8,6 +8,8 @@
 //
 // Reference: CMPUProcessor::process_cells_simd phases 0-2 (PS_SimdPoly/include/PS_Polygonizer.cpp:483-701) and
 // CSIMDMPURunBody::doMarchingCubes' cache + classify (ParsipHaptics/include/CPolyParsipOptimized.cpp:187-244).
+#include <cstdlib>
+
 #include "device_util.cuh"
 #include "interp.cuh"
 #include "kernels.h"
@@ -207,6 +209,7 @@ __global__ void __launch_bounds__(128) points_fcn_kernel(const float4* __restric
         float nx = (F[1] - F[0]) * dinv, ny = (F[2] - F[0]) * dinv, nz = (F[3] - F[0]) * dinv;
         const float l2 = nx * nx + ny * ny + nz * nz;
         if (l2 > 0.f) { const float inv = rsqrtf(l2); nx *= inv; ny *= inv; nz *= inv; }
+        else if (sem == PSGPU_SEM_SCALAR) { nx = ny = nz = 1.0f; }  // normalizeXYZ of a zero vector, FW/PS_Vector.h:1072-1086
         f[i] = F[0];
         col[i * 3] = rgb[0]; col[i * 3 + 1] = rgb[1]; col[i * 3 + 2] = rgb[2];
         nrm[i * 3] = nx; nrm[i * 3 + 1] = ny; nrm[i * 3 + 2] = nz;
@@ -273,6 +276,7 @@ void launch_field_kernel(const GridParams& G, const Region* cands, int nCand, co
     if (nCand <= 0) return;
     uint32_t cap;
     const int smem = field_kernel_smem_bytes(maxProgQuads, &cap);
+    if (getenv("PSGPU_NO_STAGE")) cap = 0;  // debugging aid: interpret straight from global memory
     const bool strict = (G.sem == PSGPU_SEM_SIMD);
     static int configured[2] = {-1, -1};
     if (smem > configured[strict]) {

@@ -276,7 +276,7 @@ __device__ __forceinline__ void prim_field(uint32_t opc, const float4 q0, const 
 
 __device__ __forceinline__ float combine_val(uint32_t cmb, float top, float v) {
     switch (cmb) {
-    case CMB_ADD: return top + v;
+    case CMB_ADD: case CMB_RADD: return top + v;
     case CMB_MAX: return fmaxf(top, v);
     case CMB_MIN: return fminf(top, v);
     case CMB_DIF: return fminf(top, 1.0f - v);
@@ -303,6 +303,8 @@ __device__ __forceinline__ void combine_color(int sem, uint32_t cmb, float tf, f
 #pragma unroll
         for (int a = 0; a < 3; a++) tc[a] = __fadd_rn(__fmul_rn(wl, tc[a]), __fmul_rn(wr, vc[a]));
     } else {  // CompactBlobTree.cpp:1186-1260, kept normalised per entry (association-invariant)
+        // taux = what the reference's `best` would be if this entry became the first child of a (smooth) difference: the
+        // entry's value so far; under DIF / SDIF the running min(f0, 1 - f_i) that picks the colour; under RADD the raw sum.
         if (cmb == CMB_ADD) {
             const float s = tf + vf;
             if (s != 0.0f) {
@@ -310,10 +312,13 @@ __device__ __forceinline__ void combine_color(int sem, uint32_t cmb, float tf, f
 #pragma unroll
                 for (int a = 0; a < 3; a++) tc[a] = (tf * tc[a] + vf * vc[a]) * inv;
             }
+            taux = result;
         } else if (cmb == CMB_MAX) {
             if (vf > tf) { tc[0] = vc[0]; tc[1] = vc[1]; tc[2] = vc[2]; }
+            taux = result;
         } else if (cmb == CMB_MIN) {
             if (vf < tf) { tc[0] = vc[0]; tc[1] = vc[1]; tc[2] = vc[2]; }
+            taux = result;
         } else {
             const float cf = 1.0f - vf;
             if (cf < taux) { taux = cf; tc[0] = vc[0]; tc[1] = vc[1]; tc[2] = vc[2]; }
@@ -389,16 +394,21 @@ __device__ void eval_program(const float4* __restrict__ prog, const float (&X)[N
             if (COLOR) {
                 float vc[3] = {tc[0], tc[1], tc[2]};
                 const float vf = top[0];
+                const float vaux = taux;
                 tc[0] = cstk[sp][0]; tc[1] = cstk[sp][1]; tc[2] = cstk[sp][2]; taux = cstk[sp][3];
                 const float tf = vs[sp][0];
                 const float r0 = combine_val(cmb, tf, vf);
-                combine_color(sem, cmb, tf, tc, taux, vf, vc, r0);
+                if (cmb == CMB_RADD) {  // weights = raw child fields: taux = raw sum so far, vaux = the incoming child's raw field
+                    const float ssum = taux + vaux;
+                    combine_color(sem, CMB_ADD, taux, tc, taux, vaux, vc, ssum);
+                } else combine_color(sem, cmb, tf, tc, taux, vf, vc, r0);
             }
 #pragma unroll
             for (int n = 0; n < N; n++) top[n] = combine_val(cmb, vs[sp][n], top[n]);
             pc += 1;
         } break;
         case OPC_POW: {
+            if (COLOR) taux = (PS_HDR_CMB(hdr) == 1u) ? top[0] : powf(top[0], q0.y);  // raw child field / the blend's value
 #pragma unroll
             for (int n = 0; n < N; n++) top[n] = powf(top[n], q0.y);
             pc += 1;

@@ -64,6 +64,8 @@ void launch_flags(const uint32_t* len, uint32_t* flag, int n, cudaStream_t st);
 void launch_prune_emit(const CullLevel& L, const Region* parents, int nParents, const float4* pool, const uint32_t* childLen,
                        const uint32_t* childOff, const uint32_t* childIdx, float4* outPool, uint32_t outBase, Region* children,
                        int32_t* candOfMpu, uint32_t* maxLen, cudaStream_t st);
+void launch_prune_one(const float4* prog, const float* lo, const float* hi, int cullMode, float iso, int colorExact, float4* out, uint32_t cap,
+                      uint32_t* lenOut, cudaStream_t st);
 size_t scan_temp_bytes(int n);
 void exclusive_scan_u32(void* temp, size_t tempBytes, const uint32_t* in, uint32_t* out, int n, cudaStream_t st);
 

@@ -182,8 +182,8 @@ struct Emitter {
             } else {
                 for (int i = 0; i < nk; i++) {
                     emit(t->child[t->first_child[n] + i], CMB_PUSH);
-                    quad(PS_HDR(OPC_POW, 0, false, 0), nexp); p->nInstr++;
-                    if (i > 0) combine(CMB_ADD);
+                    quad(PS_HDR(OPC_POW, 1, false, 0), nexp); p->nInstr++;
+                    if (i > 0) combine(CMB_RADD);
                 }
                 quad(PS_HDR(OPC_POW, 0, false, 0), inv); p->nInstr++;
             }

@@ -34,7 +34,8 @@ enum PsOpcode : uint32_t {
     OPC_NULLPRIM = 8,  // {h,0,0,0}  field 0
     OPC_FIRST_NONPRIM = 16,
     OPC_COMBINE = 16,    // {h}            v = pop; top = top (combine) v
-    OPC_POW = 17,        // {h, e}         top = pow(top, e)          (true Ricci, CompactBlobTree.cpp:813-818)
+    OPC_POW = 17,        // {h, e}         top = pow(top, e)          (true Ricci, CompactBlobTree.cpp:813-818); combine code 1 marks
+                         //                the per-child power (the colour walk remembers the raw value), 0 the closing 1/n power
     OPC_RICCI_SIMD = 18, // {h, e}         v = pop; top = fast_pow(top + v, e)   (PS_SIMDVecN.h:122-128, Q6)
     OPC_CLAMP1 = 19,     // {h}            top = min(top, 1)          (difference with an all-zero subtrahend, Q16)
     OPC_DIF0 = 20,       // {h}            top = min(0, 1 - top)      (difference with an all-zero minuend)
@@ -56,6 +57,8 @@ enum PsCombine : uint32_t {
     CMB_MIN = 3,   // intersection
     CMB_DIF = 4,   // top = min(top, 1 - v)
     CMB_SDIF = 5,  // top = top * (1 - v)
+    CMB_RADD = 6,  // top + v like CMB_ADD; sums the POWERED children of a true Ricci blend, whose colour weights are the RAW
+                   // child fields (CompactBlobTree.cpp:1186-1203), kept in the colour walk's aux slot
 };
 
 #define PS_HDR(opc, cmb, xf, prim) ((uint32_t)(opc) | ((uint32_t)(cmb) << 6) | ((uint32_t)((xf) ? 1 : 0) << 10) | ((uint32_t)(prim) << 11))
@@ -94,7 +97,7 @@ static inline int ps_algorithmic_flops(uint32_t hdr) {
     case OPC_CYLINDER: f = 33; break;
     case OPC_CUBE: f = 39; break;
     case OPC_DISC: case OPC_RING: f = 51; break;
-    case OPC_COMBINE: f = (PS_HDR_CMB(hdr) >= CMB_DIF) ? 2 : 1; break;
+    case OPC_COMBINE: f = (PS_HDR_CMB(hdr) == CMB_DIF || PS_HDR_CMB(hdr) == CMB_SDIF) ? 2 : 1; break;
     case OPC_POW: f = 2; break;
     case OPC_RICCI_SIMD: f = 4; break;
     case OPC_TWIST: f = 9; break;

@@ -77,7 +77,10 @@ def point_triangle_distance(p, a, b, c):
         put((va <= 0) & (d4 - d3 >= 0) & (d5 - d6 >= 0), b + (c - b) * ((d4 - d3) / ((d4 - d3) + (d5 - d6)))[:, None])
         den = 1.0 / (va + vb + vc)
         put(np.ones(len(p), bool), a + ab * (vb * den)[:, None] + ac * (vc * den)[:, None])
-    return np.linalg.norm(p - out, axis=1)
+    d = np.linalg.norm(p - out, axis=1)
+    # degenerate triangles (the scalar twin's shrink-wrap Newton collapses edges that share a start corner): nearest vertex
+    dv = np.minimum(np.minimum(np.linalg.norm(ap, axis=1), np.linalg.norm(bp, axis=1)), np.linalg.norm(cp, axis=1))
+    return np.where(np.isfinite(d), np.minimum(d, dv), dv)
 
 
 def one_sided_hausdorff(pts, pos, tri, k=24):

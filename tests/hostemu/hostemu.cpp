@@ -38,7 +38,8 @@ uint32_t hostemu_prune(const float* quads, const float* lo3, const float* hi3, i
     for (int a = 0; a < 3; a++) { b.lo[a] = lo3[a]; b.hi[a] = hi3[a]; }
     const uint32_t len = prune_walk<false>(prog, b, cullMode, iso, nullptr, colorExact != 0);
     if (len == 0 || len > outCapQuads || !out) return len;
-    prune_walk<true>(prog, b, cullMode, iso, reinterpret_cast<float4*>(out), colorExact != 0);
+    const uint32_t len2 = prune_walk<true>(prog, b, cullMode, iso, reinterpret_cast<float4*>(out), colorExact != 0, len);
+    if (len2 != len) return 0xFFFFFFFFu;  // the measuring and the emitting pass must agree
     return len;
 }
 
