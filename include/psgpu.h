@@ -59,7 +59,7 @@ typedef struct psgpu_params {
     float bbox_lo[3], bbox_hi[3]; /* grid domain; the MPU lattice is laid out from bbox_lo like PS_Polygonizer.cpp:328-371 */
     float iso;                    /* 0 = default ISO_VALUE 0.5 */
     int32_t root_mode;
-    int32_t root_iterations; /* 0 = default (8 Newton / 16 bisect) */
+    int32_t root_iterations; /* 0 = default (8 Newton / 20 bisect) */
     int32_t coord_mode;
     int32_t output;
     int32_t cull;

@@ -162,7 +162,7 @@ int fill_grid(psgpu_ctx* ctx, const psgpu_params* P, GridParams& G) {
     G.cellsize = P->cellsize;
     G.mpuSide = P->cellsize * (float)PS_CELLS_PER_MPU;
     G.coordMode = P->coord_mode; G.sem = ctx->semantics; G.output = P->output; G.rootMode = P->root_mode;
-    G.rootIters = P->root_iterations > 0 ? P->root_iterations : (P->root_mode == PSGPU_ROOT_NEWTON_REF ? 8 : 16);
+    G.rootIters = P->root_iterations > 0 ? P->root_iterations : (P->root_mode == PSGPU_ROOT_NEWTON_REF ? 8 : 20);
     G.insideGE = (ctx->semantics == PSGPU_SEM_SIMD) ? 1 : 0;
     G.wantColors = P->want_colors; G.wantNormals = P->want_normals;
     G.forceFv = 0;

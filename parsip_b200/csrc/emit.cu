@@ -108,6 +108,7 @@ __device__ void root_bisect(const GridParams& G, const float4* prog, const EdgeP
     float t = 0.5f;
     int side = 0;
     bool bisect = false;  // forced when the last step failed to halve the bracket (creases of CSG fields, flat tails)
+    int slow = 0;         // after two such steps the rest is plain bisection: 2^-k guaranteed
     for (int it = 0; it < iters; it++) {
         const float den = fa - fb, w0 = tb - ta;
         t = (!bisect && den != 0.f) ? ta + w0 * (fa / den) : 0.5f * (ta + tb);
@@ -120,7 +121,8 @@ __device__ void root_bisect(const GridParams& G, const float4* prog, const EdgeP
         if (fabsf(ft) < 1e-6f) break;
         if ((ft < 0.f) == (fa < 0.f)) { ta = t; fa = ft; if (side == -1) fb *= 0.5f; side = -1; }
         else { tb = t; fb = ft; if (side == 1) fa *= 0.5f; side = 1; }
-        bisect = (tb - ta) > 0.5f * w0;
+        if ((tb - ta) > 0.5f * w0) slow++;
+        bisect = (tb - ta) > 0.5f * w0 || slow >= 2;
         if (tb - ta < 1e-6f) break;
     }
     p[0] = E.e1[0]; p[1] = E.e1[1]; p[2] = E.e1[2];
