@@ -40,7 +40,7 @@ typedef struct psgpu_program psgpu_program; /* host-side linearized BlobTree */
 
 #define PSGPU_ROOT_FOURSAMPLE 0 /* PS_Polygonizer.cpp:703-762: t = 0,1/3,2/3,1, bracket, lerp */
 #define PSGPU_ROOT_NEWTON_REF 1 /* CompactBlobTree.cpp:1581-1622: shrink-wrap Newton, <= 8 iterations */
-#define PSGPU_ROOT_BISECT 2     /* bracketed secant/bisection on the edge, re-evaluating the field (native default) */
+#define PSGPU_ROOT_BISECT 2     /* bracketed section search (x5 per round) + secant on the edge, re-evaluating the field (native default) */
 
 #define PSGPU_COORD_MPU_LOCAL 0 /* corner = (lo + I*side) + i*cellsize, the reference's expressions */
 #define PSGPU_COORD_GLOBAL 1    /* corner = lo + (7I+i)*cellsize: identical across MPUs, slabs and GPUs */
@@ -59,7 +59,7 @@ typedef struct psgpu_params {
     float bbox_lo[3], bbox_hi[3]; /* grid domain; the MPU lattice is laid out from bbox_lo like PS_Polygonizer.cpp:328-371 */
     float iso;                    /* 0 = default ISO_VALUE 0.5 */
     int32_t root_mode;
-    int32_t root_iterations; /* 0 = default (8 Newton / 20 bisect) */
+    int32_t root_iterations; /* 0 = default (8 Newton iterations / 4 section rounds) */
     int32_t coord_mode;
     int32_t output;
     int32_t cull;

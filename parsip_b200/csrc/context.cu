@@ -58,7 +58,7 @@ struct psgpu_ctx {
     // field outputs
     DevBuf fv, vcount, tcount, vbase, tbase, edgeMask, edgePrefix, mixedList, mixedFlag, mixedIdx, counters, statsAcc;
     // mesh
-    DevBuf pos, nrm, col, tri, mpuIjk, mpuVbase, mpuTbase;
+    DevBuf pos, nrm, col, tri, mpuIjk, mpuVbase, mpuTbase, vperm;
     DevBuf ptsIn, ptsF, ptsCol, ptsNrm;
     uint32_t* hostScalars = nullptr;  // pinned readback
     void* hostStage = nullptr;        // pinned upload staging (program + colours)
@@ -108,7 +108,7 @@ extern "C" int psgpu_destroy(psgpu_ctx* ctx) {
     DevBuf* all[] = {&ctx->pool, &ctx->colors, &ctx->regionsA, &ctx->regionsB, &ctx->childLen, &ctx->childOff, &ctx->childFlag, &ctx->childIdx,
                      &ctx->scanTemp, &ctx->candOfMpu, &ctx->scalars, &ctx->fv, &ctx->vcount, &ctx->tcount, &ctx->vbase, &ctx->tbase,
                      &ctx->edgeMask, &ctx->edgePrefix, &ctx->mixedList, &ctx->mixedFlag, &ctx->mixedIdx, &ctx->counters, &ctx->statsAcc,
-                     &ctx->pos, &ctx->nrm, &ctx->col, &ctx->tri, &ctx->mpuIjk, &ctx->mpuVbase, &ctx->mpuTbase, &ctx->ptsIn, &ctx->ptsF,
+                     &ctx->pos, &ctx->nrm, &ctx->col, &ctx->tri, &ctx->mpuIjk, &ctx->mpuVbase, &ctx->mpuTbase, &ctx->vperm, &ctx->ptsIn, &ctx->ptsF,
                      &ctx->ptsCol, &ctx->ptsNrm};
     for (DevBuf* b : all) b->release();
     for (auto& e : ctx->ev) cudaEventDestroy(e);
@@ -162,7 +162,7 @@ int fill_grid(psgpu_ctx* ctx, const psgpu_params* P, GridParams& G) {
     G.cellsize = P->cellsize;
     G.mpuSide = P->cellsize * (float)PS_CELLS_PER_MPU;
     G.coordMode = P->coord_mode; G.sem = ctx->semantics; G.output = P->output; G.rootMode = P->root_mode;
-    G.rootIters = P->root_iterations > 0 ? P->root_iterations : (P->root_mode == PSGPU_ROOT_NEWTON_REF ? 8 : 20);
+    G.rootIters = P->root_iterations > 0 ? P->root_iterations : (P->root_mode == PSGPU_ROOT_NEWTON_REF ? 8 : 4);
     G.insideGE = (ctx->semantics == PSGPU_SEM_SIMD) ? 1 : 0;
     G.wantColors = P->want_colors; G.wantNormals = P->want_normals;
     G.forceFv = 0;
@@ -329,15 +329,17 @@ int polygonize_impl(psgpu_ctx* ctx, const psgpu_params* P, psgpu_mesh* out, bool
             CK(ctx->mpuTbase.reserve(((size_t)nMixed + 1) * 4));
             mo.mixedIdx = ctx->mixedIdx.as<uint32_t>(); mo.mpuIjk = ctx->mpuIjk.as<int32_t>();
             mo.mpuVbase = ctx->mpuVbase.as<uint32_t>(); mo.mpuTbase = ctx->mpuTbase.as<uint32_t>();
+            CK(ctx->vperm.reserve(std::max((size_t)nV, (size_t)1) * 2));
+            mo.vperm = ctx->vperm.as<uint16_t>();
             // closing entries of the per-MPU base tables
             CK(cudaMemcpyAsync(ctx->mpuVbase.as<uint32_t>() + nMixed, ctx->vbase.as<uint32_t>() + nCand, 4, cudaMemcpyDeviceToDevice, st));
             CK(cudaMemcpyAsync(ctx->mpuTbase.as<uint32_t>() + nMixed, ctx->tbase.as<uint32_t>() + nCand, 4, cudaMemcpyDeviceToDevice, st));
         }
         CK(cudaEventRecord(ctx->ev[3], st));
         if (nMixed > 0) {
-            launch_emit_kernel(G, ctx->cands, ctx->pool.as<float4>(), ctx->colors.as<float>(), fo, mo, ctx->candOfMpu.as<int32_t>(), (int)nMixed,
-                               maxLen, ctx->numSMs, st);
-            launches++;
+            launch_emit_kernels(G, ctx->cands, ctx->pool.as<float4>(), ctx->colors.as<float>(), fo, mo, ctx->candOfMpu.as<int32_t>(), (int)nMixed,
+                                ctx->numSMs, st);
+            launches += 2;
         }
         CK(cudaEventRecord(ctx->ev[4], st));
         if (P->collect_stats) {

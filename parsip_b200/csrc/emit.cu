@@ -1,15 +1,17 @@
-// Marching-cubes mesh emission (north-star subsystem 4): one CTA per surface-crossing MPU. The MPU's field
-// cache (2 KB) and pruned instruction list come back in through TMA bulk copies; cells are re-classified from
-// the cache, every crossing edge this MPU owns gets its root (4-sample + lerp / reference Newton / bracketed
-// secant, all re-evaluating the field), a forward-difference normal and a colour, and triangles are written
-// with GLOBAL vertex indices: a vertex's index is (MPU's vertex base) + (rank of its edge bit in the MPU's
-// crossing-edge mask), so neighbouring MPUs resolve shared edges with one popcount and no hashing - the
-// deterministic replacement for the reference's per-MPU EDGETABLE (PS_Polygonizer.h:211-222, cpp:832-916).
+// Marching-cubes mesh emission (north-star subsystem 4), two kernels over the surface-crossing MPUs:
 //
-// Reference: process_cells_simd phases 2-4 (PS_SimdPoly/include/PS_Polygonizer.cpp:612-829),
-// doMarchingCubes + ComputeRootNewtonRaphsonVEC4 (ParsipHaptics/include/CPolyParsipOptimized.cpp:187-327,
-// CompactBlobTree.cpp:1581-1622). PSGPU_OUT_MPU reproduces the reference's per-MPU vertex/triangle ORDER
-// (first-use order of the sequential i,j,k cell loop) with a prefix sum instead of a serial loop.
+//   tri_kernel     one CTA per MPU: re-classifies the 343 cells from the field cache and writes the triangles with GLOBAL
+//                  vertex indices. A vertex's index is (MPU's vertex base) + (rank of its edge bit in the owner MPU's
+//                  crossing-edge mask), so neighbouring MPUs resolve shared edges with one popcount and no hashing - the
+//                  deterministic replacement for the reference's per-MPU EDGETABLE (PS_Polygonizer.h:211-222, cpp:832-916).
+//                  PSGPU_OUT_MPU reproduces the reference's per-MPU vertex/triangle ORDER (first use in the sequential
+//                  i,j,k cell loop) with prefix sums and leaves the rank -> reference-order permutation for vertex_kernel.
+//   vertex_kernel  one WARP per MPU, 32 crossing edges at a time (an MPU has ~50 of them, so CTA-wide loops would leave
+//                  most lanes idle): rank -> edge bit -> root (4-sample + lerp / reference Newton / bracketed section search,
+//                  all re-evaluating the field with the MPU's pruned program), forward-difference normal, colour walk.
+//
+// Reference: process_cells_simd phases 2-4 (PS_SimdPoly/include/PS_Polygonizer.cpp:612-829), doMarchingCubes +
+// ComputeRootNewtonRaphsonVEC4 (ParsipHaptics/include/CPolyParsipOptimized.cpp:187-327, CompactBlobTree.cpp:1581-1622).
 #include "device_util.cuh"
 #include "interp.cuh"
 #include "kernels.h"
@@ -20,46 +22,11 @@ namespace psgpu {
 namespace {
 
 constexpr int kThreads = 128;
-constexpr uint32_t kMaxProgCapQuads = 1024;
 
 __device__ const int8_t g_triTable[256 * 16] = PS_MC_TRITABLE_INIT;
 __constant__ uint8_t c_corner1[12] = PS_MC_CORNER1_INIT;
 __constant__ uint8_t c_edgeAxis[12] = PS_MC_EDGEAXIS_INIT;
 __constant__ uint8_t c_nTriE[256] = PS_MC_NTRI_INIT;
-
-struct __align__(16) EmitSmem {
-    float fv[512];  // TMA destination: 16-byte aligned (first member)
-    uint64_t bar;
-    uint32_t insideW[16];
-    uint32_t edgeW[48];
-    uint16_t edgeP[48];
-    uint16_t edgeVid[1536];  // PSGPU_OUT_MPU: reference-order local vertex id per edge bit
-    int8_t tri[256 * 16];
-    uint8_t cellCase[344];
-    uint32_t warpSum[4];
-    int next;
-};
-
-__device__ __forceinline__ uint32_t inside_bit(const EmitSmem& S, int idx) { return (S.insideW[idx >> 5] >> (idx & 31)) & 1u; }
-
-// exclusive block scan of one value per thread (128 threads); returns the exclusive prefix, total in `total`
-__device__ __forceinline__ uint32_t block_excl_scan(EmitSmem& S, uint32_t v, uint32_t& total) {
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    uint32_t inc = v;
-#pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-        const uint32_t a = __shfl_up_sync(0xffffffffu, inc, o);
-        if (lane >= o) inc += a;
-    }
-    __syncthreads();
-    if (lane == 31) S.warpSum[warp] = inc;
-    __syncthreads();
-    uint32_t off = 0;
-#pragma unroll
-    for (int w = 0; w < 4; w++) { if (w < warp) off += S.warpSum[w]; }
-    total = S.warpSum[0] + S.warpSum[1] + S.warpSum[2] + S.warpSum[3];
-    return inc - v + off;
-}
 
 struct EdgePos { float e1[3]; float e2a; int axis; };
 
@@ -99,32 +66,44 @@ __device__ void root_foursample(const GridParams& G, const float4* prog, const E
     p[2] = __fadd_rn(za, __fmul_rn(scale, __fsub_rn(zb, za)));
 }
 
-// Bracketed false position (Illinois) along the edge, re-evaluating the field; the bracket is guaranteed
-// because both endpoints are lattice corners whose cached values were produced by this same program.
+// Bracketed section search along the edge (native default, PSGPU_ROOT_BISECT): every round evaluates the field at the four
+// interior fifth-points of the current bracket in ONE 4-wide interpreter pass and keeps the fifth that holds the sign
+// change (x5 per round, a fixed trip count - a warp never waits for one slow lane the way per-lane false position does);
+// the root is the secant point of the final bracket. The bracket is guaranteed: both edge ends are lattice corners whose
+// cached values came from this same program. 4 rounds: bracket 1.6e-3 cell, secant error far below 1e-4 cell.
 template <bool STRICT>
-__device__ void root_bisect(const GridParams& G, const float4* prog, const EdgePos& E, float f1, float f2, int iters, float (&p)[3]) {
+__device__ void root_section(const GridParams& G, const float4* prog, const EdgePos& E, float f1, float f2, int rounds, float (&p)[3]) {
     float ta = 0.f, tb = 1.f, fa = f1 - G.iso, fb = f2 - G.iso;
     const float d = E.e2a - E.e1[E.axis];
-    float t = 0.5f;
-    int side = 0;
-    bool bisect = false;  // forced when the last step failed to halve the bracket (creases of CSG fields, flat tails)
-    int slow = 0;         // after two such steps the rest is plain bisection: 2^-k guaranteed
-    for (int it = 0; it < iters; it++) {
-        const float den = fa - fb, w0 = tb - ta;
-        t = (!bisect && den != 0.f) ? ta + w0 * (fa / den) : 0.5f * (ta + tb);
-        if (!(t > ta && t < tb)) t = 0.5f * (ta + tb);
-        float X[1] = {E.e1[0]}, Y[1] = {E.e1[1]}, Z[1] = {E.e1[2]}, F[1];
-        const float moved = fmaf(t, d, E.e1[E.axis]);
-        if (E.axis == 0) X[0] = moved; else if (E.axis == 1) Y[0] = moved; else Z[0] = moved;
-        eval_program<1, false, STRICT>(prog, X, Y, Z, F, nullptr, nullptr, G.sem);
-        const float ft = F[0] - G.iso;
-        if (fabsf(ft) < 1e-6f) break;
-        if ((ft < 0.f) == (fa < 0.f)) { ta = t; fa = ft; if (side == -1) fb *= 0.5f; side = -1; }
-        else { tb = t; fb = ft; if (side == 1) fa *= 0.5f; side = 1; }
-        if ((tb - ta) > 0.5f * w0) slow++;
-        bisect = (tb - ta) > 0.5f * w0 || slow >= 2;
-        if (tb - ta < 1e-6f) break;
+    const bool aIn = is_inside(G, f1);
+    for (int it = 0; it < rounds; it++) {
+        const float w = (tb - ta) * 0.2f;
+        float X[4], Y[4], Z[4], F[4], T[4];
+#pragma unroll
+        for (int l = 0; l < 4; l++) {
+            T[l] = fmaf((float)(l + 1), w, ta);
+            const float moved = fmaf(T[l], d, E.e1[E.axis]);
+            X[l] = (E.axis == 0) ? moved : E.e1[0];
+            Y[l] = (E.axis == 1) ? moved : E.e1[1];
+            Z[l] = (E.axis == 2) ? moved : E.e1[2];
+        }
+        eval_program<4, false, STRICT>(prog, X, Y, Z, F, nullptr, nullptr, G.sem);
+        // first sample on the far side of the surface closes the bracket; the one before it opens it
+        float nta = ta, nfa = fa, ntb = tb, nfb = fb;
+        bool found = false;
+#pragma unroll
+        for (int l = 0; l < 4; l++) {
+            const bool in = is_inside(G, F[l]);
+            if (!found) {
+                if (in == aIn) { nta = T[l]; nfa = F[l] - G.iso; }
+                else { ntb = T[l]; nfb = F[l] - G.iso; found = true; }
+            }
+        }
+        ta = nta; fa = nfa; tb = ntb; fb = nfb;
     }
+    const float den = fa - fb;
+    float t = (den != 0.f) ? ta + (tb - ta) * (fa / den) : 0.5f * (ta + tb);
+    t = fminf(fmaxf(t, ta), tb);
     p[0] = E.e1[0]; p[1] = E.e1[1]; p[2] = E.e1[2];
     p[E.axis] = fmaf(t, d, E.e1[E.axis]);
 }
@@ -150,18 +129,47 @@ __device__ void root_newton_ref(const GridParams& G, const float4* prog, const E
     p[0] = x[0]; p[1] = x[1]; p[2] = x[2];
 }
 
-template <bool STRICT>
-__global__ void __launch_bounds__(kThreads) emit_kernel(GridParams G, const Region* __restrict__ cands, const float4* __restrict__ pool,
-                                                        const float* __restrict__ colorTab, FieldOutputs fo, MeshOutputs mo,
-                                                        const int32_t* __restrict__ candOfMpu, int nMixed, uint32_t capQuads) {
-    extern __shared__ __align__(16) unsigned char smemRaw[];
-    EmitSmem& S = *reinterpret_cast<EmitSmem*>(smemRaw);
-    float4* progBuf = reinterpret_cast<float4*>(smemRaw + sizeof(EmitSmem));
+// ---------------------------------------------------------------------------------------------------------------------
+// tri_kernel
+// ---------------------------------------------------------------------------------------------------------------------
+struct __align__(16) TriSmem {
+    uint32_t insideW[16];
+    uint32_t edgeW[48];
+    uint16_t edgeP[48];
+    uint16_t edgeVid[1536];  // PSGPU_OUT_MPU: reference-order local vertex id per edge bit
+    int8_t tri[256 * 16];
+    uint8_t cellCase[344];
+    uint32_t warpSum[4];
+    int next;
+};
+
+__device__ __forceinline__ uint32_t inside_bit(const TriSmem& S, int idx) { return (S.insideW[idx >> 5] >> (idx & 31)) & 1u; }
+
+// exclusive block scan of one value per thread (128 threads); returns the exclusive prefix, total in `total`
+__device__ __forceinline__ uint32_t block_excl_scan(TriSmem& S, uint32_t v, uint32_t& total) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    uint32_t inc = v;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const uint32_t a = __shfl_up_sync(0xffffffffu, inc, o);
+        if (lane >= o) inc += a;
+    }
+    __syncthreads();
+    if (lane == 31) S.warpSum[warp] = inc;
+    __syncthreads();
+    uint32_t off = 0;
+#pragma unroll
+    for (int w = 0; w < 4; w++) { if (w < warp) off += S.warpSum[w]; }
+    total = S.warpSum[0] + S.warpSum[1] + S.warpSum[2] + S.warpSum[3];
+    return inc - v + off;
+}
+
+__global__ void __launch_bounds__(kThreads) tri_kernel(GridParams G, const Region* __restrict__ cands, FieldOutputs fo, MeshOutputs mo,
+                                                       const int32_t* __restrict__ candOfMpu, int nMixed) {
+    __shared__ TriSmem S;
     const int t = threadIdx.x;
     for (int i = t; i < 256 * 16; i += kThreads) S.tri[i] = g_triTable[i];
-    if (t == 0) { mbar_init(&S.bar, 1); fence_mbar_init(); }
     __syncthreads();
-    uint32_t phase = 0;
     const bool perMpu = (G.output == PSGPU_OUT_MPU);
     const int ny = G.hi[1] - G.lo[1], nz = G.hi[2] - G.lo[2];
 
@@ -169,24 +177,13 @@ __global__ void __launch_bounds__(kThreads) emit_kernel(GridParams G, const Regi
     while (m < nMixed) {
         const uint32_t cand = fo.mixedList[m];
         const Region r = cands[cand];
-        const bool staged = r.len <= capQuads;
-        if (t == 0) {
-            S.next = (int)atomicAdd(&fo.counters[3], 1u) + (int)gridDim.x;
-            fence_proxy_async();
-            mbar_expect_tx(&S.bar, 2048u + (staged ? r.len * 16u : 0u));
-            tma_load_bulk(S.fv, fo.fv + (size_t)cand * 128, 2048u, &S.bar);
-            if (staged) tma_load_bulk(progBuf, pool + r.off, r.len * 16u, &S.bar);
-        }
+        if (t == 0) S.next = (int)atomicAdd(&fo.counters[3], 1u) + (int)gridDim.x;
         if (t < 16) S.insideW[t] = 0u;
         if (t < 48) { S.edgeW[t] = fo.edgeMask[(size_t)cand * 48 + t]; S.edgeP[t] = fo.edgePrefix[(size_t)cand * 48 + t]; }
         const uint32_t vbase = mo.vbase[cand], tbase = mo.tbase[cand];
-        const uint32_t nV = fo.vcount[cand];
-        mbar_wait(&S.bar, phase);
-        phase ^= 1u;
+        const float4 f4 = fo.fv[(size_t)cand * 128 + t];
         __syncthreads();
-        const float4* prog = staged ? progBuf : pool + r.off;
         {
-            const float4 f4 = reinterpret_cast<const float4*>(S.fv)[t];
             const uint32_t in4 = (is_inside(G, f4.x) ? 1u : 0u) | (is_inside(G, f4.y) ? 2u : 0u) | (is_inside(G, f4.z) ? 4u : 0u) |
                                  (is_inside(G, f4.w) ? 8u : 0u);
             atomicOr(&S.insideW[t >> 3], in4 << ((t & 7) * 4));
@@ -239,46 +236,16 @@ __global__ void __launch_bounds__(kThreads) emit_kernel(GridParams G, const Regi
                         const int e = row[k];
                         const int c1 = c_corner1[e], ax = c_edgeAxis[e];
                         const int sx = cx + ((c1 >> 2) & 1), sy = cy + ((c1 >> 1) & 1), sz = cz + (c1 & 1);
-                        S.edgeVid[(sx * 8 + sy * 64 + sz) * 3 + ax] = (uint16_t)id;
+                        const int eb = (sx * 8 + sy * 64 + sz) * 3 + ax;
+                        S.edgeVid[eb] = (uint16_t)id;
+                        // rank of this edge in the MPU's crossing-edge mask -> where vertex_kernel must put its vertex
+                        const uint32_t rank = S.edgeP[eb >> 5] + __popc(S.edgeW[eb >> 5] & ((1u << (eb & 31)) - 1u));
+                        mo.vperm[vbase + rank] = (uint16_t)id;
                         id++;
                     }
                 }
             }
             __syncthreads();
-        }
-
-        // ---- vertices: rank -> edge bit -> root, normal, colour
-        for (uint32_t rk = t; rk < nV; rk += kThreads) {
-            int lo = 0, hi = 47;  // last word whose exclusive prefix <= rk
-            while (lo < hi) {
-                const int mid = (lo + hi + 1) >> 1;
-                if (S.edgeP[mid] <= rk) lo = mid; else hi = mid - 1;
-            }
-            const int bit = __fns(S.edgeW[lo], 0, (int)(rk - S.edgeP[lo]) + 1);
-            const int e = lo * 32 + bit;
-            const int corner = e / 3, axis = e - corner * 3;
-            const int ck = corner & 7, ci = (corner >> 3) & 7, cj = corner >> 6;
-            const EdgePos E = edge_endpoints(G, r, ci, cj, ck, axis);
-            const float f1 = S.fv[corner], f2 = S.fv[corner + (axis == 0 ? 8 : (axis == 1 ? 64 : 1))];
-            float p[3];
-            if (G.rootMode == PSGPU_ROOT_FOURSAMPLE) root_foursample<STRICT>(G, prog, E, p);
-            else if (G.rootMode == PSGPU_ROOT_NEWTON_REF) root_newton_ref<STRICT>(G, prog, E, f1, f2, G.rootIters, p);
-            else root_bisect<STRICT>(G, prog, E, f1, f2, G.rootIters, p);
-            const size_t vo = (size_t)(vbase + (perMpu ? (uint32_t)S.edgeVid[e] : rk)) * 3;
-            mo.pos[vo] = p[0]; mo.pos[vo + 1] = p[1]; mo.pos[vo + 2] = p[2];
-            if (G.wantColors || G.wantNormals) {
-                const float dl = PS_NORMAL_DELTA;
-                float X[4] = {p[0], p[0] + dl, p[0], p[0]}, Y[4] = {p[1], p[1], p[1] + dl, p[1]}, Z[4] = {p[2], p[2], p[2], p[2] + dl};
-                float F[4], rgb[3];
-                eval_program<4, true, STRICT>(prog, X, Y, Z, F, rgb, colorTab, G.sem);
-                const float dinv = -1.0f / dl;
-                float nx = (F[1] - F[0]) * dinv, nyv = (F[2] - F[0]) * dinv, nzv = (F[3] - F[0]) * dinv;
-                const float l2 = nx * nx + nyv * nyv + nzv * nzv;
-                if (l2 > 0.f) { const float il = rsqrtf(l2); nx *= il; nyv *= il; nzv *= il; }
-                else if (G.sem == PSGPU_SEM_SCALAR) { nx = nyv = nzv = 1.0f; }  // normalizeXYZ, PS_Vector.h:1072-1086
-                mo.nrm[vo] = nx; mo.nrm[vo + 1] = nyv; mo.nrm[vo + 2] = nzv;
-                mo.col[vo] = rgb[0]; mo.col[vo + 1] = rgb[1]; mo.col[vo + 2] = rgb[2];
-            }
         }
 
         // ---- triangles in cell order
@@ -329,30 +296,96 @@ __global__ void __launch_bounds__(kThreads) emit_kernel(GridParams G, const Regi
     }
 }
 
+// ---------------------------------------------------------------------------------------------------------------------
+// vertex_kernel: persistent warps, one surface MPU per warp at a time
+// ---------------------------------------------------------------------------------------------------------------------
+template <bool STRICT>
+__global__ void __launch_bounds__(kThreads) vertex_kernel(GridParams G, const Region* __restrict__ cands, const float4* __restrict__ pool,
+                                                          const float* __restrict__ colorTab, FieldOutputs fo, MeshOutputs mo, int nMixed) {
+    __shared__ uint32_t sW[kThreads / 32][48];
+    __shared__ uint32_t sP[kThreads / 32][48];
+    const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+    const bool perMpu = (G.output == PSGPU_OUT_MPU);
+    const int warpsTotal = gridDim.x * (kThreads / 32);
+    int m = blockIdx.x * (kThreads / 32) + wib;  // first item is static, the rest come from the work counter
+    while (m < nMixed) {
+        const uint32_t cand = fo.mixedList[m];
+        const Region r = cands[cand];
+        const uint32_t vbase = mo.vbase[cand];
+        const uint32_t nV = fo.vcount[cand];
+        __syncwarp();
+        sW[wib][lane] = fo.edgeMask[(size_t)cand * 48 + lane];
+        sP[wib][lane] = fo.edgePrefix[(size_t)cand * 48 + lane];
+        if (lane < 16) {
+            sW[wib][32 + lane] = fo.edgeMask[(size_t)cand * 48 + 32 + lane];
+            sP[wib][32 + lane] = fo.edgePrefix[(size_t)cand * 48 + 32 + lane];
+        }
+        __syncwarp();
+        const float4* prog = pool + r.off;  // warp-uniform addresses: one L1-resident broadcast per quad
+        const float* fv = reinterpret_cast<const float*>(fo.fv + (size_t)cand * 128);
+        for (uint32_t rk = lane; rk < nV; rk += 32) {
+            int lo = 0, hi = 47;  // last word whose exclusive prefix <= rk
+            while (lo < hi) {
+                const int mid = (lo + hi + 1) >> 1;
+                if (sP[wib][mid] <= rk) lo = mid; else hi = mid - 1;
+            }
+            const int bit = __fns(sW[wib][lo], 0, (int)(rk - sP[wib][lo]) + 1);
+            const int e = lo * 32 + bit;
+            const int corner = e / 3, axis = e - corner * 3;
+            const int ck = corner & 7, ci = (corner >> 3) & 7, cj = corner >> 6;
+            const EdgePos E = edge_endpoints(G, r, ci, cj, ck, axis);
+            float p[3];
+            if (G.rootMode == PSGPU_ROOT_FOURSAMPLE) root_foursample<STRICT>(G, prog, E, p);
+            else {
+                const float f1 = fv[corner], f2 = fv[corner + (axis == 0 ? 8 : (axis == 1 ? 64 : 1))];
+                if (G.rootMode == PSGPU_ROOT_NEWTON_REF) root_newton_ref<STRICT>(G, prog, E, f1, f2, G.rootIters, p);
+                else root_section<STRICT>(G, prog, E, f1, f2, G.rootIters, p);
+            }
+            const size_t vo = (size_t)(vbase + (perMpu ? (uint32_t)mo.vperm[vbase + rk] : rk)) * 3;
+            mo.pos[vo] = p[0]; mo.pos[vo + 1] = p[1]; mo.pos[vo + 2] = p[2];
+            if (G.wantColors || G.wantNormals) {
+                const float dl = PS_NORMAL_DELTA;
+                float X[4] = {p[0], p[0] + dl, p[0], p[0]}, Y[4] = {p[1], p[1], p[1] + dl, p[1]}, Z[4] = {p[2], p[2], p[2], p[2] + dl};
+                float F[4], rgb[3];
+                eval_program<4, true, STRICT>(prog, X, Y, Z, F, rgb, colorTab, G.sem);
+                const float dinv = -1.0f / dl;
+                float nx = (F[1] - F[0]) * dinv, nyv = (F[2] - F[0]) * dinv, nzv = (F[3] - F[0]) * dinv;
+                const float l2 = nx * nx + nyv * nyv + nzv * nzv;
+                if (l2 > 0.f) { const float il = rsqrtf(l2); nx *= il; nyv *= il; nzv *= il; }
+                else if (G.sem == PSGPU_SEM_SCALAR) { nx = nyv = nzv = 1.0f; }  // normalizeXYZ, PS_Vector.h:1072-1086
+                mo.nrm[vo] = nx; mo.nrm[vo + 1] = nyv; mo.nrm[vo + 2] = nzv;
+                mo.col[vo] = rgb[0]; mo.col[vo + 1] = rgb[1]; mo.col[vo + 2] = rgb[2];
+            }
+        }
+        int nxt = 0;
+        if (lane == 0) nxt = (int)atomicAdd(&fo.counters[4], 1u) + warpsTotal;
+        m = __shfl_sync(0xffffffffu, nxt, 0);
+    }
+}
+
 }  // namespace
 
-void launch_emit_kernel(const GridParams& G, const Region* cands, const float4* pool, const float* colorTab, const FieldOutputs& fo,
-                        const MeshOutputs& mo, const int32_t* candOfMpu, int nMixed, uint32_t maxProgQuads, int numSMs, cudaStream_t st) {
+void launch_emit_kernels(const GridParams& G, const Region* cands, const float4* pool, const float* colorTab, const FieldOutputs& fo,
+                         const MeshOutputs& mo, const int32_t* candOfMpu, int nMixed, int numSMs, cudaStream_t st) {
     if (nMixed <= 0) return;
-    uint32_t cap = maxProgQuads < 8 ? 8 : maxProgQuads;
-    if (cap > kMaxProgCapQuads) cap = kMaxProgCapQuads;
-    cap = (cap + 7u) & ~7u;
-    const int smem = (int)(sizeof(EmitSmem) + cap * 16u);
-    const bool strict = (G.sem == PSGPU_SEM_SIMD);
-    static int configured[2] = {-1, -1};
-    if (smem > configured[strict]) {
-        if (strict) cudaFuncSetAttribute(emit_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
-        else cudaFuncSetAttribute(emit_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
-        configured[strict] = smem;
+    {
+        int perSM = 0;
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSM, tri_kernel, kThreads, 0);
+        if (perSM < 1) perSM = 1;
+        int grid = numSMs * perSM;
+        if (grid > nMixed) grid = nMixed;
+        tri_kernel<<<grid, kThreads, 0, st>>>(G, cands, fo, mo, candOfMpu, nMixed);
     }
+    const bool strict = (G.sem == PSGPU_SEM_SIMD);
     int perSM = 0;
-    if (strict) cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSM, emit_kernel<true>, kThreads, smem);
-    else cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSM, emit_kernel<false>, kThreads, smem);
+    if (strict) cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSM, vertex_kernel<true>, kThreads, 0);
+    else cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSM, vertex_kernel<false>, kThreads, 0);
     if (perSM < 1) perSM = 1;
     int grid = numSMs * perSM;
-    if (grid > nMixed) grid = nMixed;
-    if (strict) emit_kernel<true><<<grid, kThreads, smem, st>>>(G, cands, pool, colorTab, fo, mo, candOfMpu, nMixed, cap);
-    else emit_kernel<false><<<grid, kThreads, smem, st>>>(G, cands, pool, colorTab, fo, mo, candOfMpu, nMixed, cap);
+    const int need = (nMixed + kThreads / 32 - 1) / (kThreads / 32);
+    if (grid > need) grid = need;
+    if (strict) vertex_kernel<true><<<grid, kThreads, 0, st>>>(G, cands, pool, colorTab, fo, mo, nMixed);
+    else vertex_kernel<false><<<grid, kThreads, 0, st>>>(G, cands, pool, colorTab, fo, mo, nMixed);
 }
 
 }  // namespace psgpu

@@ -46,7 +46,7 @@ struct FieldOutputs {
     uint32_t* edgeMask;    // [cand][48] crossing-edge bits, bit e = (i*8 + j*64 + k)*3 + axis
     uint16_t* edgePrefix;  // [cand][48] exclusive popcount prefix
     uint32_t* mixedList;   // candidates with triangles (arrival order)
-    uint32_t* counters;    // [0] work counter, [1] mixed count, [2] over-capacity MPUs, [3] emit work counter
+    uint32_t* counters;    // [0] field work counter, [1] mixed count, [2] over-capacity MPUs, [3] tri work counter, [4] vertex work counter
 };
 
 struct MeshOutputs {
@@ -55,6 +55,7 @@ struct MeshOutputs {
     const uint32_t* tbase;   // [cand]
     const uint32_t* mixedIdx;  // [cand] rank among mixed candidates (PSGPU_OUT_MPU tables), may be null
     int32_t* mpuIjk; uint32_t* mpuVbase; uint32_t* mpuTbase;
+    uint16_t* vperm;           // PSGPU_OUT_MPU: [vertex base + edge rank] -> reference-order local vertex id
 };
 
 // cull.cu
@@ -80,8 +81,8 @@ void launch_program_stats(const Region* cands, int nCand, const float4* pool, co
 float run_fp32_peak(int numSMs, cudaStream_t st, float* ms_out);
 
 // emit.cu
-void launch_emit_kernel(const GridParams& G, const Region* cands, const float4* pool, const float* colorTab, const FieldOutputs& fo,
-                        const MeshOutputs& mo, const int32_t* candOfMpu, int nMixed, uint32_t maxProgQuads, int numSMs, cudaStream_t st);
+void launch_emit_kernels(const GridParams& G, const Region* cands, const float4* pool, const float* colorTab, const FieldOutputs& fo,
+                         const MeshOutputs& mo, const int32_t* candOfMpu, int nMixed, int numSMs, cudaStream_t st);
 
 }  // namespace psgpu
 #endif
