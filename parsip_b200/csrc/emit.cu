@@ -53,7 +53,7 @@ __device__ void root_foursample(const GridParams& G, const float4* prog, const E
         Y[l] = (E.axis == 1) ? moved : E.e1[1];
         Z[l] = (E.axis == 2) ? moved : E.e1[2];
     }
-    eval_program<4, false, STRICT>(prog, X, Y, Z, F, nullptr, nullptr, G.sem);
+    eval_program<4, true, STRICT>(prog, X, Y, Z, F, nullptr, nullptr, G.sem, false);  // same instantiation as the colour pass
     const bool state = is_inside(G, F[0]);
     // first lane whose flag differs from lane 0, else the last one (cpp:748-755)
     const int interval = (is_inside(G, F[1]) != state) ? 1 : ((is_inside(G, F[2]) != state) ? 2 : 3);
@@ -87,7 +87,7 @@ __device__ void root_section(const GridParams& G, const float4* prog, const Edge
             Y[l] = (E.axis == 1) ? moved : E.e1[1];
             Z[l] = (E.axis == 2) ? moved : E.e1[2];
         }
-        eval_program<4, false, STRICT>(prog, X, Y, Z, F, nullptr, nullptr, G.sem);
+        eval_program<4, true, STRICT>(prog, X, Y, Z, F, nullptr, nullptr, G.sem, false);  // same instantiation as the colour pass
         // first sample on the far side of the surface closes the bracket; the one before it opens it
         float nta = ta, nfa = fa, ntb = tb, nfb = fb;
         bool found = false;
@@ -116,7 +116,7 @@ __device__ void root_newton_ref(const GridParams& G, const float4* prog, const E
     const float eps = PS_FIELDVALUE_EPSILON, inv = 1.0f / PS_FIELDVALUE_EPSILON;
     for (int it = 0; it < iters; it++) {
         float X[4] = {x[0], x[0] + eps, x[0], x[0]}, Y[4] = {x[1], x[1], x[1] + eps, x[1]}, Z[4] = {x[2], x[2], x[2], x[2] + eps}, F[4];
-        eval_program<4, false, STRICT>(prog, X, Y, Z, F, nullptr, nullptr, G.sem);
+        eval_program<4, true, STRICT>(prog, X, Y, Z, F, nullptr, nullptr, G.sem, false);  // same instantiation as the colour pass
         const float fp = F[0];
         const float gx = (F[1] - fp) * inv, gy = (F[2] - fp) * inv, gz = (F[3] - fp) * inv;
         const float dd = G.iso - fp;
@@ -299,7 +299,7 @@ __global__ void __launch_bounds__(kThreads) tri_kernel(GridParams G, const Regio
 // ---------------------------------------------------------------------------------------------------------------------
 // vertex_kernel: persistent warps, one surface MPU per warp at a time
 // ---------------------------------------------------------------------------------------------------------------------
-template <bool STRICT>
+template <bool STRICT, int ROOT>
 __global__ void __launch_bounds__(kThreads) vertex_kernel(GridParams G, const Region* __restrict__ cands, const float4* __restrict__ pool,
                                                           const float* __restrict__ colorTab, FieldOutputs fo, MeshOutputs mo, int nMixed) {
     __shared__ uint32_t sW[kThreads / 32][48];
@@ -335,10 +335,10 @@ __global__ void __launch_bounds__(kThreads) vertex_kernel(GridParams G, const Re
             const int ck = corner & 7, ci = (corner >> 3) & 7, cj = corner >> 6;
             const EdgePos E = edge_endpoints(G, r, ci, cj, ck, axis);
             float p[3];
-            if (G.rootMode == PSGPU_ROOT_FOURSAMPLE) root_foursample<STRICT>(G, prog, E, p);
+            if (ROOT == PSGPU_ROOT_FOURSAMPLE) root_foursample<STRICT>(G, prog, E, p);
             else {
                 const float f1 = fv[corner], f2 = fv[corner + (axis == 0 ? 8 : (axis == 1 ? 64 : 1))];
-                if (G.rootMode == PSGPU_ROOT_NEWTON_REF) root_newton_ref<STRICT>(G, prog, E, f1, f2, G.rootIters, p);
+                if (ROOT == PSGPU_ROOT_NEWTON_REF) root_newton_ref<STRICT>(G, prog, E, f1, f2, G.rootIters, p);
                 else root_section<STRICT>(G, prog, E, f1, f2, G.rootIters, p);
             }
             const size_t vo = (size_t)(vbase + (perMpu ? (uint32_t)mo.vperm[vbase + rk] : rk)) * 3;
@@ -377,15 +377,18 @@ void launch_emit_kernels(const GridParams& G, const Region* cands, const float4*
         tri_kernel<<<grid, kThreads, 0, st>>>(G, cands, fo, mo, candOfMpu, nMixed);
     }
     const bool strict = (G.sem == PSGPU_SEM_SIMD);
+    using KernelT = void (*)(GridParams, const Region*, const float4*, const float*, FieldOutputs, MeshOutputs, int);
+    KernelT k;
+    if (G.rootMode == PSGPU_ROOT_FOURSAMPLE) k = strict ? vertex_kernel<true, PSGPU_ROOT_FOURSAMPLE> : vertex_kernel<false, PSGPU_ROOT_FOURSAMPLE>;
+    else if (G.rootMode == PSGPU_ROOT_NEWTON_REF) k = strict ? vertex_kernel<true, PSGPU_ROOT_NEWTON_REF> : vertex_kernel<false, PSGPU_ROOT_NEWTON_REF>;
+    else k = strict ? vertex_kernel<true, PSGPU_ROOT_BISECT> : vertex_kernel<false, PSGPU_ROOT_BISECT>;
     int perSM = 0;
-    if (strict) cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSM, vertex_kernel<true>, kThreads, 0);
-    else cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSM, vertex_kernel<false>, kThreads, 0);
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSM, k, kThreads, 0);
     if (perSM < 1) perSM = 1;
     int grid = numSMs * perSM;
     const int need = (nMixed + kThreads / 32 - 1) / (kThreads / 32);
     if (grid > need) grid = need;
-    if (strict) vertex_kernel<true><<<grid, kThreads, 0, st>>>(G, cands, pool, colorTab, fo, mo, nMixed);
-    else vertex_kernel<false><<<grid, kThreads, 0, st>>>(G, cands, pool, colorTab, fo, mo, nMixed);
+    k<<<grid, kThreads, 0, st>>>(G, cands, pool, colorTab, fo, mo, nMixed);
 }
 
 }  // namespace psgpu

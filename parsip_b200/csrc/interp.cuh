@@ -76,9 +76,12 @@ __device__ __forceinline__ void xform_points(const float4* q, const float (&x)[N
 
 // Squared skeleton distance of one primitive at N points. q0 = header quad, q = following quads.
 // (Also used by the culling pass, whose bounds rest on these being distances to a set, i.e. 1-Lipschitz.)
-template <int N>
+// LINES: 0 = both line flavours (culling pass), 1 = clamped segments only (native interpreter; the unclamped line of
+// the PS_SimdPoly semantics only exists in the STRICT interpreter, prim_d2_strict) - keeps the hot loops' code small.
+template <int N, int LINES = 0>
 __device__ __forceinline__ void prim_d2(uint32_t opc, const float4 q0, const float4* __restrict__ q,
                                            const float (&x)[N], const float (&y)[N], const float (&z)[N], float (&d2o)[N]) {
+    if (LINES == 1 && opc == OPC_LINE_INF) opc = OPC_NULLPRIM;
     switch (opc) {
     case OPC_POINT: {
 #pragma unroll
@@ -97,7 +100,7 @@ __device__ __forceinline__ void prim_d2(uint32_t opc, const float4 q0, const flo
             d2o[n] = fmaf(rx, rx, fmaf(ry, ry, rz * rz));
         }
     } break;
-    case OPC_LINE_INF: {  // PS_Polygonizer.cpp:984-1011: projection not clamped
+    case OPC_LINE_INF: if (LINES != 1) {  // PS_Polygonizer.cpp:984-1011: projection not clamped
         const float4 d = q[0];
 #pragma unroll
         for (int n = 0; n < N; n++) {
@@ -253,9 +256,10 @@ __device__ __forceinline__ void prim_d2_strict(uint32_t opc, const float4 q0, co
             }
         }
     } break;
-    default:
-        prim_d2<N>(opc, q0, q, x, y, z, d2o);
-        break;
+    default: {  // OPC_NULLPRIM (segments, the native line flavour, do not occur in PS_SimdPoly programs)
+#pragma unroll
+        for (int n = 0; n < N; n++) d2o[n] = 4.0f;
+    } break;
     }
 }
 
@@ -268,7 +272,7 @@ __device__ __forceinline__ void prim_field(uint32_t opc, const float4 q0, const 
 #pragma unroll
         for (int n = 0; n < N; n++) f[n] = wyvill_strict(d2[n]);
     } else {
-        prim_d2<N>(opc, q0, q, x, y, z, d2);
+        prim_d2<N, 1>(opc, q0, q, x, y, z, d2);
 #pragma unroll
         for (int n = 0; n < N; n++) f[n] = wyvill(d2[n]);
     }
@@ -326,16 +330,21 @@ __device__ __forceinline__ void combine_color(int sem, uint32_t cmb, float tf, f
     }
 }
 
-// Evaluates the program at N points. COLOR also produces the colour at point 0.
+// Evaluates the program at N points. COLOR_T compiles the colour walk in (colour at point 0); `doColor` switches it on at
+// run time, so a kernel that needs both plain and coloured evaluations shares ONE copy of the interpreter - the hot loop of
+// two inlined copies does not fit the instruction caches (ncu: stall_no_instruction dominated the first vertex kernel).
+// STRICT (PS_SimdPoly semantics) also compiles OUT everything those programs cannot contain (warps, powers, segments), and
+// the native build drops the unclamped line / fast_pow Ricci / colour-scale opcodes.
 // `prog` may point to shared or global memory (generic address).
-template <int N, bool COLOR, bool STRICT = false>
+template <int N, bool COLOR_T, bool STRICT = false>
 __device__ void eval_program(const float4* __restrict__ prog, const float (&X)[N], const float (&Y)[N], const float (&Z)[N],
-                             float (&F)[N], float* rgb, const float* __restrict__ colorTab, int sem) {
+                             float (&F)[N], float* rgb, const float* __restrict__ colorTab, int sem, bool doColor = true) {
+    const bool COLOR = COLOR_T && doColor;
     float x[N], y[N], z[N];
     float top[N];
     float vs[PS_MAX_VALUE_STACK][N];
-    float pstk[PS_MAX_POINT_STACK][3][N];
-    float cstk[COLOR ? PS_MAX_VALUE_STACK : 1][5];
+    float pstk[STRICT ? 1 : PS_MAX_POINT_STACK][3][N];
+    float cstk[COLOR_T ? PS_MAX_VALUE_STACK : 1][5];
     float tc[3] = {0.f, 0.f, 0.f};
     float taux = 0.f;
     int sp = 0, psp = 0;
@@ -351,16 +360,14 @@ __device__ void eval_program(const float4* __restrict__ prog, const float (&X)[N
         if (opc < OPC_FIRST_NONPRIM) {
             const uint32_t cmb = PS_HDR_CMB(hdr);
             const int nq = ps_base_quads(opc);
-            float f[N];
-            if (PS_HDR_XF(hdr)) {
-                float lx[N], ly[N], lz[N];
-                xform_points<N, STRICT>(prog + pc + nq, x, y, z, lx, ly, lz);
-                prim_field<N, STRICT>(opc, q0, prog + pc + 1, lx, ly, lz, f);
-                pc += nq + 3;
-            } else {
-                prim_field<N, STRICT>(opc, q0, prog + pc + 1, x, y, z, f);
-                pc += nq;
+            float f[N], lx[N], ly[N], lz[N];
+            if (PS_HDR_XF(hdr)) xform_points<N, STRICT>(prog + pc + nq, x, y, z, lx, ly, lz);
+            else {
+#pragma unroll
+                for (int n = 0; n < N; n++) { lx[n] = x[n]; ly[n] = y[n]; lz[n] = z[n]; }
             }
+            prim_field<N, STRICT>(opc, q0, prog + pc + 1, lx, ly, lz, f);  // ONE inlined copy of the primitive switch (i-cache)
+            pc += nq + (PS_HDR_XF(hdr) ? 3 : 0);
             float pcol[3];
             if (COLOR) {
                 const uint32_t id = PS_HDR_PRIM(hdr);
@@ -387,6 +394,7 @@ __device__ void eval_program(const float4* __restrict__ prog, const float (&X)[N
             }
             continue;
         }
+        const int pcNext = pc + ps_base_quads(opc);
         switch (opc) {
         case OPC_COMBINE: {
             const uint32_t cmb = PS_HDR_CMB(hdr);
@@ -405,15 +413,13 @@ __device__ void eval_program(const float4* __restrict__ prog, const float (&X)[N
             }
 #pragma unroll
             for (int n = 0; n < N; n++) top[n] = combine_val(cmb, vs[sp][n], top[n]);
-            pc += 1;
         } break;
-        case OPC_POW: {
+        case OPC_POW: if (!STRICT) {
             if (COLOR) taux = (PS_HDR_CMB(hdr) == 1u) ? top[0] : powf(top[0], q0.y);  // raw child field / the blend's value
 #pragma unroll
             for (int n = 0; n < N; n++) top[n] = powf(top[n], q0.y);
-            pc += 1;
         } break;
-        case OPC_RICCI_SIMD: {
+        case OPC_RICCI_SIMD: if (STRICT) {
             sp--;
             if (COLOR) {
                 float vc[3] = {tc[0], tc[1], tc[2]};
@@ -423,9 +429,8 @@ __device__ void eval_program(const float4* __restrict__ prog, const float (&X)[N
             }
 #pragma unroll
             for (int n = 0; n < N; n++) top[n] = ricci_simd(vs[sp][n] + top[n], q0.y);
-            pc += 1;
         } break;
-        case OPC_CSCALE: {
+        case OPC_CSCALE: if (STRICT) {
             if (COLOR) {
                 const float w = __fsub_rn(__fmul_rn(2.0f, __fadd_rn(0.5f, top[0])), 1.0f);
                 const uint32_t cnt = __float_as_uint(q0.y);
@@ -433,25 +438,21 @@ __device__ void eval_program(const float4* __restrict__ prog, const float (&X)[N
                     tc[0] = __fmul_rn(w, tc[0]); tc[1] = __fmul_rn(w, tc[1]); tc[2] = __fmul_rn(w, tc[2]);
                 }
             }
-            pc += 1;
         } break;
         case OPC_CLAMP1: {
 #pragma unroll
             for (int n = 0; n < N; n++) top[n] = fminf(top[n], 1.0f);
-            pc += 1;
         } break;
         case OPC_DIF0: {
 #pragma unroll
             for (int n = 0; n < N; n++) top[n] = fminf(0.0f, 1.0f - top[n]);
-            pc += 1;
         } break;
-        case OPC_POPPOINT: {
+        case OPC_POPPOINT: if (!STRICT) {
             psp--;
 #pragma unroll
             for (int n = 0; n < N; n++) { x[n] = pstk[psp][0][n]; y[n] = pstk[psp][1][n]; z[n] = pstk[psp][2][n]; }
-            pc += 1;
         } break;
-        default: {  // warps and operator affine: push the point, transform it
+        default: if (!STRICT) {  // warps and operator affine: push the point, transform it
 #pragma unroll
             for (int n = 0; n < N; n++) { pstk[psp][0][n] = x[n]; pstk[psp][1][n] = y[n]; pstk[psp][2][n] = z[n]; }
             psp++;
@@ -460,7 +461,6 @@ __device__ void eval_program(const float4* __restrict__ prog, const float (&X)[N
                 xform_points<N>(prog + pc + 1, x, y, z, ox, oy, oz);
 #pragma unroll
                 for (int n = 0; n < N; n++) { x[n] = ox[n]; y[n] = oy[n]; z[n] = oz[n]; }
-                pc += 4;
             } else if (opc == OPC_TWIST) {  // CompactBlobTree.cpp:1355-1385
                 const float k = q0.y;
                 const int axis = (int)q0.z;
@@ -481,7 +481,6 @@ __device__ void eval_program(const float4* __restrict__ prog, const float (&X)[N
                         x[n] = nx; y[n] = ny;
                     }
                 }
-                pc += 1;
             } else if (opc == OPC_TAPER) {  // CompactBlobTree.cpp:1387-1462 (incl. the taperAlongZ axis mix-up)
                 const float k = q0.y;
                 const int along = (int)q0.z, taper = (int)q0.w;
@@ -493,7 +492,6 @@ __device__ void eval_program(const float4* __restrict__ prog, const float (&X)[N
                     else if (along == 1) { if (taper == 2) z[n] *= s; else x[n] *= s; }
                     else { if (taper == 2) y[n] *= s; else x[n] *= s; }
                 }
-                pc += 1;
             } else if (opc == OPC_BEND) {  // CompactBlobTree.cpp:1315-1353 (Barr bend in y/z)
                 const float k = q0.y, y0 = q0.z, left = q0.w;
                 const float4 q1 = prog[pc + 1];
@@ -508,7 +506,6 @@ __device__ void eval_program(const float4* __restrict__ prog, const float (&X)[N
                     const float nz = c * zz + kd + s * dy;
                     y[n] = ny; z[n] = nz;
                 }
-                pc += 2;
             } else {  // OPC_SHEAR, CompactBlobTree.cpp:1464-1536
                 const float k = q0.y;
                 const int along = (int)q0.z, dep = (int)q0.w;
@@ -518,10 +515,10 @@ __device__ void eval_program(const float4* __restrict__ prog, const float (&X)[N
                     else if (along == 2) z[n] += k * ((dep == 1) ? y[n] : x[n]);
                     else x[n] += k * ((dep == 2) ? z[n] : y[n]);
                 }
-                pc += 1;
             }
         } break;
         }
+        pc = pcNext;
     }
 #pragma unroll
     for (int n = 0; n < N; n++) F[n] = top[n];
