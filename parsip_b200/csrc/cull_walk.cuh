@@ -138,6 +138,12 @@ __device__ __forceinline__ void bound_combine(uint32_t cmb, float& lo, float& hi
     case CMB_MAX: lo = fmaxf(lo, vlo); hi = fmaxf(hi, vhi); break;
     case CMB_MIN: lo = fminf(lo, vlo); hi = fminf(hi, vhi); break;
     case CMB_DIF: lo = fminf(lo, 1.0f - vhi); hi = fminf(hi, 1.0f - vlo); break;
+    case CMB_RDIF: { const float a = fminf(vlo, 1.0f - hi), b = fminf(vhi, 1.0f - lo); lo = a; hi = b; } break;
+    case CMB_RSDIF: {
+        float a, b;
+        imul(vlo, vhi, 1.0f - hi, 1.0f - lo, a, b);
+        lo = a; hi = b;
+    } break;
     default: {
         float a, b;
         imul(lo, hi, 1.0f - vhi, 1.0f - vlo, a, b);
@@ -166,15 +172,30 @@ __device__ uint32_t prune_walk(const float4* __restrict__ src, const Box3& regio
     int sp = -1, wsp = 0;
     uint32_t emit = 0;
     Box3 box = region;
+    uint32_t lastHdrPos = 0xFFFFFFFFu, lastHdrVal = 0;  // header quad of the last instruction emitted (for the colour-scale bits)
+    float4 lastHdrQuad = make_float4(0.f, 0.f, 0.f, 0.f);
     auto put = [&](float4 v) { if (EMIT && emit < limit) dst[emit] = v; emit++; };
-    auto hdrquad = [&](uint32_t h) { return make_float4(__uint_as_float(h), 0.f, 0.f, 0.f); };
+    auto hdrquad = [&](uint32_t h) { lastHdrPos = 0xFFFFFFFFu; return make_float4(__uint_as_float(h), 0.f, 0.f, 0.f); };
     uint32_t lastScale = 0xFFFFFFFFu, scaleCount = 0;  // position of the trailing OPC_CSCALE quad, if emit == lastScale + 1
     auto rewind = [&](uint32_t pos) {
         emit = pos;
         if (lastScale != 0xFFFFFFFFu && lastScale >= emit) lastScale = 0xFFFFFFFFu;
+        if (lastHdrPos != 0xFFFFFFFFu && lastHdrPos >= emit) lastHdrPos = 0xFFFFFFFFu;
     };
+    // colour-scale marker on the current top entry: first into the 4 header bits of the entry's last instruction (free for the
+    // field-only passes), the overflow into an explicit OPC_CSCALE quad
     auto cscale = [&](uint32_t n) {
         if (!colorExact || n == 0) return;
+        if (lastScale + 1 != emit && lastHdrPos != 0xFFFFFFFFu && sp >= 0 && lastHdrPos >= bstart[sp] && lastHdrPos < emit) {
+            const uint32_t have = PS_HDR_CSC(lastHdrVal), room = 15u - have, take = n < room ? n : room;
+            if (take) {
+                lastHdrVal += take << 28;
+                lastHdrQuad.x = __uint_as_float(lastHdrVal);
+                if (EMIT && lastHdrPos < limit) dst[lastHdrPos] = lastHdrQuad;
+                n -= take;
+            }
+            if (n == 0) return;
+        }
         if (lastScale + 1 == emit) scaleCount += n;
         else { lastScale = emit; scaleCount = n; emit++; }
         if (EMIT && lastScale < limit) dst[lastScale] = make_float4(__uint_as_float(PS_HDR(OPC_CSCALE, 0, 0, 0)), __uint_as_float(scaleCount), 0.f, 0.f);
@@ -186,6 +207,9 @@ __device__ uint32_t prune_walk(const float4* __restrict__ src, const Box3& regio
         if (opc == OPC_END) break;
         const int nq = ps_instr_quads(hdr);
         auto copy = [&](uint32_t newHdr) {
+            const uint32_t o = PS_HDR_OPC(newHdr);
+            if (o < OPC_FIRST_NONPRIM || o == OPC_COMBINE) { lastHdrPos = emit; lastHdrVal = newHdr; lastHdrQuad = make_float4(__uint_as_float(newHdr), q0.y, q0.z, q0.w); }
+            else lastHdrPos = 0xFFFFFFFFu;
             put(make_float4(__uint_as_float(newHdr), q0.y, q0.z, q0.w));
             for (int i = 1; i < nq; i++) put(src[pc + i]);
         };
@@ -198,7 +222,8 @@ __device__ uint32_t prune_walk(const float4* __restrict__ src, const Box3& regio
                 bstart[sp] = emit; bzero[sp] = pz; blo[sp] = flo; bhi[sp] = fhi;
                 if (!pz) copy(hdr);
             } else if (bzero[sp]) {
-                if (!pz && (cmb == CMB_ADD || cmb == CMB_MAX)) {  // 0 + f, max(0, f): the primitive becomes the entry
+                if (!pz && (cmb == CMB_ADD || cmb == CMB_MAX || cmb == CMB_RDIF || cmb == CMB_RSDIF)) {
+                    // 0 + f, max(0, f), min(f, 1 - 0) (f <= 1), f * (1 - 0): the primitive becomes the entry
                     copy((hdr & ~(15u << 6)) | (CMB_PUSH << 6));
                     bzero[sp] = false; blo[sp] = flo; bhi[sp] = fhi;
                     if (cmb == CMB_ADD) cscale(1);
@@ -212,6 +237,13 @@ __device__ uint32_t prune_walk(const float4* __restrict__ src, const Box3& regio
                 } else if (cmb == CMB_DIF) {  // min(top, 1 - 0)
                     if (bhi[sp] > 1.0f) { put(hdrquad(PS_HDR(OPC_CLAMP1, 0, 0, 0))); bhi[sp] = 1.0f; blo[sp] = fminf(blo[sp], 1.0f); }
                 } else if (cmb == CMB_ADD) cscale(1);  // top + 0 (top * (1 - 0): nothing)
+                else if (cmb == CMB_RSDIF || (cmb == CMB_RDIF && bhi[sp] <= 1.0f)) {  // 0 * (1 - top), min(0, 1 - top) with top <= 1
+                    rewind(bstart[sp]); bzero[sp] = true; blo[sp] = bhi[sp] = 0.f;
+                } else if (cmb == CMB_RDIF) {  // min(0, 1 - top) can go negative
+                    put(hdrquad(PS_HDR(OPC_DIF0, 0, 0, 0)));
+                    const float a = fminf(0.f, 1.0f - bhi[sp]) - 1e-6f, b = fminf(0.f, 1.0f - blo[sp]);
+                    blo[sp] = a; bhi[sp] = b;
+                }
             } else {
                 copy(hdr);
                 bound_combine(cmb, blo[sp], bhi[sp], flo, fhi);

@@ -284,6 +284,8 @@ __device__ __forceinline__ float combine_val(uint32_t cmb, float top, float v) {
     case CMB_MAX: return fmaxf(top, v);
     case CMB_MIN: return fminf(top, v);
     case CMB_DIF: return fminf(top, 1.0f - v);
+    case CMB_RDIF: return fminf(v, 1.0f - top);
+    case CMB_RSDIF: return v * (1.0f - top);
     default: return top * (1.0f - v);  // CMB_SDIF
     }
 }
@@ -300,6 +302,9 @@ __device__ __forceinline__ void combine_color(int sem, uint32_t cmb, float tf, f
         } else if (cmb == CMB_MAX || cmb == CMB_MIN) {  // :1489-1500
             wl = (result - tf == 0.0f) ? 1.0f : 0.0f;
             wr = (result - vf == 0.0f) ? 1.0f : 0.0f;
+        } else if (cmb == CMB_RDIF || cmb == CMB_RSDIF) {  // :1502-1512 with the incoming value as the LEFT operand
+            wl = (1.0f - tf == result) ? 1.0f : 0.0f;
+            wr = (vf == result) ? 1.0f : 0.0f;
         } else {  // :1502-1512
             wl = (tf == result) ? 1.0f : 0.0f;
             wr = (1.0f - vf == result) ? 1.0f : 0.0f;
@@ -328,6 +333,12 @@ __device__ __forceinline__ void combine_color(int sem, uint32_t cmb, float tf, f
             if (cf < taux) { taux = cf; tc[0] = vc[0]; tc[1] = vc[1]; tc[2] = vc[2]; }
         }
     }
+}
+
+// PS_SimdPoly colour weight of a blend operand whose sibling was culled as all-zero (program.h: OPC_CSCALE / header bits 28..31)
+__device__ __forceinline__ void color_scale(float top0, float (&tc)[3], uint32_t cnt) {
+    const float w = __fsub_rn(__fmul_rn(2.0f, __fadd_rn(0.5f, top0)), 1.0f);
+    for (uint32_t k = 0; k < cnt; k++) { tc[0] = __fmul_rn(w, tc[0]); tc[1] = __fmul_rn(w, tc[1]); tc[2] = __fmul_rn(w, tc[2]); }
 }
 
 // Evaluates the program at N points. COLOR_T compiles the colour walk in (colour at point 0); `doColor` switches it on at
@@ -392,6 +403,7 @@ __device__ void eval_program(const float4* __restrict__ prog, const float (&X)[N
 #pragma unroll
                 for (int n = 0; n < N; n++) top[n] = combine_val(cmb, top[n], f[n]);
             }
+            if (STRICT && COLOR && PS_HDR_CSC(hdr)) color_scale(top[0], tc, PS_HDR_CSC(hdr));
             continue;
         }
         const int pcNext = pc + ps_base_quads(opc);
@@ -431,13 +443,7 @@ __device__ void eval_program(const float4* __restrict__ prog, const float (&X)[N
             for (int n = 0; n < N; n++) top[n] = ricci_simd(vs[sp][n] + top[n], q0.y);
         } break;
         case OPC_CSCALE: if (STRICT) {
-            if (COLOR) {
-                const float w = __fsub_rn(__fmul_rn(2.0f, __fadd_rn(0.5f, top[0])), 1.0f);
-                const uint32_t cnt = __float_as_uint(q0.y);
-                for (uint32_t k = 0; k < cnt; k++) {
-                    tc[0] = __fmul_rn(w, tc[0]); tc[1] = __fmul_rn(w, tc[1]); tc[2] = __fmul_rn(w, tc[2]);
-                }
-            }
+            if (COLOR) color_scale(top[0], tc, __float_as_uint(q0.y));
         } break;
         case OPC_CLAMP1: {
 #pragma unroll
@@ -518,6 +524,7 @@ __device__ void eval_program(const float4* __restrict__ prog, const float (&X)[N
             }
         } break;
         }
+        if (STRICT && COLOR && opc == OPC_COMBINE && PS_HDR_CSC(hdr)) color_scale(top[0], tc, PS_HDR_CSC(hdr));
         pc = pcNext;
     }
 #pragma unroll

@@ -195,6 +195,16 @@ struct Emitter {
             }
             std::vector<int> kids;
             gatherKids(n, type, kids);
+            if (semantics == PSGPU_SEM_SIMD && kids.size() == 2 && PSGPU_IS_PRIM(t->type[kids[0]]) && !PSGPU_IS_PRIM(t->type[kids[1]])) {
+                // op(primitive, sub-tree): the shape of ConvertToBinaryTree's right-leaning chains (CLayerManager.cpp:131-176).
+                // Evaluate the sub-tree first and fold the primitive in as the LEFT operand: one live stack entry instead of
+                // one per chain link, and bit-identical (IEEE add / max / min commute; the differences have reverse codes).
+                emit(kids[1], CMB_PUSH);
+                emitPrim(kids[0], x == CMB_DIF ? (uint32_t)CMB_RDIF : (x == CMB_SDIF ? (uint32_t)CMB_RSDIF : x));
+                for (int i = 0; i < pops; i++) { quad(PS_HDR(OPC_POPPOINT, 0, false, 0)); p->nInstr++; pdepth--; }
+                combine(cmb);
+                return;
+            }
             emit(kids[0], CMB_PUSH);
             for (size_t i = 1; i < kids.size(); i++) {
                 if (PSGPU_IS_PRIM(t->type[kids[i]])) emitPrim(kids[i], x);

@@ -6,7 +6,10 @@
 //     bits 0..5   opcode
 //     bits 6..9   combine code (how a primitive's field, or a popped sub-tree value, meets the stack top)
 //     bit  10     XF: three more quads (rows of a backward 3x4 matrix) follow the primitive's own quads
-//     bits 11..31 primitive id (index into the colour table)
+//     bits 11..27 primitive id (index into the colour table)
+//     bits 28..31 colour-scale count: after this instruction the colour walk multiplies the top colour that many times by
+//                 (2*(0.5+top)-1) - the weight a PS_SimdPoly blend gives its surviving operand when the culling pass dropped
+//                 the all-zero other one (see OPC_CSCALE, which carries counts beyond 15). Free for the field-only passes.
 //
 // Evaluation model: a value stack whose top lives in registers, and a point stack for warps. A primitive
 // evaluates the Wyvill field (1-d^2)^3 of its skeleton distance at the current point and combines it into
@@ -57,6 +60,10 @@ enum PsCombine : uint32_t {
     CMB_MIN = 3,   // intersection
     CMB_DIF = 4,   // top = min(top, 1 - v)
     CMB_SDIF = 5,  // top = top * (1 - v)
+    CMB_RDIF = 7,  // top = min(v, 1 - top)   the incoming value is the MINUEND (left operand) ...
+    CMB_RSDIF = 8, // top = v * (1 - top)     ... of a (smooth) difference whose right operand was evaluated first: lets the
+                   // linearizer walk the right-leaning chains ConvertToBinaryTree produces (op(prim, op(prim, ...))) innermost
+                   // first with ONE live stack entry, bit-identical to the reference's association (a + b == b + a in IEEE)
     CMB_RADD = 6,  // top + v like CMB_ADD; sums the POWERED children of a true Ricci blend, whose colour weights are the RAW
                    // child fields (CompactBlobTree.cpp:1186-1203), kept in the colour walk's aux slot
 };
@@ -65,8 +72,9 @@ enum PsCombine : uint32_t {
 #define PS_HDR_OPC(h) ((h) & 63u)
 #define PS_HDR_CMB(h) (((h) >> 6) & 15u)
 #define PS_HDR_XF(h) (((h) >> 10) & 1u)
-#define PS_HDR_PRIM(h) ((h) >> 11)
-#define PS_MAX_PRIMS (1u << 21)
+#define PS_HDR_PRIM(h) (((h) >> 11) & 0x1FFFFu)
+#define PS_HDR_CSC(h) ((h) >> 28)
+#define PS_MAX_PRIMS (1u << 17)
 
 // quads per instruction, without the optional XF rows
 #if defined(__CUDACC__)
@@ -109,7 +117,7 @@ static inline int ps_algorithmic_flops(uint32_t hdr) {
     }
     if (PS_HDR_OPC(hdr) < OPC_FIRST_NONPRIM && PS_HDR_OPC(hdr) != OPC_END) {
         if (PS_HDR_XF(hdr)) f += 18;
-        if (PS_HDR_CMB(hdr) != CMB_PUSH) f += (PS_HDR_CMB(hdr) >= CMB_DIF) ? 2 : 1;
+        if (PS_HDR_CMB(hdr) != CMB_PUSH) f += (PS_HDR_CMB(hdr) == CMB_DIF || PS_HDR_CMB(hdr) == CMB_SDIF || PS_HDR_CMB(hdr) >= CMB_RDIF) ? 2 : 1;
     }
     return f;
 }
