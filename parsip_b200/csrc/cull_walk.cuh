@@ -244,6 +244,7 @@ __device__ uint32_t prune_walk(const float4* __restrict__ src, const Box3& regio
                     const float a = fminf(0.f, 1.0f - bhi[sp]) - 1e-6f, b = fminf(0.f, 1.0f - blo[sp]);
                     blo[sp] = a; bhi[sp] = b;
                 }
+                if (!bzero[sp]) cscale(PS_HDR_CSC(hdr));  // markers a coarser level left on the dropped instruction stay with the entry
             } else {
                 copy(hdr);
                 bound_combine(cmb, blo[sp], bhi[sp], flo, fhi);
@@ -271,6 +272,7 @@ __device__ uint32_t prune_walk(const float4* __restrict__ src, const Box3& regio
                     if (bhi[v] <= 1.0f) rewind(bstart[t]);
                     else { put(hdrquad(PS_HDR(OPC_DIF0, 0, 0, 0))); bzero[t] = false; blo[t] = fminf(0.f, 1.0f - bhi[v]) - 1e-6f; bhi[t] = 0.f; }
                 } else rewind(bstart[t]);  // 0 * (1 - V)
+                if (!bzero[t]) cscale(PS_HDR_CSC(hdr));
             } else if (bzero[v]) {  // T (cmb) 0
                 if (cmb == CMB_MAX) {
                     if (blo[t] < 0.f) { put(hdrquad(PS_HDR(OPC_NULLPRIM, CMB_MAX, 0, 0))); blo[t] = 0.f; bhi[t] = fmaxf(bhi[t], 0.f); }
@@ -280,6 +282,7 @@ __device__ uint32_t prune_walk(const float4* __restrict__ src, const Box3& regio
                 } else if (cmb == CMB_DIF) {
                     if (bhi[t] > 1.0f) { put(hdrquad(PS_HDR(OPC_CLAMP1, 0, 0, 0))); bhi[t] = 1.0f; blo[t] = fminf(blo[t], 1.0f); }
                 } else if (cmb == CMB_ADD) cscale(1);
+                if (!bzero[t]) cscale(PS_HDR_CSC(hdr));
             } else {
                 copy(hdr);
                 bound_combine(cmb, blo[t], bhi[t], blo[v], bhi[v]);

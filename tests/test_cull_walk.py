@@ -125,3 +125,34 @@ def test_simd_colour_rule_survives_pruning():
         assert np.array_equal(c[on].view(np.uint32), full_c[on].view(np.uint32))
         checked += int(on.sum())
     assert checked > 1000 and marked > 0
+
+
+def test_simd_colour_rule_survives_two_pruning_levels():
+    """The device prunes hierarchically (region of 4x4x4 MPUs, then each MPU): markers left by the coarse level must survive
+    when the fine level drops the instruction that carried them."""
+    root = bt.binarize(scenes_small.blob())
+    prog = ps.linearize(bt.flatten(root), ps.SEM_SIMD, 0)
+    quads, colors = prog.quads(), prog.colors()
+    lo, hi = ps.prepare_bboxes(bt.flatten(root))
+    rs = np.random.RandomState(22)
+    checked = 0
+    for _ in range(60):
+        a = rs.uniform(lo, hi - 0.6, 3).astype(np.float32)
+        coarse = emu.prune(quads, a, a + np.float32(0.6), ps.CULL_SUPPORT, ISO, color_exact=True)
+        if coarse is None:
+            continue
+        for _ in range(6):
+            c = (a + rs.uniform(0, 0.45, 3)).astype(np.float32)
+            d = (c + np.float32(0.15)).astype(np.float32)
+            fine = emu.prune(coarse, c, d, ps.CULL_SUPPORT, ISO, color_exact=True)
+            pts = rs.uniform(c, d, (24, 3)).astype(np.float32)
+            full_f, full_c = emu.field_color(quads, colors, pts, ps.SEM_SIMD)
+            if fine is None:
+                assert (full_f == 0).all()
+                continue
+            f, col = emu.field_color(fine, colors, pts, ps.SEM_SIMD)
+            on = full_f > 0
+            assert np.array_equal(f.view(np.uint32), full_f.view(np.uint32))
+            assert np.array_equal(col[on].view(np.uint32), full_c[on].view(np.uint32))
+            checked += int(on.sum())
+    assert checked > 1000
