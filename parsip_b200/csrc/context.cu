@@ -338,8 +338,8 @@ int polygonize_impl(psgpu_ctx* ctx, const psgpu_params* P, psgpu_mesh* out, bool
         CK(cudaEventRecord(ctx->ev[3], st));
         if (nMixed > 0) {
             launch_emit_kernels(G, ctx->cands, ctx->pool.as<float4>(), ctx->colors.as<float>(), fo, mo, ctx->candOfMpu.as<int32_t>(), (int)nMixed,
-                                ctx->numSMs, st);
-            launches += 2;
+                                maxLen, ctx->numSMs, st);
+            launches += 2 + (G.wantColors ? 1 : 0);  // tri_kernel, vertex_kernel, color_kernel
         }
         CK(cudaEventRecord(ctx->ev[4], st));
         if (P->collect_stats) {

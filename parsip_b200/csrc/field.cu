@@ -34,8 +34,10 @@ struct __align__(16) FieldSmemHeader {
     int flags;
 };
 
-template <bool STRICT>
-__global__ void __launch_bounds__(kThreads) field_kernel(GridParams G, const Region* __restrict__ cands, int nCand,
+// STAGED: every candidate list fits the staging buffers (the host checks the longest one) and is interpreted from shared memory;
+// the unstaged variant (brute-force mode, very long lists) reads the lists from global memory. One interpreter copy per kernel.
+template <bool STRICT, bool STAGED>
+__global__ void __launch_bounds__(kThreads, 6) field_kernel(GridParams G, const Region* __restrict__ cands, int nCand,
                                                          const float4* __restrict__ pool, FieldOutputs out, uint32_t capQuads) {
     extern __shared__ __align__(16) unsigned char smemRaw[];
     FieldSmemHeader& S = *reinterpret_cast<FieldSmemHeader*>(smemRaw);
@@ -53,37 +55,29 @@ __global__ void __launch_bounds__(kThreads) field_kernel(GridParams G, const Reg
     int item = blockIdx.x;  // first item is static, the rest come from the work counter
     int stage = 0;
     uint32_t phase[2] = {0u, 0u};
-    if (t == 0 && item < nCand) {
+    if (STAGED && t == 0 && item < nCand) {
         const Region r = cands[item];
-        if (r.len <= capQuads) {
-            mbar_expect_tx(&S.bar[0], r.len * 16u);
-            tma_load_bulk(progBuf, pool + r.off, r.len * 16u, &S.bar[0]);
-        }
+        mbar_expect_tx(&S.bar[0], r.len * 16u);
+        tma_load_bulk(progBuf, pool + r.off, r.len * 16u, &S.bar[0]);
     }
     while (item < nCand) {
         // fetch and prefetch the next work item
         if (t == 0) {
             const int nxt = (int)atomicAdd(&out.counters[0], 1u) + (int)gridDim.x;
             S.next = nxt;
-            if (nxt < nCand) {
+            if (STAGED && nxt < nCand) {
                 const Region rn = cands[nxt];
-                if (rn.len <= capQuads) {
-                    fence_proxy_async();
-                    mbar_expect_tx(&S.bar[stage ^ 1], rn.len * 16u);
-                    tma_load_bulk(progBuf + (size_t)(stage ^ 1) * capQuads, pool + rn.off, rn.len * 16u, &S.bar[stage ^ 1]);
-                }
+                fence_proxy_async();
+                mbar_expect_tx(&S.bar[stage ^ 1], rn.len * 16u);
+                tma_load_bulk(progBuf + (size_t)(stage ^ 1) * capQuads, pool + rn.off, rn.len * 16u, &S.bar[stage ^ 1]);
             }
         }
         if (t < 16) S.insideW[t] = 0u;
         if (t < 48) S.edgeW[t] = 0u;
         const Region r = cands[item];
-        const float4* prog;
-        if (r.len <= capQuads) {
+        if (STAGED) {
             mbar_wait(&S.bar[stage], phase[stage]);
             phase[stage] ^= 1u;
-            prog = progBuf + (size_t)stage * capQuads;
-        } else {
-            prog = pool + r.off;
         }
 
         // ---- evaluate 4 corners: (i, j, 4*kh .. 4*kh+3)
@@ -94,7 +88,7 @@ __global__ void __launch_bounds__(kThreads) field_kernel(GridParams G, const Reg
 #pragma unroll
             for (int n = 0; n < 4; n++) { X[n] = x; Y[n] = y; Z[n] = corner_coord(G, 2, r.z, 4 * kh + n); }
         }
-        eval_program<4, false, STRICT>(prog, X, Y, Z, F, nullptr, nullptr, G.sem);
+        eval_program<4, false, STRICT, STAGED>(STAGED ? progBuf + (size_t)stage * capQuads : pool + r.off, X, Y, Z, F, nullptr, nullptr, G.sem);
         reinterpret_cast<float4*>(S.fv)[t] = make_float4(F[0], F[1], F[2], F[3]);
         uint32_t in4 = 0;
 #pragma unroll
@@ -275,23 +269,25 @@ void launch_field_kernel(const GridParams& G, const Region* cands, int nCand, co
                          int numSMs, cudaStream_t st) {
     if (nCand <= 0) return;
     uint32_t cap;
-    const int smem = field_kernel_smem_bytes(maxProgQuads, &cap);
-    if (getenv("PSGPU_NO_STAGE")) cap = 0;  // debugging aid: interpret straight from global memory
+    int smem = field_kernel_smem_bytes(maxProgQuads, &cap);
+    bool staged = (maxProgQuads <= cap);
+    if (getenv("PSGPU_NO_STAGE")) staged = false;  // debugging aid: interpret straight from global memory
+    if (!staged) { cap = 8; smem = (int)(sizeof(FieldSmemHeader) + 2u * cap * 16u); }
     const bool strict = (G.sem == PSGPU_SEM_SIMD);
-    static int configured[2] = {-1, -1};
-    if (smem > configured[strict]) {
-        if (strict) cudaFuncSetAttribute(field_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
-        else cudaFuncSetAttribute(field_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
-        configured[strict] = smem;
+    using KernelT = void (*)(GridParams, const Region*, int, const float4*, FieldOutputs, uint32_t);
+    const KernelT k = strict ? (staged ? field_kernel<true, true> : field_kernel<true, false>)
+                             : (staged ? field_kernel<false, true> : field_kernel<false, false>);
+    static int configured[2][2] = {{-1, -1}, {-1, -1}};
+    if (smem > configured[strict][staged]) {
+        cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+        configured[strict][staged] = smem;
     }
     int perSM = 0;
-    if (strict) cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSM, field_kernel<true>, kThreads, smem);
-    else cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSM, field_kernel<false>, kThreads, smem);
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSM, k, kThreads, smem);
     if (perSM < 1) perSM = 1;
     int grid = numSMs * perSM;  // persistent CTAs: a whole number of waves on 148 SMs
     if (grid > nCand) grid = nCand;
-    if (strict) field_kernel<true><<<grid, kThreads, smem, st>>>(G, cands, nCand, pool, out, cap);
-    else field_kernel<false><<<grid, kThreads, smem, st>>>(G, cands, nCand, pool, out, cap);
+    k<<<grid, kThreads, smem, st>>>(G, cands, nCand, pool, out, cap);
 }
 
 void launch_points_field(const float4* prog, const float* xyz, int64_t n, float* f, int sem, cudaStream_t st) {

@@ -290,6 +290,42 @@ __device__ __forceinline__ float combine_val(uint32_t cmb, float top, float v) {
     }
 }
 
+// out[n] = a[n] (cmb) b[n] for all N points with ONE warp-uniform dispatch (the per-point form cost one jump-table branch
+// per point: ncu r01b, BRX x4 per OPC_COMBINE). Same expressions as combine_val.
+template <int N>
+__device__ __forceinline__ void combine_n(uint32_t cmb, const float (&a)[N], const float (&b)[N], float (&out)[N]) {
+    switch (cmb) {
+    case CMB_ADD: case CMB_RADD:
+#pragma unroll
+        for (int n = 0; n < N; n++) out[n] = a[n] + b[n];
+        break;
+    case CMB_MAX:
+#pragma unroll
+        for (int n = 0; n < N; n++) out[n] = fmaxf(a[n], b[n]);
+        break;
+    case CMB_MIN:
+#pragma unroll
+        for (int n = 0; n < N; n++) out[n] = fminf(a[n], b[n]);
+        break;
+    case CMB_DIF:
+#pragma unroll
+        for (int n = 0; n < N; n++) out[n] = fminf(a[n], 1.0f - b[n]);
+        break;
+    case CMB_RDIF:
+#pragma unroll
+        for (int n = 0; n < N; n++) out[n] = fminf(b[n], 1.0f - a[n]);
+        break;
+    case CMB_RSDIF:
+#pragma unroll
+        for (int n = 0; n < N; n++) out[n] = b[n] * (1.0f - a[n]);
+        break;
+    default:  // CMB_SDIF
+#pragma unroll
+        for (int n = 0; n < N; n++) out[n] = a[n] * (1.0f - b[n]);
+        break;
+    }
+}
+
 // colour of `top (cmb) v` for point 0; (tf, tc) = stack top before the combine, (vf, vc) = incoming value.
 // taux = running min used by the scalar twin's (smooth) difference colour pick.
 __device__ __forceinline__ void combine_color(int sem, uint32_t cmb, float tf, float (&tc)[3], float& taux, float vf,
@@ -347,22 +383,27 @@ __device__ __forceinline__ void color_scale(float top0, float (&tc)[3], uint32_t
 // STRICT (PS_SimdPoly semantics) also compiles OUT everything those programs cannot contain (warps, powers, segments), and
 // the native build drops the unclamped line / fast_pow Ricci / colour-scale opcodes.
 // `prog` may point to shared or global memory (generic address).
-template <int N, bool COLOR_T, bool STRICT = false>
+template <int N, bool COLOR_T, bool STRICT = false, bool SMEM = false>
 __device__ void eval_program(const float4* __restrict__ prog, const float (&X)[N], const float (&Y)[N], const float (&Z)[N],
                              float (&F)[N], float* rgb, const float* __restrict__ colorTab, int sem, bool doColor = true) {
+    // SMEM: the program was staged into shared memory; tells the compiler so the decode path uses LDS instead of generic loads
+#ifndef PSGPU_HOST_EMULATION
+    if (SMEM) __builtin_assume(__isShared(prog));
+#endif
     const bool COLOR = COLOR_T && doColor;
     float x[N], y[N], z[N];
     float top[N];
-    float vs[PS_MAX_VALUE_STACK][N];
+    // entry 0 of the stacks is a dummy: the first PUSH stores the (unused) initial top there, so PUSH needs no "first" test
+    float vs[PS_MAX_VALUE_STACK + 1][N];
     float pstk[STRICT ? 1 : PS_MAX_POINT_STACK][3][N];
-    float cstk[COLOR_T ? PS_MAX_VALUE_STACK : 1][5];
+    float xsave[3][N];  // the world-space points while a primitive with its own matrix is evaluated (local memory, rare path)
+    float cstk[COLOR_T ? PS_MAX_VALUE_STACK + 1 : 1][5];
     float tc[3] = {0.f, 0.f, 0.f};
     float taux = 0.f;
     int sp = 0, psp = 0;
 #pragma unroll
     for (int n = 0; n < N; n++) { x[n] = X[n]; y[n] = Y[n]; z[n] = Z[n]; top[n] = 0.0f; }
     int pc = 0;
-    bool first = true;
     for (;;) {
         const float4 q0 = prog[pc];
         const uint32_t hdr = __float_as_uint(q0.x);
@@ -371,37 +412,39 @@ __device__ void eval_program(const float4* __restrict__ prog, const float (&X)[N
         if (opc < OPC_FIRST_NONPRIM) {
             const uint32_t cmb = PS_HDR_CMB(hdr);
             const int nq = ps_base_quads(opc);
-            float f[N], lx[N], ly[N], lz[N];
-            if (PS_HDR_XF(hdr)) xform_points<N, STRICT>(prog + pc + nq, x, y, z, lx, ly, lz);
-            else {
+            const bool xf = PS_HDR_XF(hdr) != 0u;
+            float f[N];
+            if (xf) {  // evaluate in the primitive's local frame, then restore the points (in place: the common path has no copies)
+                float lx[N], ly[N], lz[N];
+                xform_points<N, STRICT>(prog + pc + nq, x, y, z, lx, ly, lz);
 #pragma unroll
-                for (int n = 0; n < N; n++) { lx[n] = x[n]; ly[n] = y[n]; lz[n] = z[n]; }
+                for (int n = 0; n < N; n++) { xsave[0][n] = x[n]; xsave[1][n] = y[n]; xsave[2][n] = z[n]; x[n] = lx[n]; y[n] = ly[n]; z[n] = lz[n]; }
             }
-            prim_field<N, STRICT>(opc, q0, prog + pc + 1, lx, ly, lz, f);  // ONE inlined copy of the primitive switch (i-cache)
-            pc += nq + (PS_HDR_XF(hdr) ? 3 : 0);
+            prim_field<N, STRICT>(opc, q0, prog + pc + 1, x, y, z, f);  // ONE inlined copy of the primitive switch (i-cache)
+            if (xf) {
+#pragma unroll
+                for (int n = 0; n < N; n++) { x[n] = xsave[0][n]; y[n] = xsave[1][n]; z[n] = xsave[2][n]; }
+            }
+            pc += nq + (xf ? 3 : 0);
             float pcol[3];
             if (COLOR) {
                 const uint32_t id = PS_HDR_PRIM(hdr);
                 pcol[0] = colorTab[id * 3]; pcol[1] = colorTab[id * 3 + 1]; pcol[2] = colorTab[id * 3 + 2];
             }
             if (cmb == CMB_PUSH) {
-                if (!first) {
 #pragma unroll
-                    for (int n = 0; n < N; n++) vs[sp][n] = top[n];
-                    if (COLOR) { cstk[sp][0] = tc[0]; cstk[sp][1] = tc[1]; cstk[sp][2] = tc[2]; cstk[sp][3] = taux; }
-                    sp++;
+                for (int n = 0; n < N; n++) { vs[sp][n] = top[n]; top[n] = f[n]; }
+                if (COLOR) {
+                    cstk[sp][0] = tc[0]; cstk[sp][1] = tc[1]; cstk[sp][2] = tc[2]; cstk[sp][3] = taux;
+                    tc[0] = pcol[0]; tc[1] = pcol[1]; tc[2] = pcol[2]; taux = f[0];
                 }
-                first = false;
-#pragma unroll
-                for (int n = 0; n < N; n++) top[n] = f[n];
-                if (COLOR) { tc[0] = pcol[0]; tc[1] = pcol[1]; tc[2] = pcol[2]; taux = f[0]; }
+                sp++;
             } else {
                 if (COLOR) {
                     const float r0 = combine_val(cmb, top[0], f[0]);
                     combine_color(sem, cmb, top[0], tc, taux, f[0], pcol, r0);
                 }
-#pragma unroll
-                for (int n = 0; n < N; n++) top[n] = combine_val(cmb, top[n], f[n]);
+                combine_n<N>(cmb, top, f, top);
             }
             if (STRICT && COLOR && PS_HDR_CSC(hdr)) color_scale(top[0], tc, PS_HDR_CSC(hdr));
             continue;
@@ -423,8 +466,12 @@ __device__ void eval_program(const float4* __restrict__ prog, const float (&X)[N
                     combine_color(sem, CMB_ADD, taux, tc, taux, vaux, vc, ssum);
                 } else combine_color(sem, cmb, tf, tc, taux, vf, vc, r0);
             }
+            {
+                float lhs[N];
 #pragma unroll
-            for (int n = 0; n < N; n++) top[n] = combine_val(cmb, vs[sp][n], top[n]);
+                for (int n = 0; n < N; n++) lhs[n] = vs[sp][n];
+                combine_n<N>(cmb, lhs, top, top);
+            }
         } break;
         case OPC_POW: if (!STRICT) {
             if (COLOR) taux = (PS_HDR_CMB(hdr) == 1u) ? top[0] : powf(top[0], q0.y);  // raw child field / the blend's value

@@ -81,12 +81,10 @@ enum PsCombine : uint32_t {
 __host__ __device__
 #endif
 static inline int ps_base_quads(uint32_t opc) {
-    switch (opc) {
-    case OPC_SEGMENT: case OPC_LINE_INF: case OPC_CUBE: case OPC_DISC: case OPC_RING: case OPC_BEND: return 2;
-    case OPC_CYLINDER: return 3;
-    case OPC_AFFINE: return 4;
-    default: return 1;
-    }
+    // 2 bits per opcode (quads - 1), opcodes 0..15 in the first word and 16..31 in the second: a shift and a mask instead of a
+    // compare chain in the interpreters' decode path. SEGMENT, LINE_INF, CUBE, DISC, RING, BEND = 2; CYLINDER = 3; AFFINE = 4.
+    const uint32_t k = (opc < 16u) ? 0x00005650u : 0x03100000u;
+    return 1 + (int)((k >> (2u * (opc & 15u))) & 3u);
 }
 #if defined(__CUDACC__)
 __host__ __device__
