@@ -52,6 +52,7 @@ struct psgpu_ctx {
     int nPrims = 0;
     int semantics = PSGPU_SEM_SCALAR;
     DevBuf pool;      // float4: [full program | level 0 programs | level 1 programs | ...]
+    DevBuf qflag;     // one byte per pool quad: 1 = first quad of an instruction (read by the warp-cooperative pruning passes)
     DevBuf colors;
     // cull scratch
     DevBuf regionsA, regionsB, childLen, childOff, childFlag, childIdx, scanTemp, candOfMpu, scalars;
@@ -105,7 +106,7 @@ extern "C" int psgpu_destroy(psgpu_ctx* ctx) {
     if (!ctx) return PSGPU_PARAM_ERROR;
     cudaSetDevice(ctx->device);
     cudaStreamSynchronize(ctx->stream);
-    DevBuf* all[] = {&ctx->pool, &ctx->colors, &ctx->regionsA, &ctx->regionsB, &ctx->childLen, &ctx->childOff, &ctx->childFlag, &ctx->childIdx,
+    DevBuf* all[] = {&ctx->pool, &ctx->qflag, &ctx->colors, &ctx->regionsA, &ctx->regionsB, &ctx->childLen, &ctx->childOff, &ctx->childFlag, &ctx->childIdx,
                      &ctx->scanTemp, &ctx->candOfMpu, &ctx->scalars, &ctx->fv, &ctx->vcount, &ctx->tcount, &ctx->vbase, &ctx->tbase,
                      &ctx->edgeMask, &ctx->edgePrefix, &ctx->mixedList, &ctx->mixedFlag, &ctx->mixedIdx, &ctx->counters, &ctx->statsAcc,
                      &ctx->pos, &ctx->nrm, &ctx->col, &ctx->tri, &ctx->mpuIjk, &ctx->mpuVbase, &ctx->mpuTbase, &ctx->vperm, &ctx->ptsIn, &ctx->ptsF,
@@ -126,16 +127,28 @@ extern "C" int psgpu_upload_program(psgpu_ctx* ctx, const psgpu_program* p) {
     CK(cudaSetDevice(ctx->device));
     const size_t bytes = p->words.size() * 4;
     const size_t cbytes = p->colors.size() * 4;
-    if (bytes + cbytes > ctx->hostStageCap) {  // host -> device copies go through pinned memory
+    if (bytes + cbytes + bytes / 16 > ctx->hostStageCap) {  // host -> device copies go through pinned memory
         if (ctx->hostStage) cudaFreeHost(ctx->hostStage);
         ctx->hostStage = nullptr;
-        ctx->hostStageCap = (bytes + cbytes) * 2;
+        ctx->hostStageCap = (bytes + cbytes + bytes / 16) * 2;
         CK(cudaMallocHost(&ctx->hostStage, ctx->hostStageCap));
     }
     memcpy(ctx->hostStage, p->words.data(), bytes);
     if (cbytes) memcpy((char*)ctx->hostStage + bytes, p->colors.data(), cbytes);
+    // instruction-start flags of the full program, staged behind the colours
+    const size_t nQuads = p->words.size() / 4;
+    uint8_t* hflag = (uint8_t*)ctx->hostStage + bytes + cbytes;
+    memset(hflag, 0, nQuads);
+    for (size_t pc = 0; pc < nQuads;) {
+        const uint32_t hdr = p->words[pc * 4];
+        hflag[pc] = 1;
+        if (PS_HDR_OPC(hdr) == OPC_END) break;
+        pc += (size_t)ps_instr_quads(hdr);
+    }
     CK(ctx->pool.reserve(std::max(bytes * 4, (size_t)64 << 20)));
+    CK(ctx->qflag.reserve(ctx->pool.cap / 16));
     CK(cudaMemcpyAsync(ctx->pool.p, ctx->hostStage, bytes, cudaMemcpyHostToDevice, ctx->stream));
+    CK(cudaMemcpyAsync(ctx->qflag.p, hflag, nQuads, cudaMemcpyHostToDevice, ctx->stream));
     CK(ctx->colors.reserve(std::max(cbytes, (size_t)256)));
     if (cbytes) CK(cudaMemcpyAsync(ctx->colors.p, (char*)ctx->hostStage + bytes, cbytes, cudaMemcpyHostToDevice, ctx->stream));
     CK(cudaStreamSynchronize(ctx->stream));
@@ -225,7 +238,7 @@ int run_cull(psgpu_ctx* ctx, const GridParams& G, int cullMode, bool colorExact,
         const size_t tb = scan_temp_bytes(n + 1);
         CK(ctx->scanTemp.reserve(tb));
         CK(cudaMemsetAsync(ctx->childLen.as<uint32_t>() + n, 0, 4, st));
-        launch_prune_count(L, cur->as<Region>(), nParents, ctx->pool.as<float4>(), ctx->childLen.as<uint32_t>(), st);
+        launch_prune_count(L, cur->as<Region>(), nParents, ctx->pool.as<float4>(), ctx->qflag.as<uint8_t>(), ctx->childLen.as<uint32_t>(), st);
         launch_flags(ctx->childLen.as<uint32_t>(), ctx->childFlag.as<uint32_t>(), n + 1, st);
         exclusive_scan_u32(ctx->scanTemp.p, tb, ctx->childLen.as<uint32_t>(), ctx->childOff.as<uint32_t>(), n + 1, st);
         exclusive_scan_u32(ctx->scanTemp.p, tb, ctx->childFlag.as<uint32_t>(), ctx->childIdx.as<uint32_t>(), n + 1, st);
@@ -236,11 +249,13 @@ int run_cull(psgpu_ctx* ctx, const GridParams& G, int cullMode, bool colorExact,
         const uint32_t totalQuads = ctx->hostScalars[0], nChildren = ctx->hostScalars[1];
         if ((uint64_t)poolUsed + totalQuads >= ((uint64_t)1 << 32)) { ctx->err = "pruned programs exceed 2^32 quads"; return PSGPU_NOT_ENOUGH_MEM; }
         CK(ctx->pool.reserve(((size_t)poolUsed + totalQuads + 16) * 16, true, st));
+        CK(ctx->qflag.reserve((size_t)poolUsed + totalQuads + 16, true, st));
         CK(nxt->reserve(std::max((size_t)nChildren, (size_t)1) * sizeof(Region)));
         if (last) CK(cudaMemsetAsync(ctx->scalars.p, 0, 4, st));
         if (nChildren > 0) {
-            launch_prune_emit(L, cur->as<Region>(), nParents, ctx->pool.as<float4>(), ctx->childLen.as<uint32_t>(), ctx->childOff.as<uint32_t>(),
-                              ctx->childIdx.as<uint32_t>(), ctx->pool.as<float4>(), poolUsed, nxt->as<Region>(),
+            launch_prune_emit(L, cur->as<Region>(), nParents, ctx->pool.as<float4>(), ctx->qflag.as<uint8_t>(), ctx->childLen.as<uint32_t>(),
+                              ctx->childOff.as<uint32_t>(), ctx->childIdx.as<uint32_t>(), ctx->pool.as<float4>(),
+                              last ? nullptr : ctx->qflag.as<uint8_t>(), poolUsed, nxt->as<Region>(),
                               last ? ctx->candOfMpu.as<int32_t>() : nullptr, last ? ctx->scalars.as<uint32_t>() : nullptr, st);
             launches++;
         }

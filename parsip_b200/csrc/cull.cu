@@ -39,6 +39,18 @@ __device__ __forceinline__ bool child_region(const CullLevel& L, const Region& p
     return true;
 }
 
+__device__ __forceinline__ void publish_child(const CullLevel& L, const int (&coord)[3], uint32_t off, uint32_t len, uint32_t idx,
+                                              Region* __restrict__ children, int32_t* __restrict__ candOfMpu, uint32_t* __restrict__ maxLen) {
+    Region r;
+    r.x = coord[0]; r.y = coord[1]; r.z = coord[2]; r.off = off; r.len = len;
+    children[idx] = r;
+    if (maxLen) atomicMax(maxLen, len);
+    if (candOfMpu) {
+        const int ny = L.hi[1] - L.lo[1], nz = L.hi[2] - L.lo[2];
+        candOfMpu[((size_t)(coord[0] - L.lo[0]) * ny + (coord[1] - L.lo[1])) * nz + (coord[2] - L.lo[2])] = (int32_t)idx;
+    }
+}
+
 __global__ void __launch_bounds__(128) prune_count_kernel(CullLevel L, const Region* __restrict__ parents, int nParents,
                                                           const float4* __restrict__ pool, uint32_t* __restrict__ childLen) {
     const int tid = blockIdx.x * blockDim.x + threadIdx.x;
@@ -55,8 +67,9 @@ __global__ void __launch_bounds__(128) prune_count_kernel(CullLevel L, const Reg
 __global__ void __launch_bounds__(128) prune_emit_kernel(CullLevel L, const Region* __restrict__ parents, int nParents,
                                                          const float4* __restrict__ pool, const uint32_t* __restrict__ childLen,
                                                          const uint32_t* __restrict__ childOff, const uint32_t* __restrict__ childIdx,
-                                                         float4* __restrict__ outPool, uint32_t outBase, Region* __restrict__ children,
-                                                         int32_t* __restrict__ candOfMpu, uint32_t* __restrict__ maxLen) {
+                                                         float4* __restrict__ outPool, uint8_t* __restrict__ outFlag, uint32_t outBase,
+                                                         Region* __restrict__ children, int32_t* __restrict__ candOfMpu,
+                                                         uint32_t* __restrict__ maxLen) {
     const int tid = blockIdx.x * blockDim.x + threadIdx.x;
     if (tid >= nParents * 64) return;
     const uint32_t len = childLen[tid];
@@ -66,17 +79,130 @@ __global__ void __launch_bounds__(128) prune_emit_kernel(CullLevel L, const Regi
     Box3 box;
     child_region(L, parent, tid & 63, coord, box);
     const uint32_t off = outBase + childOff[tid];
-    prune_walk<true>(pool + parent.off, box, L.cullMode, L.iso, outPool + off, L.colorExact != 0, len);
-    const uint32_t idx = childIdx[tid];
-    Region r;
-    r.x = coord[0]; r.y = coord[1]; r.z = coord[2]; r.off = off; r.len = len;
-    children[idx] = r;
-    if (maxLen) atomicMax(maxLen, len);
-    if (candOfMpu) {
-        const int nx = L.hi[0] - L.lo[0], ny = L.hi[1] - L.lo[1], nz = L.hi[2] - L.lo[2];
-        (void)nx;
-        candOfMpu[((size_t)(coord[0] - L.lo[0]) * ny + (coord[1] - L.lo[1])) * nz + (coord[2] - L.lo[2])] = (int32_t)idx;
+    prune_walk<true>(pool + parent.off, box, L.cullMode, L.iso, outPool + off, L.colorExact != 0, len, outFlag ? outFlag + off : nullptr);
+    publish_child(L, coord, off, len, childIdx[tid], children, candOfMpu, maxLen);
+}
+
+// ---- warp-cooperative pruning --------------------------------------------------------------------------------------
+// The coarse levels have few regions and long parent programs (level 0 walks the whole BlobTree), so one thread per region
+// is bound by the latency of ~1000 dependent primitive bounds (ncu r01b: 0.7 ms per pass on 4 CTAs). Here a WARP prunes one
+// region: 32 quad positions at a time, every lane that sits on an instruction header (flag byte) computes that primitive's
+// bound, all-zero blend operands are dropped on the spot, and lane 0 feeds the few remaining instructions to the Pruner state
+// machine in program order - the same walk, so the output is identical to prune_walk's.
+constexpr int kCoopWarps = 4;
+struct __align__(16) CoopEntry { uint32_t pc; uint32_t za; float flo, fhi; };  // pc bit 31 = primitive is all-zero here
+
+template <bool EMIT>
+__device__ uint32_t prune_walk_warp(const float4* __restrict__ src, const uint8_t* __restrict__ sflag, uint32_t srcLen, const Box3& region,
+                                    int cullMode, float iso, float4* __restrict__ dst, uint8_t* dflag, bool colorExact, uint32_t limit,
+                                    CoopEntry* ent) {
+    const int lane = threadIdx.x & 31;
+    const uint32_t FULL = 0xffffffffu;
+    Pruner<EMIT> P;
+    P.init(src, region, dst, dflag, colorExact, limit);
+    Box3 box = region;
+    uint32_t base = 0, zaTotal = 0, zaPrev = 0;
+    for (;;) {
+        const uint32_t p = base + lane;
+        const bool isInstr = (p < srcLen) && (sflag[p] != 0);
+        float4 q0 = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (isInstr) q0 = src[p];
+        const uint32_t hdr = __float_as_uint(q0.x);
+        const uint32_t opc = PS_HDR_OPC(hdr);
+        // the batch ends right after the first instruction that changes the region box (later bounds depend on it) or OPC_END
+        const bool cutter = isInstr && (opc == OPC_END || ps_changes_box(opc));
+        const uint32_t cutMask = __ballot_sync(FULL, cutter);
+        const int cutLane = cutMask ? (__ffs((int)cutMask) - 1) : 31;
+        const bool active = isInstr && lane <= cutLane;
+        bool pz = false, skip = false;
+        float flo = 0.f, fhi = 0.f;
+        uint32_t scale = 0;
+        if (active && opc != OPC_END && opc < OPC_FIRST_NONPRIM) {
+            pz = prim_bound(hdr, q0, src + p + 1, box, flo, fhi);
+            skip = Pruner<EMIT>::skippable(hdr, pz, scale);
+        }
+        const bool isEntry = active && !skip;
+        const uint32_t zs = (active && skip) ? scale : 0u;
+        uint32_t incl = zs;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const uint32_t v = __shfl_up_sync(FULL, incl, o);
+            if (lane >= o) incl += v;
+        }
+        const uint32_t entMask = __ballot_sync(FULL, isEntry);
+        if (isEntry) {
+            CoopEntry e;
+            e.pc = p | (pz ? 0x80000000u : 0u); e.za = zaTotal + incl - zs; e.flo = flo; e.fhi = fhi;
+            ent[__popc(entMask & ((1u << lane) - 1u))] = e;
+        }
+        zaTotal += __shfl_sync(FULL, incl, 31);
+        __syncwarp();
+        int endSeen = 0;
+        if (lane == 0) {
+            const int n = __popc(entMask);
+            for (int i = 0; i < n; i++) {
+                const CoopEntry e = ent[i];
+                const uint32_t pc = e.pc & 0x7FFFFFFFu;
+                P.skipped_scale(e.za - zaPrev);
+                zaPrev = e.za;
+                const float4 h0 = src[pc];
+                const uint32_t h = __float_as_uint(h0.x), o = PS_HDR_OPC(h);
+                if (o == OPC_END) { endSeen = 1; break; }
+                if (o < OPC_FIRST_NONPRIM) P.step_prim(pc, h0, h, (e.pc >> 31) != 0u, e.flo, e.fhi);
+                else P.step_op(pc, h0, h);
+            }
+        }
+        __syncwarp();
+        endSeen = __shfl_sync(FULL, endSeen, 0);
+        if (endSeen) break;
+        if (cutMask) {
+#pragma unroll
+            for (int a = 0; a < 3; a++) { box.lo[a] = __shfl_sync(FULL, P.box.lo[a], 0); box.hi[a] = __shfl_sync(FULL, P.box.hi[a], 0); }
+            const uint32_t cutHdr = __shfl_sync(FULL, hdr, cutLane);
+            base += (uint32_t)cutLane + (uint32_t)ps_instr_quads(cutHdr);
+        } else base += 32u;
+        if (base >= srcLen) break;  // malformed program without OPC_END
     }
+    uint32_t len = 0;
+    if (lane == 0) len = P.finish(cullMode, iso);
+    return __shfl_sync(FULL, len, 0);
+}
+
+__global__ void __launch_bounds__(kCoopWarps * 32) prune_count_warp_kernel(CullLevel L, const Region* __restrict__ parents, int nParents,
+                                                                           const float4* __restrict__ pool, const uint8_t* __restrict__ qflag,
+                                                                           uint32_t* __restrict__ childLen) {
+    __shared__ CoopEntry sEnt[kCoopWarps][32];
+    const int gw = blockIdx.x * kCoopWarps + (threadIdx.x >> 5);
+    if (gw >= nParents * 64) return;
+    const Region parent = parents[gw >> 6];
+    int coord[3];
+    Box3 box;
+    uint32_t len = 0;
+    if (child_region(L, parent, gw & 63, coord, box))
+        len = prune_walk_warp<false>(pool + parent.off, qflag + parent.off, parent.len, box, L.cullMode, L.iso, nullptr, nullptr, L.colorExact != 0,
+                                     0xFFFFFFFFu, sEnt[threadIdx.x >> 5]);
+    if ((threadIdx.x & 31) == 0) childLen[gw] = len;
+}
+
+__global__ void __launch_bounds__(kCoopWarps * 32) prune_emit_warp_kernel(CullLevel L, const Region* __restrict__ parents, int nParents,
+                                                                          const float4* __restrict__ pool, const uint8_t* __restrict__ qflag,
+                                                                          const uint32_t* __restrict__ childLen, const uint32_t* __restrict__ childOff,
+                                                                          const uint32_t* __restrict__ childIdx, float4* __restrict__ outPool,
+                                                                          uint8_t* __restrict__ outFlag, uint32_t outBase, Region* __restrict__ children,
+                                                                          int32_t* __restrict__ candOfMpu, uint32_t* __restrict__ maxLen) {
+    __shared__ CoopEntry sEnt[kCoopWarps][32];
+    const int gw = blockIdx.x * kCoopWarps + (threadIdx.x >> 5);
+    if (gw >= nParents * 64) return;
+    const uint32_t len = childLen[gw];
+    if (len == 0) return;
+    const Region parent = parents[gw >> 6];
+    int coord[3];
+    Box3 box;
+    child_region(L, parent, gw & 63, coord, box);
+    const uint32_t off = outBase + childOff[gw];
+    prune_walk_warp<true>(pool + parent.off, qflag + parent.off, parent.len, box, L.cullMode, L.iso, outPool + off, outFlag ? outFlag + off : nullptr,
+                          L.colorExact != 0, len, sEnt[threadIdx.x >> 5]);
+    if ((threadIdx.x & 31) == 0) publish_child(L, coord, off, len, childIdx[gw], children, candOfMpu, maxLen);
 }
 
 __global__ void flag_kernel(const uint32_t* __restrict__ len, uint32_t* __restrict__ flag, int n) {
@@ -117,19 +243,28 @@ void launch_all_mpus(const CullLevel& L, Region* out, uint32_t fullLen, int32_t*
     all_mpus_kernel<<<(n + 255) / 256, 256, 0, st>>>(L, out, fullLen, candOfMpu, n);
 }
 
-void launch_prune_count(const CullLevel& L, const Region* parents, int nParents, const float4* pool, uint32_t* childLen, cudaStream_t st) {
+// regions per level below which a warp per region pays (few regions, long parent programs)
+static bool use_warp_walk(int nParents) { return nParents * 64 <= 16384; }
+
+void launch_prune_count(const CullLevel& L, const Region* parents, int nParents, const float4* pool, const uint8_t* qflag, uint32_t* childLen,
+                        cudaStream_t st) {
     const int n = nParents * 64;
-    prune_count_kernel<<<(n + 127) / 128, 128, 0, st>>>(L, parents, nParents, pool, childLen);
+    if (use_warp_walk(nParents)) prune_count_warp_kernel<<<(n + kCoopWarps - 1) / kCoopWarps, kCoopWarps * 32, 0, st>>>(L, parents, nParents, pool, qflag, childLen);
+    else prune_count_kernel<<<(n + 127) / 128, 128, 0, st>>>(L, parents, nParents, pool, childLen);
 }
 
 void launch_flags(const uint32_t* len, uint32_t* flag, int n, cudaStream_t st) { flag_kernel<<<(n + 255) / 256, 256, 0, st>>>(len, flag, n); }
 
-void launch_prune_emit(const CullLevel& L, const Region* parents, int nParents, const float4* pool, const uint32_t* childLen,
-                       const uint32_t* childOff, const uint32_t* childIdx, float4* outPool, uint32_t outBase, Region* children,
+void launch_prune_emit(const CullLevel& L, const Region* parents, int nParents, const float4* pool, const uint8_t* qflag, const uint32_t* childLen,
+                       const uint32_t* childOff, const uint32_t* childIdx, float4* outPool, uint8_t* outFlag, uint32_t outBase, Region* children,
                        int32_t* candOfMpu, uint32_t* maxLen, cudaStream_t st) {
     const int n = nParents * 64;
-    prune_emit_kernel<<<(n + 127) / 128, 128, 0, st>>>(L, parents, nParents, pool, childLen, childOff, childIdx, outPool, outBase, children,
-                                                       candOfMpu, maxLen);
+    if (use_warp_walk(nParents))
+        prune_emit_warp_kernel<<<(n + kCoopWarps - 1) / kCoopWarps, kCoopWarps * 32, 0, st>>>(L, parents, nParents, pool, qflag, childLen, childOff, childIdx,
+                                                                                             outPool, outFlag, outBase, children, candOfMpu, maxLen);
+    else
+        prune_emit_kernel<<<(n + 127) / 128, 128, 0, st>>>(L, parents, nParents, pool, childLen, childOff, childIdx, outPool, outFlag, outBase, children,
+                                                           candOfMpu, maxLen);
 }
 
 size_t scan_temp_bytes(int n) {

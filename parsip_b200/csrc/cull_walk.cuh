@@ -154,37 +154,57 @@ __device__ __forceinline__ void bound_combine(uint32_t cmb, float& lo, float& hi
     lo -= e; hi += e;
 }
 
-// Prunes src against `box`. EMIT = false only measures. Returns the pruned length in quads including the
-// END quad, or 0 if the region needs no evaluation.
+// Prunes a program against a region box. EMIT = false only measures. finish() returns the pruned length in quads including
+// the END quad, or 0 if the region needs no evaluation.
 // colorExact (PS_SimdPoly semantics): a blend that loses an all-zero operand leaves an OPC_CSCALE marker, see program.h.
 // `limit` (EMIT only) = the length the measuring pass returned: the walk writes TENTATIVE code that a later zero-fold may
 // rewind (intersection with 0, all-zero warp bracket, ...), and such code can run past the final length - into the slot of
 // the next region's program in the pool, which another thread is writing. Nothing at or beyond `limit` survives, so it is
 // simply not stored.
+// `dflag` (EMIT, optional): one byte per emitted quad, 1 = first quad of an instruction. The warp-cooperative passes of
+// cull.cu find the instruction headers of a parent program through it (one lane per quad position).
+//
+// The walk is a state machine fed one instruction at a time, so that a warp can compute the primitive bounds of 32 quad
+// positions in parallel and let one lane step through the few instructions that matter (prune_walk below is the plain
+// sequential driver; cull.cu has the cooperative one).
 template <bool EMIT>
-__device__ uint32_t prune_walk(const float4* __restrict__ src, const Box3& region, int cullMode, float iso, float4* __restrict__ dst,
-                               bool colorExact = false, uint32_t limit = 0xFFFFFFFFu) {
+struct Pruner {
     float blo[PS_MAX_VALUE_STACK], bhi[PS_MAX_VALUE_STACK];
     uint32_t bstart[PS_MAX_VALUE_STACK];
     bool bzero[PS_MAX_VALUE_STACK];
     Box3 wbox[PS_MAX_POINT_STACK];
     uint32_t wstart[PS_MAX_POINT_STACK];
-    int sp = -1, wsp = 0;
-    uint32_t emit = 0;
-    Box3 box = region;
-    uint32_t lastHdrPos = 0xFFFFFFFFu, lastHdrVal = 0;  // header quad of the last instruction emitted (for the colour-scale bits)
-    float4 lastHdrQuad = make_float4(0.f, 0.f, 0.f, 0.f);
-    auto put = [&](float4 v) { if (EMIT && emit < limit) dst[emit] = v; emit++; };
-    auto hdrquad = [&](uint32_t h) { lastHdrPos = 0xFFFFFFFFu; return make_float4(__uint_as_float(h), 0.f, 0.f, 0.f); };
-    uint32_t lastScale = 0xFFFFFFFFu, scaleCount = 0;  // position of the trailing OPC_CSCALE quad, if emit == lastScale + 1
-    auto rewind = [&](uint32_t pos) {
+    int sp, wsp;
+    uint32_t emit;
+    Box3 box;
+    uint32_t lastHdrPos, lastHdrVal;  // header quad of the last instruction emitted (for the colour-scale bits)
+    float4 lastHdrQuad;
+    uint32_t lastScale, scaleCount;   // position of the trailing OPC_CSCALE quad, if emit == lastScale + 1
+    const float4* src;
+    float4* dst;
+    uint8_t* dflag;
+    bool colorExact;
+    uint32_t limit;
+
+    __device__ void init(const float4* src_, const Box3& region, float4* dst_, uint8_t* dflag_, bool colorExact_, uint32_t limit_) {
+        sp = -1; wsp = 0; emit = 0; box = region;
+        lastHdrPos = 0xFFFFFFFFu; lastHdrVal = 0; lastHdrQuad = make_float4(0.f, 0.f, 0.f, 0.f);
+        lastScale = 0xFFFFFFFFu; scaleCount = 0;
+        src = src_; dst = dst_; dflag = dflag_; colorExact = colorExact_; limit = limit_;
+    }
+    __device__ __forceinline__ void put(float4 v, bool start) {
+        if (EMIT && emit < limit) { dst[emit] = v; if (dflag) dflag[emit] = start ? 1 : 0; }
+        emit++;
+    }
+    __device__ __forceinline__ float4 hdrquad(uint32_t h) { lastHdrPos = 0xFFFFFFFFu; return make_float4(__uint_as_float(h), 0.f, 0.f, 0.f); }
+    __device__ __forceinline__ void rewind(uint32_t pos) {
         emit = pos;
         if (lastScale != 0xFFFFFFFFu && lastScale >= emit) lastScale = 0xFFFFFFFFu;
         if (lastHdrPos != 0xFFFFFFFFu && lastHdrPos >= emit) lastHdrPos = 0xFFFFFFFFu;
-    };
+    }
     // colour-scale marker on the current top entry: first into the 4 header bits of the entry's last instruction (free for the
-    // field-only passes), the overflow into an explicit OPC_CSCALE quad
-    auto cscale = [&](uint32_t n) {
+    // field-only passes), the overflow into an explicit OPC_CSCALE quad. cscale(a); cscale(b) == cscale(a + b).
+    __device__ void cscale(uint32_t n) {
         if (!colorExact || n == 0) return;
         if (lastScale + 1 != emit && lastHdrPos != 0xFFFFFFFFu && sp >= 0 && lastHdrPos >= bstart[sp] && lastHdrPos < emit) {
             const uint32_t have = PS_HDR_CSC(lastHdrVal), room = 15u - have, take = n < room ? n : room;
@@ -198,60 +218,75 @@ __device__ uint32_t prune_walk(const float4* __restrict__ src, const Box3& regio
         }
         if (lastScale + 1 == emit) scaleCount += n;
         else { lastScale = emit; scaleCount = n; emit++; }
-        if (EMIT && lastScale < limit) dst[lastScale] = make_float4(__uint_as_float(PS_HDR(OPC_CSCALE, 0, 0, 0)), __uint_as_float(scaleCount), 0.f, 0.f);
-    };
-    for (uint32_t pc = 0;;) {
-        const float4 q0 = src[pc];
-        const uint32_t hdr = __float_as_uint(q0.x);
-        const uint32_t opc = PS_HDR_OPC(hdr);
-        if (opc == OPC_END) break;
-        const int nq = ps_instr_quads(hdr);
-        auto copy = [&](uint32_t newHdr) {
-            const uint32_t o = PS_HDR_OPC(newHdr);
-            if (o < OPC_FIRST_NONPRIM || o == OPC_COMBINE) { lastHdrPos = emit; lastHdrVal = newHdr; lastHdrQuad = make_float4(__uint_as_float(newHdr), q0.y, q0.z, q0.w); }
-            else lastHdrPos = 0xFFFFFFFFu;
-            put(make_float4(__uint_as_float(newHdr), q0.y, q0.z, q0.w));
-            for (int i = 1; i < nq; i++) put(src[pc + i]);
-        };
-        if (opc < OPC_FIRST_NONPRIM) {
-            const uint32_t cmb = PS_HDR_CMB(hdr);
-            float flo, fhi;
-            const bool pz = prim_bound(hdr, q0, src + pc + 1, box, flo, fhi);
-            if (cmb == CMB_PUSH) {
-                sp++;
-                bstart[sp] = emit; bzero[sp] = pz; blo[sp] = flo; bhi[sp] = fhi;
-                if (!pz) copy(hdr);
-            } else if (bzero[sp]) {
-                if (!pz && (cmb == CMB_ADD || cmb == CMB_MAX || cmb == CMB_RDIF || cmb == CMB_RSDIF)) {
-                    // 0 + f, max(0, f), min(f, 1 - 0) (f <= 1), f * (1 - 0): the primitive becomes the entry
-                    copy((hdr & ~(15u << 6)) | (CMB_PUSH << 6));
-                    bzero[sp] = false; blo[sp] = flo; bhi[sp] = fhi;
-                    if (cmb == CMB_ADD) cscale(1);
-                }  // min(0,f) = 0, min(0,1-f) = 0 (f <= 1), 0*(1-f) = 0: stays zero
-            } else if (pz) {
-                if (cmb == CMB_MAX) {
-                    if (blo[sp] < 0.f) { put(hdrquad(PS_HDR(OPC_NULLPRIM, CMB_MAX, 0, 0))); blo[sp] = fmaxf(blo[sp], 0.f); }
-                } else if (cmb == CMB_MIN) {
-                    if (blo[sp] >= 0.f) { rewind(bstart[sp]); bzero[sp] = true; blo[sp] = bhi[sp] = 0.f; }
-                    else { put(hdrquad(PS_HDR(OPC_NULLPRIM, CMB_MIN, 0, 0))); bhi[sp] = fminf(bhi[sp], 0.f); }
-                } else if (cmb == CMB_DIF) {  // min(top, 1 - 0)
-                    if (bhi[sp] > 1.0f) { put(hdrquad(PS_HDR(OPC_CLAMP1, 0, 0, 0))); bhi[sp] = 1.0f; blo[sp] = fminf(blo[sp], 1.0f); }
-                } else if (cmb == CMB_ADD) cscale(1);  // top + 0 (top * (1 - 0): nothing)
-                else if (cmb == CMB_RSDIF || (cmb == CMB_RDIF && bhi[sp] <= 1.0f)) {  // 0 * (1 - top), min(0, 1 - top) with top <= 1
-                    rewind(bstart[sp]); bzero[sp] = true; blo[sp] = bhi[sp] = 0.f;
-                } else if (cmb == CMB_RDIF) {  // min(0, 1 - top) can go negative
-                    put(hdrquad(PS_HDR(OPC_DIF0, 0, 0, 0)));
-                    const float a = fminf(0.f, 1.0f - bhi[sp]) - 1e-6f, b = fminf(0.f, 1.0f - blo[sp]);
-                    blo[sp] = a; bhi[sp] = b;
-                }
-                if (!bzero[sp]) cscale(PS_HDR_CSC(hdr));  // markers a coarser level left on the dropped instruction stay with the entry
-            } else {
-                copy(hdr);
-                bound_combine(cmb, blo[sp], bhi[sp], flo, fhi);
-            }
-            pc += nq;
-            continue;
+        if (EMIT && lastScale < limit) {
+            dst[lastScale] = make_float4(__uint_as_float(PS_HDR(OPC_CSCALE, 0, 0, 0)), __uint_as_float(scaleCount), 0.f, 0.f);
+            if (dflag) dflag[lastScale] = 1;
         }
+    }
+    // copies instruction (pc, q0) with a possibly rewritten header
+    __device__ void copy(uint32_t pc, const float4 q0, uint32_t newHdr, int nq) {
+        const uint32_t o = PS_HDR_OPC(newHdr);
+        if (o < OPC_FIRST_NONPRIM || o == OPC_COMBINE) { lastHdrPos = emit; lastHdrVal = newHdr; lastHdrQuad = make_float4(__uint_as_float(newHdr), q0.y, q0.z, q0.w); }
+        else lastHdrPos = 0xFFFFFFFFu;
+        put(make_float4(__uint_as_float(newHdr), q0.y, q0.z, q0.w), true);
+        for (int i = 1; i < nq; i++) put(src[pc + i], false);
+    }
+    // `n` colour-scale steps owed by all-zero blend operands (and the markers they carried) that the caller skipped since the
+    // last instruction it fed: they apply to the current top entry if that is not itself all-zero
+    __device__ __forceinline__ void skipped_scale(uint32_t n) {
+        if (n && sp >= 0 && !bzero[sp]) cscale(n);
+    }
+    // true for an all-zero primitive the caller may skip instead of feeding it to step_prim: 0 added to / smooth-subtracted
+    // from the top changes nothing but the colour weights; `scale` = the colour-scale steps to pass to skipped_scale
+    __device__ static __forceinline__ bool skippable(uint32_t hdr, bool pz, uint32_t& scale) {
+        const uint32_t cmb = PS_HDR_CMB(hdr);
+        if (!pz || (cmb != CMB_ADD && cmb != CMB_SDIF)) return false;
+        scale = (cmb == CMB_ADD ? 1u : 0u) + PS_HDR_CSC(hdr);
+        return true;
+    }
+
+    // one primitive instruction; (pz, flo, fhi) = prim_bound over the CURRENT box
+    __device__ void step_prim(uint32_t pc, const float4 q0, uint32_t hdr, bool pz, float flo, float fhi) {
+        const uint32_t cmb = PS_HDR_CMB(hdr);
+        const int nq = ps_instr_quads(hdr);
+        if (cmb == CMB_PUSH) {
+            sp++;
+            bstart[sp] = emit; bzero[sp] = pz; blo[sp] = flo; bhi[sp] = fhi;
+            if (!pz) copy(pc, q0, hdr, nq);
+        } else if (bzero[sp]) {
+            if (!pz && (cmb == CMB_ADD || cmb == CMB_MAX || cmb == CMB_RDIF || cmb == CMB_RSDIF)) {
+                // 0 + f, max(0, f), min(f, 1 - 0) (f <= 1), f * (1 - 0): the primitive becomes the entry
+                copy(pc, q0, (hdr & ~(15u << 6)) | (CMB_PUSH << 6), nq);
+                bzero[sp] = false; blo[sp] = flo; bhi[sp] = fhi;
+                if (cmb == CMB_ADD) cscale(1);
+            }  // min(0,f) = 0, min(0,1-f) = 0 (f <= 1), 0*(1-f) = 0: stays zero
+        } else if (pz) {
+            if (cmb == CMB_MAX) {
+                if (blo[sp] < 0.f) { put(hdrquad(PS_HDR(OPC_NULLPRIM, CMB_MAX, 0, 0)), true); blo[sp] = fmaxf(blo[sp], 0.f); }
+            } else if (cmb == CMB_MIN) {
+                if (blo[sp] >= 0.f) { rewind(bstart[sp]); bzero[sp] = true; blo[sp] = bhi[sp] = 0.f; }
+                else { put(hdrquad(PS_HDR(OPC_NULLPRIM, CMB_MIN, 0, 0)), true); bhi[sp] = fminf(bhi[sp], 0.f); }
+            } else if (cmb == CMB_DIF) {  // min(top, 1 - 0)
+                if (bhi[sp] > 1.0f) { put(hdrquad(PS_HDR(OPC_CLAMP1, 0, 0, 0)), true); bhi[sp] = 1.0f; blo[sp] = fminf(blo[sp], 1.0f); }
+            } else if (cmb == CMB_ADD) cscale(1);  // top + 0 (top * (1 - 0): nothing)
+            else if (cmb == CMB_RSDIF || (cmb == CMB_RDIF && bhi[sp] <= 1.0f)) {  // 0 * (1 - top), min(0, 1 - top) with top <= 1
+                rewind(bstart[sp]); bzero[sp] = true; blo[sp] = bhi[sp] = 0.f;
+            } else if (cmb == CMB_RDIF) {  // min(0, 1 - top) can go negative
+                put(hdrquad(PS_HDR(OPC_DIF0, 0, 0, 0)), true);
+                const float a = fminf(0.f, 1.0f - bhi[sp]) - 1e-6f, b = fminf(0.f, 1.0f - blo[sp]);
+                blo[sp] = a; bhi[sp] = b;
+            }
+            if (!bzero[sp]) cscale(PS_HDR_CSC(hdr));  // markers a coarser level left on the dropped instruction stay with the entry
+        } else {
+            copy(pc, q0, hdr, nq);
+            bound_combine(cmb, blo[sp], bhi[sp], flo, fhi);
+        }
+    }
+
+    // one non-primitive instruction (not OPC_END); warps / operator matrices / OPC_POPPOINT change `box`
+    __device__ void step_op(uint32_t pc, const float4 q0, uint32_t hdr) {
+        const uint32_t opc = PS_HDR_OPC(hdr);
+        const int nq = ps_instr_quads(hdr);
         switch (opc) {
         case OPC_COMBINE: {
             const uint32_t cmbRaw = PS_HDR_CMB(hdr);
@@ -264,27 +299,27 @@ __device__ uint32_t prune_walk(const float4* __restrict__ src, const Box3& regio
                 if (cmb == CMB_ADD) { bzero[t] = false; blo[t] = blo[v]; bhi[t] = bhi[v]; cscale(1); }
                 else if (cmb == CMB_MAX) {
                     bzero[t] = false; blo[t] = blo[v]; bhi[t] = bhi[v];
-                    if (blo[v] < 0.f) { put(hdrquad(PS_HDR(OPC_NULLPRIM, CMB_MAX, 0, 0))); blo[t] = 0.f; bhi[t] = fmaxf(bhi[v], 0.f); }
+                    if (blo[v] < 0.f) { put(hdrquad(PS_HDR(OPC_NULLPRIM, CMB_MAX, 0, 0)), true); blo[t] = 0.f; bhi[t] = fmaxf(bhi[v], 0.f); }
                 } else if (cmb == CMB_MIN) {
                     if (blo[v] >= 0.f) rewind(bstart[t]);
-                    else { put(hdrquad(PS_HDR(OPC_NULLPRIM, CMB_MIN, 0, 0))); bzero[t] = false; blo[t] = fminf(blo[v], 0.f); bhi[t] = 0.f; }
+                    else { put(hdrquad(PS_HDR(OPC_NULLPRIM, CMB_MIN, 0, 0)), true); bzero[t] = false; blo[t] = fminf(blo[v], 0.f); bhi[t] = 0.f; }
                 } else if (cmb == CMB_DIF) {  // min(0, 1 - V)
                     if (bhi[v] <= 1.0f) rewind(bstart[t]);
-                    else { put(hdrquad(PS_HDR(OPC_DIF0, 0, 0, 0))); bzero[t] = false; blo[t] = fminf(0.f, 1.0f - bhi[v]) - 1e-6f; bhi[t] = 0.f; }
+                    else { put(hdrquad(PS_HDR(OPC_DIF0, 0, 0, 0)), true); bzero[t] = false; blo[t] = fminf(0.f, 1.0f - bhi[v]) - 1e-6f; bhi[t] = 0.f; }
                 } else rewind(bstart[t]);  // 0 * (1 - V)
                 if (!bzero[t]) cscale(PS_HDR_CSC(hdr));
             } else if (bzero[v]) {  // T (cmb) 0
                 if (cmb == CMB_MAX) {
-                    if (blo[t] < 0.f) { put(hdrquad(PS_HDR(OPC_NULLPRIM, CMB_MAX, 0, 0))); blo[t] = 0.f; bhi[t] = fmaxf(bhi[t], 0.f); }
+                    if (blo[t] < 0.f) { put(hdrquad(PS_HDR(OPC_NULLPRIM, CMB_MAX, 0, 0)), true); blo[t] = 0.f; bhi[t] = fmaxf(bhi[t], 0.f); }
                 } else if (cmb == CMB_MIN) {
                     if (blo[t] >= 0.f) { rewind(bstart[t]); bzero[t] = true; blo[t] = bhi[t] = 0.f; }
-                    else { put(hdrquad(PS_HDR(OPC_NULLPRIM, CMB_MIN, 0, 0))); bhi[t] = fminf(bhi[t], 0.f); }
+                    else { put(hdrquad(PS_HDR(OPC_NULLPRIM, CMB_MIN, 0, 0)), true); bhi[t] = fminf(bhi[t], 0.f); }
                 } else if (cmb == CMB_DIF) {
-                    if (bhi[t] > 1.0f) { put(hdrquad(PS_HDR(OPC_CLAMP1, 0, 0, 0))); bhi[t] = 1.0f; blo[t] = fminf(blo[t], 1.0f); }
+                    if (bhi[t] > 1.0f) { put(hdrquad(PS_HDR(OPC_CLAMP1, 0, 0, 0)), true); bhi[t] = 1.0f; blo[t] = fminf(blo[t], 1.0f); }
                 } else if (cmb == CMB_ADD) cscale(1);
                 if (!bzero[t]) cscale(PS_HDR_CSC(hdr));
             } else {
-                copy(hdr);
+                copy(pc, q0, hdr, nq);
                 bound_combine(cmb, blo[t], bhi[t], blo[v], bhi[v]);
             }
         } break;
@@ -293,7 +328,7 @@ __device__ uint32_t prune_walk(const float4* __restrict__ src, const Box3& regio
         } break;
         case OPC_POW: {
             if (!bzero[sp]) {
-                copy(hdr);
+                copy(pc, q0, hdr, nq);
                 const float e = q0.y;
                 const float a = powf(fmaxf(blo[sp], 0.f), e), b = powf(fmaxf(bhi[sp], 0.f), e);
                 blo[sp] = fminf(a, b) * 0.9999f - 1e-7f; bhi[sp] = fmaxf(a, b) * 1.0001f + 1e-7f;
@@ -306,8 +341,8 @@ __device__ uint32_t prune_walk(const float4* __restrict__ src, const Box3& regio
             if (bzero[t] && bzero[v]) {
                 // fast_pow(0) = 0
             } else {
-                if (bzero[t] || bzero[v]) put(hdrquad(PS_HDR(OPC_NULLPRIM, CMB_PUSH, 0, 0)));  // materialise the zero operand
-                copy(hdr);
+                if (bzero[t] || bzero[v]) put(hdrquad(PS_HDR(OPC_NULLPRIM, CMB_PUSH, 0, 0)), true);  // materialise the zero operand
+                copy(pc, q0, hdr, nq);
                 const float e = q0.y;
                 const float b0 = (bzero[t] ? 0.f : blo[t]) + (bzero[v] ? 0.f : blo[v]);
                 const float b1 = (bzero[t] ? 0.f : bhi[t]) + (bzero[v] ? 0.f : bhi[v]);
@@ -318,11 +353,11 @@ __device__ uint32_t prune_walk(const float4* __restrict__ src, const Box3& regio
             }
         } break;
         case OPC_CLAMP1: {
-            if (!bzero[sp]) { copy(hdr); bhi[sp] = fminf(bhi[sp], 1.0f); blo[sp] = fminf(blo[sp], 1.0f); }
+            if (!bzero[sp]) { copy(pc, q0, hdr, nq); bhi[sp] = fminf(bhi[sp], 1.0f); blo[sp] = fminf(blo[sp], 1.0f); }
         } break;
         case OPC_DIF0: {
             if (!bzero[sp]) {
-                copy(hdr);
+                copy(pc, q0, hdr, nq);
                 const float a = fminf(0.f, 1.0f - bhi[sp]) - 1e-6f, b = fminf(0.f, 1.0f - blo[sp]);
                 blo[sp] = a; bhi[sp] = b;
             }
@@ -331,25 +366,51 @@ __device__ uint32_t prune_walk(const float4* __restrict__ src, const Box3& regio
             wsp--;
             box = wbox[wsp];
             if (bzero[sp]) rewind(wstart[wsp]);
-            else copy(hdr);
+            else copy(pc, q0, hdr, nq);
             bstart[sp] = wstart[wsp];
         } break;
         default: {  // warps, operator affine
             wbox[wsp] = box;
             wstart[wsp] = emit;
             wsp++;
-            copy(hdr);
+            copy(pc, q0, hdr, nq);
             warp_box(opc, q0, src + pc + 1, box);
         } break;
         }
-        pc += nq;
     }
-    if (sp < 0 || bzero[0]) return 0;
-    if (cullMode >= PSGPU_CULL_INTERVAL) {
-        if (bhi[0] < iso - 1e-4f || blo[0] > iso + 1e-4f) return 0;
+
+    __device__ uint32_t finish(int cullMode, float iso) {
+        if (sp < 0 || bzero[0]) return 0;
+        if (cullMode >= PSGPU_CULL_INTERVAL) {
+            if (bhi[0] < iso - 1e-4f || blo[0] > iso + 1e-4f) return 0;
+        }
+        put(make_float4(__uint_as_float(PS_HDR(OPC_END, 0, 0, 0)), 0.f, 0.f, 0.f), true);
+        return emit;
     }
-    put(make_float4(__uint_as_float(PS_HDR(OPC_END, 0, 0, 0)), 0.f, 0.f, 0.f));
-    return emit;
+};
+
+// does this opcode change the region box of the walk (so that bounds of later primitives depend on it)?
+__device__ __forceinline__ bool ps_changes_box(uint32_t opc) { return opc >= OPC_TWIST && opc <= OPC_POPPOINT; }
+
+// plain sequential driver (one thread per region)
+template <bool EMIT>
+__device__ uint32_t prune_walk(const float4* __restrict__ src, const Box3& region, int cullMode, float iso, float4* __restrict__ dst,
+                               bool colorExact = false, uint32_t limit = 0xFFFFFFFFu, uint8_t* dflag = nullptr) {
+    Pruner<EMIT> P;
+    P.init(src, region, dst, dflag, colorExact, limit);
+    for (uint32_t pc = 0;;) {
+        const float4 q0 = src[pc];
+        const uint32_t hdr = __float_as_uint(q0.x);
+        const uint32_t opc = PS_HDR_OPC(hdr);
+        if (opc == OPC_END) break;
+        if (opc < OPC_FIRST_NONPRIM) {
+            float flo, fhi;
+            const bool pz = prim_bound(hdr, q0, src + pc + 1, P.box, flo, fhi);
+            P.step_prim(pc, q0, hdr, pz, flo, fhi);
+        } else P.step_op(pc, q0, hdr);
+        pc += ps_instr_quads(hdr);
+    }
+    return P.finish(cullMode, iso);
 }
 
 }  // namespace psgpu
