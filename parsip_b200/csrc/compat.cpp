@@ -185,12 +185,13 @@ int PrepareBBoxes(float cellsize, SOABlobPrims& P, SOABlobBoxMatrices& B, SOABlo
         default: break;
         }
         const int im = P.idxMatrix[i];
-        if (im != 0 && im < (int)B.count) {  // cpp:200-218: the two corners through the forward 4x4
+        if (im != 0 && im < (int)B.count) {  // cpp:200-218: the two corners through the forward 4x4; mat4Transform reads the
+            // 16 floats as e[col][row] with the translation in e[3][0..2] (PS_MATRIX4.h:199-209)
             const float* m = &B.matrix[im * BOX_MATRIX_STRIDE];
             float l2[3], h2[3];
             for (int a = 0; a < 3; a++) {
-                l2[a] = m[a * 4] * lo[0] + m[a * 4 + 1] * lo[1] + m[a * 4 + 2] * lo[2] + m[a * 4 + 3];
-                h2[a] = m[a * 4] * hi[0] + m[a * 4 + 1] * hi[1] + m[a * 4 + 2] * hi[2] + m[a * 4 + 3];
+                l2[a] = (m[0 * 4 + a] * lo[0] + m[1 * 4 + a] * lo[1] + m[2 * 4 + a] * lo[2]) + m[3 * 4 + a];
+                h2[a] = (m[0 * 4 + a] * hi[0] + m[1 * 4 + a] * hi[1] + m[2 * 4 + a] * hi[2]) + m[3 * 4 + a];
             }
             for (int a = 0; a < 3; a++) { lo[a] = l2[a]; hi[a] = h2[a]; }
         }

@@ -24,6 +24,9 @@ def _build_once():
     emu = os.path.join(ROOT, "tests", "hostemu", "libhostemu.so")
     if not os.path.exists(emu):
         subprocess.check_call(["make", "-f", os.path.join(ROOT, "tests", "hostemu", "Makefile")])
+    fac = os.path.join(ROOT, "tests", "facade", "libfacade_probe.so")
+    if not os.path.exists(fac):
+        subprocess.check_call(["make", "-f", os.path.join(ROOT, "tests", "facade", "Makefile")])
 
 
 _build_once()
