@@ -24,8 +24,6 @@ namespace {
 constexpr int kThreads = 128;
 
 __device__ const int8_t g_triTable[256 * 16] = PS_MC_TRITABLE_INIT;
-__constant__ uint8_t c_corner1[12] = PS_MC_CORNER1_INIT;
-__constant__ uint8_t c_edgeAxis[12] = PS_MC_EDGEAXIS_INIT;
 __constant__ uint8_t c_nTriE[256] = PS_MC_NTRI_INIT;
 
 struct EdgePos { float e1[3]; float e2a; int axis; };
@@ -137,169 +135,221 @@ __device__ void root_newton_ref(const GridParams& G, const float4* prog, const E
 }
 
 // ---------------------------------------------------------------------------------------------------------------------
-// tri_kernel
+// tri_kernel: persistent warps, one surface MPU per warp at a time, no block barriers. A lane owns 11 consecutive cells of the
+// 343 (cell order = the reference's i, j, k loop nest), cube cases come from the 512 inside bits read as bytes
+// (byte (i, j) = the 8 corners along k), triangle slots from one warp scan.
 // ---------------------------------------------------------------------------------------------------------------------
-struct __align__(16) TriSmem {
-    uint32_t insideW[16];
+constexpr int kCellsPerLane = 11;  // 32 * 11 >= 343
+
+struct TriWarpSmem {
+    uint32_t cellList[344];  // surface cells in cell order: cell | case << 9 | exclusive triangle offset << 17
+    uint32_t insideW[16];    // bit i*8 + j*64 + k
     uint32_t edgeW[48];
     uint16_t edgeP[48];
     uint16_t edgeVid[1536];  // PSGPU_OUT_MPU: reference-order local vertex id per edge bit
-    int8_t tri[256 * 16];
-    uint8_t cellCase[344];
-    uint32_t warpSum[4];
-    int next;
 };
 
-__device__ __forceinline__ uint32_t inside_bit(const TriSmem& S, int idx) { return (S.insideW[idx >> 5] >> (idx & 31)) & 1u; }
-
-// exclusive block scan of one value per thread (128 threads); returns the exclusive prefix, total in `total`
-__device__ __forceinline__ uint32_t block_excl_scan(TriSmem& S, uint32_t v, uint32_t& total) {
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+__device__ __forceinline__ uint32_t warp_excl_scan(uint32_t v, uint32_t& total) {
+    const int lane = threadIdx.x & 31;
     uint32_t inc = v;
 #pragma unroll
     for (int o = 1; o < 32; o <<= 1) {
         const uint32_t a = __shfl_up_sync(0xffffffffu, inc, o);
         if (lane >= o) inc += a;
     }
-    __syncthreads();
-    if (lane == 31) S.warpSum[warp] = inc;
-    __syncthreads();
-    uint32_t off = 0;
-#pragma unroll
-    for (int w = 0; w < 4; w++) { if (w < warp) off += S.warpSum[w]; }
-    total = S.warpSum[0] + S.warpSum[1] + S.warpSum[2] + S.warpSum[3];
-    return inc - v + off;
+    total = __shfl_sync(0xffffffffu, inc, 31);
+    return inc - v;
+}
+
+// corner1[e] / edgeaxis[e] (_CellConfigTable.h:48-51, mc_tables.h) packed into immediates: lanes look up different edges, which a
+// __constant__ table would serialise
+__device__ __forceinline__ int edge_corner1(int e) { return (int)((0x321054641020ull >> (4 * e)) & 7ull); }
+__device__ __forceinline__ int edge_axis(int e) { return (int)((0x5a5au >> (2 * e)) & 3u); }
+
+// cube case of cell (x, y, z): corner b = 4*dx + 2*dy + dz (PS_Polygonizer.cpp:662-669)
+__device__ __forceinline__ uint32_t cell_case(const uint8_t* B, int x, int y, int z) {
+    const uint32_t b00 = B[y * 8 + x], b10 = B[y * 8 + x + 1], b01 = B[(y + 1) * 8 + x], b11 = B[(y + 1) * 8 + x + 1];
+    return ((b00 >> z) & 3u) | (((b01 >> z) & 3u) << 2) | (((b10 >> z) & 3u) << 4) | (((b11 >> z) & 3u) << 6);
 }
 
 __global__ void __launch_bounds__(kThreads) tri_kernel(GridParams G, const Region* __restrict__ cands, FieldOutputs fo, MeshOutputs mo,
                                                        const int32_t* __restrict__ candOfMpu, int nMixed) {
-    __shared__ TriSmem S;
-    const int t = threadIdx.x;
-    for (int i = t; i < 256 * 16; i += kThreads) S.tri[i] = g_triTable[i];
+    __shared__ int8_t sTri[256 * 16];
+    __shared__ uint8_t sNTri[256];
+    __shared__ TriWarpSmem sWarp[kThreads / 32];
+    const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+    for (int i = threadIdx.x; i < 256 * 16; i += kThreads) sTri[i] = g_triTable[i];
+    for (int i = threadIdx.x; i < 256; i += kThreads) sNTri[i] = c_nTriE[i];
     __syncthreads();
+    TriWarpSmem& S = sWarp[wib];
+    const uint8_t* B = reinterpret_cast<const uint8_t*>(S.insideW);
     const bool perMpu = (G.output == PSGPU_OUT_MPU);
     const int ny = G.hi[1] - G.lo[1], nz = G.hi[2] - G.lo[2];
+    const int warpsTotal = gridDim.x * (kThreads / 32);
+    const int c0 = lane * kCellsPerLane;
+    const int x0 = c0 / 49, y0 = (c0 - x0 * 49) / 7, z0 = c0 - x0 * 49 - y0 * 7;
 
-    int m = blockIdx.x;
+    int m = blockIdx.x * (kThreads / 32) + wib;
     while (m < nMixed) {
         const uint32_t cand = fo.mixedList[m];
         const Region r = cands[cand];
-        if (t == 0) S.next = (int)atomicAdd(&fo.counters[3], 1u) + (int)gridDim.x;
-        if (t < 16) S.insideW[t] = 0u;
-        if (t < 48) { S.edgeW[t] = fo.edgeMask[(size_t)cand * 48 + t]; S.edgeP[t] = fo.edgePrefix[(size_t)cand * 48 + t]; }
         const uint32_t vbase = mo.vbase[cand], tbase = mo.tbase[cand];
-        const float4 f4 = fo.fv[(size_t)cand * 128 + t];
-        __syncthreads();
-        {
-            const uint32_t in4 = (is_inside(G, f4.x) ? 1u : 0u) | (is_inside(G, f4.y) ? 2u : 0u) | (is_inside(G, f4.z) ? 4u : 0u) |
-                                 (is_inside(G, f4.w) ? 8u : 0u);
-            atomicOr(&S.insideW[t >> 3], in4 << ((t & 7) * 4));
+        __syncwarp();
+        S.edgeW[lane] = fo.edgeMask[(size_t)cand * 48 + lane];
+        S.edgeP[lane] = fo.edgePrefix[(size_t)cand * 48 + lane];
+        if (lane < 16) {
+            S.edgeW[32 + lane] = fo.edgeMask[(size_t)cand * 48 + 32 + lane];
+            S.edgeP[32 + lane] = fo.edgePrefix[(size_t)cand * 48 + 32 + lane];
         }
-        __syncthreads();
-        for (int c = t; c < 343; c += kThreads) {
-            const int cx = c / 49, cy = (c / 7) % 7, cz = c % 7;
-            uint32_t cfg = 0;
 #pragma unroll
-            for (int b = 0; b < 8; b++) cfg |= inside_bit(S, (cx + ((b >> 2) & 1)) * 8 + (cy + ((b >> 1) & 1)) * 64 + (cz + (b & 1))) << b;
-            S.cellCase[c] = (uint8_t)cfg;
+        for (int q = 0; q < 4; q++) {  // 512 inside bits from the field cache: float4 t covers bits 4t .. 4t+3
+            const float4 f4 = fo.fv[(size_t)cand * 128 + q * 32 + lane];
+            uint32_t v = (is_inside(G, f4.x) ? 1u : 0u) | (is_inside(G, f4.y) ? 2u : 0u) | (is_inside(G, f4.z) ? 4u : 0u) | (is_inside(G, f4.w) ? 8u : 0u);
+            v <<= (lane & 7) * 4;
+            v |= __shfl_xor_sync(0xffffffffu, v, 1);
+            v |= __shfl_xor_sync(0xffffffffu, v, 2);
+            v |= __shfl_xor_sync(0xffffffffu, v, 4);
+            if ((lane & 7) == 0) S.insideW[q * 4 + (lane >> 3)] = v;
         }
-        __syncthreads();
+        __syncwarp();
+
+        // ---- cube cases of this lane's cells, triangle count
+        uint32_t cf[3] = {0u, 0u, 0u};
+        uint32_t nT = 0;
+        {
+            int x = x0, y = y0, z = z0;
+#pragma unroll
+            for (int i = 0; i < kCellsPerLane; i++) {
+                if (c0 + i < 343) {
+                    const uint32_t cfg = cell_case(B, x, y, z);
+                    cf[i >> 2] |= cfg << ((i & 3) * 8);
+                    nT += sNTri[cfg];
+                }
+                if (++z == 7) { z = 0; if (++y == 7) { y = 0; x++; } }
+            }
+        }
 
         if (perMpu) {
-            // reference vertex order: a vertex is created by the first cell (i outer, k inner) whose table row
-            // names its edge, in row order (PS_Polygonizer.cpp:647-808). The first cell of edge (corner c, axis a)
-            // is c with the two non-axis coordinates decremented (clipped at 0).
-            uint32_t carry = 0;
-            for (int round = 0; round < 3; round++) {
-                const int c = round * kThreads + t;
-                uint32_t nNew = 0;
-                uint32_t newMask = 0;  // row positions that create a vertex
-                if (c < 343) {
-                    const int cx = c / 49, cy = (c / 7) % 7, cz = c % 7;
-                    const int8_t* row = &S.tri[S.cellCase[c] * 16];
-                    uint32_t seen = 0;
-                    for (int k = 0; k < 16; k++) {
-                        const int e = row[k];
-                        if (e < 0) break;
-                        if (seen & (1u << e)) continue;
-                        seen |= 1u << e;
-                        const int c1 = c_corner1[e], ax = c_edgeAxis[e];
-                        const int sx = cx + ((c1 >> 2) & 1), sy = cy + ((c1 >> 1) & 1), sz = cz + (c1 & 1);
-                        const bool fx = (ax == 0) || (sx == cx + 1) || (sx == 0), fy = (ax == 1) || (sy == cy + 1) || (sy == 0),
-                                   fz = (ax == 2) || (sz == cz + 1) || (sz == 0);
-                        if (fx && fy && fz) { newMask |= 1u << k; nNew++; }
-                    }
-                }
-                uint32_t total;
-                const uint32_t ex = block_excl_scan(S, nNew, total) + carry;
-                carry += total;
-                if (c < 343 && nNew) {
-                    const int cx = c / 49, cy = (c / 7) % 7, cz = c % 7;
-                    const int8_t* row = &S.tri[S.cellCase[c] * 16];
-                    uint32_t id = ex;
-                    for (int k = 0; k < 16; k++) {
-                        if (!(newMask >> k)) break;
-                        if (!((newMask >> k) & 1u)) continue;
-                        const int e = row[k];
-                        const int c1 = c_corner1[e], ax = c_edgeAxis[e];
-                        const int sx = cx + ((c1 >> 2) & 1), sy = cy + ((c1 >> 1) & 1), sz = cz + (c1 & 1);
-                        const int eb = (sx * 8 + sy * 64 + sz) * 3 + ax;
-                        S.edgeVid[eb] = (uint16_t)id;
-                        // rank of this edge in the MPU's crossing-edge mask -> where vertex_kernel must put its vertex
-                        const uint32_t rank = S.edgeP[eb >> 5] + __popc(S.edgeW[eb >> 5] & ((1u << (eb & 31)) - 1u));
-                        mo.vperm[vbase + rank] = (uint16_t)id;
-                        id++;
-                    }
-                }
-            }
-            __syncthreads();
-        }
-
-        // ---- triangles in cell order
-        uint32_t carryT = 0;
-        for (int round = 0; round < 3; round++) {
-            const int c = round * kThreads + t;
-            const uint32_t cfg = (c < 343) ? S.cellCase[c] : 0u;
-            const uint32_t nTri = c_nTriE[cfg];
-            uint32_t total;
-            const uint32_t ex = block_excl_scan(S, nTri, total) + carryT;
-            carryT += total;
-            if (nTri) {
-                const int cx = c / 49, cy = (c / 7) % 7, cz = c % 7;
-                const int8_t* row = &S.tri[cfg * 16];
-                for (uint32_t k = 0; k < nTri * 3; k++) {
-                    const int e = row[k];
-                    const int c1 = c_corner1[e], ax = c_edgeAxis[e];
-                    int sx = cx + ((c1 >> 2) & 1), sy = cy + ((c1 >> 1) & 1), sz = cz + (c1 & 1);
-                    uint32_t vid;
-                    if (perMpu) vid = S.edgeVid[(sx * 8 + sy * 64 + sz) * 3 + ax];
-                    else {
-                        const int dI = (sx == 7 && ax != 0 && r.x != G.hi[0] - 1) ? 1 : 0;
-                        const int dJ = (sy == 7 && ax != 1 && r.y != G.hi[1] - 1) ? 1 : 0;
-                        const int dK = (sz == 7 && ax != 2 && r.z != G.hi[2] - 1) ? 1 : 0;
-                        if ((dI | dJ | dK) == 0) {
-                            const int eb = (sx * 8 + sy * 64 + sz) * 3 + ax;
-                            vid = vbase + S.edgeP[eb >> 5] + __popc(S.edgeW[eb >> 5] & ((1u << (eb & 31)) - 1u));
-                        } else {
-                            sx -= 7 * dI; sy -= 7 * dJ; sz -= 7 * dK;
-                            const int32_t nc = candOfMpu[((size_t)(r.x + dI - G.lo[0]) * ny + (r.y + dJ - G.lo[1])) * nz + (r.z + dK - G.lo[2])];
-                            const int eb = (sx * 8 + sy * 64 + sz) * 3 + ax;
-                            const uint32_t w = fo.edgeMask[(size_t)nc * 48 + (eb >> 5)];
-                            vid = mo.vbase[nc] + fo.edgePrefix[(size_t)nc * 48 + (eb >> 5)] + __popc(w & ((1u << (eb & 31)) - 1u));
+            // reference vertex order: a vertex is created by the first cell (i outer, k inner) whose table row names its edge, in
+            // row order (PS_Polygonizer.cpp:647-808). The first cell of edge (corner c, axis a) is c with the two non-axis
+            // coordinates decremented (clipped at 0).
+            uint32_t newMask[kCellsPerLane];
+            uint32_t nNew = 0;
+            {
+                int x = x0, y = y0, z = z0;
+#pragma unroll
+                for (int i = 0; i < kCellsPerLane; i++) {
+                    uint32_t nm = 0;
+                    if (c0 + i < 343) {
+                        const int8_t* row = &sTri[((cf[i >> 2] >> ((i & 3) * 8)) & 255u) * 16];
+                        uint32_t seen = 0;
+                        for (int k = 0; k < 16; k++) {
+                            const int e = row[k];
+                            if (e < 0) break;
+                            if (seen & (1u << e)) continue;
+                            seen |= 1u << e;
+                            const int c1 = edge_corner1(e), ax = edge_axis(e);
+                            const int sx = x + ((c1 >> 2) & 1), sy = y + ((c1 >> 1) & 1), sz = z + (c1 & 1);
+                            const bool fx = (ax == 0) || (sx == x + 1) || (sx == 0), fy = (ax == 1) || (sy == y + 1) || (sy == 0),
+                                       fz = (ax == 2) || (sz == z + 1) || (sz == 0);
+                            if (fx && fy && fz) { nm |= 1u << k; nNew++; }
                         }
                     }
-                    mo.tri[(size_t)(tbase + ex) * 3 + k] = vid;
+                    newMask[i] = nm;
+                    if (++z == 7) { z = 0; if (++y == 7) { y = 0; x++; } }
                 }
             }
+            uint32_t total;
+            uint32_t id = warp_excl_scan(nNew, total);
+            {
+                int x = x0, y = y0, z = z0;
+#pragma unroll
+                for (int i = 0; i < kCellsPerLane; i++) {
+                    uint32_t nm = newMask[i];
+                    if (nm) {
+                        const int8_t* row = &sTri[((cf[i >> 2] >> ((i & 3) * 8)) & 255u) * 16];
+                        while (nm) {
+                            const int k = __ffs((int)nm) - 1;
+                            nm &= nm - 1u;
+                            const int e = row[k];
+                            const int c1 = edge_corner1(e), ax = edge_axis(e);
+                            const int sx = x + ((c1 >> 2) & 1), sy = y + ((c1 >> 1) & 1), sz = z + (c1 & 1);
+                            const int eb = (sx * 8 + sy * 64 + sz) * 3 + ax;
+                            S.edgeVid[eb] = (uint16_t)id;
+                            // rank of this edge in the MPU's crossing-edge mask -> where vertex_kernel must put its vertex
+                            const uint32_t rank = S.edgeP[eb >> 5] + __popc(S.edgeW[eb >> 5] & ((1u << (eb & 31)) - 1u));
+                            mo.vperm[vbase + rank] = (uint16_t)id;
+                            id++;
+                        }
+                    }
+                    if (++z == 7) { z = 0; if (++y == 7) { y = 0; x++; } }
+                }
+            }
+            __syncwarp();
         }
-        if (perMpu && t == 0 && mo.mixedIdx) {
+
+        // ---- surface cells compacted in cell order, then one TRIANGLE per lane (3 indices, 12 contiguous bytes per lane)
+        uint32_t totalT, totalA;
+        {
+            uint32_t nAct = 0;
+#pragma unroll
+            for (int i = 0; i < kCellsPerLane; i++) nAct += (sNTri[(cf[i >> 2] >> ((i & 3) * 8)) & 255u] != 0) ? 1u : 0u;
+            uint32_t ex = warp_excl_scan(nT, totalT);
+            uint32_t slot = warp_excl_scan(nAct, totalA);
+#pragma unroll
+            for (int i = 0; i < kCellsPerLane; i++) {
+                const uint32_t cfg = (cf[i >> 2] >> ((i & 3) * 8)) & 255u;
+                const uint32_t nTri = sNTri[cfg];  // 0 for the padding cells (case 0)
+                if (nTri) { S.cellList[slot++] = (uint32_t)(c0 + i) | (cfg << 9) | (ex << 17); ex += nTri; }
+            }
+        }
+        __syncwarp();
+        for (uint32_t t = lane; t < totalT; t += 32) {
+            int lo = 0, hi = (int)totalA - 1;  // last surface cell whose triangle offset <= t
+            while (lo < hi) {
+                const int mid = (lo + hi + 1) >> 1;
+                if ((S.cellList[mid] >> 17) <= t) lo = mid; else hi = mid - 1;
+            }
+            const uint32_t ent = S.cellList[lo];
+            const int cell = (int)(ent & 511u);
+            const int x = cell / 49, y = (cell - x * 49) / 7, z = cell - x * 49 - y * 7;
+            const int8_t* row = &sTri[((ent >> 9) & 255u) * 16 + (t - (ent >> 17)) * 3];
+            uint32_t vid3[3];
+#pragma unroll
+            for (int k = 0; k < 3; k++) {
+                const int e = row[k];
+                const int c1 = edge_corner1(e), ax = edge_axis(e);
+                int sx = x + ((c1 >> 2) & 1), sy = y + ((c1 >> 1) & 1), sz = z + (c1 & 1);
+                uint32_t vid;
+                if (perMpu) vid = S.edgeVid[(sx * 8 + sy * 64 + sz) * 3 + ax];
+                else {
+                    const int dI = (sx == 7 && ax != 0 && r.x != G.hi[0] - 1) ? 1 : 0;
+                    const int dJ = (sy == 7 && ax != 1 && r.y != G.hi[1] - 1) ? 1 : 0;
+                    const int dK = (sz == 7 && ax != 2 && r.z != G.hi[2] - 1) ? 1 : 0;
+                    if ((dI | dJ | dK) == 0) {
+                        const int eb = (sx * 8 + sy * 64 + sz) * 3 + ax;
+                        vid = vbase + S.edgeP[eb >> 5] + __popc(S.edgeW[eb >> 5] & ((1u << (eb & 31)) - 1u));
+                    } else {
+                        sx -= 7 * dI; sy -= 7 * dJ; sz -= 7 * dK;
+                        const int32_t nc = candOfMpu[((size_t)(r.x + dI - G.lo[0]) * ny + (r.y + dJ - G.lo[1])) * nz + (r.z + dK - G.lo[2])];
+                        const int eb = (sx * 8 + sy * 64 + sz) * 3 + ax;
+                        const uint32_t w = fo.edgeMask[(size_t)nc * 48 + (eb >> 5)];
+                        vid = mo.vbase[nc] + fo.edgePrefix[(size_t)nc * 48 + (eb >> 5)] + __popc(w & ((1u << (eb & 31)) - 1u));
+                    }
+                }
+                vid3[k] = vid;
+            }
+            uint32_t* o = mo.tri + (size_t)(tbase + t) * 3;
+            o[0] = vid3[0]; o[1] = vid3[1]; o[2] = vid3[2];
+        }
+        if (perMpu && lane == 0 && mo.mixedIdx) {
             const uint32_t mi = mo.mixedIdx[cand];
             mo.mpuIjk[mi * 3] = r.x; mo.mpuIjk[mi * 3 + 1] = r.y; mo.mpuIjk[mi * 3 + 2] = r.z;
             mo.mpuVbase[mi] = vbase; mo.mpuTbase[mi] = tbase;
         }
-        __syncthreads();
-        m = S.next;
-        __syncthreads();
+        int nxt = 0;
+        if (lane == 0) nxt = (int)atomicAdd(&fo.counters[3], 1u) + warpsTotal;
+        m = __shfl_sync(0xffffffffu, nxt, 0);
     }
 }
 
@@ -427,7 +477,8 @@ void launch_emit_kernels(const GridParams& G, const Region* cands, const float4*
         cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSM, tri_kernel, kThreads, 0);
         if (perSM < 1) perSM = 1;
         int grid = numSMs * perSM;
-        if (grid > nMixed) grid = nMixed;
+        const int needT = (nMixed + kThreads / 32 - 1) / (kThreads / 32);
+        if (grid > needT) grid = needT;
         tri_kernel<<<grid, kThreads, 0, st>>>(G, cands, fo, mo, candOfMpu, nMixed);
     }
     const bool strict = (G.sem == PSGPU_SEM_SIMD);
