@@ -239,7 +239,7 @@ def run_gpu(args):
     if rank == 0:
         sampler.start()
     dev_ms, launches, stats_sum = 0.0, 0, None
-    field_ms = emit_ms = cull_ms = scan_ms = 0.0
+    field_ms = emit_ms = cull_ms = scan_ms = tri_ms = vertex_ms = color_ms = 0.0
     for _ in range(args.steps):
         flush.fill_(1)  # L2 flush between steps (untimed)
         torch.cuda.synchronize()
@@ -252,6 +252,7 @@ def run_gpu(args):
         # (16 B per rank) is added from its wall time when sharded
         dev_ms += st["ms_total"] + (max(0.0, wall - st["ms_total"]) if world > 1 else 0.0)
         field_ms += st["ms_field"]; emit_ms += st["ms_emit"]; cull_ms += st["ms_cull"]; scan_ms += st["ms_scan"]
+        tri_ms += st["ms_tri"]; vertex_ms += st["ms_vertex"]; color_ms += st["ms_color"]
         launches += st["gpu_launches"]
     barrier()
     clocks = sampler.stop() if rank == 0 else None
@@ -307,7 +308,6 @@ def run_gpu(args):
     launches_all = allsum(float(launches))
     h2d = prog.n_quads * 16 + prog.n_prims * 12
     d2h = nv * 36 + nt * 12
-    field_ms_r0, emit_ms_r0 = field_ms / args.steps, emit_ms / args.steps
     flops = float(st["algorithmic_flops"])
     nat_ms_max = allmax(nat_ms)
     if world > 1:
@@ -321,16 +321,36 @@ def run_gpu(args):
     fp32_tflops, _ = ctx.fp32_peak()
     sec = dev_ms_max * 1e-3
     value = cells_total * args.steps / sec
-    # roofline of the dominant kernel (rank 0's share of the step)
-    emit_bytes = float(st["mpus_evaluated"]) * 2048 + float(st["mpus_crossed"]) * (2048 + 343 + 48 * 6) + nv * 36.0 + nt * 12.0
-    roof_field = {"bound": "fp32", "kernel": "field_kernel", "achieved": flops / (field_ms_r0 * 1e-3) / 1e12, "peak": fp32_tflops, "unit": "TFLOP/s",
-                  "frac": flops / (field_ms_r0 * 1e-3) / 1e12 / fp32_tflops, "traffic": None,
-                  "peak_source": "FFMA-chain microbenchmark run in this process (MEASURED_PEAKS.json has no fp32 figure)",
-                  "algorithmic_flops_per_launch": flops, "ms_per_launch": field_ms_r0}
-    roof_emit = {"bound": "hbm", "kernel": "emit_kernel", "achieved": emit_bytes / (emit_ms_r0 * 1e-3) / 1e9, "peak": peaks["hbm_gbs"], "unit": "GB/s",
-                 "frac": emit_bytes / (emit_ms_r0 * 1e-3) / 1e9 / peaks["hbm_gbs"], "traffic": None, "peak_source": peak_src,
-                 "algorithmic_bytes_per_launch": emit_bytes, "ms_per_launch": emit_ms_r0}
-    dominant, other = (roof_field, roof_emit) if field_ms_r0 >= emit_ms_r0 else (roof_emit, roof_field)
+    # ---- rooflines, rank 0's launches (DESIGN.md section 5 states the per-unit figures):
+    #   field_kernel / vertex_kernel / color_kernel  FP32 pipe: SURVEY 8(d) op counts of every MPU's pruned program x points evaluated
+    #   tri_kernel                                   HBM: per surface MPU 2 KB field cache + 288 B edge masks read, 12 B per triangle written
+    K = float(args.steps)
+    traffic = {}
+    tp = os.path.join(ROOT, "profiles", "traffic.json")  # dram__bytes_read+write per launch from the committed ncu --set full capture
+    if os.path.exists(tp) and world == 1:
+        try:
+            traffic = json.load(open(tp)).get(w["name"], {})
+        except Exception:
+            traffic = {}
+    fp32_src = "FFMA-chain microbenchmark run in this process (MEASURED_PEAKS.json has no fp32 figure)"
+
+    def roof_fp32(name, fl, ms):
+        ach = fl / max(ms, 1e-9) / 1e9
+        return {"bound": "fp32", "kernel": name, "achieved": ach, "peak": fp32_tflops, "unit": "TFLOP/s", "frac": ach / fp32_tflops,
+                "traffic": traffic.get(name), "peak_source": fp32_src, "algorithmic_flops_per_launch": fl, "ms_per_launch": ms}
+
+    def roof_hbm(name, by, ms):
+        ach = by / max(ms, 1e-9) / 1e6
+        return {"bound": "hbm", "kernel": name, "achieved": ach, "peak": peaks["hbm_gbs"], "unit": "GB/s", "frac": ach / peaks["hbm_gbs"],
+                "traffic": traffic.get(name), "peak_source": peak_src, "algorithmic_bytes_per_launch": by, "ms_per_launch": ms}
+
+    vflops = float(st["vertex_eval_flops"])
+    tri_bytes = float(st["mpus_crossed"]) * (2048 + 288 + 8) + nt * 12.0
+    roofs = [roof_fp32("field_kernel", flops, field_ms / K), roof_fp32("vertex_kernel", 8.0 * vflops, vertex_ms / K),
+             roof_fp32("color_kernel", vflops, color_ms / K), roof_hbm("tri_kernel", tri_bytes, tri_ms / K)]
+    roofs.sort(key=lambda r: -r["ms_per_launch"])
+    dominant, other = roofs[0], roofs[1:]
+    field_ms_r0, emit_ms_r0 = field_ms / K, emit_ms / K
 
     out = {
         "metric": "MC cells/s", "value": value, "unit": "cells/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
@@ -344,7 +364,8 @@ def run_gpu(args):
         "triangles_per_s": tris * args.steps / sec / args.steps * 1.0,
         "ms_per_polygonization": dev_ms_max / args.steps,
         "mesh": {"vertices": int(verts), "triangles": int(tris)},
-        "stage_ms_rank0": {"cull": cull_ms / args.steps, "field": field_ms_r0, "scan": scan_ms / args.steps, "emit": emit_ms_r0},
+        "stage_ms_rank0": {"cull": cull_ms / args.steps, "field": field_ms_r0, "scan": scan_ms / args.steps, "emit": emit_ms_r0,
+                           "tri": tri_ms / K, "vertex": vertex_ms / K, "color": color_ms / K},
         "mpus_rank0": {"total": st["mpus_total"], "evaluated": st["mpus_evaluated"], "crossed": st["mpus_crossed"]},
         "e2e": {"value": cells_total * args.steps / e2e_s_max, "unit": "cells/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
                 "ms_per_step": 1e3 * e2e_s_max / args.steps},

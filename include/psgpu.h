@@ -96,6 +96,11 @@ typedef struct psgpu_stats {
     int64_t pruned_quads;     /* total size of all per-MPU pruned programs */
     float ms_cull, ms_field, ms_scan, ms_emit, ms_total; /* CUDA-event times of the last polygonize */
     int64_t gpu_launches;     /* kernels launched by the last polygonize */
+    float ms_tri, ms_vertex, ms_color; /* the three kernels inside ms_emit */
+    float reserved0;
+    int64_t vertex_eval_flops; /* collect_stats: sum over surface MPUs of vertices x SURVEY 8(d) op count of the MPU's pruned program,
+                                  i.e. the algorithmic work of ONE field evaluation per vertex (a vertex costs 8: 4 root samples,
+                                  4 gradient samples; its colour walk 1 more) */
 } psgpu_stats;
 
 /* ---- context ---- */

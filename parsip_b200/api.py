@@ -77,7 +77,8 @@ class _Stats(C.Structure):
         ("mpus_total", C.c_int64), ("mpus_evaluated", C.c_int64), ("mpus_crossed", C.c_int64), ("field_evals", C.c_int64),
         ("prim_evals", C.c_int64), ("algorithmic_flops", C.c_int64), ("program_quads", C.c_int64), ("pruned_quads", C.c_int64),
         ("ms_cull", C.c_float), ("ms_field", C.c_float), ("ms_scan", C.c_float), ("ms_emit", C.c_float), ("ms_total", C.c_float),
-        ("gpu_launches", C.c_int64),
+        ("gpu_launches", C.c_int64), ("ms_tri", C.c_float), ("ms_vertex", C.c_float), ("ms_color", C.c_float), ("reserved0", C.c_float),
+        ("vertex_eval_flops", C.c_int64),
     ]
 
 

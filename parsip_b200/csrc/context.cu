@@ -64,7 +64,7 @@ struct psgpu_ctx {
     uint32_t* hostScalars = nullptr;  // pinned readback
     void* hostStage = nullptr;        // pinned upload staging (program + colours)
     size_t hostStageCap = 0;
-    cudaEvent_t ev[6];
+    cudaEvent_t ev[8];
     psgpu_mesh last{};
     psgpu_stats stats{};
     psgpu::Region* cands = nullptr;
@@ -353,19 +353,19 @@ int polygonize_impl(psgpu_ctx* ctx, const psgpu_params* P, psgpu_mesh* out, bool
         CK(cudaEventRecord(ctx->ev[3], st));
         if (nMixed > 0) {
             launch_emit_kernels(G, ctx->cands, ctx->pool.as<float4>(), ctx->colors.as<float>(), fo, mo, ctx->candOfMpu.as<int32_t>(), (int)nMixed,
-                                maxLen, ctx->numSMs, st);
+                                maxLen, ctx->numSMs, st, ctx->ev[5], ctx->ev[6]);
             launches += 2 + (G.wantColors ? 1 : 0);  // tri_kernel, vertex_kernel, color_kernel
         }
         CK(cudaEventRecord(ctx->ev[4], st));
         if (P->collect_stats) {
             CK(ctx->statsAcc.reserve(64));
             CK(cudaMemsetAsync(ctx->statsAcc.p, 0, 64, st));
-            launch_program_stats(ctx->cands, nCand, ctx->pool.as<float4>(), nullptr, ctx->statsAcc.as<unsigned long long>(), st);
+            launch_program_stats(ctx->cands, nCand, ctx->pool.as<float4>(), fo.vcount, ctx->statsAcc.as<unsigned long long>(), st);
             launches++;
-            unsigned long long acc[4];
-            CK(cudaMemcpyAsync(acc, ctx->statsAcc.p, 32, cudaMemcpyDeviceToHost, st));
+            unsigned long long acc[5];
+            CK(cudaMemcpyAsync(acc, ctx->statsAcc.p, 40, cudaMemcpyDeviceToHost, st));
             CK(cudaStreamSynchronize(st));
-            S.algorithmic_flops = (int64_t)acc[0]; S.prim_evals = (int64_t)acc[1];
+            S.algorithmic_flops = (int64_t)acc[0]; S.prim_evals = (int64_t)acc[1]; S.vertex_eval_flops = (int64_t)acc[4];
         }
     } else {
         CK(cudaEventRecord(ctx->ev[2], st)); CK(cudaEventRecord(ctx->ev[3], st)); CK(cudaEventRecord(ctx->ev[4], st));
@@ -380,6 +380,11 @@ int polygonize_impl(psgpu_ctx* ctx, const psgpu_params* P, psgpu_mesh* out, bool
     cudaEventElapsedTime(&S.ms_scan, ctx->ev[2], ctx->ev[3]);
     cudaEventElapsedTime(&S.ms_emit, ctx->ev[3], ctx->ev[4]);
     cudaEventElapsedTime(&S.ms_total, ctx->ev[0], ctx->ev[4]);
+    if (nMixed > 0) {
+        cudaEventElapsedTime(&S.ms_tri, ctx->ev[3], ctx->ev[5]);
+        cudaEventElapsedTime(&S.ms_vertex, ctx->ev[5], ctx->ev[6]);
+        cudaEventElapsedTime(&S.ms_color, ctx->ev[6], ctx->ev[4]);
+    }
     S.mpus_crossed = nMixed;
     const int evalsPerVertex = (P->root_mode == PSGPU_ROOT_FOURSAMPLE) ? 8 : 14;
     S.field_evals = (int64_t)nCand * 512 + (int64_t)nV * evalsPerVertex;

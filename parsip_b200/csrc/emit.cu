@@ -470,7 +470,8 @@ __global__ void __launch_bounds__(kThreads) color_kernel(GridParams G, const Reg
 }  // namespace
 
 void launch_emit_kernels(const GridParams& G, const Region* cands, const float4* pool, const float* colorTab, const FieldOutputs& fo,
-                         const MeshOutputs& mo, const int32_t* candOfMpu, int nMixed, uint32_t maxProgQuads, int numSMs, cudaStream_t st) {
+                         const MeshOutputs& mo, const int32_t* candOfMpu, int nMixed, uint32_t maxProgQuads, int numSMs, cudaStream_t st,
+                         cudaEvent_t evTriDone, cudaEvent_t evVertexDone) {
     if (nMixed <= 0) return;
     {
         int perSM = 0;
@@ -480,6 +481,7 @@ void launch_emit_kernels(const GridParams& G, const Region* cands, const float4*
         const int needT = (nMixed + kThreads / 32 - 1) / (kThreads / 32);
         if (grid > needT) grid = needT;
         tri_kernel<<<grid, kThreads, 0, st>>>(G, cands, fo, mo, candOfMpu, nMixed);
+        if (evTriDone) cudaEventRecord(evTriDone, st);
     }
     const bool strict = (G.sem == PSGPU_SEM_SIMD);
     // per-warp staging slice = the longest list (multiple of 8 quads); up to 32 KB of dynamic shared memory per CTA
@@ -502,6 +504,7 @@ void launch_emit_kernels(const GridParams& G, const Region* cands, const float4*
     int grid = numSMs * perSM;
     if (grid > need) grid = need;
     k<<<grid, kThreads, smem, st>>>(G, cands, pool, fo, mo, nMixed, slice);
+    if (evVertexDone) cudaEventRecord(evVertexDone, st);
     if (G.wantColors) {
         using ColorT = void (*)(GridParams, const Region*, const float4*, const float*, FieldOutputs, MeshOutputs, int, uint32_t);
         const ColorT kc = strict ? (smemOk ? color_kernel<true, true> : color_kernel<true, false>)

@@ -213,9 +213,9 @@ __global__ void __launch_bounds__(128) points_fcn_kernel(const float4* __restric
 // exact SURVEY 8(d) bookkeeping over the final per-MPU programs: acc[0] += 512 * flops, acc[1] += 512 * prims,
 // acc[2] += quads, acc[3] += 512 (corner evaluations)
 __global__ void program_stats_kernel(const Region* __restrict__ cands, int nCand, const float4* __restrict__ pool,
-                                     unsigned long long* __restrict__ acc) {
+                                     const uint32_t* __restrict__ vcount, unsigned long long* __restrict__ acc) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    unsigned long long fl = 0, pr = 0, qd = 0, ev = 0;
+    unsigned long long fl = 0, pr = 0, qd = 0, ev = 0, vf = 0;
     if (i < nCand) {
         const Region r = cands[i];
         const float4* p = pool + r.off;
@@ -227,14 +227,16 @@ __global__ void program_stats_kernel(const Region* __restrict__ cands, int nCand
             pc += ps_instr_quads(hdr);
         }
         qd = r.len; ev = 512;
+        if (vcount) vf = fl * vcount[i];
         fl *= 512; pr *= 512;
     }
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) {
         fl += __shfl_xor_sync(0xffffffffu, fl, o); pr += __shfl_xor_sync(0xffffffffu, pr, o);
         qd += __shfl_xor_sync(0xffffffffu, qd, o); ev += __shfl_xor_sync(0xffffffffu, ev, o);
+        vf += __shfl_xor_sync(0xffffffffu, vf, o);
     }
-    if ((threadIdx.x & 31) == 0 && ev) { atomicAdd(&acc[0], fl); atomicAdd(&acc[1], pr); atomicAdd(&acc[2], qd); atomicAdd(&acc[3], ev); }
+    if ((threadIdx.x & 31) == 0 && ev) { atomicAdd(&acc[0], fl); atomicAdd(&acc[1], pr); atomicAdd(&acc[2], qd); atomicAdd(&acc[3], ev); atomicAdd(&acc[4], vf); }
 }
 
 // FP32 FMA-chain microbenchmark: 8 independent FFMA chains per thread, 2048 threads per SM
@@ -303,9 +305,9 @@ void launch_points_field_color_normal(const float4* prog, const float* colorTab,
     else points_fcn_kernel<false><<<(unsigned)((n + 127) / 128), 128, 0, st>>>(prog, colorTab, xyz, n, f, col, nrm, sem);
 }
 
-void launch_program_stats(const Region* cands, int nCand, const float4* pool, const uint32_t*, unsigned long long* acc, cudaStream_t st) {
+void launch_program_stats(const Region* cands, int nCand, const float4* pool, const uint32_t* vcount, unsigned long long* acc, cudaStream_t st) {
     if (nCand <= 0) return;
-    program_stats_kernel<<<(nCand + 127) / 128, 128, 0, st>>>(cands, nCand, pool, acc);
+    program_stats_kernel<<<(nCand + 127) / 128, 128, 0, st>>>(cands, nCand, pool, vcount, acc);
 }
 
 float run_fp32_peak(int numSMs, cudaStream_t st, float* ms_out) {

@@ -83,7 +83,8 @@ float run_fp32_peak(int numSMs, cudaStream_t st, float* ms_out);
 
 // emit.cu
 void launch_emit_kernels(const GridParams& G, const Region* cands, const float4* pool, const float* colorTab, const FieldOutputs& fo,
-                         const MeshOutputs& mo, const int32_t* candOfMpu, int nMixed, uint32_t maxProgQuads, int numSMs, cudaStream_t st);
+                         const MeshOutputs& mo, const int32_t* candOfMpu, int nMixed, uint32_t maxProgQuads, int numSMs, cudaStream_t st,
+                         cudaEvent_t evTriDone = nullptr, cudaEvent_t evVertexDone = nullptr);
 
 }  // namespace psgpu
 #endif

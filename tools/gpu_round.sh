@@ -13,3 +13,8 @@ if [ "$1" = "ncu" ]; then
   timeout 1200 ncu --set full --clock-control none --import-source on -k regex:'field_kernel|tri_kernel|vertex_kernel|color_kernel' -s 4 -c 4 -o gpurun_out/prof -f python tools/prof_step.py > gpurun_out/ncu_full.log 2>&1
   tail -3 gpurun_out/ncu_list.log gpurun_out/ncu_full.log; cat gpurun_out/plain.log
 fi
+if [ "$1" = "ncu" ]; then
+  timeout 300 python tools/prof_step.py --native > gpurun_out/plain_native.log 2>&1 &&
+  timeout 1200 ncu --set full --clock-control none --import-source on -k regex:'field_kernel|vertex_kernel' -s 2 -c 2 -o gpurun_out/prof_native -f python tools/prof_step.py --native > gpurun_out/ncu_full_native.log 2>&1
+  tail -2 gpurun_out/ncu_full_native.log
+fi
