@@ -46,6 +46,7 @@ struct psgpu_ctx {
     int device = 0;
     int numSMs = 148;
     cudaStream_t stream = nullptr;
+    cudaStream_t copyStream = nullptr;  // device -> host mesh copies that overlap the emission kernels (psgpu_polygonize_host)
     std::string err;
     // program
     uint32_t progQuads = 0;
@@ -96,6 +97,7 @@ extern "C" int psgpu_create(int device, psgpu_ctx** out) {
     ctx->device = device;
     cudaDeviceGetAttribute(&ctx->numSMs, cudaDevAttrMultiProcessorCount, device);
     if (cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking) != cudaSuccess) { delete ctx; return PSGPU_ERROR_CUDA; }
+    if (cudaStreamCreateWithFlags(&ctx->copyStream, cudaStreamNonBlocking) != cudaSuccess) { delete ctx; return PSGPU_ERROR_CUDA; }
     for (auto& e : ctx->ev) cudaEventCreate(&e);
     cudaMallocHost(&ctx->hostScalars, 64 * sizeof(uint32_t));
     *out = ctx;
@@ -115,6 +117,7 @@ extern "C" int psgpu_destroy(psgpu_ctx* ctx) {
     for (auto& e : ctx->ev) cudaEventDestroy(e);
     if (ctx->hostScalars) cudaFreeHost(ctx->hostScalars);
     if (ctx->hostStage) cudaFreeHost(ctx->hostStage);
+    cudaStreamDestroy(ctx->copyStream);
     cudaStreamDestroy(ctx->stream);
     delete ctx;
     return PSGPU_SUCCESS;
@@ -274,7 +277,14 @@ int run_cull(psgpu_ctx* ctx, const GridParams& G, int cullMode, bool colorExact,
     return PSGPU_SUCCESS;
 }
 
-int polygonize_impl(psgpu_ctx* ctx, const psgpu_params* P, psgpu_mesh* out, bool forceFv) {
+// caller-provided HOST buffers the mesh is streamed into while the emission kernels still run
+struct HostSink {
+    float *pos, *nrm, *col;
+    uint32_t* tri;
+    int64_t capV, capT;
+};
+
+int polygonize_impl(psgpu_ctx* ctx, const psgpu_params* P, psgpu_mesh* out, bool forceFv, const HostSink* sink = nullptr) {
     if (!ctx || !P || ctx->progQuads == 0) return PSGPU_PARAM_ERROR;
     CK(cudaSetDevice(ctx->device));
     cudaStream_t st = ctx->stream;
@@ -303,6 +313,7 @@ int polygonize_impl(psgpu_ctx* ctx, const psgpu_params* P, psgpu_mesh* out, bool
     psgpu_mesh M{};
     for (int a = 0; a < 3; a++) M.lattice[a] = G.dims[a];
     uint32_t nV = 0, nT = 0, nMixed = 0, nOver = 0;
+    bool streamed = false;
     if (nCand > 0) {
         const size_t n1 = (size_t)nCand + 1;
         CK(ctx->fv.reserve((size_t)nCand * 2048));
@@ -350,6 +361,12 @@ int polygonize_impl(psgpu_ctx* ctx, const psgpu_params* P, psgpu_mesh* out, bool
             CK(cudaMemcpyAsync(ctx->mpuVbase.as<uint32_t>() + nMixed, ctx->vbase.as<uint32_t>() + nCand, 4, cudaMemcpyDeviceToDevice, st));
             CK(cudaMemcpyAsync(ctx->mpuTbase.as<uint32_t>() + nMixed, ctx->tbase.as<uint32_t>() + nCand, 4, cudaMemcpyDeviceToDevice, st));
         }
+        if (sink && ((int64_t)nV > sink->capV || (int64_t)nT > sink->capT)) {
+            ctx->err = "host buffers too small";
+            M.n_vertices = nV; M.n_triangles = nT;
+            if (out) *out = M;
+            return PSGPU_NOT_ENOUGH_MEM;
+        }
         CK(cudaEventRecord(ctx->ev[3], st));
         if (nMixed > 0) {
             launch_emit_kernels(G, ctx->cands, ctx->pool.as<float4>(), ctx->colors.as<float>(), fo, mo, ctx->candOfMpu.as<int32_t>(), (int)nMixed,
@@ -357,6 +374,19 @@ int polygonize_impl(psgpu_ctx* ctx, const psgpu_params* P, psgpu_mesh* out, bool
             launches += 2 + (G.wantColors ? 1 : 0);  // tri_kernel, vertex_kernel, color_kernel
         }
         CK(cudaEventRecord(ctx->ev[4], st));
+        if (sink && nMixed > 0 && P->output == PSGPU_OUT_INDEXED) {
+            // each array leaves for the host as soon as the kernel that writes it is done: triangles behind tri_kernel (while
+            // vertex_kernel runs), positions + normals behind vertex_kernel (while color_kernel runs), colours last
+            cudaStream_t cs = ctx->copyStream;
+            CK(cudaStreamWaitEvent(cs, ctx->ev[5], 0));
+            if (sink->tri && nT) CK(cudaMemcpyAsync(sink->tri, ctx->tri.p, (size_t)nT * 12, cudaMemcpyDeviceToHost, cs));
+            CK(cudaStreamWaitEvent(cs, ctx->ev[6], 0));
+            if (sink->pos && nV) CK(cudaMemcpyAsync(sink->pos, ctx->pos.p, (size_t)nV * 12, cudaMemcpyDeviceToHost, cs));
+            if (sink->nrm && nV && P->want_normals) CK(cudaMemcpyAsync(sink->nrm, ctx->nrm.p, (size_t)nV * 12, cudaMemcpyDeviceToHost, cs));
+            CK(cudaStreamWaitEvent(cs, ctx->ev[4], 0));
+            if (sink->col && nV && P->want_colors) CK(cudaMemcpyAsync(sink->col, ctx->col.p, (size_t)nV * 12, cudaMemcpyDeviceToHost, cs));
+            streamed = true;
+        }
         if (P->collect_stats) {
             CK(ctx->statsAcc.reserve(64));
             CK(cudaMemsetAsync(ctx->statsAcc.p, 0, 64, st));
@@ -371,6 +401,7 @@ int polygonize_impl(psgpu_ctx* ctx, const psgpu_params* P, psgpu_mesh* out, bool
         CK(cudaEventRecord(ctx->ev[2], st)); CK(cudaEventRecord(ctx->ev[3], st)); CK(cudaEventRecord(ctx->ev[4], st));
     }
     CK(cudaStreamSynchronize(st));
+    if (streamed) CK(cudaStreamSynchronize(ctx->copyStream));
     {
         cudaError_t e = cudaGetLastError();
         if (e != cudaSuccess) { ctx->err = std::string("kernel failure: ") + cudaGetErrorString(e); return PSGPU_ERROR_CUDA; }
@@ -400,6 +431,7 @@ int polygonize_impl(psgpu_ctx* ctx, const psgpu_params* P, psgpu_mesh* out, bool
         ctx->err = "MPU mesh exceeds the reference's 512 vertex/triangle capacity (SURVEY Q10)";
         return PSGPU_NOT_ENOUGH_MEM;
     }
+    if (sink && !streamed && (nV || nT)) return PSGPU_SUCCESS + 1;  // nothing was copied yet (per-MPU output): caller downloads
     return PSGPU_SUCCESS;
 }
 
@@ -429,14 +461,11 @@ extern "C" int psgpu_mesh_download(psgpu_ctx* ctx, float* pos, float* nrm, float
 extern "C" int psgpu_polygonize_host(psgpu_ctx* ctx, const psgpu_params* params, psgpu_mesh* out, float* pos, float* nrm, float* col,
                                      uint32_t* tri, int64_t cap_vertices, int64_t cap_triangles) {
     psgpu_mesh M{};
-    int rc = polygonize_impl(ctx, params, &M, false);
+    const HostSink sink{pos, nrm, col, tri, cap_vertices, cap_triangles};
+    int rc = polygonize_impl(ctx, params, &M, false, &sink);
     if (out) *out = M;
-    if (rc != PSGPU_SUCCESS) return rc;
-    if (M.n_vertices > cap_vertices || M.n_triangles > cap_triangles) {
-        ctx->err = "host buffers too small";
-        return PSGPU_NOT_ENOUGH_MEM;
-    }
-    return psgpu_mesh_download(ctx, pos, nrm, col, tri, nullptr, nullptr, nullptr);
+    if (rc == PSGPU_SUCCESS + 1) return psgpu_mesh_download(ctx, pos, nrm, col, tri, nullptr, nullptr, nullptr);
+    return rc;
 }
 
 extern "C" int psgpu_field_eval(psgpu_ctx* ctx, const float* xyz, int64_t n, float* f_out) {

@@ -210,3 +210,27 @@ def test_native_mesh_is_independent_of_culling_and_slab_sharding(ctx):
         # whole mesh, bit for bit; only the vertices on the cut planes exist once per side
         assert np.array_equal(s2.view(np.uint32), soup.view(np.uint32)), "slab stitching is not exact (world %d)" % world
         assert nv >= whole["n_vertices"]
+
+
+def test_polygonize_host_streams_the_same_mesh_and_checks_capacity(ctx):
+    """psgpu_polygonize_host copies each mesh array to the caller's HOST buffers behind the kernel that produced it (on a second
+    stream); the result must equal psgpu_polygonize + psgpu_mesh_download, in both output modes, and a buffer that is too small
+    is PSGPU_NOT_ENOUGH_MEM with the needed sizes reported."""
+    _, orc = simd_setup(ctx, "blob")
+    lo, hi = orc.bbox()
+    cs = scenes.cellsize_for(lo, hi, 64)
+    for prm in (ps.Params.make(cs, lo, hi, root_mode=ps.ROOT_FOURSAMPLE), compat_params(cs, lo, hi)):
+        ref = ctx.polygonize(prm)
+        nv, nt = ref["n_vertices"], ref["n_triangles"]
+        assert nv > 1000
+        pos, nrm, col = (np.full((nv + 7, 3), np.nan, np.float32) for _ in range(3))
+        tri = np.zeros((nt + 5, 3), np.uint32)
+        m = ctx.polygonize_host(prm, pos, nrm, col, tri)
+        assert (m["n_vertices"], m["n_triangles"]) == (nv, nt)
+        assert np.array_equal(bits(pos[:nv]), bits(ref["pos"])) and np.array_equal(bits(nrm[:nv]), bits(ref["nrm"]))
+        assert np.array_equal(bits(col[:nv]), bits(ref["col"])) and np.array_equal(tri[:nt], ref["tri"])
+        assert np.isnan(pos[nv:]).all()
+    small = np.zeros((10, 3), np.float32)
+    with pytest.raises(ps.PsGpuError) as e:
+        ctx.polygonize_host(prm, small, small.copy(), small.copy(), np.zeros((10, 3), np.uint32))
+    assert e.value.code == -2
