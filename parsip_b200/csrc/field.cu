@@ -21,7 +21,8 @@ __constant__ uint8_t c_nTri[256] = PS_MC_NTRI_INIT;
 
 namespace {
 
-constexpr int kThreads = 128;
+constexpr int kPts = 8;                 // z-consecutive corners per thread: a whole z-column of the 8x8x8 lattice
+constexpr int kThreads = 512 / kPts;    // 64: decode cost per interpreted instruction is shared by 8 points (ncu r01c: issue-bound on decode)
 constexpr uint32_t kMaxProgCapQuads = 1024;  // 16 KB per staging buffer; longer lists are read from global
 
 struct __align__(16) FieldSmemHeader {
@@ -30,6 +31,7 @@ struct __align__(16) FieldSmemHeader {
     uint32_t insideW[16];
     uint32_t edgeW[48];
     uint32_t warpSum[8];
+    uint8_t nTri[256];  // triangles per cube case (lanes look up different cases: shared memory, not __constant__)
     int next;
     int flags;
 };
@@ -37,7 +39,7 @@ struct __align__(16) FieldSmemHeader {
 // STAGED: every candidate list fits the staging buffers (the host checks the longest one) and is interpreted from shared memory;
 // the unstaged variant (brute-force mode, very long lists) reads the lists from global memory. One interpreter copy per kernel.
 template <bool STRICT, bool STAGED>
-__global__ void __launch_bounds__(kThreads, 6) field_kernel(GridParams G, const Region* __restrict__ cands, int nCand,
+__global__ void __launch_bounds__(kThreads, 8) field_kernel(GridParams G, const Region* __restrict__ cands, int nCand,
                                                          const float4* __restrict__ pool, FieldOutputs out, uint32_t capQuads) {
     extern __shared__ __align__(16) unsigned char smemRaw[];
     FieldSmemHeader& S = *reinterpret_cast<FieldSmemHeader*>(smemRaw);
@@ -50,6 +52,7 @@ __global__ void __launch_bounds__(kThreads, 6) field_kernel(GridParams G, const 
         mbar_init(&S.bar[1], 1);
         fence_mbar_init();
     }
+    for (int i = t; i < 256; i += kThreads) S.nTri[i] = c_nTri[i];
     __syncthreads();
 
     int item = blockIdx.x;  // first item is static, the rest come from the work counter
@@ -80,62 +83,63 @@ __global__ void __launch_bounds__(kThreads, 6) field_kernel(GridParams G, const 
             phase[stage] ^= 1u;
         }
 
-        // ---- evaluate 4 corners: (i, j, 4*kh .. 4*kh+3)
-        const int kh = t & 1, ci = (t >> 1) & 7, cj = t >> 4;
-        float X[4], Y[4], Z[4], F[4];
+        // ---- evaluate kPts corners: flat index kPts*t + n = i*8 + j*64 + k
+        const int k0 = (kPts * t) & 7, ci = ((kPts * t) >> 3) & 7, cj = (kPts * t) >> 6;
+        float X[kPts], Y[kPts], Z[kPts], F[kPts];
         {
             const float x = corner_coord(G, 0, r.x, ci), y = corner_coord(G, 1, r.y, cj);
 #pragma unroll
-            for (int n = 0; n < 4; n++) { X[n] = x; Y[n] = y; Z[n] = corner_coord(G, 2, r.z, 4 * kh + n); }
+            for (int n = 0; n < kPts; n++) { X[n] = x; Y[n] = y; Z[n] = corner_coord(G, 2, r.z, k0 + n); }
         }
-        eval_program<4, false, STRICT, STAGED>(STAGED ? progBuf + (size_t)stage * capQuads : pool + r.off, X, Y, Z, F, nullptr, nullptr, G.sem);
-        reinterpret_cast<float4*>(S.fv)[t] = make_float4(F[0], F[1], F[2], F[3]);
-        uint32_t in4 = 0;
+        eval_program<kPts, false, STRICT, STAGED>(STAGED ? progBuf + (size_t)stage * capQuads : pool + r.off, X, Y, Z, F, nullptr, nullptr, G.sem);
+        uint32_t inb = 0;
 #pragma unroll
-        for (int n = 0; n < 4; n++) in4 |= (is_inside(G, F[n]) ? 1u : 0u) << n;
+        for (int n = 0; n < kPts; n++) inb |= (is_inside(G, F[n]) ? 1u : 0u) << n;
+#pragma unroll
+        for (int q = 0; q < kPts / 4; q++)
+            reinterpret_cast<float4*>(S.fv)[t * (kPts / 4) + q] = make_float4(F[4 * q], F[4 * q + 1], F[4 * q + 2], F[4 * q + 3]);
         // early discard like PS_Polygonizer.cpp:602-609: all corners inside or all outside
-        const int anyIn = __syncthreads_or(in4 != 0u);
-        const int anyOut = __syncthreads_or(in4 != 0xFu);
+        const int anyIn = __syncthreads_or(inb != 0u);
+        const int anyOut = __syncthreads_or(inb != ((1u << kPts) - 1u));
         uint32_t nV = 0, nT = 0;
         if (anyIn && anyOut) {
-            atomicOr(&S.insideW[t >> 3], in4 << ((t & 7) * 4));
+            atomicOr(&S.insideW[(kPts * t) >> 5], inb << ((kPts * t) & 31));
             __syncthreads();
-            // ---- crossing edges this MPU owns: 12 bits per thread (4 corners x 3 axes)
+            // ---- crossing edges this MPU owns: 3 bits per corner (x, y, z edge leaving it)
             const bool lastX = (r.x == G.hi[0] - 1), lastY = (r.y == G.hi[1] - 1), lastZ = (r.z == G.hi[2] - 1);
             const bool perMpu = (G.output == PSGPU_OUT_MPU);
-            uint32_t bits12 = 0;
+            const bool ownX = perMpu || ci < 7 || lastX, ownY = perMpu || cj < 7 || lastY;
+            uint32_t ebits = 0;
 #pragma unroll
-            for (int n = 0; n < 4; n++) {
-                const int ck = 4 * kh + n;
-                const int idx = 4 * t + n;
-                const bool me = (in4 >> n) & 1u;
-                const bool ownX = perMpu || ci < 7 || lastX, ownY = perMpu || cj < 7 || lastY, ownZ = perMpu || ck < 7 || lastZ;
-                if (ci < 7 && ownY && ownZ) { const int nb = idx + 8; if (((S.insideW[nb >> 5] >> (nb & 31)) & 1u) != (uint32_t)me) bits12 |= 1u << (n * 3 + 0); }
-                if (cj < 7 && ownX && ownZ) { const int nb = idx + 64; if (((S.insideW[nb >> 5] >> (nb & 31)) & 1u) != (uint32_t)me) bits12 |= 1u << (n * 3 + 1); }
-                if (ck < 7 && ownX && ownY) { const int nb = idx + 1; if (((S.insideW[nb >> 5] >> (nb & 31)) & 1u) != (uint32_t)me) bits12 |= 1u << (n * 3 + 2); }
+            for (int n = 0; n < kPts; n++) {
+                const int ck = k0 + n;
+                const int idx = kPts * t + n;
+                const uint32_t me = (inb >> n) & 1u;
+                const bool ownZ = perMpu || ck < 7 || lastZ;
+                if (ci < 7 && ownY && ownZ) { const int nb = idx + 8; if (((S.insideW[nb >> 5] >> (nb & 31)) & 1u) != me) ebits |= 1u << (n * 3 + 0); }
+                if (cj < 7 && ownX && ownZ) { const int nb = idx + 64; if (((S.insideW[nb >> 5] >> (nb & 31)) & 1u) != me) ebits |= 1u << (n * 3 + 1); }
+                if (ck < 7 && ownX && ownY) { const int nb = idx + 1; if (((S.insideW[nb >> 5] >> (nb & 31)) & 1u) != me) ebits |= 1u << (n * 3 + 2); }
             }
-            if (bits12) {
-                const int e0 = 12 * t;
-                atomicOr(&S.edgeW[e0 >> 5], bits12 << (e0 & 31));
-                if ((e0 & 31) > 20) atomicOr(&S.edgeW[(e0 >> 5) + 1], bits12 >> (32 - (e0 & 31)));
+            if (ebits) {
+                const int e0 = 3 * kPts * t, sh = e0 & 31;
+                atomicOr(&S.edgeW[e0 >> 5], ebits << sh);
+                if (sh + 3 * kPts > 32) atomicOr(&S.edgeW[(e0 >> 5) + 1], ebits >> (32 - sh));
             }
-            // ---- triangles
+            // ---- triangles: cube case of cell (x, y, z) from the inside bits read as bytes (byte i + 8j = the 8 corners along k)
+            const uint8_t* B = reinterpret_cast<const uint8_t*>(S.insideW);
             uint32_t myT = 0;
             for (int c = t; c < 343; c += kThreads) {
-                const int cx = c / 49, cy = (c / 7) % 7, cz = c % 7;
-                uint32_t cfg = 0;
-#pragma unroll
-                for (int b = 0; b < 8; b++) {
-                    const int idx = (cx + ((b >> 2) & 1)) * 8 + (cy + ((b >> 1) & 1)) * 64 + (cz + (b & 1));
-                    cfg |= ((S.insideW[idx >> 5] >> (idx & 31)) & 1u) << b;
-                }
-                myT += c_nTri[cfg];
+                const int cx = c / 49, cy = (c - cx * 49) / 7, cz = c - cx * 49 - cy * 7;
+                const uint32_t b00 = B[cy * 8 + cx], b10 = B[cy * 8 + cx + 1], b01 = B[(cy + 1) * 8 + cx], b11 = B[(cy + 1) * 8 + cx + 1];
+                const uint32_t cfg = ((b00 >> cz) & 3u) | (((b01 >> cz) & 3u) << 2) | (((b10 >> cz) & 3u) << 4) | (((b11 >> cz) & 3u) << 6);
+                myT += S.nTri[cfg];
             }
 #pragma unroll
             for (int o = 16; o > 0; o >>= 1) myT += __shfl_xor_sync(0xffffffffu, myT, o);
             if (lane == 0) S.warpSum[t >> 5] = myT;
             __syncthreads();
-            nT = S.warpSum[0] + S.warpSum[1] + S.warpSum[2] + S.warpSum[3];
+#pragma unroll
+            for (int w = 0; w < kThreads / 32; w++) nT += S.warpSum[w];
             // ---- exclusive popcount prefix over the 48 edge words (warp 0)
             if (t < 32) {
                 const uint32_t w0 = S.edgeW[t], w1 = (t < 16) ? S.edgeW[32 + t] : 0u;
@@ -153,13 +157,15 @@ __global__ void __launch_bounds__(kThreads, 6) field_kernel(GridParams G, const 
                     out.edgeMask[(size_t)item * 48 + 32 + t] = w1;
                     out.edgePrefix[(size_t)item * 48 + 32 + t] = (uint16_t)(tot0 + s1 - p1);
                 }
-                if (t == 0) S.warpSum[4] = tot0 + tot1;
+                if (t == 0) S.warpSum[7] = tot0 + tot1;
             }
             __syncthreads();
-            nV = S.warpSum[4];
-            if (nT > 0 && !G.forceFv) out.fv[(size_t)item * 128 + t] = reinterpret_cast<float4*>(S.fv)[t];
+            nV = S.warpSum[7];
         }
-        if (G.forceFv) out.fv[(size_t)item * 128 + t] = reinterpret_cast<float4*>(S.fv)[t];
+        if (G.forceFv || nT > 0) {
+#pragma unroll
+            for (int q = 0; q < kPts / 4; q++) out.fv[(size_t)item * 128 + t * (kPts / 4) + q] = reinterpret_cast<float4*>(S.fv)[t * (kPts / 4) + q];
+        }
         if (t == 0) {
             out.vcount[item] = (nT > 0) ? nV : 0u;
             out.tcount[item] = nT;
