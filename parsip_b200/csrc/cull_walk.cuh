@@ -207,9 +207,9 @@ struct Pruner {
     __device__ void cscale(uint32_t n) {
         if (!colorExact || n == 0) return;
         if (lastScale + 1 != emit && lastHdrPos != 0xFFFFFFFFu && sp >= 0 && lastHdrPos >= bstart[sp] && lastHdrPos < emit) {
-            const uint32_t have = PS_HDR_CSC(lastHdrVal), room = 15u - have, take = n < room ? n : room;
+            const uint32_t have = PS_HDR_CSC(lastHdrVal), room = PS_HDR_CSC_MAX - have, take = n < room ? n : room;
             if (take) {
-                lastHdrVal += take << 28;
+                lastHdrVal += take << PS_HDR_CSC_SHIFT;
                 lastHdrQuad.x = __uint_as_float(lastHdrVal);
                 if (EMIT && lastHdrPos < limit) dst[lastHdrPos] = lastHdrQuad;
                 n -= take;
@@ -241,7 +241,7 @@ struct Pruner {
     __device__ static __forceinline__ bool skippable(uint32_t hdr, bool pz, uint32_t& scale) {
         const uint32_t cmb = PS_HDR_CMB(hdr);
         if (!pz || (cmb != CMB_ADD && cmb != CMB_SDIF)) return false;
-        scale = (cmb == CMB_ADD ? 1u : 0u) + PS_HDR_CSC(hdr);
+        scale = (cmb == CMB_ADD ? 1u : 0u) + (PS_HDR_PRE(hdr) ? 0u : PS_HDR_CSC(hdr));  // a PRE count scaled the dropped primitive's own colour
         return true;
     }
 
@@ -256,7 +256,7 @@ struct Pruner {
         } else if (bzero[sp]) {
             if (!pz && (cmb == CMB_ADD || cmb == CMB_MAX || cmb == CMB_RDIF || cmb == CMB_RSDIF)) {
                 // 0 + f, max(0, f), min(f, 1 - 0) (f <= 1), f * (1 - 0): the primitive becomes the entry
-                copy(pc, q0, (hdr & ~(15u << 6)) | (CMB_PUSH << 6), nq);
+                copy(pc, q0, PS_HDR_SET_CMB(hdr, CMB_PUSH) & ~PS_HDR_PRE_BIT, nq);  // alone on the stack, pre- and post-scale are the same
                 bzero[sp] = false; blo[sp] = flo; bhi[sp] = fhi;
                 if (cmb == CMB_ADD) cscale(1);
             }  // min(0,f) = 0, min(0,1-f) = 0 (f <= 1), 0*(1-f) = 0: stays zero
@@ -276,7 +276,7 @@ struct Pruner {
                 const float a = fminf(0.f, 1.0f - bhi[sp]) - 1e-6f, b = fminf(0.f, 1.0f - blo[sp]);
                 blo[sp] = a; bhi[sp] = b;
             }
-            if (!bzero[sp]) cscale(PS_HDR_CSC(hdr));  // markers a coarser level left on the dropped instruction stay with the entry
+            if (!bzero[sp] && !PS_HDR_PRE(hdr)) cscale(PS_HDR_CSC(hdr));  // markers a coarser level left on the dropped instruction stay with the entry
         } else {
             copy(pc, q0, hdr, nq);
             bound_combine(cmb, blo[sp], bhi[sp], flo, fhi);
@@ -319,7 +319,22 @@ struct Pruner {
                 } else if (cmb == CMB_ADD) cscale(1);
                 if (!bzero[t]) cscale(PS_HDR_CSC(hdr));
             } else {
-                copy(pc, q0, hdr, nq);
+                // peephole: V shrank to ONE primitive (its blend partners were culled): fold it into T with the combine code in
+                // its own header instead of PUSH + OPC_COMBINE - same operands in the same order, so the same bits, and the
+                // interpreters save a stack round trip and a dispatch (most groups of a pruned list are single primitives)
+                // If the primitive carries colour-scale steps of its own they become a PRE count (they scaled V's colour before the
+                // combine); the OPC_COMBINE's own steps (after the combine) can ride along only if the primitive has none.
+                const bool single = cmbRaw != CMB_RADD && lastHdrPos != 0xFFFFFFFFu && lastHdrPos == bstart[v] && lastScale + 1 != emit &&
+                                    PS_HDR_OPC(lastHdrVal) < OPC_FIRST_NONPRIM && PS_HDR_CMB(lastHdrVal) == CMB_PUSH &&
+                                    (PS_HDR_CSC(lastHdrVal) == 0u || PS_HDR_CSC(hdr) == 0u) &&
+                                    emit == lastHdrPos + (uint32_t)ps_instr_quads(lastHdrVal);
+                if (single) {
+                    const bool pre = PS_HDR_CSC(lastHdrVal) != 0u;
+                    lastHdrVal = PS_HDR_SET_CMB(lastHdrVal, cmb) | (pre ? PS_HDR_PRE_BIT : (PS_HDR_CSC(hdr) << PS_HDR_CSC_SHIFT));
+                    lastHdrQuad.x = __uint_as_float(lastHdrVal);
+                    if (EMIT && lastHdrPos < limit) dst[lastHdrPos] = lastHdrQuad;
+                    if (pre) lastHdrPos = 0xFFFFFFFFu;  // its count field now means something else: later steps go to an OPC_CSCALE quad
+                } else copy(pc, q0, hdr, nq);
                 bound_combine(cmb, blo[t], bhi[t], blo[v], bhi[v]);
             }
         } break;

@@ -431,6 +431,7 @@ __device__ void eval_program(const float4* __restrict__ prog, const float (&X)[N
                 const uint32_t id = PS_HDR_PRIM(hdr);
                 pcol[0] = colorTab[id * 3]; pcol[1] = colorTab[id * 3 + 1]; pcol[2] = colorTab[id * 3 + 2];
             }
+            if (STRICT && COLOR && PS_HDR_PRE(hdr)) color_scale(f[0], pcol, PS_HDR_CSC(hdr));  // folded one-primitive group (program.h)
             if (cmb == CMB_PUSH) {
 #pragma unroll
                 for (int n = 0; n < N; n++) { vs[sp][n] = top[n]; top[n] = f[n]; }
@@ -446,7 +447,7 @@ __device__ void eval_program(const float4* __restrict__ prog, const float (&X)[N
                 }
                 combine_n<N>(cmb, top, f, top);
             }
-            if (STRICT && COLOR && PS_HDR_CSC(hdr)) color_scale(top[0], tc, PS_HDR_CSC(hdr));
+            if (STRICT && COLOR && PS_HDR_CSC(hdr) && !PS_HDR_PRE(hdr)) color_scale(top[0], tc, PS_HDR_CSC(hdr));
             continue;
         }
         const int pcNext = pc + ps_base_quads(opc);

@@ -3,13 +3,15 @@
 // The stream is a sequence of 16-byte "quads" (4 x 32-bit words) so that every parameter block is
 // one or two LDS.128 / LDG.128 and a whole program is a legal cp.async.bulk (TMA) transfer.
 // Quad 0 of an instruction is {header, p0, p1, p2}; the header word is
-//     bits 0..5   opcode
-//     bits 6..9   combine code (how a primitive's field, or a popped sub-tree value, meets the stack top)
-//     bit  10     XF: three more quads (rows of a backward 3x4 matrix) follow the primitive's own quads
-//     bits 11..27 primitive id (index into the colour table)
-//     bits 28..31 colour-scale count: after this instruction the colour walk multiplies the top colour that many times by
+//     bits 0..4   opcode
+//     bits 5..8   combine code (how a primitive's field, or a popped sub-tree value, meets the stack top)
+//     bit  9      XF: three more quads (rows of a backward 3x4 matrix) follow the primitive's own quads
+//     bit  10     PRE: the colour-scale count below applies to THIS primitive's colour before it is combined (left by the culling
+//                 pass when it folds a one-primitive group "p:PUSH ... OPC_COMBINE" into "p:<combine>")
+//     bits 11..26 primitive id (index into the colour table)
+//     bits 27..31 colour-scale count: after this instruction the colour walk multiplies the top colour that many times by
 //                 (2*(0.5+top)-1) - the weight a PS_SimdPoly blend gives its surviving operand when the culling pass dropped
-//                 the all-zero other one (see OPC_CSCALE, which carries counts beyond 15). Free for the field-only passes.
+//                 the all-zero other one (see OPC_CSCALE, which carries counts beyond 31). Free for the field-only passes.
 //
 // Evaluation model: a value stack whose top lives in registers, and a point stack for warps. A primitive
 // evaluates the Wyvill field (1-d^2)^3 of its skeleton distance at the current point and combines it into
@@ -68,13 +70,19 @@ enum PsCombine : uint32_t {
                    // child fields (CompactBlobTree.cpp:1186-1203), kept in the colour walk's aux slot
 };
 
-#define PS_HDR(opc, cmb, xf, prim) ((uint32_t)(opc) | ((uint32_t)(cmb) << 6) | ((uint32_t)((xf) ? 1 : 0) << 10) | ((uint32_t)(prim) << 11))
-#define PS_HDR_OPC(h) ((h) & 63u)
-#define PS_HDR_CMB(h) (((h) >> 6) & 15u)
-#define PS_HDR_XF(h) (((h) >> 10) & 1u)
-#define PS_HDR_PRIM(h) (((h) >> 11) & 0x1FFFFu)
-#define PS_HDR_CSC(h) ((h) >> 28)
-#define PS_MAX_PRIMS (1u << 17)
+#define PS_HDR_CMB_SHIFT 5
+#define PS_HDR_CSC_SHIFT 27
+#define PS_HDR_CSC_MAX 31u
+#define PS_HDR_PRE_BIT (1u << 10)
+#define PS_HDR(opc, cmb, xf, prim) ((uint32_t)(opc) | ((uint32_t)(cmb) << PS_HDR_CMB_SHIFT) | ((uint32_t)((xf) ? 1 : 0) << 9) | ((uint32_t)(prim) << 11))
+#define PS_HDR_OPC(h) ((h) & 31u)
+#define PS_HDR_CMB(h) (((h) >> PS_HDR_CMB_SHIFT) & 15u)
+#define PS_HDR_XF(h) (((h) >> 9) & 1u)
+#define PS_HDR_PRE(h) (((h) >> 10) & 1u)
+#define PS_HDR_PRIM(h) (((h) >> 11) & 0xFFFFu)
+#define PS_HDR_CSC(h) ((h) >> PS_HDR_CSC_SHIFT)
+#define PS_HDR_SET_CMB(h, cmb) (((h) & ~(15u << PS_HDR_CMB_SHIFT)) | ((uint32_t)(cmb) << PS_HDR_CMB_SHIFT))
+#define PS_MAX_PRIMS (1u << 16)
 
 // quads per instruction, without the optional XF rows
 #if defined(__CUDACC__)

@@ -81,24 +81,24 @@ def test_zero_folding_rules_of_difference():
     full = emu.field(quads, pts, ps.SEM_SCALAR)
     assert full.max() == 1.0  # the clamp is active here
     pr = emu.prune(quads, a, b, ps.CULL_SUPPORT, ISO)
-    assert pr is not None and (pr[-2, 0] & 63) == 19  # the subtrahend is replaced by OPC_CLAMP1
+    assert pr is not None and (pr[-2, 0] & 31) == 19  # the subtrahend is replaced by OPC_CLAMP1
     assert np.array_equal(emu.field(pr, pts, ps.SEM_SCALAR), full)
     # all-inside region: the interval cull may drop it (no surface), the support cull must not
     assert emu.prune(quads, a, b, ps.CULL_INTERVAL, ISO) is None
 
 
 def _has_colour_scale(quads):
-    """walks the instruction headers: OPC_CSCALE quad or a non-zero colour-scale count in header bits 28..31"""
+    """walks the instruction headers: OPC_CSCALE quad or a non-zero colour-scale count in header bits 27..31"""
     base = {2: 2, 3: 2, 5: 2, 6: 2, 7: 2, 26: 2, 4: 3, 28: 4}
     pc = 0
     while pc < len(quads):
         h = int(quads[pc, 0])
-        opc = h & 63
+        opc = h & 31
         if opc == 0:
             return False
-        if opc == 21 or (h >> 28):
+        if opc == 21 or (h >> 27):
             return True
-        pc += base.get(opc, 1) + (3 if (opc < 16 and (h >> 10) & 1) else 0)
+        pc += base.get(opc, 1) + (3 if (opc < 16 and (h >> 9) & 1) else 0)
     return False
 
 

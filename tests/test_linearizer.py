@@ -63,7 +63,7 @@ def test_program_structure_and_stack_depths():
     prog = ps.linearize(bt.flatten(root), ps.SEM_SCALAR, ps.LIN_REASSOCIATE)
     q = prog.quads()
     assert q.shape == (prog.n_quads, 4)
-    assert (q[-1, 0] & 63) == 0  # OPC_END terminates the stream
+    assert (q[-1, 0] & 31) == 0  # OPC_END terminates the stream
     assert prog.max_point_stack == 3  # bend(taper(twist(...)))
     assert 2 <= prog.max_value_stack <= 8
     assert prog.n_prims == sum(1 for t in bt.flatten(root)["type"] if t < 16)

@@ -29,5 +29,5 @@ for cull in (ps.CULL_NONE, ps.CULL_SUPPORT):
                 a = (lo + np.float32(k) * np.float32(cs) * np.float32(7)).astype(np.float32) - np.float32(6e-5)
                 b = (a + np.float32(cs) * np.float32(7)) + np.float32(1.2e-4)
                 g = ctx.prune_region(a, b, cull)
-                print("     program:", None if g is None else [(int(w & 63), int((w >> 6) & 15)) for w in g[:, 0]])
+                print("     program:", None if g is None else [(int(w & 31), int((w >> 5) & 15)) for w in g[:, 0]])
     print("cull", cull, "evaluated", len(ijk), "MPUs whose cache differs from the full program:", nbad)

@@ -33,5 +33,5 @@ for I in range(dims[0]):
                     print("DIFF", (I, J, K), "gpu", None if g is None else len(g), "host", None if h is None else len(h))
                     for name, q in (("gpu", g), ("host", h)):
                         if q is not None:
-                            print("  ", name, [(int(w & 63), int((w >> 6) & 15)) for w in q[:, 0] if (w & 63) not in (0,)][:40])
+                            print("  ", name, [(int(w & 31), int((w >> 5) & 15)) for w in q[:, 0] if (w & 31) not in (0,)][:40])
 print("boxes", dims[0] * dims[1] * dims[2], "differences", ndiff)
