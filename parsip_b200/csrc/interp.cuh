@@ -278,6 +278,15 @@ __device__ __forceinline__ void prim_field(uint32_t opc, const float4 q0, const 
     }
 }
 
+// primitive under its own backward matrix (header bit XF): out of line, see eval_program
+template <int N, bool STRICT>
+__device__ __noinline__ void prim_field_xf(uint32_t opc, const float4 q0, const float4* __restrict__ q, const float4* __restrict__ m,
+                                           const float (&x)[N], const float (&y)[N], const float (&z)[N], float (&f)[N]) {
+    float lx[N], ly[N], lz[N];
+    xform_points<N, STRICT>(m, x, y, z, lx, ly, lz);
+    prim_field<N, STRICT>(opc, q0, q, lx, ly, lz, f);
+}
+
 __device__ __forceinline__ float combine_val(uint32_t cmb, float top, float v) {
     switch (cmb) {
     case CMB_ADD: case CMB_RADD: return top + v;
@@ -396,7 +405,6 @@ __device__ void eval_program(const float4* __restrict__ prog, const float (&X)[N
     // entry 0 of the stacks is a dummy: the first PUSH stores the (unused) initial top there, so PUSH needs no "first" test
     float vs[PS_MAX_VALUE_STACK + 1][N];
     float pstk[STRICT ? 1 : PS_MAX_POINT_STACK][3][N];
-    float xsave[3][N];  // the world-space points while a primitive with its own matrix is evaluated (local memory, rare path)
     float cstk[COLOR_T ? PS_MAX_VALUE_STACK + 1 : 1][5];
     float tc[3] = {0.f, 0.f, 0.f};
     float taux = 0.f;
@@ -414,16 +422,26 @@ __device__ void eval_program(const float4* __restrict__ prog, const float (&X)[N
             const int nq = ps_base_quads(opc);
             const bool xf = PS_HDR_XF(hdr) != 0u;
             float f[N];
-            if (xf) {  // evaluate in the primitive's local frame, then restore the points (in place: the common path has no copies)
-                float lx[N], ly[N], lz[N];
-                xform_points<N, STRICT>(prog + pc + nq, x, y, z, lx, ly, lz);
+            // a primitive with its own matrix is evaluated by an out-of-line copy (cold: matrices are rare), so that the hot path
+            // never writes x/y/z: where a caller passes the same x and y for all N points (the field kernel's z-columns) the
+            // compiler then shares the x/y part of every distance across the points
+            // (the native interpreter rewrites x/y/z under warps anyway and measured faster with the matrix applied in place)
+            if (STRICT) {
+                if (xf) prim_field_xf<N, STRICT>(opc, q0, prog + pc + 1, prog + pc + nq, x, y, z, f);
+                else prim_field<N, STRICT>(opc, q0, prog + pc + 1, x, y, z, f);  // ONE inlined copy of the primitive switch (i-cache)
+            } else {
+                float xsave[3][N];
+                if (xf) {
+                    float lx[N], ly[N], lz[N];
+                    xform_points<N, STRICT>(prog + pc + nq, x, y, z, lx, ly, lz);
 #pragma unroll
-                for (int n = 0; n < N; n++) { xsave[0][n] = x[n]; xsave[1][n] = y[n]; xsave[2][n] = z[n]; x[n] = lx[n]; y[n] = ly[n]; z[n] = lz[n]; }
-            }
-            prim_field<N, STRICT>(opc, q0, prog + pc + 1, x, y, z, f);  // ONE inlined copy of the primitive switch (i-cache)
-            if (xf) {
+                    for (int n = 0; n < N; n++) { xsave[0][n] = x[n]; xsave[1][n] = y[n]; xsave[2][n] = z[n]; x[n] = lx[n]; y[n] = ly[n]; z[n] = lz[n]; }
+                }
+                prim_field<N, STRICT>(opc, q0, prog + pc + 1, x, y, z, f);
+                if (xf) {
 #pragma unroll
-                for (int n = 0; n < N; n++) { x[n] = xsave[0][n]; y[n] = xsave[1][n]; z[n] = xsave[2][n]; }
+                    for (int n = 0; n < N; n++) { x[n] = xsave[0][n]; y[n] = xsave[1][n]; z[n] = xsave[2][n]; }
+                }
             }
             pc += nq + (xf ? 3 : 0);
             float pcol[3];

@@ -11,6 +11,7 @@
 #define __host__
 #define __global__
 #define __forceinline__ inline
+#define __noinline__
 #define __restrict__
 #define __align__(n) __attribute__((aligned(n)))
 #define __launch_bounds__(...)
