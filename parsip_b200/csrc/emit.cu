@@ -387,7 +387,7 @@ __device__ __forceinline__ void vertex_at(const GridParams& G, const float4* pro
 }
 
 template <bool STRICT, int ROOT, bool SMEM>
-__global__ void __launch_bounds__(kThreads, 5) vertex_kernel(GridParams G, const Region* __restrict__ cands, const float4* __restrict__ pool,
+__global__ void __launch_bounds__(kThreads, 6) vertex_kernel(GridParams G, const Region* __restrict__ cands, const float4* __restrict__ pool,
                                                              FieldOutputs fo, MeshOutputs mo, int nMixed, uint32_t sliceQuads) {
     __shared__ uint32_t sW[kThreads / 32][48];
     __shared__ uint32_t sP[kThreads / 32][48];

@@ -39,7 +39,7 @@ struct __align__(16) FieldSmemHeader {
 // STAGED: every candidate list fits the staging buffers (the host checks the longest one) and is interpreted from shared memory;
 // the unstaged variant (brute-force mode, very long lists) reads the lists from global memory. One interpreter copy per kernel.
 template <bool STRICT, bool STAGED>
-__global__ void __launch_bounds__(kThreads, 8) field_kernel(GridParams G, const Region* __restrict__ cands, int nCand,
+__global__ void __launch_bounds__(kThreads, STRICT ? 12 : 16) field_kernel(GridParams G, const Region* __restrict__ cands, int nCand,
                                                          const float4* __restrict__ pool, FieldOutputs out, uint32_t capQuads) {
     extern __shared__ __align__(16) unsigned char smemRaw[];
     FieldSmemHeader& S = *reinterpret_cast<FieldSmemHeader*>(smemRaw);
