@@ -56,7 +56,7 @@ struct psgpu_ctx {
     DevBuf qflag;     // one byte per pool quad: 1 = first quad of an instruction (read by the warp-cooperative pruning passes)
     DevBuf colors;
     // cull scratch
-    DevBuf regionsA, regionsB, childLen, childOff, childFlag, childIdx, scanTemp, candOfMpu, scalars;
+    DevBuf regionsA, regionsB, childLen, childOff, childFlag, childIdx, scanTemp, candOfMpu, scalars, cullScratch, cullScratchFlag;
     // field outputs
     DevBuf fv, vcount, tcount, vbase, tbase, edgeMask, edgePrefix, mixedList, mixedFlag, mixedIdx, counters, statsAcc;
     // mesh
@@ -109,7 +109,7 @@ extern "C" int psgpu_destroy(psgpu_ctx* ctx) {
     cudaSetDevice(ctx->device);
     cudaStreamSynchronize(ctx->stream);
     DevBuf* all[] = {&ctx->pool, &ctx->qflag, &ctx->colors, &ctx->regionsA, &ctx->regionsB, &ctx->childLen, &ctx->childOff, &ctx->childFlag, &ctx->childIdx,
-                     &ctx->scanTemp, &ctx->candOfMpu, &ctx->scalars, &ctx->fv, &ctx->vcount, &ctx->tcount, &ctx->vbase, &ctx->tbase,
+                     &ctx->scanTemp, &ctx->candOfMpu, &ctx->scalars, &ctx->cullScratch, &ctx->cullScratchFlag, &ctx->fv, &ctx->vcount, &ctx->tcount, &ctx->vbase, &ctx->tbase,
                      &ctx->edgeMask, &ctx->edgePrefix, &ctx->mixedList, &ctx->mixedFlag, &ctx->mixedIdx, &ctx->counters, &ctx->statsAcc,
                      &ctx->pos, &ctx->nrm, &ctx->col, &ctx->tri, &ctx->mpuIjk, &ctx->mpuVbase, &ctx->mpuTbase, &ctx->vperm, &ctx->ptsIn, &ctx->ptsF,
                      &ctx->ptsCol, &ctx->ptsNrm};
@@ -232,6 +232,7 @@ int run_cull(psgpu_ctx* ctx, const GridParams& G, int cullMode, bool colorExact,
     int nParents = (int)top.size();
     CK(ctx->scalars.reserve(64));
     maxLen = 0;
+    uint32_t parentMaxLen = ctx->progQuads;  // longest program among the current level's parents
     for (size_t lv = 0; lv < sizes.size(); lv++) {
         L.childSize = sizes[lv];
         const bool last = (lv + 1 == sizes.size());
@@ -241,21 +242,42 @@ int run_cull(psgpu_ctx* ctx, const GridParams& G, int cullMode, bool colorExact,
         const size_t tb = scan_temp_bytes(n + 1);
         CK(ctx->scanTemp.reserve(tb));
         CK(cudaMemsetAsync(ctx->childLen.as<uint32_t>() + n, 0, 4, st));
-        launch_prune_count(L, cur->as<Region>(), nParents, ctx->pool.as<float4>(), ctx->qflag.as<uint8_t>(), ctx->childLen.as<uint32_t>(), st);
+        // coarse levels (few regions, long programs): ONE warp-cooperative walk per region into scratch slots, compacted after the scans;
+        // the scratch bound keeps 10k-primitive trees within ~1 GB
+        const size_t scratchQuads = (size_t)n * parentMaxLen;
+        const bool fused = prune_level_is_fused(nParents) && scratchQuads <= ((size_t)64 << 20) && !getenv("PSGPU_CULL_TWO_PASS");
+        uint32_t* levelMax = ctx->scalars.as<uint32_t>() + 1 + lv;
+        if (fused) {
+            CK(ctx->cullScratch.reserve(scratchQuads * 16)); CK(ctx->cullScratchFlag.reserve(scratchQuads));
+            CK(cudaMemsetAsync(levelMax, 0, 4, st));
+            launch_prune_fused(L, cur->as<Region>(), nParents, ctx->pool.as<float4>(), ctx->qflag.as<uint8_t>(), ctx->cullScratch.as<float4>(),
+                               ctx->cullScratchFlag.as<uint8_t>(), parentMaxLen, ctx->childLen.as<uint32_t>(), levelMax, st);
+        } else
+            launch_prune_count(L, cur->as<Region>(), nParents, ctx->pool.as<float4>(), ctx->qflag.as<uint8_t>(), ctx->childLen.as<uint32_t>(), st);
         launch_flags(ctx->childLen.as<uint32_t>(), ctx->childFlag.as<uint32_t>(), n + 1, st);
         exclusive_scan_u32(ctx->scanTemp.p, tb, ctx->childLen.as<uint32_t>(), ctx->childOff.as<uint32_t>(), n + 1, st);
         exclusive_scan_u32(ctx->scanTemp.p, tb, ctx->childFlag.as<uint32_t>(), ctx->childIdx.as<uint32_t>(), n + 1, st);
         launches += 4;
         CK(cudaMemcpyAsync(&ctx->hostScalars[0], ctx->childOff.as<uint32_t>() + n, 4, cudaMemcpyDeviceToHost, st));
         CK(cudaMemcpyAsync(&ctx->hostScalars[1], ctx->childIdx.as<uint32_t>() + n, 4, cudaMemcpyDeviceToHost, st));
+        if (fused) CK(cudaMemcpyAsync(&ctx->hostScalars[3], levelMax, 4, cudaMemcpyDeviceToHost, st));
         CK(cudaStreamSynchronize(st));
         const uint32_t totalQuads = ctx->hostScalars[0], nChildren = ctx->hostScalars[1];
+        if (fused && ctx->hostScalars[3] > parentMaxLen) { ctx->err = "pruned program longer than its parent"; return PSGPU_ERROR_CUDA; }
         if ((uint64_t)poolUsed + totalQuads >= ((uint64_t)1 << 32)) { ctx->err = "pruned programs exceed 2^32 quads"; return PSGPU_NOT_ENOUGH_MEM; }
         CK(ctx->pool.reserve(((size_t)poolUsed + totalQuads + 16) * 16, true, st));
         CK(ctx->qflag.reserve((size_t)poolUsed + totalQuads + 16, true, st));
         CK(nxt->reserve(std::max((size_t)nChildren, (size_t)1) * sizeof(Region)));
         if (last) CK(cudaMemsetAsync(ctx->scalars.p, 0, 4, st));
-        if (nChildren > 0) {
+        if (nChildren > 0 && fused) {
+            launch_prune_compact(L, cur->as<Region>(), nParents, ctx->cullScratch.as<float4>(), ctx->cullScratchFlag.as<uint8_t>(), parentMaxLen,
+                                 ctx->childLen.as<uint32_t>(), ctx->childOff.as<uint32_t>(), ctx->childIdx.as<uint32_t>(), ctx->pool.as<float4>(),
+                                 last ? nullptr : ctx->qflag.as<uint8_t>(), poolUsed, nxt->as<Region>(), last ? ctx->candOfMpu.as<int32_t>() : nullptr, st);
+            if (last) CK(cudaMemcpyAsync(ctx->scalars.p, levelMax, 4, cudaMemcpyDeviceToDevice, st));
+            launches++;
+            parentMaxLen = ctx->hostScalars[3];
+        } else if (nChildren > 0) {
+            parentMaxLen = std::min(parentMaxLen, totalQuads);  // a bound: no per-level maximum is tracked on the two-pass path
             launch_prune_emit(L, cur->as<Region>(), nParents, ctx->pool.as<float4>(), ctx->qflag.as<uint8_t>(), ctx->childLen.as<uint32_t>(),
                               ctx->childOff.as<uint32_t>(), ctx->childIdx.as<uint32_t>(), ctx->pool.as<float4>(),
                               last ? nullptr : ctx->qflag.as<uint8_t>(), poolUsed, nxt->as<Region>(),

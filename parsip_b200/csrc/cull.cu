@@ -205,6 +205,57 @@ __global__ void __launch_bounds__(kCoopWarps * 32) prune_emit_warp_kernel(CullLe
     if ((threadIdx.x & 31) == 0) publish_child(L, coord, off, len, childIdx[gw], children, candOfMpu, maxLen);
 }
 
+// ---- single-walk variant of the warp levels: the walk emits straight into a private scratch slot of `stride` quads (a pruned
+// list is never longer than its parent's), the scans run on the lengths it returns, and prune_compact_kernel moves the slots to
+// their final pool offsets - one walk per region instead of count + emit.
+__global__ void __launch_bounds__(kCoopWarps * 32) prune_fused_warp_kernel(CullLevel L, const Region* __restrict__ parents, int nParents,
+                                                                           const float4* __restrict__ pool, const uint8_t* __restrict__ qflag,
+                                                                           float4* __restrict__ scratch, uint8_t* __restrict__ scratchFlag, uint32_t stride,
+                                                                           uint32_t* __restrict__ childLen, uint32_t* __restrict__ maxLen) {
+    __shared__ CoopEntry sEnt[kCoopWarps][32];
+    const int gw = blockIdx.x * kCoopWarps + (threadIdx.x >> 5);
+    if (gw >= nParents * 64) return;
+    const Region parent = parents[gw >> 6];
+    int coord[3];
+    Box3 box;
+    uint32_t len = 0;
+    if (child_region(L, parent, gw & 63, coord, box))
+        len = prune_walk_warp<true>(pool + parent.off, qflag + parent.off, parent.len, box, L.cullMode, L.iso, scratch + (size_t)gw * stride,
+                                    scratchFlag + (size_t)gw * stride, L.colorExact != 0, stride, sEnt[threadIdx.x >> 5]);
+    if ((threadIdx.x & 31) == 0) {
+        if (len > stride) len = 0xFFFFFFFFu;  // cannot happen (emitted <= source); poisons the total so the host notices
+        childLen[gw] = len;
+        if (len) atomicMax(maxLen, len);
+    }
+}
+
+__global__ void __launch_bounds__(kCoopWarps * 32) prune_compact_kernel(CullLevel L, const Region* __restrict__ parents, int nParents,
+                                                                        const float4* __restrict__ scratch, const uint8_t* __restrict__ scratchFlag,
+                                                                        uint32_t stride, const uint32_t* __restrict__ childLen,
+                                                                        const uint32_t* __restrict__ childOff, const uint32_t* __restrict__ childIdx,
+                                                                        float4* __restrict__ outPool, uint8_t* __restrict__ outFlag, uint32_t outBase,
+                                                                        Region* __restrict__ children, int32_t* __restrict__ candOfMpu) {
+    const int gw = blockIdx.x * kCoopWarps + (threadIdx.x >> 5);
+    if (gw >= nParents * 64) return;
+    const uint32_t len = childLen[gw];
+    if (len == 0) return;
+    const int lane = threadIdx.x & 31;
+    const uint32_t off = outBase + childOff[gw];
+    const float4* src = scratch + (size_t)gw * stride;
+    const uint8_t* sf = scratchFlag + (size_t)gw * stride;
+    for (uint32_t i = lane; i < len; i += 32) {
+        outPool[off + i] = src[i];
+        if (outFlag) outFlag[off + i] = sf[i];
+    }
+    if (lane == 0) {
+        const Region parent = parents[gw >> 6];
+        int coord[3];
+        Box3 box;
+        child_region(L, parent, gw & 63, coord, box);
+        publish_child(L, coord, off, len, childIdx[gw], children, candOfMpu, nullptr);
+    }
+}
+
 __global__ void flag_kernel(const uint32_t* __restrict__ len, uint32_t* __restrict__ flag, int n) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i < n) flag[i] = len[i] ? 1u : 0u;
@@ -265,6 +316,23 @@ void launch_prune_emit(const CullLevel& L, const Region* parents, int nParents, 
     else
         prune_emit_kernel<<<(n + 127) / 128, 128, 0, st>>>(L, parents, nParents, pool, childLen, childOff, childIdx, outPool, outFlag, outBase, children,
                                                            candOfMpu, maxLen);
+}
+
+bool prune_level_is_fused(int nParents) { return use_warp_walk(nParents); }
+
+void launch_prune_fused(const CullLevel& L, const Region* parents, int nParents, const float4* pool, const uint8_t* qflag, float4* scratch,
+                        uint8_t* scratchFlag, uint32_t stride, uint32_t* childLen, uint32_t* maxLen, cudaStream_t st) {
+    const int n = nParents * 64;
+    prune_fused_warp_kernel<<<(n + kCoopWarps - 1) / kCoopWarps, kCoopWarps * 32, 0, st>>>(L, parents, nParents, pool, qflag, scratch, scratchFlag, stride,
+                                                                                          childLen, maxLen);
+}
+
+void launch_prune_compact(const CullLevel& L, const Region* parents, int nParents, const float4* scratch, const uint8_t* scratchFlag, uint32_t stride,
+                          const uint32_t* childLen, const uint32_t* childOff, const uint32_t* childIdx, float4* outPool, uint8_t* outFlag,
+                          uint32_t outBase, Region* children, int32_t* candOfMpu, cudaStream_t st) {
+    const int n = nParents * 64;
+    prune_compact_kernel<<<(n + kCoopWarps - 1) / kCoopWarps, kCoopWarps * 32, 0, st>>>(L, parents, nParents, scratch, scratchFlag, stride, childLen, childOff,
+                                                                                       childIdx, outPool, outFlag, outBase, children, candOfMpu);
 }
 
 size_t scan_temp_bytes(int n) {

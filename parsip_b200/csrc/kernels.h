@@ -66,6 +66,12 @@ void launch_flags(const uint32_t* len, uint32_t* flag, int n, cudaStream_t st);
 void launch_prune_emit(const CullLevel& L, const Region* parents, int nParents, const float4* pool, const uint8_t* qflag, const uint32_t* childLen,
                        const uint32_t* childOff, const uint32_t* childIdx, float4* outPool, uint8_t* outFlag, uint32_t outBase, Region* children,
                        int32_t* candOfMpu, uint32_t* maxLen, cudaStream_t st);
+bool prune_level_is_fused(int nParents);
+void launch_prune_fused(const CullLevel& L, const Region* parents, int nParents, const float4* pool, const uint8_t* qflag, float4* scratch,
+                        uint8_t* scratchFlag, uint32_t stride, uint32_t* childLen, uint32_t* maxLen, cudaStream_t st);
+void launch_prune_compact(const CullLevel& L, const Region* parents, int nParents, const float4* scratch, const uint8_t* scratchFlag, uint32_t stride,
+                          const uint32_t* childLen, const uint32_t* childOff, const uint32_t* childIdx, float4* outPool, uint8_t* outFlag,
+                          uint32_t outBase, Region* children, int32_t* candOfMpu, cudaStream_t st);
 void launch_prune_one(const float4* prog, const float* lo, const float* hi, int cullMode, float iso, int colorExact, float4* out, uint32_t cap,
                       uint32_t* lenOut, cudaStream_t st);
 size_t scan_temp_bytes(int n);
