@@ -52,6 +52,7 @@ struct psgpu_ctx {
     uint32_t progQuads = 0;
     int nPrims = 0;
     int semantics = PSGPU_SEM_SCALAR;
+    bool hasWarps = false;  // the program uses the point stack (warps / operator matrices)
     DevBuf pool;      // float4: [full program | level 0 programs | level 1 programs | ...]
     DevBuf qflag;     // one byte per pool quad: 1 = first quad of an instruction (read by the warp-cooperative pruning passes)
     DevBuf colors;
@@ -158,6 +159,7 @@ extern "C" int psgpu_upload_program(psgpu_ctx* ctx, const psgpu_program* p) {
     ctx->progQuads = (uint32_t)(p->words.size() / 4);
     ctx->nPrims = p->nPrims;
     ctx->semantics = p->semantics;
+    ctx->hasWarps = p->maxPointStack > 0;
     return PSGPU_SUCCESS;
 }
 
@@ -350,7 +352,7 @@ int polygonize_impl(psgpu_ctx* ctx, const psgpu_params* P, psgpu_mesh* out, bool
         fo.fv = ctx->fv.as<float4>(); fo.vcount = ctx->vcount.as<uint32_t>(); fo.tcount = ctx->tcount.as<uint32_t>();
         fo.edgeMask = ctx->edgeMask.as<uint32_t>(); fo.edgePrefix = ctx->edgePrefix.as<uint16_t>();
         fo.mixedList = ctx->mixedList.as<uint32_t>(); fo.counters = ctx->counters.as<uint32_t>();
-        launch_field_kernel(G, ctx->cands, nCand, ctx->pool.as<float4>(), fo, maxLen, ctx->numSMs, st);
+        launch_field_kernel(G, ctx->cands, nCand, ctx->pool.as<float4>(), fo, maxLen, ctx->hasWarps, ctx->numSMs, st);
         launches++;
         CK(cudaEventRecord(ctx->ev[2], st));
         const size_t tb = scan_temp_bytes((int)n1);
@@ -541,7 +543,7 @@ extern "C" int psgpu_mpu_cache(psgpu_ctx* ctx, const psgpu_params* params, const
     fo.fv = ctx->fv.as<float4>(); fo.vcount = ctx->vcount.as<uint32_t>(); fo.tcount = ctx->tcount.as<uint32_t>();
     fo.edgeMask = ctx->edgeMask.as<uint32_t>(); fo.edgePrefix = ctx->edgePrefix.as<uint16_t>();
     fo.mixedList = ctx->mixedList.as<uint32_t>(); fo.counters = ctx->counters.as<uint32_t>();
-    psgpu::launch_field_kernel(G, ctx->regionsA.as<psgpu::Region>(), 1, ctx->pool.as<float4>(), fo, ctx->progQuads, ctx->numSMs, st);
+    psgpu::launch_field_kernel(G, ctx->regionsA.as<psgpu::Region>(), 1, ctx->pool.as<float4>(), fo, ctx->progQuads, ctx->hasWarps, ctx->numSMs, st);
     CK(cudaMemcpyAsync(fv512, ctx->fv.p, 2048, cudaMemcpyDeviceToHost, st));
     CK(cudaStreamSynchronize(st));
     CK(cudaGetLastError());

@@ -21,8 +21,10 @@ __constant__ uint8_t c_nTri[256] = PS_MC_NTRI_INIT;
 
 namespace {
 
-constexpr int kPts = 8;                 // z-consecutive corners per thread: a whole z-column of the 8x8x8 lattice
-constexpr int kThreads = 512 / kPts;    // 64: decode cost per interpreted instruction is shared by 8 points (ncu r01c: issue-bound on decode)
+// z-consecutive corners per thread: 8 = a whole z-column of the 8x8x8 lattice, 64 threads per MPU - the decode cost of an interpreted
+// instruction is shared by 8 points (ncu r01c: issue-bound on decode). Programs with warps (sincos per point, point stack) spill at
+// 8 points per thread and run the 4-point / 128-thread variant.
+constexpr int kMaxThreads = 128;
 constexpr uint32_t kMaxProgCapQuads = 1024;  // 16 KB per staging buffer; longer lists are read from global
 
 struct __align__(16) FieldSmemHeader {
@@ -38,12 +40,13 @@ struct __align__(16) FieldSmemHeader {
 
 // STAGED: every candidate list fits the staging buffers (the host checks the longest one) and is interpreted from shared memory;
 // the unstaged variant (brute-force mode, very long lists) reads the lists from global memory. One interpreter copy per kernel.
-template <bool STRICT, bool STAGED>
-__global__ void __launch_bounds__(kThreads, STRICT ? 12 : 16) field_kernel(GridParams G, const Region* __restrict__ cands, int nCand,
+template <bool STRICT, bool STAGED, int kPts>
+__global__ void __launch_bounds__(512 / kPts, kPts == 4 ? 6 : (STRICT ? 12 : 16)) field_kernel(GridParams G, const Region* __restrict__ cands, int nCand,
                                                          const float4* __restrict__ pool, FieldOutputs out, uint32_t capQuads) {
     extern __shared__ __align__(16) unsigned char smemRaw[];
     FieldSmemHeader& S = *reinterpret_cast<FieldSmemHeader*>(smemRaw);
     float4* progBuf = reinterpret_cast<float4*>(smemRaw + sizeof(FieldSmemHeader));
+    constexpr int kThreads = 512 / kPts;
     const int t = threadIdx.x;
     const int lane = t & 31;
 
@@ -274,7 +277,7 @@ int field_kernel_smem_bytes(uint32_t maxProgQuads, uint32_t* capQuads) {
 }
 
 void launch_field_kernel(const GridParams& G, const Region* cands, int nCand, const float4* pool, const FieldOutputs& out, uint32_t maxProgQuads,
-                         int numSMs, cudaStream_t st) {
+                         bool hasWarps, int numSMs, cudaStream_t st) {
     if (nCand <= 0) return;
     uint32_t cap;
     int smem = field_kernel_smem_bytes(maxProgQuads, &cap);
@@ -282,20 +285,25 @@ void launch_field_kernel(const GridParams& G, const Region* cands, int nCand, co
     if (getenv("PSGPU_NO_STAGE")) staged = false;  // debugging aid: interpret straight from global memory
     if (!staged) { cap = 8; smem = (int)(sizeof(FieldSmemHeader) + 2u * cap * 16u); }
     const bool strict = (G.sem == PSGPU_SEM_SIMD);
+    const bool four = !strict && hasWarps;
     using KernelT = void (*)(GridParams, const Region*, int, const float4*, FieldOutputs, uint32_t);
-    const KernelT k = strict ? (staged ? field_kernel<true, true> : field_kernel<true, false>)
-                             : (staged ? field_kernel<false, true> : field_kernel<false, false>);
-    static int configured[2][2] = {{-1, -1}, {-1, -1}};
-    if (smem > configured[strict][staged]) {
+    KernelT k;
+    if (strict) k = staged ? field_kernel<true, true, 8> : field_kernel<true, false, 8>;
+    else if (four) k = staged ? field_kernel<false, true, 4> : field_kernel<false, false, 4>;
+    else k = staged ? field_kernel<false, true, 8> : field_kernel<false, false, 8>;
+    const int threads = four ? 128 : 64;
+    static int configured[3][2] = {{-1, -1}, {-1, -1}, {-1, -1}};
+    const int vi = strict ? 0 : (four ? 1 : 2);
+    if (smem > configured[vi][staged]) {
         cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
-        configured[strict][staged] = smem;
+        configured[vi][staged] = smem;
     }
     int perSM = 0;
-    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSM, k, kThreads, smem);
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSM, k, threads, smem);
     if (perSM < 1) perSM = 1;
     int grid = numSMs * perSM;  // persistent CTAs: a whole number of waves on 148 SMs
     if (grid > nCand) grid = nCand;
-    k<<<grid, kThreads, smem, st>>>(G, cands, nCand, pool, out, cap);
+    k<<<grid, threads, smem, st>>>(G, cands, nCand, pool, out, cap);
 }
 
 void launch_points_field(const float4* prog, const float* xyz, int64_t n, float* f, int sem, cudaStream_t st) {

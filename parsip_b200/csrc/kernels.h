@@ -80,7 +80,7 @@ void exclusive_scan_u32(void* temp, size_t tempBytes, const uint32_t* in, uint32
 // field.cu
 int field_kernel_smem_bytes(uint32_t maxProgQuads, uint32_t* progCapQuads);
 void launch_field_kernel(const GridParams& G, const Region* cands, int nCand, const float4* pool, const FieldOutputs& out, uint32_t maxProgQuads,
-                         int numSMs, cudaStream_t st);
+                         bool hasWarps, int numSMs, cudaStream_t st);
 void launch_points_field(const float4* prog, const float* xyz, int64_t n, float* f, int sem, cudaStream_t st);
 void launch_points_field_color_normal(const float4* prog, const float* colorTab, const float* xyz, int64_t n, float* f, float* col, float* nrm,
                                       int sem, cudaStream_t st);
