@@ -176,7 +176,7 @@ def run_reference(args):
         "dtype": "f32", "data": "synthetic",
         "config": {"workload": w["name"], "semantics": "PS_SimdPoly (infinite lines, f>=iso, 4-sample roots)", "cells": w["cells"],
                    "primitives": w["prims"], "cellsize": cs, "lattice_mpus": dims},
-        "field_evals_per_s": st["simd_evals"] * 4.0 * args.steps / sec / max(1, args.steps) * 1.0,
+        "field_evals_per_s": st["simd_evals"] * 4.0 * args.steps / sec,
         "triangles_per_s": st["triangles"] * args.steps / sec,
         "cpu_baseline": {"value": value, "unit": "cells/s", "cores": cores, "kind": kind, "sample": sample},
         "e2e": {"value": value, "unit": "cells/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
