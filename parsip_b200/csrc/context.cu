@@ -252,8 +252,11 @@ int run_cull(psgpu_ctx* ctx, const GridParams& G, int cullMode, bool colorExact,
         if (fused) {
             CK(ctx->cullScratch.reserve(scratchQuads * 16)); CK(ctx->cullScratchFlag.reserve(scratchQuads));
             CK(cudaMemsetAsync(levelMax, 0, 4, st));
+            // few regions with a long program (the top level): a whole CTA per region instead of a warp
+            const char* ctaMin = getenv("PSGPU_CULL_CTA_MINLEN");
+            const bool ctaPerRegion = n <= 4096 && parentMaxLen >= (uint32_t)(ctaMin ? atoi(ctaMin) : 1024);
             launch_prune_fused(L, cur->as<Region>(), nParents, ctx->pool.as<float4>(), ctx->qflag.as<uint8_t>(), ctx->cullScratch.as<float4>(),
-                               ctx->cullScratchFlag.as<uint8_t>(), parentMaxLen, ctx->childLen.as<uint32_t>(), levelMax, st);
+                               ctx->cullScratchFlag.as<uint8_t>(), parentMaxLen, ctx->childLen.as<uint32_t>(), levelMax, ctaPerRegion, st);
         } else
             launch_prune_count(L, cur->as<Region>(), nParents, ctx->pool.as<float4>(), ctx->qflag.as<uint8_t>(), ctx->childLen.as<uint32_t>(), st);
         launch_flags(ctx->childLen.as<uint32_t>(), ctx->childFlag.as<uint32_t>(), n + 1, st);

@@ -229,6 +229,144 @@ __global__ void __launch_bounds__(kCoopWarps * 32) prune_fused_warp_kernel(CullL
     }
 }
 
+// ---- CTA-cooperative pruning for the top level ----------------------------------------------------------------------
+// Level 0 walks the WHOLE program for a few hundred regions (blob10k@1024^3 / 8 ranks: 200 regions x 17.5k quads): one warp per
+// region leaves 1-2 warps per SM, each ~5000 cycles per 32-quad batch with nothing to overlap (ncu r01e: 1.38 ms). Here a CTA
+// of kCtaWarps warps takes the region: kCtaWarps*32 quad positions per step, the surviving instructions of the step are
+// compacted IN PROGRAM ORDER into shared memory (with their header quad, so the serial part never touches global memory for a
+// header), and thread 0 feeds them to the same Pruner state machine - the output is identical to prune_walk's.
+constexpr int kCtaWarps = 16;
+struct __align__(16) CtaEntry { float4 h0; uint32_t pc, za; float flo, fhi; };
+struct CtaWalkSmem {
+    CtaEntry ent[kCtaWarps * 32];
+    uint32_t cnt[kCtaWarps], za[kCtaWarps];
+    uint32_t cut, cutHdr, endSeen, len;
+    float box[6];
+};
+
+template <bool EMIT>
+__device__ uint32_t prune_walk_cta(const float4* __restrict__ src, const uint8_t* __restrict__ sflag, uint32_t srcLen, const Box3& region,
+                                   int cullMode, float iso, float4* __restrict__ dst, uint8_t* dflag, bool colorExact, uint32_t limit,
+                                   CtaWalkSmem& S) {
+    const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
+    const uint32_t FULL = 0xffffffffu, NONE = 0xffffffffu;
+    Pruner<EMIT> P;
+    P.init(src, region, dst, dflag, colorExact, limit);
+    Box3 box = region;
+    uint32_t base = 0, zaTotal = 0, zaPrev = 0;
+    for (;;) {
+        if (tid == 0) S.cut = NONE;
+        __syncthreads();
+        const uint32_t p = base + (uint32_t)tid;
+        const bool isInstr = (p < srcLen) && (sflag[p] != 0);
+        float4 q0 = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (isInstr) q0 = src[p];
+        const uint32_t hdr = __float_as_uint(q0.x);
+        const uint32_t opc = PS_HDR_OPC(hdr);
+        // the step ends right after the first instruction that changes the region box (later bounds depend on it) or OPC_END
+        const bool cutter = isInstr && (opc == OPC_END || ps_changes_box(opc));
+        const uint32_t cutMask = __ballot_sync(FULL, cutter);
+        if (cutMask && lane == __ffs((int)cutMask) - 1) atomicMin(&S.cut, p);
+        __syncthreads();
+        const uint32_t cut = S.cut;
+        if (cutter && p == cut) S.cutHdr = hdr;
+        const bool active = isInstr && p <= cut;
+        bool pz = false, skip = false;
+        float flo = 0.f, fhi = 0.f;
+        uint32_t scale = 0;
+        if (active && opc != OPC_END && opc < OPC_FIRST_NONPRIM) {
+            pz = prim_bound(hdr, q0, src + p + 1, box, flo, fhi);
+            skip = Pruner<EMIT>::skippable(hdr, pz, scale);
+        }
+        const bool isEntry = active && !skip;
+        const uint32_t zs = (active && skip) ? scale : 0u;
+        uint32_t incl = zs;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const uint32_t v = __shfl_up_sync(FULL, incl, o);
+            if (lane >= o) incl += v;
+        }
+        const uint32_t entMask = __ballot_sync(FULL, isEntry);
+        if (lane == 31) S.za[w] = incl;
+        if (lane == 0) S.cnt[w] = (uint32_t)__popc(entMask);
+        __syncthreads();
+        uint32_t eoff = 0, zoff = 0, etot = 0, ztot = 0;
+#pragma unroll
+        for (int i = 0; i < kCtaWarps; i++) {
+            const uint32_t c = S.cnt[i], z = S.za[i];
+            if (i < w) { eoff += c; zoff += z; }
+            etot += c; ztot += z;
+        }
+        if (isEntry) {
+            CtaEntry e;
+            e.h0 = q0; e.pc = p | (pz ? 0x80000000u : 0u); e.za = zaTotal + zoff + incl - zs; e.flo = flo; e.fhi = fhi;
+            S.ent[eoff + (uint32_t)__popc(entMask & ((1u << lane) - 1u))] = e;
+        }
+        zaTotal += ztot;
+        __syncthreads();
+        if (tid == 0) {
+            uint32_t endSeen = 0;
+            for (uint32_t i = 0; i < etot; i++) {
+                const CtaEntry e = S.ent[i];
+                const uint32_t pc = e.pc & 0x7FFFFFFFu;
+                P.skipped_scale(e.za - zaPrev);
+                zaPrev = e.za;
+                const uint32_t h = __float_as_uint(e.h0.x), o = PS_HDR_OPC(h);
+                if (o == OPC_END) { endSeen = 1; break; }
+                if (o < OPC_FIRST_NONPRIM) {
+                    const bool zero = (e.pc >> 31) != 0u;
+                    if (zero && PS_HDR_CMB(h) == CMB_PUSH && i + 1 < etot) {
+                        // an all-zero operand whose OPC_COMBINE is the very next surviving instruction (its blend partners were
+                        // all skipped): fold the pair in one step. Scale steps owed between the two belong to the zero entry: dropped
+                        const uint32_t h2 = __float_as_uint(S.ent[i + 1].h0.x);
+                        if (PS_HDR_OPC(h2) == OPC_COMBINE) {
+                            zaPrev = S.ent[i + 1].za;
+                            P.step_zero_operand(h2);
+                            i++;
+                            continue;
+                        }
+                    }
+                    P.step_prim(pc, e.h0, h, zero, e.flo, e.fhi);
+                } else P.step_op(pc, e.h0, h);
+            }
+            S.endSeen = endSeen;
+#pragma unroll
+            for (int a = 0; a < 3; a++) { S.box[a] = P.box.lo[a]; S.box[3 + a] = P.box.hi[a]; }
+        }
+        __syncthreads();
+        if (S.endSeen) break;
+        if (cut != NONE) {
+#pragma unroll
+            for (int a = 0; a < 3; a++) { box.lo[a] = S.box[a]; box.hi[a] = S.box[3 + a]; }
+            base = cut + (uint32_t)ps_instr_quads(S.cutHdr);
+        } else base += (uint32_t)(kCtaWarps * 32);
+        if (base >= srcLen) break;  // malformed program without OPC_END
+    }
+    if (tid == 0) S.len = P.finish(cullMode, iso);
+    __syncthreads();
+    return S.len;
+}
+
+__global__ void __launch_bounds__(kCtaWarps * 32) prune_fused_cta_kernel(CullLevel L, const Region* __restrict__ parents, int nParents,
+                                                                         const float4* __restrict__ pool, const uint8_t* __restrict__ qflag,
+                                                                         float4* __restrict__ scratch, uint8_t* __restrict__ scratchFlag, uint32_t stride,
+                                                                         uint32_t* __restrict__ childLen, uint32_t* __restrict__ maxLen) {
+    __shared__ CtaWalkSmem S;
+    const int gw = blockIdx.x;
+    const Region parent = parents[gw >> 6];
+    int coord[3];
+    Box3 box;
+    uint32_t len = 0;
+    if (child_region(L, parent, gw & 63, coord, box))  // uniform over the CTA
+        len = prune_walk_cta<true>(pool + parent.off, qflag + parent.off, parent.len, box, L.cullMode, L.iso, scratch + (size_t)gw * stride,
+                                   scratchFlag + (size_t)gw * stride, L.colorExact != 0, stride, S);
+    if (threadIdx.x == 0) {
+        if (len > stride) len = 0xFFFFFFFFu;
+        childLen[gw] = len;
+        if (len) atomicMax(maxLen, len);
+    }
+}
+
 __global__ void __launch_bounds__(kCoopWarps * 32) prune_compact_kernel(CullLevel L, const Region* __restrict__ parents, int nParents,
                                                                         const float4* __restrict__ scratch, const uint8_t* __restrict__ scratchFlag,
                                                                         uint32_t stride, const uint32_t* __restrict__ childLen,
@@ -321,8 +459,12 @@ void launch_prune_emit(const CullLevel& L, const Region* parents, int nParents, 
 bool prune_level_is_fused(int nParents) { return use_warp_walk(nParents); }
 
 void launch_prune_fused(const CullLevel& L, const Region* parents, int nParents, const float4* pool, const uint8_t* qflag, float4* scratch,
-                        uint8_t* scratchFlag, uint32_t stride, uint32_t* childLen, uint32_t* maxLen, cudaStream_t st) {
+                        uint8_t* scratchFlag, uint32_t stride, uint32_t* childLen, uint32_t* maxLen, bool ctaPerRegion, cudaStream_t st) {
     const int n = nParents * 64;
+    if (ctaPerRegion) {
+        prune_fused_cta_kernel<<<n, kCtaWarps * 32, 0, st>>>(L, parents, nParents, pool, qflag, scratch, scratchFlag, stride, childLen, maxLen);
+        return;
+    }
     prune_fused_warp_kernel<<<(n + kCoopWarps - 1) / kCoopWarps, kCoopWarps * 32, 0, st>>>(L, parents, nParents, pool, qflag, scratch, scratchFlag, stride,
                                                                                           childLen, maxLen);
 }

@@ -283,6 +283,26 @@ struct Pruner {
         }
     }
 
+    // T (cmb) 0 for a non-zero entry T = stack slot t (the slot of the all-zero operand is already popped)
+    __device__ __forceinline__ void combine_with_zero(int t, uint32_t cmb, uint32_t hdr) {
+        if (cmb == CMB_MAX) {
+            if (blo[t] < 0.f) { put(hdrquad(PS_HDR(OPC_NULLPRIM, CMB_MAX, 0, 0)), true); blo[t] = 0.f; bhi[t] = fmaxf(bhi[t], 0.f); }
+        } else if (cmb == CMB_MIN) {
+            if (blo[t] >= 0.f) { rewind(bstart[t]); bzero[t] = true; blo[t] = bhi[t] = 0.f; }
+            else { put(hdrquad(PS_HDR(OPC_NULLPRIM, CMB_MIN, 0, 0)), true); bhi[t] = fminf(bhi[t], 0.f); }
+        } else if (cmb == CMB_DIF) {
+            if (bhi[t] > 1.0f) { put(hdrquad(PS_HDR(OPC_CLAMP1, 0, 0, 0)), true); bhi[t] = 1.0f; blo[t] = fminf(blo[t], 1.0f); }
+        } else if (cmb == CMB_ADD) cscale(1);
+        if (!bzero[t]) cscale(PS_HDR_CSC(hdr));
+    }
+    // "PUSH <all-zero primitive>; OPC_COMBINE" with nothing fed in between, in one step: what step_prim + step_op would do,
+    // without the stack round trip (the cooperative walks of cull.cu meet this pair once per culled blend group)
+    __device__ __forceinline__ void step_zero_operand(uint32_t combineHdr) {
+        const uint32_t cmbRaw = PS_HDR_CMB(combineHdr);
+        const uint32_t cmb = (cmbRaw == CMB_RADD) ? (uint32_t)CMB_ADD : cmbRaw;
+        if (sp >= 0 && !bzero[sp]) combine_with_zero(sp, cmb, combineHdr);
+    }
+
     // one non-primitive instruction (not OPC_END); warps / operator matrices / OPC_POPPOINT change `box`
     __device__ void step_op(uint32_t pc, const float4 q0, uint32_t hdr) {
         const uint32_t opc = PS_HDR_OPC(hdr);
@@ -309,15 +329,7 @@ struct Pruner {
                 } else rewind(bstart[t]);  // 0 * (1 - V)
                 if (!bzero[t]) cscale(PS_HDR_CSC(hdr));
             } else if (bzero[v]) {  // T (cmb) 0
-                if (cmb == CMB_MAX) {
-                    if (blo[t] < 0.f) { put(hdrquad(PS_HDR(OPC_NULLPRIM, CMB_MAX, 0, 0)), true); blo[t] = 0.f; bhi[t] = fmaxf(bhi[t], 0.f); }
-                } else if (cmb == CMB_MIN) {
-                    if (blo[t] >= 0.f) { rewind(bstart[t]); bzero[t] = true; blo[t] = bhi[t] = 0.f; }
-                    else { put(hdrquad(PS_HDR(OPC_NULLPRIM, CMB_MIN, 0, 0)), true); bhi[t] = fminf(bhi[t], 0.f); }
-                } else if (cmb == CMB_DIF) {
-                    if (bhi[t] > 1.0f) { put(hdrquad(PS_HDR(OPC_CLAMP1, 0, 0, 0)), true); bhi[t] = 1.0f; blo[t] = fminf(blo[t], 1.0f); }
-                } else if (cmb == CMB_ADD) cscale(1);
-                if (!bzero[t]) cscale(PS_HDR_CSC(hdr));
+                combine_with_zero(t, cmb, hdr);
             } else {
                 // peephole: V shrank to ONE primitive (its blend partners were culled): fold it into T with the combine code in
                 // its own header instead of PUSH + OPC_COMBINE - same operands in the same order, so the same bits, and the

@@ -212,6 +212,34 @@ def test_native_mesh_is_independent_of_culling_and_slab_sharding(ctx):
         assert nv >= whole["n_vertices"]
 
 
+@pytest.mark.parametrize("name,native", [("blob", False), ("csg", False), ("xforms", False), ("csgwarp", True), ("blob", True)])
+def test_cull_walk_variants_emit_identical_programs(ctx, name, native, monkeypatch):
+    """The three schedules of the pruning walk (a CTA per region at the top level, a warp per region, a thread per region in
+    two passes) run the same state machine: same pruned pool size, same evaluated MPUs, same mesh bytes. The CTA walk is forced
+    onto these short programs through PSGPU_CULL_CTA_MINLEN (default: only programs of 1024+ quads); csgwarp exercises its
+    step cuts at warp instructions."""
+    if native:
+        flat, lo, hi, cs = native_setup(ctx, name, 150)
+        prm = ps.Params.make(cs, lo, hi)
+    else:
+        _, orc = simd_setup(ctx, name)
+        lo, hi = orc.bbox()
+        cs = scenes.cellsize_for(lo, hi, 150)
+        prm = compat_params(cs, lo, hi, cull=ps.CULL_INTERVAL)
+    outs = []
+    for env in ({"PSGPU_CULL_CTA_MINLEN": "0"}, {"PSGPU_CULL_CTA_MINLEN": "1000000000"}, {"PSGPU_CULL_TWO_PASS": "1"}):
+        for k in ("PSGPU_CULL_CTA_MINLEN", "PSGPU_CULL_TWO_PASS"):
+            monkeypatch.delenv(k, raising=False)
+        for k, v in env.items():
+            monkeypatch.setenv(k, v)
+        m = ctx.polygonize(prm)
+        st = ctx.stats()
+        outs.append((st["pruned_quads"], st["mpus_evaluated"], m["n_vertices"], m["n_triangles"], gh.sha(m["pos"]), gh.sha(m["tri"]),
+                     gh.sha(m["col"])))
+    assert outs[0] == outs[1] == outs[2], outs
+    assert outs[0][0] > 0 and outs[0][2] > 0
+
+
 def test_polygonize_host_streams_the_same_mesh_and_checks_capacity(ctx):
     """psgpu_polygonize_host copies each mesh array to the caller's HOST buffers behind the kernel that produced it (on a second
     stream); the result must equal psgpu_polygonize + psgpu_mesh_download, in both output modes, and a buffer that is too small

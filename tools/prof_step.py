@@ -10,7 +10,12 @@ cells = 512
 for a in sys.argv[1:]:
     if a.startswith("--cells="):
         cells = int(a.split("=")[1])
-root = scenes.blob1k()
+slab = None  # --slab=r/R : rank r's z-slab of R on blob10k@1024^3 (one rank of BASELINE configs[3])
+for a in sys.argv[1:]:
+    if a.startswith("--slab="):
+        slab = tuple(int(v) for v in a.split("=")[1].split("/"))
+        cells = 1024
+root = scenes.blob10k() if slab else scenes.blob1k()
 flat_bin = bt.flatten(bt.binarize(root))
 lo, hi = ps.prepare_bboxes(flat_bin)
 cs = scenes.cellsize_for(lo, hi, cells)
@@ -21,6 +26,9 @@ if native:
 else:
     ctx.upload(ps.linearize(flat_bin, ps.SEM_SIMD, 0))
     prm = ps.Params.make(cs, lo, hi, root_mode=ps.ROOT_FOURSAMPLE)
+if slab:
+    from parsip_b200 import sharding
+    prm.z_begin, prm.z_end = sharding.slab_bounds(ps.lattice_dims(cs, lo, hi)[2], slab[1], slab[0])
 for i in range(3):
     m = ctx.polygonize(prm, download=False)
     st = ctx.stats()
