@@ -134,6 +134,12 @@ int psgpu_polygonize_host(psgpu_ctx* ctx, const psgpu_params* params, psgpu_mesh
 /* Copies the last device mesh (and the PSGPU_OUT_MPU tables) to host buffers. */
 int psgpu_mesh_download(psgpu_ctx* ctx, float* pos, float* nrm, float* col, uint32_t* tri, int32_t* mpu_ijk,
                         uint32_t* mpu_vbase, uint32_t* mpu_tbase);
+/* Same content without a caller buffer: the arrays land in a context-owned PINNED host arena (full link rate, no pageable
+ * staging) and the pointers stay valid until the next psgpu_polygonize* / psgpu_mesh_map_host on this context. NULL outputs are
+ * skipped. This is what the PolyMPUs writer of the facade reads from (the scatter into the reference's MPU structs,
+ * PS_SimdPoly/include/PS_Polygonizer.h:180-198, happens on the host). */
+int psgpu_mesh_map_host(psgpu_ctx* ctx, const float** pos, const float** nrm, const float** col, const uint32_t** tri,
+                        const int32_t** mpu_ijk, const uint32_t** mpu_vbase, const uint32_t** mpu_tbase);
 /* Parity hooks: field (and colour / normal) at arbitrary HOST points with the full, unculled program. */
 int psgpu_field_eval(psgpu_ctx* ctx, const float* xyz, int64_t n, float* f_out);
 int psgpu_field_color_normal(psgpu_ctx* ctx, const float* xyz, int64_t n, float* f, float* col, float* nrm);

@@ -20,7 +20,7 @@ ERRORS = {-1: "PARAM_ERROR", -2: "NOT_ENOUGH_MEM", -3: "INVALID_BVH", -4: "UNSUP
 EXPORTS = [
     "psgpu_create", "psgpu_destroy", "psgpu_last_error", "psgpu_device_count", "psgpu_linearize", "psgpu_program_free",
     "psgpu_program_info", "psgpu_program_copy", "psgpu_program_colors", "psgpu_prepare_bboxes", "psgpu_count_mpus", "psgpu_upload_program",
-    "psgpu_polygonize", "psgpu_polygonize_host", "psgpu_mesh_download", "psgpu_field_eval", "psgpu_field_color_normal",
+    "psgpu_polygonize", "psgpu_polygonize_host", "psgpu_mesh_download", "psgpu_mesh_map_host", "psgpu_field_eval", "psgpu_field_color_normal",
     "psgpu_mpu_cache", "psgpu_mpu_caches_culled", "psgpu_prune_region", "psgpu_get_stats", "psgpu_measure_fp32_peak",
 ]
 
@@ -116,6 +116,7 @@ def load_library():
     lib.psgpu_polygonize.argtypes = [vp, C.POINTER(Params), C.POINTER(_Mesh)]
     lib.psgpu_polygonize_host.argtypes = [vp, C.POINTER(Params), C.POINTER(_Mesh), vp, vp, vp, vp, C.c_int64, C.c_int64]
     lib.psgpu_mesh_download.argtypes = [vp] * 8
+    lib.psgpu_mesh_map_host.argtypes = [vp] * 8
     lib.psgpu_field_eval.argtypes = [vp, vp, C.c_int64, vp]
     lib.psgpu_field_color_normal.argtypes = [vp, vp, C.c_int64, vp, vp, vp]
     lib.psgpu_mpu_cache.argtypes = [vp, C.POINTER(Params), vp, vp, vp]

@@ -5,6 +5,11 @@
 #include <cmath>
 #include <cstdio>
 #include <cstring>
+#include <algorithm>
+#include <atomic>
+#include <chrono>
+#include <functional>
+#include <thread>
 #include <mutex>
 #include <vector>
 
@@ -231,8 +236,15 @@ int PrepareBBoxes(float cellsize, SOABlobPrims& P, SOABlobBoxMatrices& B, SOABlo
 int Polygonize(float cellsize, const SOABlobPrims& P, const SOABlobPrimMatrices& M, const SOABlobOps& O, PolyMPUs& out, MPUSTATS* stats) {
     if (P.ctPrims == 0) return RET_PARAM_ERROR;
     std::lock_guard<std::mutex> guard(g_lock);
+    const bool timing = getenv("PSGPU_FACADE_TIMING") != nullptr;  // stage times of this call on stderr
+    const auto tStart = std::chrono::steady_clock::now();
+    auto lap = [&](const char* what) {
+        if (timing) fprintf(stderr, "[PS_SimdPolyCompat] %-10s %8.3f ms\n", what,
+                            std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - tStart).count());
+    };
     int rc = uploadScene(P, M, O);
     if (rc != RET_SUCCESS) return rc;
+    lap("upload");
     psgpu_params prm;
     memset(&prm, 0, sizeof(prm));
     prm.cellsize = cellsize;
@@ -243,44 +255,74 @@ int Polygonize(float cellsize, const SOABlobPrims& P, const SOABlobPrimMatrices&
     psgpu_mesh mesh;
     rc = psgpu_polygonize(g_ctx, &prm, &mesh);
     if (rc != RET_SUCCESS) return rc;
+    lap("polygonize");
     // MPU lattice exactly as cpp:328-371
     const float side = cellsize * (float)(GRID_DIM - 1);
-    out.ctMPUs = 0;
     const int nx = mesh.lattice[0], ny = mesh.lattice[1], nz = mesh.lattice[2];
-    if ((long long)nx * ny * nz >= MAX_MPU_COUNT) printf("WARNING! MAX MPU Count Reached! Total = %d MAX = %d\n", nx * ny * nz, MAX_MPU_COUNT);
-    for (int i = 0; i < nx; i++) for (int j = 0; j < ny; j++) for (int k = 0; k < nz; k++) {
-        if (out.ctMPUs < MAX_MPU_COUNT) {
-            MPU& m = out.vMPUs[out.ctMPUs++];
-            m.bboxLo = svec3f(P.bboxLo.x + (float)i * side, P.bboxLo.y + (float)j * side, P.bboxLo.z + (float)k * side);
-            m.ctVertices = 0; m.ctTriangles = 0; m.ctFieldEvals = 0;
-        }
-    }
-    const size_t nv = (size_t)mesh.n_vertices, nt = (size_t)mesh.n_triangles, nm = (size_t)mesh.n_mpus_out;
-    std::vector<float> pos(nv * 3 + 3), nrm(nv * 3 + 3), col(nv * 3 + 3);
-    std::vector<uint32_t> tri(nt * 3 + 3), vb(nm + 1), tb(nm + 1);
-    std::vector<int32_t> ijk(nm * 3 + 3);
-    rc = psgpu_mesh_download(g_ctx, pos.data(), nrm.data(), col.data(), tri.data(), ijk.data(), vb.data(), tb.data());
+    const long long lattice = (long long)nx * ny * nz;
+    if (lattice >= MAX_MPU_COUNT) printf("WARNING! MAX MPU Count Reached! Total = %lld MAX = %d\n", lattice, MAX_MPU_COUNT);
+    out.ctMPUs = (U32)std::min<long long>(lattice, MAX_MPU_COUNT);
+    const size_t nm = (size_t)mesh.n_mpus_out;
+    const float *pos = nullptr, *nrm = nullptr, *col = nullptr;
+    const uint32_t *tri = nullptr, *vb = nullptr, *tb = nullptr;
+    const int32_t* ijk = nullptr;
+    rc = psgpu_mesh_map_host(g_ctx, &pos, &nrm, &col, &tri, &ijk, &vb, &tb);
     if (rc != RET_SUCCESS) return rc;
+    lap("download");
     psgpu_stats st;
     psgpu_get_stats(g_ctx, &st);
-    if (stats) for (U32 q = 0; q < out.ctMPUs; q++) { stats[q].idxThread = -1; stats[q].bIntersected = 0; stats[q].msStart = 0; stats[q].msEnd = st.ms_total; }
-    // ranks follow the candidate order, so both base tables are monotone and closed by the totals
-    for (size_t r = 0; r < nm; r++) {
-        const uint32_t t0 = tb[r], t1 = tb[r + 1], v0 = vb[r], v1 = vb[r + 1];
-        const long long idx = ((long long)ijk[r * 3] * ny + ijk[r * 3 + 1]) * nz + ijk[r * 3 + 2];
-        if (idx < 0 || idx >= (long long)out.ctMPUs) continue;
-        MPU& m = out.vMPUs[idx];
-        const uint32_t cv = v1 - v0, ct = t1 - t0;
-        if (cv > MAX_MPU_VERTEX_COUNT || ct > MAX_MPU_TRIANGLE_COUNT) return RET_NOT_ENOUGH_MEM;
-        memcpy(m.vPos, &pos[(size_t)v0 * 3], (size_t)cv * 12);
-        memcpy(m.vNorm, &nrm[(size_t)v0 * 3], (size_t)cv * 12);
-        memcpy(m.vColor, &col[(size_t)v0 * 3], (size_t)cv * 12);
-        for (uint32_t q = 0; q < ct * 3; q++) m.triangles[q] = (U16)tri[(size_t)t0 * 3 + q];
-        m.ctVertices = (U16)cv; m.ctTriangles = (U16)ct;
-        m.ctFieldEvals = 128;  // SIMD evaluations of the cache phase, the reference's unit (cpp:594)
-        if (stats) { stats[idx].idxThread = (int)r; stats[idx].bIntersected = 1; }
-    }
+    // The writer touches ~3 cache lines of every MPU struct (21.5 KB apart) and copies the surface MPUs' arrays: memory-latency
+    // work, split over a few host threads when the lattice is large (the reference fills PolyMPUs from all its TBB workers)
+    const unsigned hw = std::max(1u, std::thread::hardware_concurrency());
+    const int nThreads = (int)std::min<size_t>(std::min(hw, 8u), 1 + (out.ctMPUs + 4 * nm) / 8192);
+    std::atomic<int> overflow(0);
+    auto work = [&](int w) {
+        const size_t m0 = (size_t)out.ctMPUs * w / nThreads, m1 = (size_t)out.ctMPUs * (w + 1) / nThreads;
+        for (size_t q = m0; q < m1; q++) {  // q = (i * ny + j) * nz + k: x outer, z inner
+            const int k = (int)(q % nz), j = (int)((q / nz) % ny), i = (int)(q / ((size_t)nz * ny));
+            MPU& m = out.vMPUs[q];
+            m.bboxLo = svec3f(P.bboxLo.x + (float)i * side, P.bboxLo.y + (float)j * side, P.bboxLo.z + (float)k * side);
+            m.ctVertices = 0; m.ctTriangles = 0; m.ctFieldEvals = 0;
+            if (stats) { stats[q].idxThread = -1; stats[q].bIntersected = 0; stats[q].msStart = 0; stats[q].msEnd = st.ms_total; }
+        }
+        // ranks follow the candidate order, so both base tables are monotone and closed by the totals; a thread takes a
+        // contiguous range of ranks (their MPU structs may lie in another thread's lattice range: disjoint fields)
+        for (size_t r = nm * w / nThreads; r < nm * (w + 1) / nThreads; r++) {
+            const uint32_t t0 = tb[r], t1 = tb[r + 1], v0 = vb[r], v1 = vb[r + 1];
+            const long long idx = ((long long)ijk[r * 3] * ny + ijk[r * 3 + 1]) * nz + ijk[r * 3 + 2];
+            if (idx < 0 || idx >= (long long)out.ctMPUs) continue;
+            MPU& m = out.vMPUs[idx];
+            const uint32_t cv = v1 - v0, ct = t1 - t0;
+            if (cv > MAX_MPU_VERTEX_COUNT || ct > MAX_MPU_TRIANGLE_COUNT) { overflow = 1; continue; }
+            memcpy(m.vPos, &pos[(size_t)v0 * 3], (size_t)cv * 12);
+            memcpy(m.vNorm, &nrm[(size_t)v0 * 3], (size_t)cv * 12);
+            memcpy(m.vColor, &col[(size_t)v0 * 3], (size_t)cv * 12);
+            const uint32_t* src = &tri[(size_t)t0 * 3];
+            for (uint32_t q = 0; q < ct * 3; q++) m.triangles[q] = (U16)src[q];
+        }
+    };
+    auto counts = [&](int w) {  // after every thread's lattice pass: the counters of the surface MPUs
+        for (size_t r = nm * w / nThreads; r < nm * (w + 1) / nThreads; r++) {
+            const long long idx = ((long long)ijk[r * 3] * ny + ijk[r * 3 + 1]) * nz + ijk[r * 3 + 2];
+            if (idx < 0 || idx >= (long long)out.ctMPUs) continue;
+            MPU& m = out.vMPUs[idx];
+            m.ctVertices = (U16)(vb[r + 1] - vb[r]); m.ctTriangles = (U16)(tb[r + 1] - tb[r]);
+            m.ctFieldEvals = 128;  // SIMD evaluations of the cache phase, the reference's unit (cpp:594)
+            if (stats) { stats[idx].idxThread = (int)r; stats[idx].bIntersected = 1; }
+        }
+    };
+    auto fan = [&](const std::function<void(int)>& f) {
+        if (nThreads <= 1) { f(0); return; }
+        std::vector<std::thread> pool;
+        for (int w = 1; w < nThreads; w++) pool.emplace_back(f, w);
+        f(0);
+        for (auto& t : pool) t.join();
+    };
+    fan(work);
+    if (overflow) return RET_NOT_ENOUGH_MEM;  // the reference overruns the MPU's arrays here
+    fan(counts);
     g_processed = out.ctMPUs; g_crossed = (U32)nm;
+    lap("fill");
     return RET_SUCCESS;
 }
 

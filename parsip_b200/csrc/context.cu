@@ -66,6 +66,8 @@ struct psgpu_ctx {
     uint32_t* hostScalars = nullptr;  // pinned readback
     void* hostStage = nullptr;        // pinned upload staging (program + colours)
     size_t hostStageCap = 0;
+    void* hostMesh = nullptr;         // pinned arena behind psgpu_mesh_map_host
+    size_t hostMeshCap = 0;
     cudaEvent_t ev[8];
     psgpu_mesh last{};
     psgpu_stats stats{};
@@ -118,6 +120,7 @@ extern "C" int psgpu_destroy(psgpu_ctx* ctx) {
     for (auto& e : ctx->ev) cudaEventDestroy(e);
     if (ctx->hostScalars) cudaFreeHost(ctx->hostScalars);
     if (ctx->hostStage) cudaFreeHost(ctx->hostStage);
+    if (ctx->hostMesh) cudaFreeHost(ctx->hostMesh);
     cudaStreamDestroy(ctx->copyStream);
     cudaStreamDestroy(ctx->stream);
     delete ctx;
@@ -482,6 +485,46 @@ extern "C" int psgpu_mesh_download(psgpu_ctx* ctx, float* pos, float* nrm, float
         if (mpu_tbase) CK(cudaMemcpyAsync(mpu_tbase, M.mpu_tbase, ((size_t)M.n_mpus_out + 1) * 4, cudaMemcpyDeviceToHost, st));
     }
     CK(cudaStreamSynchronize(st));
+    return PSGPU_SUCCESS;
+}
+
+// The last mesh in a context-owned PINNED arena: one asynchronous copy per array at full link rate (a copy into pageable
+// caller memory is staged by the driver chunk by chunk), pointers valid until the next polygonize / map on this context.
+extern "C" int psgpu_mesh_map_host(psgpu_ctx* ctx, const float** pos, const float** nrm, const float** col, const uint32_t** tri,
+                                   const int32_t** mpu_ijk, const uint32_t** mpu_vbase, const uint32_t** mpu_tbase) {
+    if (!ctx) return PSGPU_PARAM_ERROR;
+    CK(cudaSetDevice(ctx->device));
+    const psgpu_mesh& M = ctx->last;
+    cudaStream_t st = ctx->stream;
+    auto pad = [](size_t b) { return (b + 255) & ~(size_t)255; };
+    const size_t vB = pad((size_t)M.n_vertices * 12), tB = pad((size_t)M.n_triangles * 12);
+    const size_t iB = pad((size_t)M.n_mpus_out * 12), bB = pad(((size_t)M.n_mpus_out + 1) * 4);
+    const size_t need = (pos ? vB : 0) + (nrm ? vB : 0) + (col ? vB : 0) + (tri ? tB : 0) + (mpu_ijk ? iB : 0) + (mpu_vbase ? bB : 0) + (mpu_tbase ? bB : 0) + 256;
+    if (need > ctx->hostMeshCap) {
+        if (ctx->hostMesh) cudaFreeHost(ctx->hostMesh);
+        ctx->hostMesh = nullptr;
+        ctx->hostMeshCap = 0;
+        const size_t cap = need + need / 4;
+        CK(cudaMallocHost(&ctx->hostMesh, cap));
+        ctx->hostMeshCap = cap;
+    }
+    char* cur = (char*)ctx->hostMesh;
+    auto take = [&](const void* dev, size_t bytes, size_t padded) -> const void* {
+        char* dst = cur;
+        cur += padded;
+        if (dev && bytes) cudaMemcpyAsync(dst, dev, bytes, cudaMemcpyDeviceToHost, st);
+        return dst;
+    };
+    if (pos) *pos = (const float*)take(M.pos, (size_t)M.n_vertices * 12, vB);
+    if (nrm) *nrm = (const float*)take(M.nrm, (size_t)M.n_vertices * 12, vB);
+    if (col) *col = (const float*)take(M.col, (size_t)M.n_vertices * 12, vB);
+    if (tri) *tri = (const uint32_t*)take(M.tri, (size_t)M.n_triangles * 12, tB);
+    const bool tables = M.n_mpus_out > 0;
+    if (mpu_ijk) *mpu_ijk = (const int32_t*)take(tables ? M.mpu_ijk : nullptr, (size_t)M.n_mpus_out * 12, iB);
+    if (mpu_vbase) *mpu_vbase = (const uint32_t*)take(tables ? M.mpu_vbase : nullptr, ((size_t)M.n_mpus_out + 1) * 4, bB);
+    if (mpu_tbase) *mpu_tbase = (const uint32_t*)take(tables ? M.mpu_tbase : nullptr, ((size_t)M.n_mpus_out + 1) * 4, bB);
+    CK(cudaStreamSynchronize(st));
+    CK(cudaGetLastError());
     return PSGPU_SUCCESS;
 }
 

@@ -1,0 +1,73 @@
+"""Drop-in comparison on BASELINE configs[0] (small BlobTree, 10 point/line primitives, 128^3 cells), development aid:
+the SAME caller-side code - fill the SoA tables, PrepareBBoxes, Polygonize into a caller-owned 516 MB PolyMPUs - run once
+against the reference's own unmodified build (oracle/_ref: PS_Polygonizer.cpp + the parallel TBB shim, all host threads) and
+once against this repo's facade (include/PS_SimdPolyCompat.h -> libpsgpu.so, tests/facade/facade_probe.cpp is the caller).
+Wall clock around Polygonize only, host buffers on both sides; checks that the two PolyMPUs hold the same mesh.
+One JSON line (kept under profiles/). Nothing here is on a product path: the reference build is the checker / baseline."""
+import json, os, sys, time
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+import ctypes as C
+import parsip_b200 as ps
+from parsip_b200 import blobtree as bt, scenes
+from oracle.pyoracle import RefScene
+import test_gpu_facade as tf
+import gpu_helpers as gh
+
+cells = 128
+soa = bt.to_binary_soa(bt.binarize(scenes.small()))
+ref = RefScene(soa)
+ref.prepare_bboxes(0.05)
+lo, hi = ref.bbox()
+cs = scenes.cellsize_for(lo, hi, cells)
+reps = 7
+
+
+def timed(fn):
+    ts, out = [], None
+    for _ in range(reps):
+        t = time.perf_counter()
+        out = fn()
+        ts.append((time.perf_counter() - t) * 1e3)
+    return float(np.median(ts[2:])), float(min(ts[2:])), out
+
+
+# reference build, all host threads
+ref_ms, ref_best, (ret, rst) = timed(lambda: ref.polygonize(cs))
+assert ret == 1, ret
+asis = dict(vertices=rst["vertices"], triangles=rst["triangles"])
+# as-is the reference's depth>3 operator-box prune zeroes small field values near box corners (boxes padded by 0.504, support 1.0:
+# SURVEY Q8), which moves a few dozen vertices; the byte comparison is against the same build with that prune neutralised
+ref.pad_op_boxes(1.0e6)
+pad_ms, _, (ret, rst) = timed(lambda: ref.polygonize(cs))
+assert ret == 1, ret
+rpos, rnrm, rcol, rtri = ref.mesh(rst)
+
+# facade
+lib = tf._lib()
+sc = tf.Scene(lib, soa)
+assert lib.fac_prepare_bboxes(sc.h, 0.05) == 1
+st = np.zeros(4, np.int64)
+fac_ms, fac_best, ret = timed(lambda: lib.fac_polygonize(sc.h, C.c_float(cs), st.ctypes.data))
+assert ret == 1, ret
+nv, nt = int(st[2]), int(st[3])
+pos, nrm, col = (np.zeros((nv, 3), np.float32) for _ in range(3))
+tri = np.zeros((nt, 3), np.uint32)
+lib.fac_mesh_concat(sc.h, pos.ctypes.data, nrm.ctypes.data, col.ctypes.data, tri.ctypes.data, None)
+same = dict(counts=(int(st[0]), nv, nt) == (rst["mpus"], rst["vertices"], rst["triangles"]),
+            pos=bool(np.array_equal(pos.view(np.uint32), rpos.view(np.uint32))), tri=bool(np.array_equal(tri, rtri)),
+            col=bool(np.array_equal(col.view(np.uint32), rcol.view(np.uint32))),
+            nrm_max_abs=float(np.nanmax(np.abs(nrm - rnrm))) if nv else 0.0)
+n_cells = rst["mpus"] * 343
+print(json.dumps({
+    "config": "configs[0] small@128^3 through Polygonize(cellsize, prims, mats, ops, PolyMPUs&), host buffers both sides",
+    "cellsize": cs, "mpus": rst["mpus"], "vertices": nv, "triangles": nt,
+    "reference": {"build": "oracle/_ref (unmodified PS_Polygonizer.cpp, parallel TBB shim)", "cores": os.cpu_count(), "ms_median": ref_ms,
+                  "ms_best": ref_best, "cells_per_s": n_cells / (ref_ms * 1e-3), "as_is_counts": asis, "ms_median_op_boxes_padded": pad_ms},
+    "facade": {"build": "libpsgpu.so behind PS_SimdPolyCompat.h", "ms_median": fac_ms, "ms_best": fac_best,
+               "cells_per_s": n_cells / (fac_ms * 1e-3), "includes": "SoA -> tree, linearize, upload, cull, field, MC, D2H, PolyMPUs fill"},
+    "speedup_median": ref_ms / fac_ms, "same_output": same}))
+sc.close()
