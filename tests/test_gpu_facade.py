@@ -120,3 +120,42 @@ def test_simdpoly_wrapper_class_and_error_codes(lib):
     # an n-ary operator is PS_ERROR_NON_BINARY_OP (-3), as in PS_HighPerformanceRender.cpp:81-86
     nary, keep2 = ps_api._tree_struct(bt.flatten(scenes_small.SIMD_SCENES["s1"]()))
     assert lib.fac_simdpoly_run(C.addressof(nary), 0.1, st.ctypes.data) == -3
+
+
+def test_facade_large_lattice_uses_the_threaded_writer(lib, ctx):
+    """~20 000 MPUs (just under the reference's MAX_MPU_COUNT of 24 000): the PolyMPUs writer splits the lattice over several
+    host threads; its content must be the C ABI's PSGPU_OUT_MPU mesh of the same scene, MPU by MPU in lattice order."""
+    from test_gpu_parity import compat_params, simd_setup
+    from parsip_b200 import scenes
+    name = "blob"
+    soa = bt.to_binary_soa(bt.binarize(scenes_small.SIMD_SCENES[name]()))
+    sc = Scene(lib, soa)
+    try:
+        assert lib.fac_prepare_bboxes(sc.h, 0.05) == 1
+        lo, hi = np.zeros(3, np.float32), np.zeros(3, np.float32)
+        lib.fac_get_bbox(sc.h, lo.ctypes.data, hi.ctypes.data)
+        cs = scenes.cellsize_for(lo, hi, 186)  # 27 MPUs on the longest axis
+        n_mpus = lib.fac_count_mpus(sc.h, cs)
+        assert 8192 < n_mpus < 24000
+        st = np.zeros(4, np.int64)
+        assert lib.fac_polygonize(sc.h, cs, st.ctypes.data) == 1
+        nv, nt = int(st[2]), int(st[3])
+        pos, nrm, col = (np.zeros((nv, 3), np.float32) for _ in range(3))
+        tri = np.zeros((nt, 3), np.uint32)
+        mlo = np.zeros((int(st[0]), 3), np.float32)
+        lib.fac_mesh_concat(sc.h, pos.ctypes.data, nrm.ctypes.data, col.ctypes.data, tri.ctypes.data, mlo.ctypes.data)
+    finally:
+        sc.close()
+    simd_setup(ctx, name)
+    m = ctx.polygonize(compat_params(cs, lo, hi))
+    p2, n2, c2, t2, ijk, counts = gh.lattice_ordered(m)
+    assert int(st[0]) == n_mpus == ctx.stats()["mpus_total"] and int(st[1]) == m["n_mpus_out"]
+    assert (nv, nt) == (m["n_vertices"], m["n_triangles"]) and nv > 100000
+    for a, b in ((pos, p2), (nrm, n2), (col, c2)):
+        assert np.array_equal(bits(a), bits(b))
+    assert np.array_equal(tri, t2)
+    # lattice origins: x outer, z inner, lo + idx * side (PS_Polygonizer.cpp:360-370)
+    dims = ps.lattice_dims(cs, lo, hi)
+    side = np.float32(cs) * np.float32(7)
+    q = (3 * dims[1] + 5) * dims[2] + 7
+    assert np.array_equal(bits(mlo[q]), bits(np.array([lo[0] + np.float32(3) * side, lo[1] + np.float32(5) * side, lo[2] + np.float32(7) * side], np.float32)))
