@@ -119,6 +119,16 @@ int psgpu_program_info(const psgpu_program* p, int64_t* info5);
 int psgpu_program_copy(const psgpu_program* p, uint32_t* quads_out /* 4 words per quad */);
 /* diffuse colour table, 3 floats per primitive id (the id in each primitive's header word) */
 int psgpu_program_colors(const psgpu_program* p, float* rgb_out /* 3 * primitives */);
+/* Pre-linearization pass (host only): ConvertToBinaryTree::run, ParsipHaptics/include/CLayerManager.cpp:81-233. Operators with
+ * more than two children become right-leaning chains of clones of themselves - op(c0, op(c1, ... op(c_{n-2}, c_{n-1}))) - unless
+ * split_always == 0 and all the children are primitives; a non-unary operator with one child gets a PSGPU_PRIM_NULL sibling when
+ * pad_with_null != 0. Output nodes are numbered in the reference's clone order (= the ids its converted tree carries).
+ * n_converted (optional) = operators split + NULL pads. The result is what SimdPoly::linearizeBlobTree requires (exactly two
+ * children per operator, PS_HighPerformanceRender.cpp:81-86); psgpu_linearize itself also accepts n-ary trees. */
+typedef struct psgpu_tree_buf psgpu_tree_buf;
+int psgpu_tree_binarize(const psgpu_tree* in, int split_always, int pad_with_null, psgpu_tree_buf** out, int32_t* n_converted);
+const psgpu_tree* psgpu_tree_view(const psgpu_tree_buf* buf);
+int psgpu_tree_free(psgpu_tree_buf* buf);
 /* Grid-domain box of the tree the way PrepareBBoxes computes it (iso distance 0.4542 + 0.05 padding). */
 int psgpu_prepare_bboxes(const psgpu_tree* tree, float cellsize, float* lo3, float* hi3);
 uint32_t psgpu_count_mpus(float cellsize, const float* lo3, const float* hi3);

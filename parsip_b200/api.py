@@ -21,7 +21,7 @@ EXPORTS = [
     "psgpu_create", "psgpu_destroy", "psgpu_last_error", "psgpu_device_count", "psgpu_linearize", "psgpu_program_free",
     "psgpu_program_info", "psgpu_program_copy", "psgpu_program_colors", "psgpu_prepare_bboxes", "psgpu_count_mpus", "psgpu_upload_program",
     "psgpu_polygonize", "psgpu_polygonize_host", "psgpu_mesh_download", "psgpu_mesh_map_host", "psgpu_field_eval", "psgpu_field_color_normal",
-    "psgpu_mpu_cache", "psgpu_mpu_caches_culled", "psgpu_prune_region", "psgpu_get_stats", "psgpu_measure_fp32_peak",
+    "psgpu_tree_binarize", "psgpu_tree_view", "psgpu_tree_free", "psgpu_mpu_cache", "psgpu_mpu_caches_culled", "psgpu_prune_region", "psgpu_get_stats", "psgpu_measure_fp32_peak",
 ]
 
 
@@ -117,6 +117,10 @@ def load_library():
     lib.psgpu_polygonize_host.argtypes = [vp, C.POINTER(Params), C.POINTER(_Mesh), vp, vp, vp, vp, C.c_int64, C.c_int64]
     lib.psgpu_mesh_download.argtypes = [vp] * 8
     lib.psgpu_mesh_map_host.argtypes = [vp] * 8
+    lib.psgpu_tree_binarize.argtypes = [vp, C.c_int, C.c_int, vp, vp]
+    lib.psgpu_tree_view.restype = vp
+    lib.psgpu_tree_view.argtypes = [vp]
+    lib.psgpu_tree_free.argtypes = [vp]
     lib.psgpu_field_eval.argtypes = [vp, vp, C.c_int64, vp]
     lib.psgpu_field_color_normal.argtypes = [vp, vp, C.c_int64, vp, vp, vp]
     lib.psgpu_mpu_cache.argtypes = [vp, C.POINTER(Params), vp, vp, vp]
@@ -183,6 +187,29 @@ def prepare_bboxes(flat: dict, cellsize: float = 0.14):
     if rc != SUCCESS:
         raise PsGpuError(rc, "psgpu_prepare_bboxes")
     return lo, hi
+
+
+def binarize_tree(flat: dict, split_always: bool = True, pad_with_null: bool = True):
+    """psgpu_tree_binarize (ConvertToBinaryTree, CLayerManager.cpp:81-233) on a flat tree -> (flat tree dict, n_converted)."""
+    lib = load_library()
+    t, keep = _tree_struct(flat)
+    h, nconv = C.c_void_p(), C.c_int32(0)
+    rc = lib.psgpu_tree_binarize(C.byref(t), int(split_always), int(pad_with_null), C.byref(h), C.byref(nconv))
+    if rc != SUCCESS:
+        raise PsGpuError(rc, "psgpu_tree_binarize")
+    try:
+        v = C.cast(lib.psgpu_tree_view(h), C.POINTER(_Tree)).contents
+        N = v.n_nodes
+        arr = lambda ptr, n, dt: np.ctypeslib.as_array(ptr, shape=(n,)).astype(dt).copy() if n else np.zeros(0, dt)
+        nk = arr(v.n_children, N, np.int32)
+        out = dict(n_nodes=N, root=v.root, type=arr(v.type, N, np.int32), first_child=arr(v.first_child, N, np.int32), n_children=nk,
+                   child=arr(v.child, max(1, int(nk.sum())), np.int32), pos=arr(v.pos, N * 3, np.float32).reshape(N, 3),
+                   dir=arr(v.dir, N * 3, np.float32).reshape(N, 3), res=arr(v.res, N * 4, np.float32).reshape(N, 4),
+                   color=arr(v.color, N * 3, np.float32).reshape(N, 3), xform=arr(v.xform, N * 12, np.float32).reshape(N, 12),
+                   has_xform=arr(v.has_xform, N, np.uint8))
+    finally:
+        lib.psgpu_tree_free(h)
+    return out, int(nconv.value)
 
 
 def count_mpus(cellsize, lo, hi) -> int:
