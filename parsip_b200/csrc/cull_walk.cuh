@@ -79,7 +79,9 @@ __device__ void warp_box(uint32_t opc, const float4 q0, const float4* __restrict
         const float ta = k * (yh0 - y0), tb = k * (yh1 - y0);
         float cmin, cmax, smin, smax;
         trig_range(fminf(ta, tb), fmaxf(ta, tb), cmin, cmax, smin, smax);
-        const float dy0 = fminf(b.lo[1] - left, 0.f), dy1 = fmaxf(b.hi[1] - right, 0.f);
+        // the straight extension outside [left, right]: e(y) = y - left below, 0 inside, y - right above - monotone in y, so
+        // its range over the box is [e(lo), e(hi)] (not the hull with 0: a box far outside the bent region keeps its size)
+        const float dy0 = fminf(b.lo[1] - left, 0.f) + fmaxf(b.lo[1] - right, 0.f), dy1 = fminf(b.hi[1] - left, 0.f) + fmaxf(b.hi[1] - right, 0.f);
         const float z0 = b.lo[2] - kd, z1 = b.hi[2] - kd;
         float a0, a1, b0, b1;
         imul(smin, smax, z0, z1, a0, a1); imul(cmin, cmax, dy0, dy1, b0, b1);
