@@ -181,6 +181,7 @@ int fill_grid(psgpu_ctx* ctx, const psgpu_params* P, GridParams& G) {
         G.hi[2] = std::min(nm[2], P->z_end);
     }
     G.cellsize = P->cellsize;
+    G.hasWarps = ctx->hasWarps ? 1 : 0;
     G.mpuSide = P->cellsize * (float)PS_CELLS_PER_MPU;
     G.coordMode = P->coord_mode; G.sem = ctx->semantics; G.output = P->output; G.rootMode = P->root_mode;
     G.rootIters = P->root_iterations > 0 ? P->root_iterations : (P->root_mode == PSGPU_ROOT_NEWTON_REF ? 8 : 4);

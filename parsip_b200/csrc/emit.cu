@@ -39,14 +39,14 @@ __device__ __forceinline__ EdgePos edge_endpoints(const GridParams& G, const Reg
 
 // ONE out-of-line copy of the plain 4-wide interpreter per kernel: the root search and the normal both call it (inlining it
 // at every call site multiplied the hot code past the instruction caches)
-template <bool STRICT, bool SMEM>
+template <bool STRICT, bool SMEM, bool WARPS>
 __device__ __noinline__ void eval4(const float4* prog, const float (&X)[4], const float (&Y)[4], const float (&Z)[4], float (&F)[4], int sem) {
-    eval_program<4, false, STRICT, SMEM>(prog, X, Y, Z, F, nullptr, nullptr, sem);
+    eval_program<4, false, STRICT, SMEM, WARPS>(prog, X, Y, Z, F, nullptr, nullptr, sem);
 }
 
 // PS_Polygonizer.cpp:728-762: samples at t = 0, 1/3, 2/3, 1 in one 4-wide evaluation, first lane whose
 // inside flag differs from lane 0 brackets the root, linear interpolation inside that sub-interval.
-template <bool STRICT, bool SMEM>
+template <bool STRICT, bool SMEM, bool WARPS>
 __device__ void root_foursample(const GridParams& G, const float4* prog, const EdgePos& E, float (&p)[3]) {
     float X[4], Y[4], Z[4], F[4];
     const float d = __fsub_rn(E.e2a, E.e1[E.axis]);
@@ -58,7 +58,7 @@ __device__ void root_foursample(const GridParams& G, const float4* prog, const E
         Y[l] = (E.axis == 1) ? moved : E.e1[1];
         Z[l] = (E.axis == 2) ? moved : E.e1[2];
     }
-    eval4<STRICT, SMEM>(prog, X, Y, Z, F, G.sem);
+    eval4<STRICT, SMEM, WARPS>(prog, X, Y, Z, F, G.sem);
     const bool state = is_inside(G, F[0]);
     // first lane whose flag differs from lane 0, else the last one (cpp:748-755)
     const int interval = (is_inside(G, F[1]) != state) ? 1 : ((is_inside(G, F[2]) != state) ? 2 : 3);
@@ -76,7 +76,7 @@ __device__ void root_foursample(const GridParams& G, const float4* prog, const E
 // change (x5 per round, a fixed trip count - a warp never waits for one slow lane the way per-lane false position does);
 // the root is the secant point of the final bracket. The bracket is guaranteed: both edge ends are lattice corners whose
 // cached values came from this same program. 4 rounds: bracket 1.6e-3 cell, secant error far below 1e-4 cell.
-template <bool STRICT, bool SMEM>
+template <bool STRICT, bool SMEM, bool WARPS>
 __device__ void root_section(const GridParams& G, const float4* prog, const EdgePos& E, float f1, float f2, int rounds, float (&p)[3]) {
     float ta = 0.f, tb = 1.f, fa = f1 - G.iso, fb = f2 - G.iso;
     const float d = E.e2a - E.e1[E.axis];
@@ -92,7 +92,7 @@ __device__ void root_section(const GridParams& G, const float4* prog, const Edge
             Y[l] = (E.axis == 1) ? moved : E.e1[1];
             Z[l] = (E.axis == 2) ? moved : E.e1[2];
         }
-        eval4<STRICT, SMEM>(prog, X, Y, Z, F, G.sem);
+        eval4<STRICT, SMEM, WARPS>(prog, X, Y, Z, F, G.sem);
         // first sample on the far side of the surface closes the bracket; the one before it opens it
         float nta = ta, nfa = fa, ntb = tb, nfb = fb;
         bool found = false;
@@ -114,21 +114,21 @@ __device__ void root_section(const GridParams& G, const float4* prog, const Edge
 }
 
 // ComputeRootNewtonRaphsonVEC4 (CompactBlobTree.cpp:1581-1622) incl. the fp^2 damping of its vec4 dot
-template <bool STRICT, bool SMEM>
+template <bool STRICT, bool SMEM, bool WARPS>
 __device__ void root_newton_ref(const GridParams& G, const float4* prog, const EdgePos& E, float f1, float f2, int iters, float (&p)[3]) {
     float x[3] = {E.e1[0], E.e1[1], E.e1[2]};
     if (!(fabsf(f1 - G.iso) < fabsf(f2 - G.iso))) x[E.axis] = E.e2a;
     const float eps = PS_FIELDVALUE_EPSILON, inv = 1.0f / PS_FIELDVALUE_EPSILON;
     for (int it = 0; it < iters; it++) {
         float X[4] = {x[0], x[0] + eps, x[0], x[0]}, Y[4] = {x[1], x[1], x[1] + eps, x[1]}, Z[4] = {x[2], x[2], x[2], x[2] + eps}, F[4];
-        eval4<STRICT, SMEM>(prog, X, Y, Z, F, G.sem);
+        eval4<STRICT, SMEM, WARPS>(prog, X, Y, Z, F, G.sem);
         const float fp = F[0];
         const float gx = (F[1] - fp) * inv, gy = (F[2] - fp) * inv, gz = (F[3] - fp) * inv;
         const float dd = G.iso - fp;
         const float g = 1.0f / (gx * gx + gy * gy + gz * gz + fp * fp);
         x[0] = x[0] + (dd * gx) * g; x[1] = x[1] + (dd * gy) * g; x[2] = x[2] + (dd * gz) * g;
         float X1[1] = {x[0]}, Y1[1] = {x[1]}, Z1[1] = {x[2]}, F1[1];
-        eval_program<1, false, STRICT, SMEM>(prog, X1, Y1, Z1, F1, nullptr, nullptr, G.sem);
+        eval_program<1, false, STRICT, SMEM, WARPS>(prog, X1, Y1, Z1, F1, nullptr, nullptr, G.sem);
         if (fabsf(F1[0] - G.iso) < eps) break;
     }
     p[0] = x[0]; p[1] = x[1]; p[2] = x[2];
@@ -367,16 +367,16 @@ __device__ __forceinline__ void stage_warp_program(float4* slice, const float4* 
 // position (root on the edge) and forward-difference normal of one vertex; the plain 4-wide interpreter, the same code the
 // field kernel runs (the colour walk lives in color_kernel so that neither hot loop outgrows the instruction caches: with
 // both inlined here ncu r01b showed stall_no_instruction at 12.7 cycles per issue)
-template <bool STRICT, int ROOT, bool SMEM>
+template <bool STRICT, int ROOT, bool SMEM, bool WARPS>
 __device__ __forceinline__ void vertex_at(const GridParams& G, const float4* prog, const EdgePos& E, float f1, float f2, float (&p)[3], float (&nrm)[3]) {
-    if (ROOT == PSGPU_ROOT_FOURSAMPLE) root_foursample<STRICT, SMEM>(G, prog, E, p);
-    else if (ROOT == PSGPU_ROOT_NEWTON_REF) root_newton_ref<STRICT, SMEM>(G, prog, E, f1, f2, G.rootIters, p);
-    else root_section<STRICT, SMEM>(G, prog, E, f1, f2, G.rootIters, p);
+    if (ROOT == PSGPU_ROOT_FOURSAMPLE) root_foursample<STRICT, SMEM, WARPS>(G, prog, E, p);
+    else if (ROOT == PSGPU_ROOT_NEWTON_REF) root_newton_ref<STRICT, SMEM, WARPS>(G, prog, E, f1, f2, G.rootIters, p);
+    else root_section<STRICT, SMEM, WARPS>(G, prog, E, f1, f2, G.rootIters, p);
     if (G.wantNormals) {
         const float dl = PS_NORMAL_DELTA;
         float X[4] = {p[0], p[0] + dl, p[0], p[0]}, Y[4] = {p[1], p[1], p[1] + dl, p[1]}, Z[4] = {p[2], p[2], p[2], p[2] + dl};
         float F[4];
-        eval4<STRICT, SMEM>(prog, X, Y, Z, F, G.sem);
+        eval4<STRICT, SMEM, WARPS>(prog, X, Y, Z, F, G.sem);
         const float dinv = -1.0f / dl;
         float nx = (F[1] - F[0]) * dinv, nyv = (F[2] - F[0]) * dinv, nzv = (F[3] - F[0]) * dinv;
         const float l2 = nx * nx + nyv * nyv + nzv * nzv;
@@ -386,7 +386,7 @@ __device__ __forceinline__ void vertex_at(const GridParams& G, const float4* pro
     }
 }
 
-template <bool STRICT, int ROOT, bool SMEM>
+template <bool STRICT, int ROOT, bool SMEM, bool WARPS>
 __global__ void __launch_bounds__(kThreads, 6) vertex_kernel(GridParams G, const Region* __restrict__ cands, const float4* __restrict__ pool,
                                                              FieldOutputs fo, MeshOutputs mo, int nMixed, uint32_t sliceQuads) {
     __shared__ uint32_t sW[kThreads / 32][48];
@@ -426,7 +426,7 @@ __global__ void __launch_bounds__(kThreads, 6) vertex_kernel(GridParams G, const
             float f1 = 0.f, f2 = 0.f;
             if (ROOT != PSGPU_ROOT_FOURSAMPLE) { f1 = fv[corner]; f2 = fv[corner + (axis == 0 ? 8 : (axis == 1 ? 64 : 1))]; }
             float p[3], nr[3] = {0.f, 0.f, 0.f};
-            vertex_at<STRICT, ROOT, SMEM>(G, prog, E, f1, f2, p, nr);
+            vertex_at<STRICT, ROOT, SMEM, WARPS>(G, prog, E, f1, f2, p, nr);
             const size_t vo = (size_t)(vbase + (perMpu ? (uint32_t)mo.vperm[vbase + rk] : rk)) * 3;
             mo.pos[vo] = p[0]; mo.pos[vo + 1] = p[1]; mo.pos[vo + 2] = p[2];
             if (G.wantNormals) { mo.nrm[vo] = nr[0]; mo.nrm[vo + 1] = nr[1]; mo.nrm[vo + 2] = nr[2]; }
@@ -439,7 +439,7 @@ __global__ void __launch_bounds__(kThreads, 6) vertex_kernel(GridParams G, const
 
 // colour walk at the final vertex positions (fieldValueAndColor, PS_Polygonizer.cpp:1378-1551 / baseColorOp,
 // CompactBlobTree.cpp:1124-1294): one vertex per lane, the 1-wide coloured interpreter
-template <bool STRICT, bool SMEM>
+template <bool STRICT, bool SMEM, bool WARPS>
 __global__ void __launch_bounds__(kThreads) color_kernel(GridParams G, const Region* __restrict__ cands, const float4* __restrict__ pool,
                                                          const float* __restrict__ colorTab, FieldOutputs fo, MeshOutputs mo, int nMixed,
                                                          uint32_t sliceQuads) {
@@ -458,7 +458,7 @@ __global__ void __launch_bounds__(kThreads) color_kernel(GridParams G, const Reg
         for (uint32_t rk = lane; rk < nV; rk += 32) {
             const size_t vo = (size_t)(vbase + rk) * 3;
             float X[1] = {mo.pos[vo]}, Y[1] = {mo.pos[vo + 1]}, Z[1] = {mo.pos[vo + 2]}, F[1], rgb[3];
-            eval_program<1, true, STRICT, SMEM>(prog, X, Y, Z, F, rgb, colorTab, G.sem);
+            eval_program<1, true, STRICT, SMEM, WARPS>(prog, X, Y, Z, F, rgb, colorTab, G.sem);
             mo.col[vo] = rgb[0]; mo.col[vo + 1] = rgb[1]; mo.col[vo + 2] = rgb[2];
         }
         int nxt = 0;
@@ -491,8 +491,10 @@ void launch_emit_kernels(const GridParams& G, const Region* cands, const float4*
     const int smem = (int)((size_t)slice * 16u * (kThreads / 32));
     using KernelT = void (*)(GridParams, const Region*, const float4*, FieldOutputs, MeshOutputs, int, uint32_t);
     KernelT k;
-#define PS_PICK(ROOT) (strict ? (smemOk ? vertex_kernel<true, ROOT, true> : vertex_kernel<true, ROOT, false>) \
-                              : (smemOk ? vertex_kernel<false, ROOT, true> : vertex_kernel<false, ROOT, false>))
+    const bool warps = !strict && G.hasWarps != 0;
+#define PS_PICK(ROOT) (strict ? (smemOk ? vertex_kernel<true, ROOT, true, false> : vertex_kernel<true, ROOT, false, false>) \
+                       : warps ? (smemOk ? vertex_kernel<false, ROOT, true, true> : vertex_kernel<false, ROOT, false, true>) \
+                               : (smemOk ? vertex_kernel<false, ROOT, true, false> : vertex_kernel<false, ROOT, false, false>))
     if (G.rootMode == PSGPU_ROOT_FOURSAMPLE) k = PS_PICK(PSGPU_ROOT_FOURSAMPLE);
     else if (G.rootMode == PSGPU_ROOT_NEWTON_REF) k = PS_PICK(PSGPU_ROOT_NEWTON_REF);
     else k = PS_PICK(PSGPU_ROOT_BISECT);
@@ -507,8 +509,9 @@ void launch_emit_kernels(const GridParams& G, const Region* cands, const float4*
     if (evVertexDone) cudaEventRecord(evVertexDone, st);
     if (G.wantColors) {
         using ColorT = void (*)(GridParams, const Region*, const float4*, const float*, FieldOutputs, MeshOutputs, int, uint32_t);
-        const ColorT kc = strict ? (smemOk ? color_kernel<true, true> : color_kernel<true, false>)
-                                 : (smemOk ? color_kernel<false, true> : color_kernel<false, false>);
+        const ColorT kc = strict ? (smemOk ? color_kernel<true, true, false> : color_kernel<true, false, false>)
+                          : warps ? (smemOk ? color_kernel<false, true, true> : color_kernel<false, false, true>)
+                                  : (smemOk ? color_kernel<false, true, false> : color_kernel<false, false, false>);
         perSM = 0;
         cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSM, kc, kThreads, smem);
         if (perSM < 1) perSM = 1;

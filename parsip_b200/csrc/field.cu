@@ -94,7 +94,7 @@ __global__ void __launch_bounds__(512 / kPts, kPts == 4 ? 6 : (STRICT ? 12 : 16)
 #pragma unroll
             for (int n = 0; n < kPts; n++) { X[n] = x; Y[n] = y; Z[n] = corner_coord(G, 2, r.z, k0 + n); }
         }
-        eval_program<kPts, false, STRICT, STAGED>(STAGED ? progBuf + (size_t)stage * capQuads : pool + r.off, X, Y, Z, F, nullptr, nullptr, G.sem);
+        eval_program<kPts, false, STRICT, STAGED, (kPts == 4)>(STAGED ? progBuf + (size_t)stage * capQuads : pool + r.off, X, Y, Z, F, nullptr, nullptr, G.sem);
         uint32_t inb = 0;
 #pragma unroll
         for (int n = 0; n < kPts; n++) inb |= (is_inside(G, F[n]) ? 1u : 0u) << n;

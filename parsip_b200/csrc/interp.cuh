@@ -279,6 +279,10 @@ __device__ __forceinline__ void prim_field(uint32_t opc, const float4 q0, const 
 }
 
 // primitive under its own backward matrix (header bit XF): out of line, see eval_program
+// sincosf out of line: its argument reduction (with the slow path for large angles) is ~150 SASS instructions, and the warps
+// would inline it once per point and call site - csgwarp's vertex kernel stalled 6 cycles per issue on instruction fetch
+static __device__ __noinline__ void ps_sincosf(float a, float& s, float& c) { sincosf(a, &s, &c); }
+
 template <int N, bool STRICT>
 __device__ __noinline__ void prim_field_xf(uint32_t opc, const float4 q0, const float4* __restrict__ q, const float4* __restrict__ m,
                                            const float (&x)[N], const float (&y)[N], const float (&z)[N], float (&f)[N]) {
@@ -392,7 +396,10 @@ __device__ __forceinline__ void color_scale(float top0, float (&tc)[3], uint32_t
 // STRICT (PS_SimdPoly semantics) also compiles OUT everything those programs cannot contain (warps, powers, segments), and
 // the native build drops the unclamped line / fast_pow Ricci / colour-scale opcodes.
 // `prog` may point to shared or global memory (generic address).
-template <int N, bool COLOR_T, bool STRICT = false, bool SMEM = false>
+// WARPS = the program is known to contain warp instructions: their sincosf goes through ONE out-of-line copy (ps_sincosf) so
+// the hot loop stays inside the instruction cache. Kernels for warp-free programs (WARPS = false) keep the inline form: it is
+// never executed there, and a call in the loop costs the 8-point field kernel 6 % (measured A/B on blob1k, native semantics)
+template <int N, bool COLOR_T, bool STRICT = false, bool SMEM = false, bool WARPS = true>
 __device__ void eval_program(const float4* __restrict__ prog, const float (&X)[N], const float (&Y)[N], const float (&Z)[N],
                              float (&F)[N], float* rgb, const float* __restrict__ colorTab, int sem, bool doColor = true) {
     // SMEM: the program was staged into shared memory; tells the compiler so the decode path uses LDS instead of generic loads
@@ -539,16 +546,15 @@ __device__ void eval_program(const float4* __restrict__ prog, const float (&X)[N
 #pragma unroll
                 for (int n = 0; n < N; n++) {
                     float s, c;
+                    const float ang = ((axis == 0) ? x[n] : ((axis == 1) ? y[n] : z[n])) * k;
+                    if (WARPS) ps_sincosf(ang, s, c); else sincosf(ang, &s, &c);
                     if (axis == 0) {
-                        sincosf(x[n] * k, &s, &c);
                         const float ny = y[n] * c - z[n] * s, nz = y[n] * s + z[n] * c;
                         y[n] = ny; z[n] = nz;
                     } else if (axis == 1) {
-                        sincosf(y[n] * k, &s, &c);
                         const float nx = x[n] * c - z[n] * s, nz = x[n] * s + z[n] * c;
                         x[n] = nx; z[n] = nz;
                     } else {
-                        sincosf(z[n] * k, &s, &c);
                         const float nx = x[n] * c - y[n] * s, ny = x[n] * s + y[n] * c;
                         x[n] = nx; y[n] = ny;
                     }
@@ -572,7 +578,7 @@ __device__ void eval_program(const float4* __restrict__ prog, const float (&X)[N
                 for (int n = 0; n < N; n++) {
                     const float yh = fminf(fmaxf(y[n], left), right);
                     float s, c;
-                    sincosf(k * (yh - y0), &s, &c);
+                    if (WARPS) ps_sincosf(k * (yh - y0), s, c); else sincosf(k * (yh - y0), &s, &c);
                     const float dy = y[n] - yh, zz = z[n] - kd;
                     const float ny = -s * zz + y0 + c * dy;
                     const float nz = c * zz + kd + s * dy;

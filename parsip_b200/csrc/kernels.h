@@ -35,6 +35,7 @@ struct GridParams {
     int insideGE;        // 1: inside = f >= iso (SIMD path), 0: f > iso (scalar twin)
     int wantColors, wantNormals;
     int forceFv;         // parity hook: write the field cache of every candidate
+    int hasWarps;        // the uploaded program contains warp instructions (picks the kernels compiled with them)
     float iso;
 };
 

@@ -15,7 +15,9 @@ for a in sys.argv[1:]:
     if a.startswith("--slab="):
         slab = tuple(int(v) for v in a.split("=")[1].split("/"))
         cells = 1024
-root = scenes.blob10k() if slab else scenes.blob1k()
+csgwarp = "--csgwarp" in sys.argv  # BASELINE configs[2], native semantics only (the SIMD path ignores warps)
+root = scenes.csgwarp() if csgwarp else (scenes.blob10k() if slab else scenes.blob1k())
+native = native or csgwarp
 flat_bin = bt.flatten(bt.binarize(root))
 lo, hi = ps.prepare_bboxes(flat_bin)
 cs = scenes.cellsize_for(lo, hi, cells)
