@@ -109,11 +109,17 @@ __device__ uint32_t prune_walk_warp(const float4* __restrict__ src, const uint8_
         if (isInstr) q0 = src[p];
         const uint32_t hdr = __float_as_uint(q0.x);
         const uint32_t opc = PS_HDR_OPC(hdr);
-        // the batch ends right after the first instruction that changes the region box (later bounds depend on it) or OPC_END
-        const bool cutter = isInstr && (opc == OPC_END || ps_changes_box(opc));
-        const uint32_t cutMask = __ballot_sync(FULL, cutter);
-        const int cutLane = cutMask ? (__ffs((int)cutMask) - 1) : 31;
-        const bool active = isInstr && lane <= cutLane;
+        // Primitive bounds are computed for the whole batch against the box at its start, so the batch ends BEFORE the first
+        // primitive that follows an instruction changing the region box (warp, operator matrix, OPC_POPPOINT): lane 0 steps through
+        // the changers themselves (a run of them costs one batch, not one each), and the next batch starts at that primitive with
+        // the updated box. OPC_END closes the walk.
+        const bool isPrim = isInstr && opc != OPC_END && opc < OPC_FIRST_NONPRIM;
+        const uint32_t chMask = __ballot_sync(FULL, isInstr && ps_changes_box(opc));
+        const uint32_t staleMask = __ballot_sync(FULL, isPrim && (chMask & ((1u << lane) - 1u)) != 0u);
+        const uint32_t endMask = __ballot_sync(FULL, isInstr && opc == OPC_END);
+        const int staleLane = staleMask ? (__ffs((int)staleMask) - 1) : 32;
+        const int endLane = endMask ? (__ffs((int)endMask) - 1) : 32;
+        const bool active = isInstr && lane < staleLane && lane <= endLane;
         bool pz = false, skip = false;
         float flo = 0.f, fhi = 0.f;
         uint32_t scale = 0;
@@ -155,12 +161,11 @@ __device__ uint32_t prune_walk_warp(const float4* __restrict__ src, const uint8_
         __syncwarp();
         endSeen = __shfl_sync(FULL, endSeen, 0);
         if (endSeen) break;
-        if (cutMask) {
+        if (chMask) {
 #pragma unroll
             for (int a = 0; a < 3; a++) { box.lo[a] = __shfl_sync(FULL, P.box.lo[a], 0); box.hi[a] = __shfl_sync(FULL, P.box.hi[a], 0); }
-            const uint32_t cutHdr = __shfl_sync(FULL, hdr, cutLane);
-            base += (uint32_t)cutLane + (uint32_t)ps_instr_quads(cutHdr);
-        } else base += 32u;
+        }
+        base += (uint32_t)staleLane;  // 32 when no primitive of the batch was left behind
         if (base >= srcLen) break;  // malformed program without OPC_END
     }
     uint32_t len = 0;
@@ -240,7 +245,8 @@ struct __align__(16) CtaEntry { float4 h0; uint32_t pc, za; float flo, fhi; };
 struct CtaWalkSmem {
     CtaEntry ent[kCtaWarps * 32];
     uint32_t cnt[kCtaWarps], za[kCtaWarps];
-    uint32_t cut, cutHdr, endSeen, len;
+    uint32_t chg[kCtaWarps];  // per warp: ballot of box-changing instructions in this step
+    uint32_t cut, stale, endSeen, len;
     float box[6];
 };
 
@@ -255,7 +261,7 @@ __device__ uint32_t prune_walk_cta(const float4* __restrict__ src, const uint8_t
     Box3 box = region;
     uint32_t base = 0, zaTotal = 0, zaPrev = 0;
     for (;;) {
-        if (tid == 0) S.cut = NONE;
+        if (tid == 0) { S.cut = NONE; S.stale = NONE; }
         __syncthreads();
         const uint32_t p = base + (uint32_t)tid;
         const bool isInstr = (p < srcLen) && (sflag[p] != 0);
@@ -263,14 +269,24 @@ __device__ uint32_t prune_walk_cta(const float4* __restrict__ src, const uint8_t
         if (isInstr) q0 = src[p];
         const uint32_t hdr = __float_as_uint(q0.x);
         const uint32_t opc = PS_HDR_OPC(hdr);
-        // the step ends right after the first instruction that changes the region box (later bounds depend on it) or OPC_END
-        const bool cutter = isInstr && (opc == OPC_END || ps_changes_box(opc));
-        const uint32_t cutMask = __ballot_sync(FULL, cutter);
-        if (cutMask && lane == __ffs((int)cutMask) - 1) atomicMin(&S.cut, p);
+        // as in prune_walk_warp: the step ends before the first primitive that follows a box-changing instruction, and at OPC_END
+        const bool isPrim = isInstr && opc != OPC_END && opc < OPC_FIRST_NONPRIM;
+        const uint32_t chMask = __ballot_sync(FULL, isInstr && ps_changes_box(opc));
+        const uint32_t endMask = __ballot_sync(FULL, isInstr && opc == OPC_END);
+        if (lane == 0) S.chg[w] = chMask;
+        if (endMask && lane == __ffs((int)endMask) - 1) atomicMin(&S.cut, p);
         __syncthreads();
-        const uint32_t cut = S.cut;
-        if (cutter && p == cut) S.cutHdr = hdr;
-        const bool active = isInstr && p <= cut;
+        bool changerBefore = (chMask & ((1u << lane) - 1u)) != 0u;
+#pragma unroll
+        for (int i = 0; i < kCtaWarps; i++) changerBefore = changerBefore || (i < w && S.chg[i] != 0u);
+        const uint32_t staleMask = __ballot_sync(FULL, isPrim && changerBefore);
+        if (staleMask && lane == __ffs((int)staleMask) - 1) atomicMin(&S.stale, p);
+        bool anyChanger = false;
+#pragma unroll
+        for (int i = 0; i < kCtaWarps; i++) anyChanger = anyChanger || S.chg[i] != 0u;
+        __syncthreads();
+        const uint32_t cut = S.cut, stale = S.stale;
+        const bool active = isInstr && p < stale && p <= cut;
         bool pz = false, skip = false;
         float flo = 0.f, fhi = 0.f;
         uint32_t scale = 0;
@@ -335,11 +351,11 @@ __device__ uint32_t prune_walk_cta(const float4* __restrict__ src, const uint8_t
         }
         __syncthreads();
         if (S.endSeen) break;
-        if (cut != NONE) {
+        if (anyChanger) {
 #pragma unroll
             for (int a = 0; a < 3; a++) { box.lo[a] = S.box[a]; box.hi[a] = S.box[3 + a]; }
-            base = cut + (uint32_t)ps_instr_quads(S.cutHdr);
-        } else base += (uint32_t)(kCtaWarps * 32);
+        }
+        base = (stale != NONE) ? stale : base + (uint32_t)(kCtaWarps * 32);
         if (base >= srcLen) break;  // malformed program without OPC_END
     }
     if (tid == 0) S.len = P.finish(cullMode, iso);
