@@ -218,10 +218,19 @@ int run_cull(psgpu_ctx* ctx, const GridParams& G, int cullMode, bool colorExact,
     if (maxDim > 64) sizes = {16, 4, 1};
     else if (maxDim > 4) sizes = {4, 1};
     else sizes = {1};
-    if (const char* ov = getenv("PSGPU_CULL_LEVELS")) {  // tuning / debugging aid: "16,4,1", "4,1" or "1"
+    if (sizes.size() == 3 && ctx->progQuads <= 4096) {
+        // A short program does not pay for the 16^3 level: its walk is bound by the serial Pruner, about as long per region as the
+        // 4^3 level's own (blob1k@512^3: cull 0.72 -> 0.64 ms without it; the 17.5k-quad blob10k needs it: 1.6 vs 5.6 ms). Only while
+        // the 4^3 level still gets a warp per region (<= 256 top regions of 16^3 MPUs).
+        const auto cdiv = [](int a, int b) { return (a + b - 1) / b; };
+        if ((long long)cdiv(nx + 15, 16) * cdiv(ny + 15, 16) * cdiv(nz + 15, 16) <= 256) sizes = {4, 1};
+    }
+    if (const char* ov = getenv("PSGPU_CULL_LEVELS")) {  // tuning / debugging aid: "16,4,1", "4,1" or "1" (each level 4x the next)
         std::vector<int> o;
         for (const char* c = ov; *c;) { o.push_back(atoi(c)); while (*c && *c != ',') c++; if (*c == ',') c++; }
-        if (!o.empty() && o.back() == 1) sizes = o;
+        bool ok = !o.empty() && o.back() == 1;
+        for (size_t i = 0; ok && i + 1 < o.size(); i++) ok = o[i] == 4 * o[i + 1];
+        if (ok) sizes = o;
     }
     // top-level parents: regions of 4 * sizes[0] MPUs carrying the full program
     std::vector<Region> top;
