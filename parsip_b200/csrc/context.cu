@@ -225,6 +225,8 @@ int run_cull(psgpu_ctx* ctx, const GridParams& G, int cullMode, bool colorExact,
         const auto cdiv = [](int a, int b) { return (a + b - 1) / b; };
         if ((long long)cdiv(nx + 15, 16) * cdiv(ny + 15, 16) * cdiv(nz + 15, 16) <= 256) sizes = {4, 1};
     }
+    // a tiny program (a dozen primitives) is cheaper to test once per MPU than to refine level by level (small@128^3: 0.27 -> 0.23 ms)
+    if (ctx->progQuads <= 64) sizes = {1};
     if (const char* ov = getenv("PSGPU_CULL_LEVELS")) {  // tuning / debugging aid: "16,4,1", "4,1" or "1" (each level 4x the next)
         std::vector<int> o;
         for (const char* c = ov; *c;) { o.push_back(atoi(c)); while (*c && *c != ',') c++; if (*c == ',') c++; }
