@@ -13,7 +13,7 @@
 // Reference: process_cells_simd phases 2-4 (PS_SimdPoly/include/PS_Polygonizer.cpp:612-829), doMarchingCubes +
 // ComputeRootNewtonRaphsonVEC4 (ParsipHaptics/include/CPolyParsipOptimized.cpp:187-327, CompactBlobTree.cpp:1581-1622).
 #include "device_util.cuh"
-#include "interp.cuh"
+#include "interp_packed.cuh"
 #include "kernels.h"
 #include "mc_tables.h"
 
@@ -41,7 +41,16 @@ __device__ __forceinline__ EdgePos edge_endpoints(const GridParams& G, const Reg
 // at every call site multiplied the hot code past the instruction caches)
 template <bool STRICT, bool SMEM, bool WARPS>
 __device__ __noinline__ void eval4(const float4* prog, const float (&X)[4], const float (&Y)[4], const float (&Z)[4], float (&F)[4], int sem) {
-    eval_program<4, false, STRICT, SMEM, WARPS>(prog, X, Y, Z, F, nullptr, nullptr, sem);
+    if constexpr (STRICT) {  // PS_SimdPoly semantics: packed-pair arithmetic (interp_packed.cuh), same bits
+        PairPts<2, false> P;
+        P.x[0] = pk(X[0], X[1]); P.x[1] = pk(X[2], X[3]);
+        P.y[0] = pk(Y[0], Y[1]); P.y[1] = pk(Y[2], Y[3]);
+        P.z[0] = pk(Z[0], Z[1]); P.z[1] = pk(Z[2], Z[3]);
+        F2 FP[2];
+        eval_program_packed<2, false, SMEM>(prog, P, FP);
+        up(FP[0], F[0], F[1]); up(FP[1], F[2], F[3]);
+    } else
+        eval_program<4, false, STRICT, SMEM, WARPS>(prog, X, Y, Z, F, nullptr, nullptr, sem);
 }
 
 // PS_Polygonizer.cpp:728-762: samples at t = 0, 1/3, 2/3, 1 in one 4-wide evaluation, first lane whose

@@ -11,7 +11,7 @@
 #include <cstdlib>
 
 #include "device_util.cuh"
-#include "interp.cuh"
+#include "interp_packed.cuh"
 #include "kernels.h"
 #include "mc_tables.h"
 
@@ -94,7 +94,18 @@ __global__ void __launch_bounds__(512 / kPts, kPts == 4 ? 6 : (STRICT ? 12 : 16)
 #pragma unroll
             for (int n = 0; n < kPts; n++) { X[n] = x; Y[n] = y; Z[n] = corner_coord(G, 2, r.z, k0 + n); }
         }
-        eval_program<kPts, false, STRICT, STAGED, (kPts == 4)>(STAGED ? progBuf + (size_t)stage * capQuads : pool + r.off, X, Y, Z, F, nullptr, nullptr, G.sem);
+        if constexpr (STRICT) {
+            // PS_SimdPoly semantics: packed-pair arithmetic, the column shares x and y (interp_packed.cuh)
+            PairPts<kPts / 2, true> P;
+            P.x[0] = X[0]; P.y[0] = Y[0];
+#pragma unroll
+            for (int n = 0; n < kPts / 2; n++) P.z[n] = pk(Z[2 * n], Z[2 * n + 1]);
+            F2 FP[kPts / 2];
+            eval_program_packed<kPts / 2, true, STAGED>(STAGED ? progBuf + (size_t)stage * capQuads : pool + r.off, P, FP);
+#pragma unroll
+            for (int n = 0; n < kPts / 2; n++) up(FP[n], F[2 * n], F[2 * n + 1]);
+        } else
+            eval_program<kPts, false, STRICT, STAGED, (kPts == 4)>(STAGED ? progBuf + (size_t)stage * capQuads : pool + r.off, X, Y, Z, F, nullptr, nullptr, G.sem);
         uint32_t inb = 0;
 #pragma unroll
         for (int n = 0; n < kPts; n++) inb |= (is_inside(G, F[n]) ? 1u : 0u) << n;

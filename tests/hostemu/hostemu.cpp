@@ -4,6 +4,7 @@
 // machine without a GPU. Never loaded by the product.
 #include "cuda_shim.h"
 #include "../../parsip_b200/csrc/cull_walk.cuh"
+#include "../../parsip_b200/csrc/interp_packed.cuh"
 
 using namespace psgpu;
 
@@ -27,6 +28,35 @@ void hostemu_field_color(const float* quads, const float* colorTab, const float*
         if (sem == PSGPU_SEM_SIMD) eval_program<1, true, true>(prog, X, Y, Z, F, col + i * 3, colorTab, sem);
         else eval_program<1, true, false>(prog, X, Y, Z, F, col + i * 3, colorTab, sem);
         f[i] = F[0];
+    }
+}
+
+// the packed-pair STRICT interpreter (interp_packed.cuh): columns = groups of 8 points sharing x and y (the field kernel's
+// z-columns), xy[2*c], z[8*c + k] -> f[8*c + k]
+void hostemu_field_packed_columns(const float* quads, const float* xy, const float* z, int64_t nCols, float* f) {
+    const float4* prog = reinterpret_cast<const float4*>(quads);
+    for (int64_t c = 0; c < nCols; c++) {
+        PairPts<4, true> P;
+        P.x[0] = xy[c * 2]; P.y[0] = xy[c * 2 + 1];
+        for (int i = 0; i < 4; i++) P.z[i] = pk(z[c * 8 + 2 * i], z[c * 8 + 2 * i + 1]);
+        F2 F[4];
+        eval_program_packed<4, true, false>(prog, P, F);
+        for (int i = 0; i < 4; i++) up(F[i], f[c * 8 + 2 * i], f[c * 8 + 2 * i + 1]);
+    }
+}
+
+// ... and its general form: 4 arbitrary points per call (the vertex kernel's root / gradient samples); n is rounded down to a multiple of 4
+void hostemu_field_packed(const float* quads, const float* xyz, int64_t n, float* f) {
+    const float4* prog = reinterpret_cast<const float4*>(quads);
+    for (int64_t b = 0; b + 4 <= n; b += 4) {
+        PairPts<2, false> P;
+        for (int i = 0; i < 2; i++) {
+            const float* a = xyz + (b + 2 * i) * 3;
+            P.x[i] = pk(a[0], a[3]); P.y[i] = pk(a[1], a[4]); P.z[i] = pk(a[2], a[5]);
+        }
+        F2 F[2];
+        eval_program_packed<2, false, false>(prog, P, F);
+        for (int i = 0; i < 2; i++) up(F[i], f[b + 2 * i], f[b + 2 * i + 1]);
     }
 }
 

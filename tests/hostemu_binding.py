@@ -16,6 +16,8 @@ def lib():
         vp = C.c_void_p
         l.hostemu_field.argtypes = [vp, vp, C.c_int64, vp, C.c_int]
         l.hostemu_field_color.argtypes = [vp, vp, vp, C.c_int64, vp, vp, C.c_int]
+        l.hostemu_field_packed_columns.argtypes = [vp, vp, vp, C.c_int64, vp]
+        l.hostemu_field_packed.argtypes = [vp, vp, C.c_int64, vp]
         l.hostemu_prune.restype = C.c_uint32
         l.hostemu_prune.argtypes = [vp, vp, vp, C.c_int, C.c_float, vp, C.c_uint32, C.c_int]
         _lib = l
@@ -27,6 +29,26 @@ def field(quads: np.ndarray, xyz, sem: int) -> np.ndarray:
     xyz = np.ascontiguousarray(xyz, np.float32).reshape(-1, 3)
     out = np.zeros(len(xyz), np.float32)
     lib().hostemu_field(quads.ctypes.data, xyz.ctypes.data, len(xyz), out.ctypes.data, sem)
+    return out
+
+
+def field_packed_columns(quads, xy, z) -> np.ndarray:
+    """interp_packed.cuh, column form: xy (n, 2), z (n, 8) -> f (n, 8)"""
+    quads = np.ascontiguousarray(quads, np.uint32)
+    xy = np.ascontiguousarray(xy, np.float32).reshape(-1, 2)
+    z = np.ascontiguousarray(z, np.float32).reshape(-1, 8)
+    out = np.zeros((len(xy), 8), np.float32)
+    lib().hostemu_field_packed_columns(quads.ctypes.data, xy.ctypes.data, z.ctypes.data, len(xy), out.ctypes.data)
+    return out
+
+
+def field_packed(quads, xyz) -> np.ndarray:
+    """interp_packed.cuh, general form (4 points per call); len(xyz) must be a multiple of 4"""
+    quads = np.ascontiguousarray(quads, np.uint32)
+    xyz = np.ascontiguousarray(xyz, np.float32).reshape(-1, 3)
+    assert len(xyz) % 4 == 0
+    out = np.zeros(len(xyz), np.float32)
+    lib().hostemu_field_packed(quads.ctypes.data, xyz.ctypes.data, len(xyz), out.ctypes.data)
     return out
 
 
