@@ -144,17 +144,24 @@ int FieldValues(const SOABlobPrims& blobPrims, const SOABlobPrimMatrices& blobPr
 }  // namespace PS
 
 // The wrapper class of ParsipHaptics/include/PS_HighPerformanceRender.h:15-33 minus draw() (no GL here).
-// linearizeBlobTree takes the flat tree of psgpu_types.h; INTEGRATION.md shows the 30-line CBlobNode* walker
-// that fills it inside the reference tree.
+// linearizeBlobTree(CBlobNode*) keeps the reference signature (PS_HighPerformanceRender.h:27); it is defined inline in
+// include/psgpu_blobtree_walk.h, which a TU includes after the reference's scene API (only such a TU can walk a CBlobNode).
+// The flat-tree overload is what it forwards to and what callers without the scene API use.
 struct psgpu_tree;
+namespace PS { namespace BLOBTREE { class CBlobNode; } }
 class SimdPoly {
 public:
     SimdPoly();
     ~SimdPoly();
     void reset();
+    int linearizeBlobTree(PS::BLOBTREE::CBlobNode* root);
     int linearizeBlobTree(const psgpu_tree* root);
     int run(float cellsize);
     const PS::SIMDPOLY::PolyMPUs& polyMPUs() const { return *m_polyMPUs; }
+    // the linearized tables (read-only; the reference keeps them private and draws from them)
+    const PS::SIMDPOLY::SOABlobPrims& blobPrims() const { return m_blobPrims; }
+    const PS::SIMDPOLY::SOABlobOps& blobOps() const { return m_blobOps; }
+    const PS::SIMDPOLY::SOABlobPrimMatrices& blobPrimMatrices() const { return m_blobPrimMatrices; }
 
 private:
     PS::SIMDPOLY::SOABlobPrims m_blobPrims;

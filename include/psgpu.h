@@ -53,6 +53,9 @@ typedef struct psgpu_program psgpu_program; /* host-side linearized BlobTree */
 #define PSGPU_CULL_INTERVAL 2 /* + MPUs whose field interval excludes the iso value are skipped (default) */
 
 #define PSGPU_LIN_REASSOCIATE 1 /* flatten blend-in-blend chains (changes summation order by a few ulp) */
+#define PSGPU_LIN_FULL_AFFINE 2 /* PSGPU_SEM_SCALAR: apply an operator's whole backward matrix. Default (0) reproduces the compact
+                                   tree, whose vec4 w lane is 0 at the root and below warps, so an operator's translation column
+                                   only acts directly below another operator matrix (CompactBlobTree.cpp:685-694) */
 
 typedef struct psgpu_params {
     float cellsize;

@@ -20,6 +20,11 @@ enum psgpu_node_type {
     PSGPU_PRIM_RING = 4,      /* pos, dir = normal (unit), res[0] = radius */
     PSGPU_PRIM_CUBE = 5,      /* pos, res[0] = half side */
     PSGPU_PRIM_NULL = 6,      /* field == 0 */
+    /* non-skeletal primitives of the scene API; PSGPU_SEM_SCALAR only, the SIMD evaluator has neither */
+    PSGPU_PRIM_QUADRICPOINT = 7, /* pos, res[0] = field radius R, res[1] = field scale s: f = s (1 - d2/R2)^2 inside R
+                                    (PS_BlobTree/include/CQuadricPoint.h:43-52, CompactBlobTree.cpp:1051-1064) */
+    PSGPU_PRIM_INSTANCE = 8,     /* res[0] = flat index of the instanced node; its own xform is applied first
+                                    (CompactBlobTree.cpp:1069-1078) */
     /* n-ary operators */
     PSGPU_OP_UNION = 16,
     PSGPU_OP_INTERSECT = 17,

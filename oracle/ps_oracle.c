@@ -733,6 +733,7 @@ struct pso_scalar {
     int nChild;
     pso_mesh mesh;
     float lo[3], hi[3];
+    float *octLo, *octHi; /* per node, optional: the scene API's primitive octrees for the MPU filter */
 };
 
 pso_scalar* pso_scalar_create(const psgpu_tree* t) {
@@ -759,7 +760,18 @@ pso_scalar* pso_scalar_create(const psgpu_tree* t) {
 void pso_scalar_destroy(pso_scalar* s) {
     if (!s) return;
     free(s->type); free(s->first); free(s->nkids); free(s->child); free(s->pos); free(s->dir); free(s->res);
-    free(s->col); free(s->xf); free(s->hasxf); mesh_free(&s->mesh); free(s);
+    free(s->col); free(s->xf); free(s->hasxf); free(s->octLo); free(s->octHi); mesh_free(&s->mesh); free(s);
+}
+
+/* The scalar polygonizer skips an MPU unless its box overlaps some primitive's octree, PH/CPolyParsipOptimized.cpp:160-183
+ * (strict overlap test :117-127). The octrees are the scene API's heuristic bounds (CSkeleton::bound(), e.g. BT/CSkeletonLine.h:80-85
+ * shrinks the box of a line whose end is below its start), so they are an INPUT here: one box per node of the flat
+ * tree, read for primitive nodes only. Without boxes every MPU is processed. */
+void pso_scalar_set_prim_boxes(pso_scalar* s, const float* lo3n, const float* hi3n) {
+    free(s->octLo); free(s->octHi); s->octLo = s->octHi = NULL;
+    if (!lo3n || !hi3n) return;
+    s->octLo = (float*)malloc(sizeof(float) * 3 * (size_t)s->n); s->octHi = (float*)malloc(sizeof(float) * 3 * (size_t)s->n);
+    memcpy(s->octLo, lo3n, sizeof(float) * 3 * (size_t)s->n); memcpy(s->octHi, hi3n, sizeof(float) * 3 * (size_t)s->n);
 }
 
 /* ComputeWyvillFieldValueSquare, SP/PS_Polygonizer.h:410-416 == BT/CFieldFunction.h:104-114 */
@@ -776,7 +788,7 @@ static void warp_bend(const float* pin, float k, float y0, float left, float rig
     else if (pin[1] > left && pin[1] < right) yh = pin[1];
     else if (pin[1] >= right) yh = right;
     float theta = k * (yh - y0);
-    float ct = (float)cos(theta), st = (float)sin(theta);
+    float ct = cosf(theta), st = sinf(theta);
     int inside = (pin[1] >= left) && (pin[1] <= right); /* CInterval::isInside, FW/PS_Interval.h:50 */
     float oy = 0.0f, oz = 0.0f;
     if (inside) oy = -st * (pin[2] - kDiv) + y0;
@@ -790,9 +802,9 @@ static void warp_bend(const float* pin, float k, float y0, float left, float rig
 static void warp_twist(const float* pin, float factor, int axis, float* pout) {
     float x = pin[0], y = pin[1], z = pin[2], theta;
     switch (axis) {
-    case 0: theta = x * factor; pout[0] = x; pout[1] = y * (float)cos(theta) - z * (float)sin(theta); pout[2] = y * (float)sin(theta) + z * (float)cos(theta); break;
-    case 1: theta = y * factor; pout[0] = x * (float)cos(theta) - z * (float)sin(theta); pout[1] = y; pout[2] = x * (float)sin(theta) + z * (float)cos(theta); break;
-    default: theta = z * factor; pout[0] = x * (float)cos(theta) - y * (float)sin(theta); pout[1] = x * (float)sin(theta) + y * (float)cos(theta); pout[2] = z; break;
+    case 0: theta = x * factor; pout[0] = x; pout[1] = y * cosf(theta) - z * sinf(theta); pout[2] = y * sinf(theta) + z * cosf(theta); break;
+    case 1: theta = y * factor; pout[0] = x * cosf(theta) - z * sinf(theta); pout[1] = y; pout[2] = x * sinf(theta) + z * cosf(theta); break;
+    default: theta = z * factor; pout[0] = x * cosf(theta) - y * sinf(theta); pout[1] = x * sinf(theta) + y * cosf(theta); pout[2] = z; break;
     }
 }
 static void warp_taper(const float* p, float factor, int along, int taper, float* o) {
@@ -1057,6 +1069,17 @@ static int scalar_cell_case(const float* fv, int i, int j, int k) {
 static void scalar_process_mpu(const pso_scalar* s, float* store, float cellsize, pso_mpu* mpu) {
     float fv[GD * GD * GD];
     mpu->nv = mpu->nt = 0; mpu->fieldEvals = 0;
+    if (s->octLo) {
+        const float side = (float)(GD - 1) * cellsize;
+        const float hi[3] = {mpu->lo[0] + side, mpu->lo[1] + side, mpu->lo[2] + side};
+        int hit = 0;
+        for (int i = 0; i < s->n && !hit; i++) {
+            if (!PSGPU_IS_PRIM(s->type[i])) continue;
+            const float *a = &s->octLo[i * 3], *b = &s->octHi[i * 3];
+            hit = !((a[0] >= hi[0]) || (b[0] <= mpu->lo[0]) || (a[1] >= hi[1]) || (b[1] <= mpu->lo[1]) || (a[2] >= hi[2]) || (b[2] <= mpu->lo[2]));
+        }
+        if (!hit) return;
+    }
     scalar_fill_cache(s, mpu->lo, cellsize, fv);
     mpu->fieldEvals = GD * GD * GD;
     unsigned char hasEdge[GD * GD * GD * 3];

@@ -79,6 +79,7 @@ void pso_simd_result_copy(const pso_simd* s, float* pos, float* nrm, float* col,
 /* ---- scalar-twin semantics ---- */
 pso_scalar* pso_scalar_create(const psgpu_tree* t);
 void pso_scalar_destroy(pso_scalar* s);
+void pso_scalar_set_prim_boxes(pso_scalar* s, const float* lo3n, const float* hi3n);
 void pso_scalar_field(const pso_scalar* s, int64_t n, const float* xyz, float* out);
 void pso_scalar_field_color_normal(const pso_scalar* s, int64_t n, const float* xyz, float* f, float* col, float* nrm);
 /* ComputeRootNewtonRaphsonVEC4 for n edges: p1,p2 (n*3), f1,f2 (n) -> root (n*3), field (n), evals (n) */

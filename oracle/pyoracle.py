@@ -264,6 +264,7 @@ def _load_oracle():
     lib.pso_scalar_create.restype = vp
     lib.pso_scalar_create.argtypes = [C.POINTER(_Tree)]
     lib.pso_scalar_destroy.argtypes = [vp]
+    lib.pso_scalar_set_prim_boxes.argtypes = [vp, vp, vp]
     lib.pso_scalar_field.argtypes = [vp, C.c_int64, vp, vp]
     lib.pso_scalar_field_color_normal.argtypes = [vp, C.c_int64, vp, vp, vp, vp]
     lib.pso_scalar_newton.argtypes = [vp, C.c_int64, vp, vp, vp, vp, C.c_float, C.c_int, vp, vp, vp]
@@ -390,6 +391,14 @@ class ScalarOracle:
             self.lib.pso_scalar_destroy(self.h)
             self.h = None
 
+    def set_prim_boxes(self, lo, hi):
+        """Per-node octrees for the scalar polygonizer's MPU filter (CPolyParsipOptimized.cpp:160-183); None switches it off."""
+        if lo is None:
+            self.lib.pso_scalar_set_prim_boxes(self.h, None, None)
+            return
+        lo, hi = np.ascontiguousarray(lo, np.float32), np.ascontiguousarray(hi, np.float32)
+        self.lib.pso_scalar_set_prim_boxes(self.h, lo.ctypes.data, hi.ctypes.data)
+
     def field(self, xyz):
         xyz = np.ascontiguousarray(xyz, np.float32).reshape(-1, 3)
         out = np.zeros(len(xyz), np.float32)
@@ -434,3 +443,155 @@ class ScalarOracle:
         if keep_mesh:
             _fetch_mesh(self.lib.pso_scalar_result_counts, self.lib.pso_scalar_result_copy, self.h, stats)
         return ret, stats
+
+
+# ----------------------------------------------------------------------------------------------
+# the reference's own scalar twin (oracle/_ref/libcompactref.so, oracle/compact_wrap.cpp)
+# ----------------------------------------------------------------------------------------------
+class _CrefDesc(C.Structure):
+    _fields_ = [
+        ("n_nodes", C.c_int32),
+        ("type", C.POINTER(C.c_int32)), ("first_child", C.POINTER(C.c_int32)),
+        ("n_children", C.POINTER(C.c_int32)), ("child", C.POINTER(C.c_int32)),
+        ("pos", C.POINTER(C.c_float)), ("dir", C.POINTER(C.c_float)), ("res", C.POINTER(C.c_float)),
+        ("color", C.POINTER(C.c_float)), ("srt", C.POINTER(C.c_float)), ("has_srt", C.POINTER(C.c_uint8)),
+    ]
+
+
+def compactref_lib_path():
+    return os.path.join(HERE, "_ref", "libcompactref.so")
+
+
+def compactref_available():
+    return os.path.exists(compactref_lib_path())
+
+
+_clib = None
+
+
+def _load_compactref():
+    global _clib
+    if _clib is not None:
+        return _clib
+    lib = C.CDLL(compactref_lib_path())
+    vp = C.c_void_p
+    lib.cref_create.restype = vp
+    lib.cref_create.argtypes = [C.POINTER(_CrefDesc)]
+    lib.cref_destroy.argtypes = [vp]
+    lib.cref_convert_rc.argtypes = [vp]
+    lib.cref_walk_rc.argtypes = [vp]
+    lib.cref_counts.argtypes = [vp, vp]
+    lib.cref_walk_copy.argtypes = [vp] * 13
+    lib.cref_octree.argtypes = [vp, vp, vp]
+    lib.cref_field.argtypes = [vp, C.c_int64, vp, vp]
+    lib.cref_field_color_normal.argtypes = [vp, C.c_int64, vp, vp, vp, vp]
+    lib.cref_newton.argtypes = [vp, C.c_int64, vp, vp, vp, vp, C.c_float, C.c_int, vp, vp, vp]
+    lib.cref_scene_field.argtypes = [vp, C.c_int64, vp, vp]
+    lib.cref_polygonize.argtypes = [vp, vp, vp, C.c_float, C.c_float, C.c_int]
+    lib.cref_result_counts.argtypes = [vp, vp]
+    lib.cref_result_copy.argtypes = [vp] * 7
+    lib.cref_export_mesh.argtypes = [vp] * 6
+    _clib = lib
+    return lib
+
+
+class CompactRef:
+    """The reference's OWN scalar path on a tree built with its scene-API classes: COMPACTBLOBTREE::convert / fieldvalue /
+    normal / baseColor, ComputeRootNewtonRaphsonVEC4, CBlobNode::fieldValue, CParsipOptimized (all compiled unmodified from
+    /root/reference). `flat` is blobtree.flatten() output; nodes may carry `srt` (scale, quaternion xyzw, translate), which the
+    reference turns into its backward matrix itself. `walk()` returns the tree as the PRODUCT walker
+    include/psgpu_blobtree_walk.h reads it back from the CBlobNode objects."""
+
+    def __init__(self, flat: dict):
+        self.lib = _load_compactref()
+        k = {n: np.ascontiguousarray(v) for n, v in flat.items() if isinstance(v, np.ndarray)}
+        self._keep = k
+        if flat.get("root", 0) != 0:
+            raise ValueError("CompactRef expects the root at index 0 (blobtree.flatten order)")
+        srt = k.get("srt")
+        has = k.get("has_srt")
+        d = _CrefDesc(flat["n_nodes"], _p(k["type"], C.c_int32), _p(k["first_child"], C.c_int32), _p(k["n_children"], C.c_int32),
+                      _p(k["child"], C.c_int32), _p(k["pos"], C.c_float), _p(k["dir"], C.c_float), _p(k["res"], C.c_float),
+                      _p(k["color"], C.c_float), _p(srt, C.c_float) if srt is not None else None,
+                      _p(has, C.c_uint8) if has is not None else None)
+        self.h = self.lib.cref_create(C.byref(d))
+        if not self.h:
+            raise RuntimeError("cref_create: a node kind the reference builder does not know")
+        c = np.zeros(4, np.int32)
+        self.lib.cref_counts(self.h, c.ctypes.data)
+        self.n_prims, self.n_ops, self.n_nodes, self.n_child = (int(v) for v in c)
+        self.convert_rc = self.lib.cref_convert_rc(self.h)
+        self.walk_rc = self.lib.cref_walk_rc(self.h)
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            self.lib.cref_destroy(self.h)
+            self.h = None
+
+    def walk(self):
+        N = self.n_nodes
+        out = dict(n_nodes=N, root=0, type=np.zeros(N, np.int32), first_child=np.zeros(N, np.int32), n_children=np.zeros(N, np.int32),
+                   child=np.zeros(max(1, self.n_child), np.int32), pos=np.zeros((N, 3), np.float32), dir=np.zeros((N, 3), np.float32),
+                   res=np.zeros((N, 4), np.float32), color=np.zeros((N, 3), np.float32), xform=np.zeros((N, 12), np.float32),
+                   has_xform=np.zeros(N, np.uint8), oct_lo=np.zeros((N, 3), np.float32), oct_hi=np.zeros((N, 3), np.float32))
+        self.lib.cref_walk_copy(self.h, *(out[k].ctypes.data for k in ("type", "first_child", "n_children", "child", "pos", "dir", "res",
+                                                                        "color", "xform", "has_xform", "oct_lo", "oct_hi")))
+        return out
+
+    def octree(self):
+        lo, hi = np.zeros(3, np.float32), np.zeros(3, np.float32)
+        self.lib.cref_octree(self.h, lo.ctypes.data, hi.ctypes.data)
+        return lo, hi
+
+    def field(self, xyz):
+        xyz = np.ascontiguousarray(xyz, np.float32).reshape(-1, 3)
+        out = np.zeros(len(xyz), np.float32)
+        self.lib.cref_field(self.h, len(xyz), xyz.ctypes.data, out.ctypes.data)
+        return out
+
+    def scene_field(self, xyz):
+        xyz = np.ascontiguousarray(xyz, np.float32).reshape(-1, 3)
+        out = np.zeros(len(xyz), np.float32)
+        self.lib.cref_scene_field(self.h, len(xyz), xyz.ctypes.data, out.ctypes.data)
+        return out
+
+    def field_color_normal(self, xyz):
+        xyz = np.ascontiguousarray(xyz, np.float32).reshape(-1, 3)
+        n = len(xyz)
+        f, col, nrm = np.zeros(n, np.float32), np.zeros((n, 4), np.float32), np.zeros((n, 3), np.float32)
+        self.lib.cref_field_color_normal(self.h, n, xyz.ctypes.data, f.ctypes.data, col.ctypes.data, nrm.ctypes.data)
+        return f, col, nrm
+
+    def newton(self, p1, p2, f1, f2, iso=0.5, iterations=8):
+        p1 = np.ascontiguousarray(p1, np.float32).reshape(-1, 3)
+        p2 = np.ascontiguousarray(p2, np.float32).reshape(-1, 3)
+        f1 = np.ascontiguousarray(f1, np.float32)
+        f2 = np.ascontiguousarray(f2, np.float32)
+        n = len(p1)
+        root, fr, ev = np.zeros((n, 3), np.float32), np.zeros(n, np.float32), np.zeros(n, np.int32)
+        self.lib.cref_newton(self.h, n, p1.ctypes.data, p2.ctypes.data, f1.ctypes.data, f2.ctypes.data, float(iso), int(iterations),
+                             root.ctypes.data, fr.ctypes.data, ev.ctypes.data)
+        return root, fr, ev
+
+    def polygonize(self, lo, hi, cellsize, iso=0.5, nthreads=1):
+        """CParsipOptimized::setup(box) + run(). Returns the per-MPU meshes of the MPUs that kept surface, in list order."""
+        lo, hi = np.ascontiguousarray(lo, np.float32), np.ascontiguousarray(hi, np.float32)
+        self.lib.cref_polygonize(self.h, lo.ctypes.data, hi.ctypes.data, float(cellsize), float(iso), int(nthreads))
+        c = np.zeros(4, np.int64)
+        self.lib.cref_result_counts(self.h, c.ctypes.data)
+        nm, nv, nt = int(c[0]), int(c[1]), int(c[2])
+        pos, nrm, col = np.zeros((nv, 3), np.float32), np.zeros((nv, 3), np.float32), np.zeros((nv, 4), np.float32)
+        tri = np.zeros((nt, 3), np.uint32)
+        org, cnt = np.zeros((nm, 3), np.float32), np.zeros((nm, 2), np.int32)
+        self.lib.cref_result_copy(self.h, pos.ctypes.data, nrm.ctypes.data, col.ctypes.data, tri.ctypes.data, org.ctypes.data, cnt.ctypes.data)
+        return dict(mpus=nm, vertices=nv, triangles=nt, field_evals=int(c[3]), pos=pos, nrm=nrm, col=col, tri=tri, mpu_origin=org, mpu_counts=cnt)
+
+    def export_mesh(self):
+        """CParsipOptimized::exportMesh of the last polygonize()."""
+        c = np.zeros(2, np.int64)
+        self.lib.cref_export_mesh(self.h, None, None, None, None, c.ctypes.data)
+        nv, nt = int(c[0]), int(c[1])
+        pos, nrm, col = np.zeros((nv, 3), np.float32), np.zeros((nv, 3), np.float32), np.zeros((nv, 4), np.float32)
+        tri = np.zeros((nt, 3), np.uint32)
+        ok = self.lib.cref_export_mesh(self.h, pos.ctypes.data, nrm.ctypes.data, col.ctypes.data, tri.ctypes.data, c.ctypes.data)
+        return ok, dict(vertices=nv, triangles=nt, pos=pos, nrm=nrm, col=col, tri=tri)

@@ -11,13 +11,13 @@ from __future__ import annotations
 import numpy as np
 
 # include/psgpu_types.h
-PRIM_POINT, PRIM_LINE, PRIM_CYLINDER, PRIM_DISC, PRIM_RING, PRIM_CUBE, PRIM_NULL = range(7)
+PRIM_POINT, PRIM_LINE, PRIM_CYLINDER, PRIM_DISC, PRIM_RING, PRIM_CUBE, PRIM_NULL, PRIM_QUADRICPOINT, PRIM_INSTANCE = range(9)
 OP_UNION, OP_INTERSECT, OP_DIF, OP_SMOOTHDIF, OP_BLEND, OP_RICCI = range(16, 22)
 OP_WARP_TWIST, OP_WARP_TAPER, OP_WARP_BEND, OP_WARP_SHEAR = range(32, 36)
 
 TYPE_NAMES = {
     PRIM_POINT: "point", PRIM_LINE: "line", PRIM_CYLINDER: "cylinder", PRIM_DISC: "disc",
-    PRIM_RING: "ring", PRIM_CUBE: "cube", PRIM_NULL: "null",
+    PRIM_RING: "ring", PRIM_CUBE: "cube", PRIM_NULL: "null", PRIM_QUADRICPOINT: "quadricpoint", PRIM_INSTANCE: "instance",
     OP_UNION: "union", OP_INTERSECT: "intersect", OP_DIF: "dif", OP_SMOOTHDIF: "smoothdif",
     OP_BLEND: "blend", OP_RICCI: "ricci",
     OP_WARP_TWIST: "twist", OP_WARP_TAPER: "taper", OP_WARP_BEND: "bend", OP_WARP_SHEAR: "shear",
@@ -33,10 +33,10 @@ def is_warp(t: int) -> bool:
 
 
 class Node:
-    __slots__ = ("type", "children", "pos", "dir", "res", "color", "xform")
+    __slots__ = ("type", "children", "pos", "dir", "res", "color", "xform", "srt", "origin")
 
     def __init__(self, type, children=(), pos=(0, 0, 0), dir=(0, 0, 0), res=(0, 0, 0, 0),
-                 color=(1, 1, 1), xform=None):
+                 color=(1, 1, 1), xform=None, srt=None, origin=None):
         self.type = int(type)
         self.children = list(children)
         self.pos = tuple(float(v) for v in pos)
@@ -46,6 +46,12 @@ class Node:
         self.color = tuple(float(v) for v in color)
         # backward (world -> local) 3x4 row-major, or None for identity
         self.xform = None if xform is None else np.asarray(xform, np.float32).reshape(3, 4)
+        # the scene API's own parametrisation (CAffineTransformation: scale xyz, quaternion xyzw, translate xyz). A node built
+        # with srt and no xform gets its backward matrix from srt_backward(); the reference-built oracle derives its own.
+        self.srt = None if srt is None else np.asarray(srt, np.float32).reshape(10)
+        if self.srt is not None and self.xform is None:
+            self.xform = srt_backward(self.srt)
+        self.origin = origin  # PRIM_INSTANCE: the instanced node (must be part of the same tree)
 
     @property
     def is_op(self):
@@ -91,6 +97,38 @@ def Cube(pos, side, color=(1, 1, 1), xform=None):
 
 def Null():
     return Node(PRIM_NULL)
+
+
+def QuadricPoint(pos, radius, scale, color=(1, 1, 1), xform=None, srt=None):
+    """CQuadricPoint (PS_BlobTree/include/CQuadricPoint.h:43-52): f = scale * (1 - d^2/R^2)^2 inside R."""
+    return Node(PRIM_QUADRICPOINT, pos=pos, res=(radius, scale, 0), color=color, xform=xform, srt=srt)
+
+
+def Instance(origin, xform=None, srt=None):
+    """CInstance (PS_BlobTree/include/CInstance.h): the origin's field at the instance's backward-transformed point."""
+    return Node(PRIM_INSTANCE, origin=origin, xform=xform, srt=srt)
+
+
+def with_srt(node, scale=(1, 1, 1), quat=(0, 0, 0, 1), translate=(0, 0, 0)):
+    """Gives a node the scene API's transform (CAffineTransformation::set(scale, rotation, translate))."""
+    node.srt = np.asarray(tuple(scale) + tuple(quat) + tuple(translate), np.float32)
+    node.xform = srt_backward(node.srt)
+    return node
+
+
+def srt_backward(srt):
+    """Backward 3x4 of CAffineTransformation::setReverseTransformations (PS_FrameWork/include/PS_AffineTransformation.h:160-181):
+    forward = T(t) . R(q) . S(s) about the origin, backward = its inverse. Float64 here; the reference inverts in float32, so a
+    tree evaluated against the reference-built oracle takes the matrix the product walker reads back instead."""
+    s, q, t = np.asarray(srt[0:3], np.float64), np.asarray(srt[3:7], np.float64), np.asarray(srt[7:10], np.float64)
+    x, y, z, w = q
+    R = np.array([[1 - 2 * (y * y + z * z), 2 * (x * y - z * w), 2 * (x * z + y * w)],
+                  [2 * (x * y + z * w), 1 - 2 * (x * x + z * z), 2 * (y * z - x * w)],
+                  [2 * (x * z - y * w), 2 * (y * z + x * w), 1 - 2 * (x * x + y * y)]])
+    F = np.eye(4)
+    F[:3, :3] = R @ np.diag(s)
+    F[:3, 3] = t
+    return np.linalg.inv(F)[:3, :].astype(np.float32)
 
 
 def Union(*kids):
@@ -152,6 +190,7 @@ def flatten(root: Node) -> dict:
         type=np.zeros(N, np.int32), first_child=np.zeros(N, np.int32), n_children=np.zeros(N, np.int32),
         pos=np.zeros((N, 3), np.float32), dir=np.zeros((N, 3), np.float32), res=np.zeros((N, 4), np.float32),
         color=np.zeros((N, 3), np.float32), xform=np.zeros((N, 12), np.float32), has_xform=np.zeros(N, np.uint8),
+        srt=np.zeros((N, 10), np.float32), has_srt=np.zeros(N, np.uint8),
     )
     child = []
     for i, n in enumerate(nodes):
@@ -168,6 +207,11 @@ def flatten(root: Node) -> dict:
             out["has_xform"][i] = 1
         else:
             out["xform"][i] = np.eye(3, 4, dtype=np.float32).reshape(12)
+        if n.srt is not None:
+            out["srt"][i] = n.srt
+            out["has_srt"][i] = 1
+        if n.type == PRIM_INSTANCE:
+            out["res"][i, 0] = order[id(n.origin)]
     out["child"] = np.asarray(child if child else [0], np.int32)
     return out
 

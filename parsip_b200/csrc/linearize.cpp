@@ -43,6 +43,19 @@ struct Emitter {
 
     void rows(const float* m) { quadf(m[0], m[1], m[2], m[3]); quadf(m[4], m[5], m[6], m[7]); quadf(m[8], m[9], m[10], m[11]); }
 
+    // An OPERATOR's own backward matrix in the compact tree is applied as row . (x, y, z, w) with the w lane of the incoming
+    // vec4: 0 from COMPACTBLOBTREE::fieldvalue and after any warp (Vector4d() zero-initialises w, FW/PS_Vector.h:1004-1007),
+    // 1 right after another operator's matrix (CompactBlobTree.cpp:685-694). So the translation column only acts below an
+    // affine-only parent. The lane is a static property of the node's ancestors: w == 0 drops the column here, at no cost to
+    // the interpreter. PSGPU_LIN_FULL_AFFINE applies the whole matrix instead (what the scene API's authors meant).
+    void opAffine(int n, int w) {
+        const float* m = &t->xform[n * 12];
+        quad(PS_HDR(OPC_AFFINE, 0, false, 0));
+        if (w || (flags & PSGPU_LIN_FULL_AFFINE)) rows(m);
+        else { quadf(m[0], m[1], m[2], 0.f); quadf(m[4], m[5], m[6], 0.f); quadf(m[8], m[9], m[10], 0.f); }
+        p->nInstr++; ppush();
+    }
+
     bool hasXf(int n) const { return t->xform && t->has_xform && t->has_xform[n]; }
 
     void emitPrim(int n, uint32_t cmb) {
@@ -100,6 +113,13 @@ struct Emitter {
         if (xf && t->type[n] != PSGPU_PRIM_NULL) rows(&t->xform[n * 12]);
     }
 
+    // SimdPoly::linearizeBlobTree never reads an operator's transform (PS_HighPerformanceRender.cpp:70-160): its callers run
+    // flattenTransformations first (CLayerManager.cpp:604-641). Refuse instead of silently evaluating a different surface.
+    void simdOpXform() {
+        err = PSGPU_ERROR_UNSUPPORTED_NODE;
+        msg = "SIMD semantics ignore operator transforms: flatten them into the primitives first (psgpu_tree_flatten_transforms)";
+    }
+
     void combine(uint32_t cmb) {
         if (cmb == CMB_PUSH) return;
         quad(PS_HDR(OPC_COMBINE, cmb, false, 0));
@@ -131,7 +151,7 @@ struct Emitter {
     }
 
     // Emits the sub-tree `n`; its value meets the current stack top with `cmb` (CMB_PUSH: new entry).
-    void emit(int n, uint32_t cmb) {
+    void emit(int n, uint32_t cmb, int w = 0) {
         if (err != PSGPU_SUCCESS) return;
         const int type = t->type[n];
         if (PSGPU_IS_PRIM(type)) { emitPrim(n, cmb); return; }
@@ -144,13 +164,13 @@ struct Emitter {
         if (PSGPU_IS_WARP(type)) {
             const int c0 = t->child[t->first_child[n]];
             if (semantics == PSGPU_SEM_SIMD) {  // PS_Polygonizer.cpp:1318-1337: warps return the left child unchanged (Q4)
+                if (hasXf(n)) { simdOpXform(); return; }
                 emit(c0, cmb);
                 return;
             }
             int pops = 0;
             if (hasXf(n)) {  // operator's own matrix, then the warp (CompactBlobTree.cpp:685-746)
-                quad(PS_HDR(OPC_AFFINE, 0, false, 0)); rows(&t->xform[n * 12]);
-                p->nInstr++; ppush(); pops++;
+                opAffine(n, w); pops++;
             }
             const float* r = &t->res[n * 4];
             switch (type) {
@@ -161,27 +181,27 @@ struct Emitter {
             }
             p->nInstr++; ppush(); pops++;
             if (pdepth > PS_MAX_POINT_STACK) { err = PSGPU_NOT_ENOUGH_MEM; msg = "warp nesting deeper than PS_MAX_POINT_STACK"; return; }
-            emit(c0, CMB_PUSH);
+            emit(c0, CMB_PUSH, 0);  // every warp returns a fresh vec4: w == 0 below it
             for (int i = 0; i < pops; i++) { quad(PS_HDR(OPC_POPPOINT, 0, false, 0)); p->nInstr++; pdepth--; }
             combine(cmb);
             return;
         }
         int pops = 0;
         if (hasXf(n)) {  // un-flattened operator transform (Q14): same treatment as the compact tree
-            quad(PS_HDR(OPC_AFFINE, 0, false, 0)); rows(&t->xform[n * 12]);
-            p->nInstr++; ppush(); pops++;
+            if (semantics == PSGPU_SEM_SIMD) { simdOpXform(); return; }
+            opAffine(n, w); pops++; w = 1;
             if (pdepth > PS_MAX_POINT_STACK) { err = PSGPU_NOT_ENOUGH_MEM; msg = "affine nesting deeper than PS_MAX_POINT_STACK"; return; }
         }
         if (type == PSGPU_OP_RICCI) {
             const float nexp = t->res[n * 4], inv = (nexp != 0.f) ? 1.0f / nexp : 0.f;
             if (semantics == PSGPU_SEM_SIMD) {
                 if (nk != 2) { err = PSGPU_INVALID_BVH; msg = "SIMD semantics need binary operators (PS_HighPerformanceRender.cpp:81-86)"; return; }
-                emit(t->child[t->first_child[n]], CMB_PUSH);
-                emit(t->child[t->first_child[n] + 1], CMB_PUSH);
+                emit(t->child[t->first_child[n]], CMB_PUSH, w);
+                emit(t->child[t->first_child[n] + 1], CMB_PUSH, w);
                 quad(PS_HDR(OPC_RICCI_SIMD, 0, false, 0), inv); p->nInstr++; pop();
             } else {
                 for (int i = 0; i < nk; i++) {
-                    emit(t->child[t->first_child[n] + i], CMB_PUSH);
+                    emit(t->child[t->first_child[n] + i], CMB_PUSH, w);
                     quad(PS_HDR(OPC_POW, 1, false, 0), nexp); p->nInstr++;
                     if (i > 0) combine(CMB_RADD);
                 }
@@ -199,16 +219,16 @@ struct Emitter {
                 // op(primitive, sub-tree): the shape of ConvertToBinaryTree's right-leaning chains (CLayerManager.cpp:131-176).
                 // Evaluate the sub-tree first and fold the primitive in as the LEFT operand: one live stack entry instead of
                 // one per chain link, and bit-identical (IEEE add / max / min commute; the differences have reverse codes).
-                emit(kids[1], CMB_PUSH);
+                emit(kids[1], CMB_PUSH, w);
                 emitPrim(kids[0], x == CMB_DIF ? (uint32_t)CMB_RDIF : (x == CMB_SDIF ? (uint32_t)CMB_RSDIF : x));
                 for (int i = 0; i < pops; i++) { quad(PS_HDR(OPC_POPPOINT, 0, false, 0)); p->nInstr++; pdepth--; }
                 combine(cmb);
                 return;
             }
-            emit(kids[0], CMB_PUSH);
+            emit(kids[0], CMB_PUSH, w);
             for (size_t i = 1; i < kids.size(); i++) {
                 if (PSGPU_IS_PRIM(t->type[kids[i]])) emitPrim(kids[i], x);
-                else { emit(kids[i], CMB_PUSH); combine(x); }
+                else { emit(kids[i], CMB_PUSH, w); combine(x); }
                 if (err != PSGPU_SUCCESS) return;
             }
         }

@@ -59,8 +59,35 @@ def ricci():
     return bt.Ricci(2.5, bt.Point([1.0, 1.0, 1.0], (1, 0, 0)), bt.Point([1.5, 1.0, 1.0], (0, 1, 0)), bt.Line([1.0, 1.4, 1.0], [1.6, 1.5, 1.1], (0, 0, 1)))
 
 
+def _quat(rs):
+    q = rs.normal(size=4)
+    return tuple(float(v) for v in (q / np.linalg.norm(q)).astype(np.float32))
+
+
+def xforms_srt(seed=19):
+    """primitives AND operators carrying the scene API's scale / rotation / translation (CAffineTransformation); the compact
+    tree applies operator matrices too (CompactBlobTree.cpp:685-694). Only the reference-built oracle and the
+    walker know the float32 backward matrices the reference derives from them."""
+    rs = np.random.RandomState(seed)
+    col = lambda: rs.uniform(0, 1, 3)
+    P = lambda: rs.uniform(0.8, 2.2, 3).astype(np.float32)
+    S = lambda: tuple(float(v) for v in rs.uniform(0.7, 1.3, 3).astype(np.float32))
+    T = lambda: tuple(float(v) for v in rs.uniform(-0.3, 0.3, 3).astype(np.float32))
+    a = bt.with_srt(bt.Point(P(), col()), S(), _quat(rs), T())
+    b = bt.with_srt(bt.Cylinder(P(), rs.normal(size=3), 0.15, 0.5, col()), S(), _quat(rs), T())
+    c = bt.with_srt(bt.Cube(P(), 0.2, col()), S(), _quat(rs), T())
+    d = bt.with_srt(bt.Line(P(), P(), col()), (1, 1, 1), _quat(rs), T())
+    e = bt.with_srt(bt.Disc(P(), rs.normal(size=3), 0.3, col()), S(), (0, 0, 0, 1), T())
+    grp = bt.with_srt(bt.Blend(a, b, bt.Point(P(), col())), (1, 1, 1), _quat(rs), T())
+    tw = bt.with_srt(bt.Twist(0.4, 1, bt.Blend(c, d)), S(), (0, 0, 0, 1), T())
+    return bt.Union(grp, tw, e)
+
+
 SIMD_SCENES = {"s1": s1, "blob": blob, "csg": csg_simd, "discs_rings": discs_rings, "xforms": with_xforms}
 SCALAR_SCENES = {"s1": s1, "blob": blob, "csg": csg_simd, "discs_rings": discs_rings, "xforms": with_xforms, "csgwarp": csgwarp_small, "ricci": ricci}
+# scenes only the reference-built scalar twin can judge (tests/golden/scalar_*.npz carry the tree the walker read back)
+COMPACTREF_SCENES = dict(SCALAR_SCENES, xforms_srt=xforms_srt)
+del COMPACTREF_SCENES["xforms"]  # raw backward matrices have no scale / rotation / translation form
 
 
 def simd_oracle(root, pad_op_boxes=True):

@@ -1,8 +1,13 @@
-"""Generates tests/golden/*.npz from the reference's OWN polygonizer (oracle/_ref/libpsref.so = unmodified
-Parsip100/PS_SimdPoly/include/PS_Polygonizer.cpp compiled by oracle/Makefile). Run in the build container, where
-/root/reference exists; the fixtures are committed so the GPU box (no reference there) can check against them.
+"""Generates tests/golden/*.npz from the reference's OWN code, compiled unmodified by oracle/Makefile:
+  * <scene>_{asis,padded}.npz  - the SIMD polygonizer, oracle/_ref/libpsref.so (Parsip100/PS_SimdPoly/include/PS_Polygonizer.cpp)
+  * scalar_<scene>.npz         - the scalar twin, oracle/_ref/libcompactref.so (PS_BlobTree scene API + COMPACTBLOBTREE +
+                                 CParsipOptimized): the tree as include/psgpu_blobtree_walk.h reads it back from the reference's
+                                 CBlobNode objects, fields / colours / normals / scene-API fields at random points, Newton roots
+                                 on crossing lattice edges, and the per-MPU meshes of CParsipOptimized::run.
+Run in the build container, where /root/reference exists; the fixtures are committed so the GPU box (no reference there) can
+check against them.
 
-    python tools/gen_golden.py
+    python tools/gen_golden.py [simd|scalar]
 """
 import hashlib
 import os
@@ -14,7 +19,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 sys.path.insert(0, os.path.join(ROOT, "tests"))
 
-from oracle.pyoracle import RefScene  # noqa: E402
+from oracle.pyoracle import CompactRef, RefScene  # noqa: E402
 from parsip_b200 import blobtree as bt, scenes  # noqa: E402
 import scenes_small  # noqa: E402
 
@@ -59,5 +64,47 @@ def main():
             print(name, "padded" if padded else "asis", st)
 
 
+SCALAR_CELLS = 36
+WALK_KEYS = ("type", "first_child", "n_children", "child", "pos", "dir", "res", "color", "xform", "has_xform", "oct_lo", "oct_hi")
+
+
+def main_scalar():
+    out = os.path.join(ROOT, "tests", "golden")
+    for name, mk in scenes_small.COMPACTREF_SCENES.items():
+        ref = CompactRef(bt.flatten(mk()))
+        assert ref.convert_rc >= 0 and ref.walk_rc == 0, (name, ref.convert_rc, ref.walk_rc)
+        w = ref.walk()
+        lo, hi = ref.octree()
+        rs = np.random.RandomState(43)
+        pts = rs.uniform(lo - 0.2, hi + 0.2, (3000, 3)).astype(np.float32)
+        f, col, nrm = ref.field_color_normal(pts)
+        cs = np.float32(scenes.cellsize_for(lo, hi, SCALAR_CELLS))
+        # Newton inputs: lattice-style edges (one cell long, axis-aligned) whose ends lie on different sides of the iso-surface
+        cand = rs.uniform(lo, hi, (60000, 3)).astype(np.float32)
+        axis = rs.randint(0, 3, len(cand))
+        p2 = cand.copy()
+        p2[np.arange(len(cand)), axis] += cs
+        f1, f2 = ref.field(cand), ref.field(p2)
+        cross = np.nonzero((f1 > 0.5) != (f2 > 0.5))[0][:400]
+        root, fr, ev = ref.newton(cand[cross], p2[cross], f1[cross], f2[cross])
+        m = ref.polygonize(lo, hi, float(cs), nthreads=1)
+        ok, em = ref.export_mesh()
+        assert ok and em["vertices"] == m["vertices"] and em["triangles"] == m["triangles"]
+        np.savez_compressed(
+            os.path.join(out, "scalar_%s.npz" % name),
+            n_nodes=np.int32(w["n_nodes"]), **{"tree_" + k: w[k] for k in WALK_KEYS},
+            n_prims=np.int32(ref.n_prims), n_ops=np.int32(ref.n_ops), bbox_lo=lo, bbox_hi=hi, pts=pts, field=f, color=col, normal=nrm,
+            scene_field=ref.scene_field(pts), newton_p1=cand[cross], newton_p2=p2[cross], newton_f1=f1[cross], newton_f2=f2[cross],
+            newton_root=root, newton_field=fr, newton_evals=ev, cellsize=cs, mesh_mpus=np.int64(m["mpus"]),
+            mesh_field_evals=np.int64(m["field_evals"]), mesh_origin=m["mpu_origin"], mesh_counts=m["mpu_counts"], mesh_pos=m["pos"],
+            mesh_nrm=m["nrm"], mesh_col=m["col"], mesh_tri=m["tri"], export_pos_sha=sha(em["pos"]), export_tri_sha=sha(em["tri"]))
+        print("scalar", name, "prims", ref.n_prims, "ops", ref.n_ops, "surface pts", int((f > 0.5).sum()), "newton edges", len(cross),
+              "mesh", m["mpus"], m["vertices"], m["triangles"])
+
+
 if __name__ == "__main__":
-    main()
+    what = sys.argv[1] if len(sys.argv) > 1 else "all"
+    if what in ("all", "simd"):
+        main()
+    if what in ("all", "scalar"):
+        main_scalar()
