@@ -281,13 +281,27 @@ __device__ __forceinline__ void prim_field(uint32_t opc, const float4 q0, const 
 // primitive under its own backward matrix (header bit XF): out of line, see eval_program
 // sincosf out of line: its argument reduction (with the slow path for large angles) is ~150 SASS instructions, and the warps
 // would inline it once per point and call site - csgwarp's vertex kernel stalled 6 cycles per issue on instruction fetch
-static __device__ __noinline__ void ps_sincosf(float a, float& s, float& c) { sincosf(a, &s, &c); }
+// Evaluated in double and rounded once: CUDA's sincosf is a 2-ulp routine, the reference's CPU build calls glibc's sinf / cosf
+// (< 1 ulp), and a warp multiplies coordinates of size ~5 by these factors - two ulps there showed up as 6e-5 relative in the
+// field under three nested warps (tests/test_gpu_compactref.py). One double sincos per warp instruction and point is noise next
+// to the primitives below it (B200 keeps full-rate FP64 units; measured on csgwarp@512^3 in profiles/r02_configs.json).
+static __device__ __noinline__ void ps_sincosf(float a, float& s, float& c) {
+#ifndef PSGPU_SINCOS_F32
+    double sd, cd;
+    sincos((double)a, &sd, &cd);
+    s = (float)sd; c = (float)cd;
+#else
+    sincosf(a, &s, &c);
+#endif
+}
 
 template <int N, bool STRICT>
 __device__ __noinline__ void prim_field_xf(uint32_t opc, const float4 q0, const float4* __restrict__ q, const float4* __restrict__ m,
                                            const float (&x)[N], const float (&y)[N], const float (&z)[N], float (&f)[N]) {
     float lx[N], ly[N], lz[N];
-    xform_points<N, STRICT>(m, x, y, z, lx, ly, lz);
+    // both semantics: row . (x, y, z, 1) summed left to right with separate roundings (PS_Polygonizer.cpp:951-969,
+    // CompactBlobTree.cpp:897-905 Vector4d::dot), so the local point has the reference's bits
+    xform_points<N, true>(m, x, y, z, lx, ly, lz);
     prim_field<N, STRICT>(opc, q0, q, lx, ly, lz, f);
 }
 
@@ -440,7 +454,7 @@ __device__ void eval_program(const float4* __restrict__ prog, const float (&X)[N
                 float xsave[3][N];
                 if (xf) {
                     float lx[N], ly[N], lz[N];
-                    xform_points<N, STRICT>(prog + pc + nq, x, y, z, lx, ly, lz);
+                    xform_points<N, true>(prog + pc + nq, x, y, z, lx, ly, lz);
 #pragma unroll
                     for (int n = 0; n < N; n++) { xsave[0][n] = x[n]; xsave[1][n] = y[n]; xsave[2][n] = z[n]; x[n] = lx[n]; y[n] = ly[n]; z[n] = lz[n]; }
                 }
@@ -535,9 +549,14 @@ __device__ void eval_program(const float4* __restrict__ prog, const float (&X)[N
 #pragma unroll
             for (int n = 0; n < N; n++) { pstk[psp][0][n] = x[n]; pstk[psp][1][n] = y[n]; pstk[psp][2][n] = z[n]; }
             psp++;
+            // Point transforms keep the reference's operation order with separately rounded multiplies and adds (its CPU build
+            // has no FMA): the Barr bend subtracts and re-adds 1/k (10-50 for gentle bends), so one fused rounding at that
+            // magnitude moved the warped point by ulp(50) ~ 4e-6 and the field by 6e-5 relative (tests/test_gpu_compactref.py,
+            // reproduced on the host with -ffp-contract=fast). With this form and the double-rounded sin / cos the warped point
+            // has the reference's bits; a handful of instructions per warp and point.
             if (opc == OPC_AFFINE) {
                 float ox[N], oy[N], oz[N];
-                xform_points<N>(prog + pc + 1, x, y, z, ox, oy, oz);
+                xform_points<N, true>(prog + pc + 1, x, y, z, ox, oy, oz);
 #pragma unroll
                 for (int n = 0; n < N; n++) { x[n] = ox[n]; y[n] = oy[n]; z[n] = oz[n]; }
             } else if (opc == OPC_TWIST) {  // CompactBlobTree.cpp:1355-1385
@@ -546,16 +565,16 @@ __device__ void eval_program(const float4* __restrict__ prog, const float (&X)[N
 #pragma unroll
                 for (int n = 0; n < N; n++) {
                     float s, c;
-                    const float ang = ((axis == 0) ? x[n] : ((axis == 1) ? y[n] : z[n])) * k;
+                    const float ang = PS_MUL((axis == 0) ? x[n] : ((axis == 1) ? y[n] : z[n]), k);
                     if (WARPS) ps_sincosf(ang, s, c); else sincosf(ang, &s, &c);
                     if (axis == 0) {
-                        const float ny = y[n] * c - z[n] * s, nz = y[n] * s + z[n] * c;
+                        const float ny = PS_SUB(PS_MUL(y[n], c), PS_MUL(z[n], s)), nz = PS_ADD(PS_MUL(y[n], s), PS_MUL(z[n], c));
                         y[n] = ny; z[n] = nz;
                     } else if (axis == 1) {
-                        const float nx = x[n] * c - z[n] * s, nz = x[n] * s + z[n] * c;
+                        const float nx = PS_SUB(PS_MUL(x[n], c), PS_MUL(z[n], s)), nz = PS_ADD(PS_MUL(x[n], s), PS_MUL(z[n], c));
                         x[n] = nx; z[n] = nz;
                     } else {
-                        const float nx = x[n] * c - y[n] * s, ny = x[n] * s + y[n] * c;
+                        const float nx = PS_SUB(PS_MUL(x[n], c), PS_MUL(y[n], s)), ny = PS_ADD(PS_MUL(x[n], s), PS_MUL(y[n], c));
                         x[n] = nx; y[n] = ny;
                     }
                 }
@@ -565,10 +584,10 @@ __device__ void eval_program(const float4* __restrict__ prog, const float (&X)[N
 #pragma unroll
                 for (int n = 0; n < N; n++) {
                     const float a = (along == 0) ? x[n] : ((along == 1) ? y[n] : z[n]);
-                    const float s = 1.0f + a * k;
-                    if (along == 0) { if (taper == 2) z[n] *= s; else y[n] *= s; }
-                    else if (along == 1) { if (taper == 2) z[n] *= s; else x[n] *= s; }
-                    else { if (taper == 2) y[n] *= s; else x[n] *= s; }
+                    const float s = PS_ADD(1.0f, PS_MUL(a, k));
+                    if (along == 0) { if (taper == 2) z[n] = PS_MUL(z[n], s); else y[n] = PS_MUL(y[n], s); }
+                    else if (along == 1) { if (taper == 2) z[n] = PS_MUL(z[n], s); else x[n] = PS_MUL(x[n], s); }
+                    else { if (taper == 2) y[n] = PS_MUL(y[n], s); else x[n] = PS_MUL(x[n], s); }
                 }
             } else if (opc == OPC_BEND) {  // CompactBlobTree.cpp:1315-1353 (Barr bend in y/z)
                 const float k = q0.y, y0 = q0.z, left = q0.w;
@@ -578,10 +597,15 @@ __device__ void eval_program(const float4* __restrict__ prog, const float (&X)[N
                 for (int n = 0; n < N; n++) {
                     const float yh = fminf(fmaxf(y[n], left), right);
                     float s, c;
-                    if (WARPS) ps_sincosf(k * (yh - y0), s, c); else sincosf(k * (yh - y0), &s, &c);
-                    const float dy = y[n] - yh, zz = z[n] - kd;
-                    const float ny = -s * zz + y0 + c * dy;
-                    const float nz = c * zz + kd + s * dy;
+                    const float th = PS_MUL(k, PS_SUB(yh, y0));
+                    if (WARPS) ps_sincosf(th, s, c); else sincosf(th, &s, &c);
+                    const float dy = PS_SUB(y[n], yh), zz = PS_SUB(z[n], kd);
+                    float ny = PS_ADD(PS_MUL(-s, zz), y0);
+                    float nz = PS_ADD(PS_MUL(c, zz), kd);
+                    if (y[n] < left || y[n] > right) {  // the straight extension outside the bent region (:1339-1350)
+                        ny = PS_ADD(ny, PS_MUL(c, dy));
+                        nz = PS_ADD(nz, PS_MUL(s, dy));
+                    }
                     y[n] = ny; z[n] = nz;
                 }
             } else {  // OPC_SHEAR, CompactBlobTree.cpp:1464-1536
@@ -589,9 +613,9 @@ __device__ void eval_program(const float4* __restrict__ prog, const float (&X)[N
                 const int along = (int)q0.z, dep = (int)q0.w;
 #pragma unroll
                 for (int n = 0; n < N; n++) {
-                    if (along == 1) y[n] += k * ((dep == 2) ? z[n] : x[n]);
-                    else if (along == 2) z[n] += k * ((dep == 1) ? y[n] : x[n]);
-                    else x[n] += k * ((dep == 2) ? z[n] : y[n]);
+                    if (along == 1) y[n] = PS_ADD(y[n], PS_MUL(k, (dep == 2) ? z[n] : x[n]));
+                    else if (along == 2) z[n] = PS_ADD(z[n], PS_MUL(k, (dep == 1) ? y[n] : x[n]));
+                    else x[n] = PS_ADD(x[n], PS_MUL(k, (dep == 2) ? z[n] : y[n]));
                 }
             }
         } break;
