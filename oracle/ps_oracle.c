@@ -833,6 +833,8 @@ static void warp_shear(const float* p, float factor, int along, int dep, float* 
 static float scalar_node(const pso_scalar* s, int id, const float* p, float w, float* store);
 
 /* fieldvaluePrim, PH/CompactBlobTree.cpp:893-1092 */
+static float scalar_node(const pso_scalar* s, int id, const float* p, float w, float* store);
+
 static float scalar_prim(const pso_scalar* s, int id, const float* p) {
     float pn[3] = {p[0], p[1], p[2]};
     if (s->hasxf[id]) {
@@ -905,6 +907,18 @@ static float scalar_prim(const pso_scalar* s, int id, const float* p) {
         float dx = np[0] - pn[0], dy = np[1] - pn[1], dz = np[2] - pn[2];
         return wyvill_sq(dx * dx + dy * dy + dz * dz);
     }
+    case PSGPU_PRIM_QUADRICPOINT: { /* :1051-1064 (BT/CQuadricPoint.h:43-52): scale * (1 - d^2 / R^2)^2 inside R */
+        float dx = pn[0] - c[0], dy = pn[1] - c[1], dz = pn[2] - c[2];
+        float fDist2 = dx * dx + dy * dy + dz * dz;
+        float fValue = 1.0f - (fDist2 / (r[0] * r[0]));
+        if (fValue <= 0.0f) return 0.0f;
+        return r[1] * fValue * fValue;
+    }
+    case PSGPU_PRIM_INSTANCE: { /* :1069-1078: the origin node at the instance's local point, w = 1, no stores */
+        int origin = (int)r[0];
+        if (origin < 0 || origin >= s->n || origin == id) return 0.0f;
+        return scalar_node(s, origin, pn, 1.0f, NULL);
+    }
     default: return 0.0f; /* bntPrimNull :1066-1068 */
     }
 }
@@ -964,6 +978,10 @@ static float scalar_field(const pso_scalar* s, const float* p, float* store) { r
 /* baseColorOp with cached node fields, PH/CompactBlobTree.cpp:1124-1294 (evaluated at the un-warped p) */
 static void scalar_color(const pso_scalar* s, int id, const float* store, float* out) {
     int t = s->type[id];
+    if (t == PSGPU_PRIM_INSTANCE) { /* baseColorPrim :1109-1122: the ORIGIN's colour from the stores of the origin's own evaluation */
+        int origin = (int)s->res[id * 4];
+        if (origin >= 0 && origin < s->n && origin != id) { scalar_color(s, origin, store, out); return; }
+    }
     if (PSGPU_IS_PRIM(t)) { memcpy(out, &s->col[id * 3], 12); return; }
     int nk = s->nkids[id];
     const int* kids = &s->child[s->first[id]];

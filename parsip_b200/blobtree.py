@@ -220,8 +220,12 @@ def binarize(root: Node) -> Node:
     """Right-leaning binary split of every operator with more than two children, the shape the
     reference's ConvertToBinaryTree produces (Parsip100/ParsipHaptics/include/CLayerManager.cpp:
     131-176: op(c0, op(c1, ... op(c_{n-2}, c_{n-1})))). Iterative (deep chains)."""
+    clones = []
+
     def clone(n, kids):
-        m = Node(n.type, kids, n.pos, n.dir, n.res, n.color, n.xform)
+        m = Node(n.type, kids, n.pos, n.dir, n.res, n.color, n.xform, origin=n.origin)
+        m.srt = n.srt
+        clones.append(m)
         return m
 
     # post-order rebuild without recursion
@@ -242,6 +246,9 @@ def binarize(root: Node) -> Node:
             done[id(n)] = acc
         else:
             done[id(n)] = clone(n, kids)
+    for m in clones:  # instances point at the rebuilt copy of their origin
+        if m.origin is not None:
+            m.origin = done[id(m.origin)]
     return done[id(root)]
 
 

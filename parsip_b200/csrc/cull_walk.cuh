@@ -128,6 +128,14 @@ __device__ bool prim_bound(uint32_t hdr, const float4 q0, const float4* __restri
     const float d = sqrtf(d2[0]);
     const float eps = 4e-6f * (fabsf(x[0]) + fabsf(y[0]) + fabsf(z[0]) + 1.0f) + 1e-5f * r + 1e-5f * d;
     const float dmin = fmaxf(d - r - eps, 0.f), dmax = d + r + eps;
+    if (opc == OPC_QUADRIC) {  // support radius R, law scale * (1 - d^2/R^2)^2 (scale > 0 is checked by the linearizer)
+        const float4 a = q[0];
+        if (dmin >= a.z) { flo = fhi = 0.f; return true; }
+        const float vhi = fmaxf(1.0f - dmin * dmin * a.x, 0.f), vlo = fmaxf(1.0f - dmax * dmax * a.x, 0.f);
+        fhi = a.y * vhi * vhi * 1.00001f + 1e-7f;
+        flo = fmaxf(a.y * vlo * vlo * 0.99999f - 1e-7f, 0.f);
+        return false;
+    }
     if (dmin >= 1.0f) { flo = fhi = 0.f; return true; }
     fhi = fminf(wyvill(dmin * dmin) * 1.00001f + 1e-7f, 1.0f);
     flo = fmaxf(wyvill(dmax * dmax) * 0.99999f - 1e-7f, 0.f);

@@ -83,7 +83,7 @@ __device__ __forceinline__ void prim_d2(uint32_t opc, const float4 q0, const flo
                                            const float (&x)[N], const float (&y)[N], const float (&z)[N], float (&d2o)[N]) {
     if (LINES == 1 && opc == OPC_LINE_INF) opc = OPC_NULLPRIM;
     switch (opc) {
-    case OPC_POINT: {
+    case OPC_POINT: case OPC_QUADRIC: {  // the quadric point's d2 is the plain distance too; its field law differs (prim_field)
 #pragma unroll
         for (int n = 0; n < N; n++) {
             const float dx = q0.y - x[n], dy = q0.z - y[n], dz = q0.w - z[n];
@@ -273,6 +273,12 @@ __device__ __forceinline__ void prim_field(uint32_t opc, const float4 q0, const 
         for (int n = 0; n < N; n++) f[n] = wyvill_strict(d2[n]);
     } else {
         prim_d2<N, 1>(opc, q0, q, x, y, z, d2);
+        if (opc == OPC_QUADRIC) {  // CompactBlobTree.cpp:1051-1064: scale * v * v with v = 1 - d2 / R^2, 0 where v <= 0
+            const float4 a = q[0];
+#pragma unroll
+            for (int n = 0; n < N; n++) { const float v = fmaxf(fmaf(-d2[n], a.x, 1.0f), 0.0f); f[n] = (a.y * v) * v; }
+            return;
+        }
 #pragma unroll
         for (int n = 0; n < N; n++) f[n] = wyvill(d2[n]);
     }

@@ -105,6 +105,13 @@ struct Emitter {
         case PSGPU_PRIM_NULL:
             quad(PS_HDR(OPC_NULLPRIM, cmb, false, id));
             break;
+        case PSGPU_PRIM_QUADRICPOINT: {
+            if (semantics == PSGPU_SEM_SIMD) { err = PSGPU_ERROR_UNSUPPORTED_NODE; msg = "quadric points exist only in the scalar semantics"; return; }
+            // the culling pass folds operands that are identically zero, which needs fields >= 0
+            if (!(res[0] > 0.f) || !(res[1] >= 0.f)) { err = PSGPU_PARAM_ERROR; msg = "quadric point needs radius > 0 and scale >= 0"; return; }
+            quad(PS_HDR(OPC_QUADRIC, cmb, xf, id), pos[0], pos[1], pos[2]);
+            quadf(1.0f / (res[0] * res[0]), res[1], res[0], 0.f);
+        } break;
         default:
             err = PSGPU_ERROR_UNSUPPORTED_NODE;
             msg = "primitive type " + std::to_string(t->type[n]) + " is not lowered to the GPU (SURVEY Q13)";
@@ -150,10 +157,34 @@ struct Emitter {
         }
     }
 
+    // CInstance (BT/CInstance.h, CompactBlobTree.cpp:1069-1078): the origin node evaluated at the instance's local point
+    // (row . (p, 1), so the whole matrix acts), with w = 1 below it. There is no call instruction on the device: the origin's
+    // sub-tree is emitted again in place. Colours: the copy is coloured at the instance's own point (the reference looks the
+    // origin's colour up from the stores of the origin's OWN evaluation elsewhere in the tree, CompactBlobTree.cpp:1109-1122).
+    int instanceDepth = 0;
+    void emitInstance(int n, uint32_t cmb) {
+        if (semantics == PSGPU_SEM_SIMD) { err = PSGPU_ERROR_UNSUPPORTED_NODE; msg = "instances exist only in the scalar semantics"; return; }
+        const int origin = (int)t->res[n * 4];
+        if (origin < 0 || origin >= t->n_nodes || origin == n || instanceDepth > 8) {
+            err = PSGPU_PARAM_ERROR; msg = "instance " + std::to_string(n) + ": origin index out of range or instancing too deep"; return;
+        }
+        const bool xf = hasXf(n);
+        if (xf) {
+            quad(PS_HDR(OPC_AFFINE, 0, false, 0)); rows(&t->xform[n * 12]);
+            p->nInstr++; ppush();
+            if (pdepth > PS_MAX_POINT_STACK) { err = PSGPU_NOT_ENOUGH_MEM; msg = "instance nesting deeper than PS_MAX_POINT_STACK"; return; }
+        }
+        instanceDepth++;
+        if (xf) { emit(origin, CMB_PUSH, 1); quad(PS_HDR(OPC_POPPOINT, 0, false, 0)); p->nInstr++; pdepth--; combine(cmb); }
+        else emit(origin, cmb, 1);
+        instanceDepth--;
+    }
+
     // Emits the sub-tree `n`; its value meets the current stack top with `cmb` (CMB_PUSH: new entry).
     void emit(int n, uint32_t cmb, int w = 0) {
         if (err != PSGPU_SUCCESS) return;
         const int type = t->type[n];
+        if (type == PSGPU_PRIM_INSTANCE) { emitInstance(n, cmb); return; }
         if (PSGPU_IS_PRIM(type)) { emitPrim(n, cmb); return; }
         const int nk = t->n_children[n];
         if (nk == 0) {  // an operator without children contributes nothing (CompactBlobTree.cpp:1138-1139)
@@ -227,7 +258,8 @@ struct Emitter {
             }
             emit(kids[0], CMB_PUSH, w);
             for (size_t i = 1; i < kids.size(); i++) {
-                if (PSGPU_IS_PRIM(t->type[kids[i]])) emitPrim(kids[i], x);
+                if (t->type[kids[i]] == PSGPU_PRIM_INSTANCE) emit(kids[i], x, w);
+                else if (PSGPU_IS_PRIM(t->type[kids[i]])) emitPrim(kids[i], x);
                 else { emit(kids[i], CMB_PUSH, w); combine(x); }
                 if (err != PSGPU_SUCCESS) return;
             }

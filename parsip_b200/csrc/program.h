@@ -37,6 +37,8 @@ enum PsOpcode : uint32_t {
     OPC_DISC = 6,      // {h, px,py,pz}{nx,ny,nz, radius}
     OPC_RING = 7,      // {h, px,py,pz}{nx,ny,nz, radius}
     OPC_NULLPRIM = 8,  // {h,0,0,0}  field 0
+    OPC_QUADRIC = 9,   // {h, px,py,pz}{1/R^2, scale, R, 0}  quadric point: scale * (1 - d^2/R^2)^2 inside R (CQuadricPoint.h:43-52);
+                       //                                    native semantics only, the only primitive whose law is not Wyvill's
     OPC_FIRST_NONPRIM = 16,
     OPC_COMBINE = 16,    // {h}            v = pop; top = top (combine) v
     OPC_POW = 17,        // {h, e}         top = pow(top, e)          (true Ricci, CompactBlobTree.cpp:813-818); combine code 1 marks
@@ -91,7 +93,7 @@ __host__ __device__
 static inline int ps_base_quads(uint32_t opc) {
     // 2 bits per opcode (quads - 1), opcodes 0..15 in the first word and 16..31 in the second: a shift and a mask instead of a
     // compare chain in the interpreters' decode path. SEGMENT, LINE_INF, CUBE, DISC, RING, BEND = 2; CYLINDER = 3; AFFINE = 4.
-    const uint32_t k = (opc < 16u) ? 0x00005650u : 0x03100000u;
+    const uint32_t k = (opc < 16u) ? 0x00045650u : 0x03100000u;  // QUADRIC (9) = 2
     return 1 + (int)((k >> (2u * (opc & 15u))) & 3u);
 }
 #if defined(__CUDACC__)
@@ -106,7 +108,7 @@ __host__ __device__
 static inline int ps_algorithmic_flops(uint32_t hdr) {
     int f = 0;
     switch (PS_HDR_OPC(hdr)) {
-    case OPC_POINT: f = 12; break;
+    case OPC_POINT: case OPC_QUADRIC: f = 12; break;
     case OPC_SEGMENT: case OPC_LINE_INF: f = 27; break;
     case OPC_CYLINDER: f = 33; break;
     case OPC_CUBE: f = 39; break;

@@ -83,10 +83,31 @@ def xforms_srt(seed=19):
     return bt.Union(grp, tw, e)
 
 
+def quadric(seed=23):
+    """CQuadricPoint primitives (Medusa's building block, PS_BlobTree/include/CQuadricPoint.h) blended with skeletal ones."""
+    rs = np.random.RandomState(seed)
+    col = lambda: rs.uniform(0, 1, 3)
+    P = lambda: rs.uniform(0.8, 2.4, 3).astype(np.float32)
+    qs = [bt.QuadricPoint(P(), float(np.float32(rs.uniform(0.5, 0.9))), float(np.float32(rs.uniform(0.6, 1.2))), col()) for _ in range(9)]
+    return bt.Union(bt.Blend(*qs[:5]), bt.Blend(qs[5], qs[6], bt.Point(P(), col())), bt.Dif(bt.Blend(qs[7], qs[8]), bt.Point(P(), col())))
+
+
+def instances(seed=29):
+    """CInstance: a sub-tree (and a single primitive) re-used under the instance's own transform (CompactBlobTree.cpp:1069-1078)."""
+    rs = np.random.RandomState(seed)
+    col = lambda: rs.uniform(0, 1, 3)
+    arm = bt.Blend(bt.Point([1.0, 1.0, 1.0], col()), bt.Line([1.0, 1.0, 1.0], [1.5, 1.2, 1.1], col()), bt.Cylinder([1.5, 1.2, 1.1], [0, 1, 0], 0.12, 0.4, col()))
+    ball = bt.Point([2.2, 2.0, 1.0], col())
+    i1 = bt.with_srt(bt.Instance(arm), (1, 1, 1), _quat(rs), (0.9, 0.4, 0.3))
+    i2 = bt.with_srt(bt.Instance(arm), (0.8, 0.8, 0.8), (0, 0, 0, 1), (-0.2, 1.1, 0.6))
+    i3 = bt.with_srt(bt.Instance(ball), (1, 1, 1), (0, 0, 0, 1), (0.0, -0.9, 0.5))
+    return bt.Union(arm, ball, bt.Blend(i1, i3), i2)
+
+
 SIMD_SCENES = {"s1": s1, "blob": blob, "csg": csg_simd, "discs_rings": discs_rings, "xforms": with_xforms}
 SCALAR_SCENES = {"s1": s1, "blob": blob, "csg": csg_simd, "discs_rings": discs_rings, "xforms": with_xforms, "csgwarp": csgwarp_small, "ricci": ricci}
 # scenes only the reference-built scalar twin can judge (tests/golden/scalar_*.npz carry the tree the walker read back)
-COMPACTREF_SCENES = dict(SCALAR_SCENES, xforms_srt=xforms_srt)
+COMPACTREF_SCENES = dict(SCALAR_SCENES, xforms_srt=xforms_srt, quadric=quadric, instances=instances)
 del COMPACTREF_SCENES["xforms"]  # raw backward matrices have no scale / rotation / translation form
 
 

@@ -17,10 +17,10 @@ def _regions(lo, hi, rs, n, side):
     return c, (c + np.float32(side)).astype(np.float32)
 
 
-@pytest.mark.parametrize("name", sorted(scenes_small.SCALAR_SCENES))
+@pytest.mark.parametrize("name", sorted(set(scenes_small.SCALAR_SCENES) | {"quadric", "instances", "xforms_srt"}))
 @pytest.mark.parametrize("side", [0.14, 0.56])
 def test_pruned_program_is_bit_identical_inside_its_region(name, side):
-    root = scenes_small.SCALAR_SCENES[name]()
+    root = scenes_small.COMPACTREF_SCENES.get(name, scenes_small.SCALAR_SCENES.get(name))()
     prog = ps.linearize(bt.flatten(root), ps.SEM_SCALAR, ps.LIN_REASSOCIATE)
     quads = prog.quads()
     lo, hi = ps.prepare_bboxes(bt.flatten(bt.binarize(root)))
