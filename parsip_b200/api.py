@@ -83,7 +83,8 @@ class _Stats(C.Structure):
 
 
 def lib_path() -> str:
-    return os.path.join(os.path.dirname(os.path.abspath(__file__)), "libpsgpu.so")
+    # PSGPU_LIB: development aid for A/B runs of two builds of the same library (never a fallback: the file must exist)
+    return os.environ.get("PSGPU_LIB") or os.path.join(os.path.dirname(os.path.abspath(__file__)), "libpsgpu.so")
 
 
 _lib = None

@@ -15,6 +15,12 @@
 #include "kernels.h"
 #include "mc_tables.h"
 
+// resident 64-thread CTAs per SM asked of ptxas for the STRICT 8-point kernel: 12 = 80 registers, 16 = 64 registers (A/B in
+// profiles/r02_*: see DESIGN.md section 9)
+#ifndef PSGPU_STRICT_CTAS
+#define PSGPU_STRICT_CTAS 12
+#endif
+
 namespace psgpu {
 
 __constant__ uint8_t c_nTri[256] = PS_MC_NTRI_INIT;
@@ -34,6 +40,7 @@ struct __align__(16) FieldSmemHeader {
     uint32_t edgeW[48];
     uint32_t warpSum[8];
     uint8_t nTri[256];  // triangles per cube case (lanes look up different cases: shared memory, not __constant__)
+    uint32_t spread3[256];  // bit n of the index -> bit 3n (interleaves the x / y / z crossing bytes of a z-column into 24 edge bits)
     int next;
     int flags;
 };
@@ -41,7 +48,7 @@ struct __align__(16) FieldSmemHeader {
 // STAGED: every candidate list fits the staging buffers (the host checks the longest one) and is interpreted from shared memory;
 // the unstaged variant (brute-force mode, very long lists) reads the lists from global memory. One interpreter copy per kernel.
 template <bool STRICT, bool STAGED, int kPts>
-__global__ void __launch_bounds__(512 / kPts, kPts == 4 ? 6 : (STRICT ? 12 : 16)) field_kernel(GridParams G, const Region* __restrict__ cands, int nCand,
+__global__ void __launch_bounds__(512 / kPts, kPts == 4 ? 6 : (STRICT ? PSGPU_STRICT_CTAS : 16)) field_kernel(GridParams G, const Region* __restrict__ cands, int nCand,
                                                          const float4* __restrict__ pool, FieldOutputs out, uint32_t capQuads) {
     extern __shared__ __align__(16) unsigned char smemRaw[];
     FieldSmemHeader& S = *reinterpret_cast<FieldSmemHeader*>(smemRaw);
@@ -55,7 +62,13 @@ __global__ void __launch_bounds__(512 / kPts, kPts == 4 ? 6 : (STRICT ? 12 : 16)
         mbar_init(&S.bar[1], 1);
         fence_mbar_init();
     }
-    for (int i = t; i < 256; i += kThreads) S.nTri[i] = c_nTri[i];
+    for (int i = t; i < 256; i += kThreads) {
+        S.nTri[i] = c_nTri[i];
+        uint32_t sp = 0;
+#pragma unroll
+        for (int b = 0; b < 8; b++) sp |= ((uint32_t)(i >> b) & 1u) << (3 * b);
+        S.spread3[i] = sp;
+    }
     __syncthreads();
 
     int item = blockIdx.x;  // first item is static, the rest come from the work counter
@@ -78,8 +91,10 @@ __global__ void __launch_bounds__(512 / kPts, kPts == 4 ? 6 : (STRICT ? 12 : 16)
                 tma_load_bulk(progBuf + (size_t)(stage ^ 1) * capQuads, pool + rn.off, rn.len * 16u, &S.bar[stage ^ 1]);
             }
         }
-        if (t < 16) S.insideW[t] = 0u;
-        if (t < 48) S.edgeW[t] = 0u;
+        if (kPts != 8) {  // the 8-point variant writes whole bytes of both masks
+            if (t < 16) S.insideW[t] = 0u;
+            if (t < 48) S.edgeW[t] = 0u;
+        }
         const Region r = cands[item];
         if (STAGED) {
             mbar_wait(&S.bar[stage], phase[stage]);
@@ -112,11 +127,52 @@ __global__ void __launch_bounds__(512 / kPts, kPts == 4 ? 6 : (STRICT ? 12 : 16)
 #pragma unroll
         for (int q = 0; q < kPts / 4; q++)
             reinterpret_cast<float4*>(S.fv)[t * (kPts / 4) + q] = make_float4(F[4 * q], F[4 * q + 1], F[4 * q + 2], F[4 * q + 3]);
+        uint32_t nV = 0, nT = 0;
+        bool mixed;
+        uint32_t myT = 0;
+        if constexpr (kPts == 8) {
+            // A thread owns one z-column = exactly one byte of the inside bits (byte i + 8j = the 8 corners along k), so the
+            // classification works on bytes with plain stores: no shared-memory atomics, one barrier instead of four
+            // (ncu r02a: this epilogue was ~30 % of the kernel's samples, barrier stalls 0.9 per issue at 2 warps per CTA).
+            uint8_t* B = reinterpret_cast<uint8_t*>(S.insideW);
+            B[t] = (uint8_t)inb;
+            __syncthreads();
+            {   // early discard like PS_Polygonizer.cpp:602-609: all corners inside or all outside
+                const uint4* W4 = reinterpret_cast<const uint4*>(S.insideW);
+                const uint4 a = W4[0], b = W4[1], c = W4[2], d = W4[3];
+                const uint32_t o = a.x | a.y | a.z | a.w | b.x | b.y | b.z | b.w | c.x | c.y | c.z | c.w | d.x | d.y | d.z | d.w;
+                const uint32_t n = a.x & a.y & a.z & a.w & b.x & b.y & b.z & b.w & c.x & c.y & c.z & c.w & d.x & d.y & d.z & d.w;
+                mixed = (o != 0u) && (n != 0xffffffffu);
+            }
+            if (mixed) {
+                // ---- crossing edges this MPU owns: per corner the x, y, z edge leaving it; bit 3*(8t + n) + axis of the edge mask
+                const bool lastX = (r.x == G.hi[0] - 1), lastY = (r.y == G.hi[1] - 1), lastZ = (r.z == G.hi[2] - 1);
+                const bool perMpu = (G.output == PSGPU_OUT_MPU);
+                const bool ownX = perMpu || ci < 7 || lastX, ownY = perMpu || cj < 7 || lastY;
+                const uint32_t zmask = (perMpu || lastZ) ? 0xffu : 0x7fu;  // edges starting at ck = 7 belong to the next MPU in z
+                const uint32_t bx = (ci < 7) ? B[t + 1] : inb, by = (cj < 7) ? B[t + 8] : inb;
+                const uint32_t xc = (ownY ? zmask : 0u) & (inb ^ bx);
+                const uint32_t yc = (ownX ? zmask : 0u) & (inb ^ by);
+                const uint32_t zc = ((ownX && ownY) ? 0x7fu : 0u) & (inb ^ (inb >> 1));
+                const uint32_t ebits = S.spread3[xc] | (S.spread3[yc] << 1) | (S.spread3[zc] << 2);
+                uint8_t* E = reinterpret_cast<uint8_t*>(S.edgeW);  // 24 bits at bit 24 t = bytes 3t .. 3t + 2
+                E[3 * t] = (uint8_t)ebits; E[3 * t + 1] = (uint8_t)(ebits >> 8); E[3 * t + 2] = (uint8_t)(ebits >> 16);
+                // ---- triangles: the 7 cells above (ci, cj), cube case from the four neighbouring columns' bytes
+                if (ci < 7 && cj < 7) {
+                    const uint32_t b00 = inb, b10 = bx, b01 = by, b11 = B[t + 9];
+#pragma unroll
+                    for (int cz = 0; cz < 7; cz++) {
+                        const uint32_t cfg = ((b00 >> cz) & 3u) | (((b01 >> cz) & 3u) << 2) | (((b10 >> cz) & 3u) << 4) | (((b11 >> cz) & 3u) << 6);
+                        myT += S.nTri[cfg];
+                    }
+                }
+            }
+        } else {
         // early discard like PS_Polygonizer.cpp:602-609: all corners inside or all outside
         const int anyIn = __syncthreads_or(inb != 0u);
         const int anyOut = __syncthreads_or(inb != ((1u << kPts) - 1u));
-        uint32_t nV = 0, nT = 0;
-        if (anyIn && anyOut) {
+        mixed = anyIn && anyOut;
+        if (mixed) {
             atomicOr(&S.insideW[(kPts * t) >> 5], inb << ((kPts * t) & 31));
             __syncthreads();
             // ---- crossing edges this MPU owns: 3 bits per corner (x, y, z edge leaving it)
@@ -141,13 +197,15 @@ __global__ void __launch_bounds__(512 / kPts, kPts == 4 ? 6 : (STRICT ? 12 : 16)
             }
             // ---- triangles: cube case of cell (x, y, z) from the inside bits read as bytes (byte i + 8j = the 8 corners along k)
             const uint8_t* B = reinterpret_cast<const uint8_t*>(S.insideW);
-            uint32_t myT = 0;
             for (int c = t; c < 343; c += kThreads) {
                 const int cx = c / 49, cy = (c - cx * 49) / 7, cz = c - cx * 49 - cy * 7;
                 const uint32_t b00 = B[cy * 8 + cx], b10 = B[cy * 8 + cx + 1], b01 = B[(cy + 1) * 8 + cx], b11 = B[(cy + 1) * 8 + cx + 1];
                 const uint32_t cfg = ((b00 >> cz) & 3u) | (((b01 >> cz) & 3u) << 2) | (((b10 >> cz) & 3u) << 4) | (((b11 >> cz) & 3u) << 6);
                 myT += S.nTri[cfg];
             }
+        }
+        }
+        if (mixed) {
 #pragma unroll
             for (int o = 16; o > 0; o >>= 1) myT += __shfl_xor_sync(0xffffffffu, myT, o);
             if (lane == 0) S.warpSum[t >> 5] = myT;
@@ -303,12 +361,8 @@ void launch_field_kernel(const GridParams& G, const Region* cands, int nCand, co
     else if (four) k = staged ? field_kernel<false, true, 4> : field_kernel<false, false, 4>;
     else k = staged ? field_kernel<false, true, 8> : field_kernel<false, false, 8>;
     const int threads = four ? 128 : 64;
-    static int configured[3][2] = {{-1, -1}, {-1, -1}, {-1, -1}};
-    const int vi = strict ? 0 : (four ? 1 : 2);
-    if (smem > configured[vi][staged]) {
-        cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
-        configured[vi][staged] = smem;
-    }
+    // per launch: the attribute is per device and function, a process may drive several devices (a microsecond of host time)
+    if (smem > 48 * 1024) cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
     int perSM = 0;
     cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSM, k, threads, smem);
     if (perSM < 1) perSM = 1;

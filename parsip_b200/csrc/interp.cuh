@@ -407,6 +407,9 @@ __device__ __forceinline__ void combine_color(int sem, uint32_t cmb, float tf, f
 // PS_SimdPoly colour weight of a blend operand whose sibling was culled as all-zero (program.h: OPC_CSCALE / header bits 28..31)
 __device__ __forceinline__ void color_scale(float top0, float (&tc)[3], uint32_t cnt) {
     const float w = __fsub_rn(__fmul_rn(2.0f, __fadd_rn(0.5f, top0)), 1.0f);
+    // one separately rounded multiply per dropped sibling and channel, in the reference's order (no power shortcut): unrolled so
+    // that a long run (a blend that lost 17 of 20 operands) costs the 3 multiplies per step and little else
+#pragma unroll 4
     for (uint32_t k = 0; k < cnt; k++) { tc[0] = __fmul_rn(w, tc[0]); tc[1] = __fmul_rn(w, tc[1]); tc[2] = __fmul_rn(w, tc[2]); }
 }
 
