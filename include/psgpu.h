@@ -100,11 +100,26 @@ typedef struct psgpu_stats {
     float ms_cull, ms_field, ms_scan, ms_emit, ms_total; /* CUDA-event times of the last polygonize */
     int64_t gpu_launches;     /* kernels launched by the last polygonize */
     float ms_tri, ms_vertex, ms_color; /* the three kernels inside ms_emit */
-    float reserved0;
+    float ms_exchange;                 /* psgpu_polygonize_sharded: count all-gather + halo send/recv (inside ms_total) */
     int64_t vertex_eval_flops; /* collect_stats: sum over surface MPUs of vertices x SURVEY 8(d) op count of the MPU's pruned program,
                                   i.e. the algorithmic work of ONE field evaluation per vertex (a vertex costs 8: 4 root samples,
                                   4 gradient samples; its colour walk 1 more) */
+    int64_t unresolved_edges;  /* PSGPU_OUT_INDEXED: shared edges missing from their owner's crossing mask (always 0; else the call fails) */
 } psgpu_stats;
+
+/* One rank's share of a mesh polygonized over several GPUs (psgpu_polygonize_sharded). The MPU lattice is cut into z-slabs of MPU
+ * layers (the reference's parallel_for over independent MPUs, PS_Polygonizer.cpp:379-381, spread over devices); slab-boundary corners
+ * come from global lattice indices, so both sides compute bit-identical values, the lower-z rank leaves the vertices of the shared
+ * plane to the rank above and learns their ids from it. tri[] of every rank then holds GLOBAL vertex ids: rank r's vertices are
+ * [vertex_offset, vertex_offset + n_vertices) of the concatenated array - the same mesh a single GPU produces. */
+typedef struct psgpu_shard {
+    int32_t nranks, rank;
+    int32_t z_begin, z_end;          /* MPU layers of this rank */
+    int64_t vertex_offset, triangle_offset;
+    int64_t total_vertices, total_triangles;
+    float ms_exchange;               /* count all-gather + halo exchange, CUDA events on the context's stream */
+    int32_t stitched;                /* 1: boundary vertices exist once and tri[] is globally indexed */
+} psgpu_shard;
 
 /* ---- context ---- */
 int psgpu_create(int device, psgpu_ctx** out);
@@ -140,6 +155,23 @@ uint32_t psgpu_count_mpus(float cellsize, const float* lo3, const float* hi3);
 int psgpu_upload_program(psgpu_ctx* ctx, const psgpu_program* p);
 /* Runs cull -> field -> scan -> emit. The mesh stays on the device (see psgpu_mesh). */
 int psgpu_polygonize(psgpu_ctx* ctx, const psgpu_params* params, psgpu_mesh* out);
+/* ---- multi-GPU: one process (or thread) per GPU, one context per rank, NCCL over NVLink. NCCL is bound at run time (libnccl.so.2);
+ * single-GPU use never loads it. Rank 0 creates the id, the application hands the 128 bytes to the other ranks by any channel it has
+ * (MPI, torch.distributed, a file), every rank calls psgpu_comm_init. */
+#define PSGPU_UNIQUE_ID_BYTES 128
+int psgpu_comm_get_unique_id(void* id128);
+int psgpu_comm_init(psgpu_ctx* ctx, int nranks, int rank, const void* id128);
+int psgpu_comm_destroy(psgpu_ctx* ctx);
+/* [z_begin, z_end) of `rank`: equal slabs (layer_weights == NULL) or balanced by one weight per MPU layer. */
+int psgpu_slab_bounds(int n_layers, int nranks, int rank, const float* layer_weights, int32_t* z_begin, int32_t* z_end);
+/* Collective over the communicator: polygonizes this rank's slab (params->z_begin/z_end, or an equal share if z_end <= 0), exchanges
+ * counts and the boundary layer's vertex tables, and leaves a stitched share of ONE mesh on every rank (see psgpu_shard).
+ * PSGPU_OUT_INDEXED + PSGPU_COORD_GLOBAL only. Without psgpu_comm_init it is psgpu_polygonize. */
+int psgpu_polygonize_sharded(psgpu_ctx* ctx, const psgpu_params* params, psgpu_mesh* out, psgpu_shard* shard);
+/* Collective: gathers the shares into DEVICE buffers on `root` (3 * total_vertices floats each, 3 * total_triangles indices);
+ * every rank passes the same set of non-NULL arguments (any valid non-NULL value on the senders means "send this array"). */
+int psgpu_mesh_gather(psgpu_ctx* ctx, int root, float* pos, float* nrm, float* col, uint32_t* tri);
+
 /* Same, then copies the mesh into caller-provided HOST buffers (capacity in vertices / triangles;
  * PSGPU_NOT_ENOUGH_MEM if too small, with the needed sizes in out). NULL buffers are skipped. */
 int psgpu_polygonize_host(psgpu_ctx* ctx, const psgpu_params* params, psgpu_mesh* out, float* pos, float* nrm,

@@ -22,6 +22,7 @@ EXPORTS = [
     "psgpu_program_info", "psgpu_program_copy", "psgpu_program_colors", "psgpu_prepare_bboxes", "psgpu_count_mpus", "psgpu_upload_program",
     "psgpu_polygonize", "psgpu_polygonize_host", "psgpu_mesh_download", "psgpu_mesh_map_host", "psgpu_field_eval", "psgpu_field_color_normal",
     "psgpu_tree_binarize", "psgpu_tree_view", "psgpu_tree_free", "psgpu_mpu_cache", "psgpu_mpu_caches_culled", "psgpu_prune_region", "psgpu_get_stats", "psgpu_measure_fp32_peak",
+    "psgpu_comm_get_unique_id", "psgpu_comm_init", "psgpu_comm_destroy", "psgpu_slab_bounds", "psgpu_polygonize_sharded", "psgpu_mesh_gather",
 ]
 
 
@@ -77,8 +78,16 @@ class _Stats(C.Structure):
         ("mpus_total", C.c_int64), ("mpus_evaluated", C.c_int64), ("mpus_crossed", C.c_int64), ("field_evals", C.c_int64),
         ("prim_evals", C.c_int64), ("algorithmic_flops", C.c_int64), ("program_quads", C.c_int64), ("pruned_quads", C.c_int64),
         ("ms_cull", C.c_float), ("ms_field", C.c_float), ("ms_scan", C.c_float), ("ms_emit", C.c_float), ("ms_total", C.c_float),
-        ("gpu_launches", C.c_int64), ("ms_tri", C.c_float), ("ms_vertex", C.c_float), ("ms_color", C.c_float), ("reserved0", C.c_float),
-        ("vertex_eval_flops", C.c_int64),
+        ("gpu_launches", C.c_int64), ("ms_tri", C.c_float), ("ms_vertex", C.c_float), ("ms_color", C.c_float), ("ms_exchange", C.c_float),
+        ("vertex_eval_flops", C.c_int64), ("unresolved_edges", C.c_int64),
+    ]
+
+
+class _Shard(C.Structure):
+    _fields_ = [
+        ("nranks", C.c_int32), ("rank", C.c_int32), ("z_begin", C.c_int32), ("z_end", C.c_int32),
+        ("vertex_offset", C.c_int64), ("triangle_offset", C.c_int64), ("total_vertices", C.c_int64), ("total_triangles", C.c_int64),
+        ("ms_exchange", C.c_float), ("stitched", C.c_int32),
     ]
 
 
@@ -128,6 +137,12 @@ def load_library():
     lib.psgpu_mpu_caches_culled.argtypes = [vp, C.POINTER(Params), vp, vp, C.c_int64, vp]
     lib.psgpu_prune_region.argtypes = [vp, vp, vp, C.c_int, C.c_float, C.c_int, vp, C.c_uint32, vp]
     lib.psgpu_get_stats.argtypes = [vp, C.POINTER(_Stats)]
+    lib.psgpu_comm_get_unique_id.argtypes = [vp]
+    lib.psgpu_comm_init.argtypes = [vp, C.c_int, C.c_int, vp]
+    lib.psgpu_comm_destroy.argtypes = [vp]
+    lib.psgpu_slab_bounds.argtypes = [C.c_int, C.c_int, C.c_int, vp, vp, vp]
+    lib.psgpu_polygonize_sharded.argtypes = [vp, C.POINTER(Params), C.POINTER(_Mesh), C.POINTER(_Shard)]
+    lib.psgpu_mesh_gather.argtypes = [vp, C.c_int, vp, vp, vp, vp]
     lib.psgpu_measure_fp32_peak.argtypes = [vp, vp, vp]
     _lib = lib
     return lib
@@ -211,6 +226,26 @@ def binarize_tree(flat: dict, split_always: bool = True, pad_with_null: bool = T
     finally:
         lib.psgpu_tree_free(h)
     return out, int(nconv.value)
+
+
+def comm_unique_id() -> bytes:
+    """psgpu_comm_get_unique_id: 128 bytes rank 0 hands to the other ranks."""
+    lib = load_library()
+    buf = C.create_string_buffer(128)
+    rc = lib.psgpu_comm_get_unique_id(buf)
+    if rc != SUCCESS:
+        raise PsGpuError(rc, "psgpu_comm_get_unique_id (libnccl.so.2 missing?)")
+    return buf.raw
+
+
+def slab_bounds(n_layers: int, nranks: int, rank: int, weights=None):
+    lib = load_library()
+    b, e = C.c_int32(), C.c_int32()
+    w = None if weights is None else np.ascontiguousarray(weights, np.float32)
+    rc = lib.psgpu_slab_bounds(int(n_layers), int(nranks), int(rank), None if w is None else w.ctypes.data, C.byref(b), C.byref(e))
+    if rc != SUCCESS:
+        raise PsGpuError(rc, "psgpu_slab_bounds")
+    return int(b.value), int(e.value)
 
 
 def count_mpus(cellsize, lo, hi) -> int:
@@ -308,6 +343,34 @@ class Context:
                                                      ijk.ctypes.data, vb.ctypes.data, tb.ctypes.data), "psgpu_mesh_download")
             out.update(pos=pos, nrm=nrm, col=col, tri=tri, mpu_ijk=ijk, mpu_vbase=vb, mpu_tbase=tb)
         return out
+
+    # ---- multi-GPU: one Context per rank --------------------------------------------------------------------------------
+    def comm_init(self, nranks: int, rank: int, unique_id: bytes):
+        """psgpu_comm_init: joins the NCCL communicator whose 128-byte id rank 0 made with comm_unique_id()."""
+        buf = C.create_string_buffer(bytes(unique_id), 128)
+        self._check(self.lib.psgpu_comm_init(self.h, int(nranks), int(rank), buf), "psgpu_comm_init")
+        self.nranks, self.rank = int(nranks), int(rank)
+
+    def polygonize_sharded(self, params: Params, download: bool = False) -> dict:
+        """psgpu_polygonize_sharded (collective): this rank's stitched share of one mesh; tri[] holds GLOBAL vertex ids."""
+        m, sh = _Mesh(), _Shard()
+        self._check(self.lib.psgpu_polygonize_sharded(self.h, C.byref(params), C.byref(m), C.byref(sh)), "psgpu_polygonize_sharded")
+        out = dict(n_vertices=int(m.n_vertices), n_triangles=int(m.n_triangles), lattice=tuple(m.lattice),
+                   shard={f: getattr(sh, f) for f, _ in _Shard._fields_})
+        if download:
+            nv, nt = out["n_vertices"], out["n_triangles"]
+            pos, nrm, col = (np.zeros((nv, 3), np.float32) for _ in range(3))
+            tri = np.zeros((nt, 3), np.uint32)
+            self._check(self.lib.psgpu_mesh_download(self.h, pos.ctypes.data, nrm.ctypes.data, col.ctypes.data, tri.ctypes.data, None, None, None),
+                        "psgpu_mesh_download")
+            out.update(pos=pos, nrm=nrm, col=col, tri=tri)
+        return out
+
+    def mesh_gather(self, root: int, pos_ptr: int, nrm_ptr: int, col_ptr: int, tri_ptr: int):
+        """psgpu_mesh_gather (collective): device pointers on the root (ints, e.g. torch tensors' data_ptr()); any non-zero value on
+        the other ranks means "send this array"."""
+        self._check(self.lib.psgpu_mesh_gather(self.h, int(root), C.c_void_p(pos_ptr or None), C.c_void_p(nrm_ptr or None),
+                                               C.c_void_p(col_ptr or None), C.c_void_p(tri_ptr or None)), "psgpu_mesh_gather")
 
     def polygonize_host(self, params: Params, pos, nrm, col, tri) -> dict:
         """The reference-facing call with HOST buffers (device -> host copies inside)."""

@@ -14,6 +14,7 @@
 
 #include "../../include/psgpu.h"
 #include "host_program.h"
+#include "nccl_dl.h"
 #include "kernels.h"
 
 extern "C" void psgpu_lattice_dims(float cellsize, const float* lo, const float* hi, int32_t* nm);
@@ -31,7 +32,10 @@ struct DevBuf {
         void* np = nullptr;
         cudaError_t e = cudaMalloc(&np, ncap);
         if (e != cudaSuccess) return e;
-        if (keep && p && cap) cudaMemcpyAsync(np, p, cap, cudaMemcpyDeviceToDevice, st);
+        if (keep && p && cap) {
+            e = cudaMemcpyAsync(np, p, cap, cudaMemcpyDeviceToDevice, st);
+            if (e != cudaSuccess) { cudaFree(np); return e; }
+        }
         if (p) { cudaStreamSynchronize(st); cudaFree(p); }
         p = np; cap = ncap;
         return cudaSuccess;
@@ -68,11 +72,19 @@ struct psgpu_ctx {
     size_t hostStageCap = 0;
     void* hostMesh = nullptr;         // pinned arena behind psgpu_mesh_map_host
     size_t hostMeshCap = 0;
-    cudaEvent_t ev[8];
+    cudaEvent_t ev[10];
     psgpu_mesh last{};
     psgpu_stats stats{};
     psgpu::Region* cands = nullptr;
     int nCand = 0;
+    // multi-GPU (psgpu_comm_init): one context = one rank
+    void* comm = nullptr;
+    int nranks = 1, rank = 0;
+    DevBuf shardCounts, haloSend, haloRecv;
+    std::vector<uint64_t> rankCounts;  // {vertices, triangles} of every rank after the last sharded polygonize
+    // slab program: the uploaded program pruned once against this rank's slab box, cached behind the full program in the pool
+    struct SlabProg { bool valid = false; int zb = 0, ze = 0; float lo[3] = {0, 0, 0}, side = 0.f; int nx = 0, ny = 0; int colorExact = 0; uint32_t len = 0; } slab;
+    uint32_t rootOff = 0, rootLen = 0;  // program the cull hierarchy starts from in the current polygonize
 };
 
 #define CK(call)                                                                                              \
@@ -101,8 +113,10 @@ extern "C" int psgpu_create(int device, psgpu_ctx** out) {
     cudaDeviceGetAttribute(&ctx->numSMs, cudaDevAttrMultiProcessorCount, device);
     if (cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking) != cudaSuccess) { delete ctx; return PSGPU_ERROR_CUDA; }
     if (cudaStreamCreateWithFlags(&ctx->copyStream, cudaStreamNonBlocking) != cudaSuccess) { delete ctx; return PSGPU_ERROR_CUDA; }
-    for (auto& e : ctx->ev) cudaEventCreate(&e);
-    cudaMallocHost(&ctx->hostScalars, 64 * sizeof(uint32_t));
+    bool ok = true;
+    for (auto& e : ctx->ev) { e = nullptr; ok = ok && cudaEventCreate(&e) == cudaSuccess; }
+    ok = ok && cudaMallocHost(&ctx->hostScalars, 64 * sizeof(uint32_t)) == cudaSuccess;
+    if (!ok) { psgpu_destroy(ctx); return PSGPU_ERROR_CUDA; }
     *out = ctx;
     return PSGPU_SUCCESS;
 }
@@ -115,9 +129,10 @@ extern "C" int psgpu_destroy(psgpu_ctx* ctx) {
                      &ctx->scanTemp, &ctx->candOfMpu, &ctx->scalars, &ctx->cullScratch, &ctx->cullScratchFlag, &ctx->fv, &ctx->vcount, &ctx->tcount, &ctx->vbase, &ctx->tbase,
                      &ctx->edgeMask, &ctx->edgePrefix, &ctx->mixedList, &ctx->mixedFlag, &ctx->mixedIdx, &ctx->counters, &ctx->statsAcc,
                      &ctx->pos, &ctx->nrm, &ctx->col, &ctx->tri, &ctx->mpuIjk, &ctx->mpuVbase, &ctx->mpuTbase, &ctx->vperm, &ctx->ptsIn, &ctx->ptsF,
-                     &ctx->ptsCol, &ctx->ptsNrm};
+                     &ctx->ptsCol, &ctx->ptsNrm, &ctx->shardCounts, &ctx->haloSend, &ctx->haloRecv};
+    if (ctx->comm) { psgpu::nccl_api().CommDestroy(ctx->comm); ctx->comm = nullptr; }
     for (DevBuf* b : all) b->release();
-    for (auto& e : ctx->ev) cudaEventDestroy(e);
+    for (auto& e : ctx->ev) if (e) cudaEventDestroy(e);
     if (ctx->hostScalars) cudaFreeHost(ctx->hostScalars);
     if (ctx->hostStage) cudaFreeHost(ctx->hostStage);
     if (ctx->hostMesh) cudaFreeHost(ctx->hostMesh);
@@ -160,6 +175,7 @@ extern "C" int psgpu_upload_program(psgpu_ctx* ctx, const psgpu_program* p) {
     if (cbytes) CK(cudaMemcpyAsync(ctx->colors.p, (char*)ctx->hostStage + bytes, cbytes, cudaMemcpyHostToDevice, ctx->stream));
     CK(cudaStreamSynchronize(ctx->stream));
     ctx->progQuads = (uint32_t)(p->words.size() / 4);
+    ctx->slab.valid = false;
     ctx->nPrims = p->nPrims;
     ctx->semantics = p->semantics;
     ctx->hasWarps = p->maxPointStack > 0;
@@ -188,6 +204,8 @@ int fill_grid(psgpu_ctx* ctx, const psgpu_params* P, GridParams& G) {
     G.insideGE = (ctx->semantics == PSGPU_SEM_SIMD) ? 1 : 0;
     G.wantColors = P->want_colors; G.wantNormals = P->want_normals;
     G.forceFv = 0;
+    G.zOwnLast = G.hi[2] - 1;
+    G.vertexOffset = 0u;
     G.iso = (P->iso > 0.f) ? P->iso : PS_ISO_VALUE;
     return PSGPU_SUCCESS;
 }
@@ -201,7 +219,7 @@ int run_cull(psgpu_ctx* ctx, const GridParams& G, int cullMode, bool colorExact,
     CullLevel L;
     for (int a = 0; a < 3; a++) { L.lo[a] = G.lo[a]; L.hi[a] = G.hi[a]; L.gridLo[a] = G.gridLo[a]; }
     L.mpuSide = G.mpuSide; L.cullMode = cullMode; L.iso = G.iso; L.childSize = 1; L.colorExact = colorExact ? 1 : 0;
-    poolUsed = ctx->progQuads;
+    poolUsed = ctx->rootOff + ctx->rootLen;  // [full program | slab program] stay; the levels are rebuilt behind them
     if (cullMode == PSGPU_CULL_NONE) {
         if (nMpu > (size_t)1 << 30) { ctx->err = "lattice too large"; return PSGPU_NOT_ENOUGH_MEM; }
         CK(ctx->regionsA.reserve(nMpu * sizeof(Region)));
@@ -218,7 +236,7 @@ int run_cull(psgpu_ctx* ctx, const GridParams& G, int cullMode, bool colorExact,
     if (maxDim > 64) sizes = {16, 4, 1};
     else if (maxDim > 4) sizes = {4, 1};
     else sizes = {1};
-    if (sizes.size() == 3 && ctx->progQuads <= 4096) {
+    if (sizes.size() == 3 && ctx->rootLen <= 4096) {
         // A short program does not pay for the 16^3 level: its walk is bound by the serial Pruner, about as long per region as the
         // 4^3 level's own (blob1k@512^3: cull 0.72 -> 0.64 ms without it; the 17.5k-quad blob10k needs it: 1.6 vs 5.6 ms). Only while
         // the 4^3 level still gets a warp per region (<= 256 top regions of 16^3 MPUs).
@@ -226,7 +244,7 @@ int run_cull(psgpu_ctx* ctx, const GridParams& G, int cullMode, bool colorExact,
         if ((long long)cdiv(nx + 15, 16) * cdiv(ny + 15, 16) * cdiv(nz + 15, 16) <= 256) sizes = {4, 1};
     }
     // a tiny program (a dozen primitives) is cheaper to test once per MPU than to refine level by level (small@128^3: 0.27 -> 0.23 ms)
-    if (ctx->progQuads <= 64) sizes = {1};
+    if (ctx->rootLen <= 64) sizes = {1};
     if (const char* ov = getenv("PSGPU_CULL_LEVELS")) {  // tuning / debugging aid: "16,4,1", "4,1" or "1" (each level 4x the next)
         std::vector<int> o;
         for (const char* c = ov; *c;) { o.push_back(atoi(c)); while (*c && *c != ',') c++; if (*c == ',') c++; }
@@ -240,7 +258,7 @@ int run_cull(psgpu_ctx* ctx, const GridParams& G, int cullMode, bool colorExact,
         const int ps = sizes[0] * 4;
         for (int x = G.lo[0] / ps; x * ps < G.hi[0]; x++)
             for (int y = G.lo[1] / ps; y * ps < G.hi[1]; y++)
-                for (int z = G.lo[2] / ps; z * ps < G.hi[2]; z++) top.push_back(Region{x, y, z, 0u, ctx->progQuads});
+                for (int z = G.lo[2] / ps; z * ps < G.hi[2]; z++) top.push_back(Region{x, y, z, ctx->rootOff, ctx->rootLen});
     }
     DevBuf* cur = &ctx->regionsA;
     DevBuf* nxt = &ctx->regionsB;
@@ -249,7 +267,7 @@ int run_cull(psgpu_ctx* ctx, const GridParams& G, int cullMode, bool colorExact,
     int nParents = (int)top.size();
     CK(ctx->scalars.reserve(64));
     maxLen = 0;
-    uint32_t parentMaxLen = ctx->progQuads;  // longest program among the current level's parents
+    uint32_t parentMaxLen = ctx->rootLen;  // longest program among the current level's parents
     for (size_t lv = 0; lv < sizes.size(); lv++) {
         L.childSize = sizes[lv];
         const bool last = (lv + 1 == sizes.size());
@@ -326,7 +344,115 @@ struct HostSink {
     int64_t capV, capT;
 };
 
-int polygonize_impl(psgpu_ctx* ctx, const psgpu_params* P, psgpu_mesh* out, bool forceFv, const HostSink* sink = nullptr) {
+#define NK(call)                                                                                                       \
+    do {                                                                                                               \
+        int _r = (call);                                                                                               \
+        if (_r != 0) { ctx->err = std::string(#call) + ": " + psgpu::nccl_api().GetErrorString(_r); return PSGPU_ERROR_CUDA; } \
+    } while (0)
+
+// The uploaded program pruned ONCE against the slab's box (support culling, colour markers as the levels leave them): with R
+// ranks every rank's hierarchy then walks ~1/R of the primitives instead of all of them at its top level (SCALE_r01: cull 0.64 ms
+// at N = 1 but 1.30 ms per rank at N = 8). A single-thread walk of the whole program - milliseconds for 10k primitives - so it is
+// a plan-time cost like the upload: cached behind the full program until the program or the slab changes, and only taken for
+// programs long enough to pay back (>= 2048 quads) on a slab that is a proper part of the lattice.
+int ensure_slab_program(psgpu_ctx* ctx, const GridParams& G, bool colorExact) {
+    ctx->rootOff = 0; ctx->rootLen = ctx->progQuads;
+    const bool partial = (G.hi[2] - G.lo[2]) < G.dims[2];
+    if (!partial || ctx->progQuads < 2048 || getenv("PSGPU_NO_SLAB_PROGRAM")) { ctx->slab.valid = false; return PSGPU_SUCCESS; }
+    psgpu_ctx::SlabProg& S = ctx->slab;
+    const bool hit = S.valid && S.zb == G.lo[2] && S.ze == G.hi[2] && S.side == G.mpuSide && S.nx == G.dims[0] && S.ny == G.dims[1] &&
+                     S.lo[0] == G.gridLo[0] && S.lo[1] == G.gridLo[1] && S.lo[2] == G.gridLo[2] && S.colorExact == (colorExact ? 1 : 0);
+    if (!hit) {
+        cudaStream_t st = ctx->stream;
+        float lo[3], hi[3];
+        for (int a = 0; a < 3; a++) {
+            const float pad = 1.0e-3f * G.mpuSide;  // child boxes are computed as gridLo + index * side: keep them inside
+            lo[a] = G.gridLo[a] + (float)G.lo[a] * G.mpuSide - pad;
+            hi[a] = G.gridLo[a] + (float)G.hi[a] * G.mpuSide + pad;
+        }
+        const uint32_t cap = ctx->progQuads;
+        CK(ctx->pool.reserve(((size_t)ctx->progQuads * 2 + 16) * 16, true, st));
+        CK(ctx->qflag.reserve((size_t)ctx->progQuads * 2 + 16, true, st));
+        CK(ctx->scalars.reserve(64));
+        launch_prune_slab(ctx->pool.as<float4>(), lo, hi, PS_ISO_VALUE, colorExact ? 1 : 0, ctx->pool.as<float4>() + ctx->progQuads,
+                          ctx->qflag.as<uint8_t>() + ctx->progQuads, cap, ctx->scalars.as<uint32_t>() + 12, st);
+        CK(cudaMemcpyAsync(&ctx->hostScalars[12], ctx->scalars.as<uint32_t>() + 12, 4, cudaMemcpyDeviceToHost, st));
+        CK(cudaStreamSynchronize(st));
+        CK(cudaGetLastError());
+        S.valid = true; S.zb = G.lo[2]; S.ze = G.hi[2]; S.side = G.mpuSide; S.nx = G.dims[0]; S.ny = G.dims[1];
+        for (int a = 0; a < 3; a++) S.lo[a] = G.gridLo[a];
+        S.colorExact = colorExact ? 1 : 0;
+        S.len = ctx->hostScalars[12];
+        if (S.len > cap) { ctx->err = "slab program longer than the program"; S.valid = false; return PSGPU_ERROR_CUDA; }
+    }
+    ctx->rootOff = ctx->progQuads; ctx->rootLen = S.len;  // len 0: nothing of the program reaches this slab
+    return PSGPU_SUCCESS;
+}
+
+// stitching state of one sharded polygonize (psgpu_polygonize_sharded)
+struct ShardCtl {
+    bool stitch;
+    psgpu_shard* info;
+};
+
+// Count exchange + halo exchange of a stitched z-slab run, on the context's stream between the scans and the emission kernels:
+//   1. ncclAllGather of {vertices, triangles} (16 bytes per rank) -> every rank's global vertex / triangle offset;
+//   2. every rank but the first sends the table of its FIRST MPU layer (global vertex base + crossing-edge mask / prefix per MPU)
+//      to the rank below, which resolves the edges of its closing z-plane through it (tri_kernel) - the lower-z rank does not emit
+//      those vertices, so the ranks' meshes concatenate to the single-GPU mesh (same vertex count, same triangle soup).
+int shard_exchange(psgpu_ctx* ctx, GridParams& G, uint32_t nV, uint32_t nT, const FieldOutputs* fo, MeshOutputs& mo, psgpu_shard* info) {
+    psgpu::NcclApi& N = psgpu::nccl_api();
+    cudaStream_t st = ctx->stream;
+    const int R = ctx->nranks, me = ctx->rank;
+    CK(cudaEventRecord(ctx->ev[8], st));
+    CK(ctx->shardCounts.reserve((size_t)(2 + 2 * R) * 8));
+    uint64_t* hsend = reinterpret_cast<uint64_t*>(&ctx->hostScalars[16]);
+    hsend[0] = nV; hsend[1] = nT;
+    uint64_t* dsend = ctx->shardCounts.as<uint64_t>();
+    uint64_t* drecv = dsend + 2;
+    CK(cudaMemcpyAsync(dsend, hsend, 16, cudaMemcpyHostToDevice, st));
+    NK(N.AllGather(dsend, drecv, 2, psgpu::NcclApi::kUint64, ctx->comm, st));
+    ctx->rankCounts.assign((size_t)2 * R, 0);
+    CK(cudaMemcpyAsync(ctx->rankCounts.data(), drecv, (size_t)2 * R * 8, cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
+    uint64_t vOff = 0, tOff = 0, vTot = 0, tTot = 0;
+    for (int r = 0; r < R; r++) {
+        if (r < me) { vOff += ctx->rankCounts[2 * r]; tOff += ctx->rankCounts[2 * r + 1]; }
+        vTot += ctx->rankCounts[2 * r]; tTot += ctx->rankCounts[2 * r + 1];
+    }
+    if (vTot >= ((uint64_t)1 << 32)) { ctx->err = "stitched mesh exceeds 2^32 vertices"; return PSGPU_NOT_ENOUGH_MEM; }
+    G.vertexOffset = (uint32_t)vOff;
+    const int nx = G.hi[0] - G.lo[0], ny = G.hi[1] - G.lo[1];
+    const size_t nxy = (size_t)nx * ny;
+    const size_t bytes = nxy * (4 + 192 + 96);
+    auto carve = [&](DevBuf& b, uint32_t*& vb, uint32_t*& mk, uint16_t*& pf) {
+        vb = b.as<uint32_t>(); mk = vb + nxy; pf = reinterpret_cast<uint16_t*>(mk + nxy * 48);
+    };
+    uint32_t *sv = nullptr, *sm = nullptr, *rv = nullptr, *rm = nullptr;
+    uint16_t *sp = nullptr, *rp = nullptr;
+    if (me > 0) {
+        CK(ctx->haloSend.reserve(bytes));
+        carve(ctx->haloSend, sv, sm, sp);
+        if (fo) launch_halo_build(G, ctx->candOfMpu.as<int32_t>(), *fo, ctx->vbase.as<uint32_t>(), sv, sm, sp, (int)nxy, st);
+        else CK(cudaMemsetAsync(sv, 0xFF, nxy * 4, st));  // no candidates in this slab: no surface anywhere in the layer
+    }
+    if (me < R - 1) { CK(ctx->haloRecv.reserve(bytes)); carve(ctx->haloRecv, rv, rm, rp); }
+    NK(N.GroupStart());
+    if (me > 0) NK(N.Send(sv, bytes, psgpu::NcclApi::kUint8, me - 1, ctx->comm, st));
+    if (me < R - 1) NK(N.Recv(rv, bytes, psgpu::NcclApi::kUint8, me + 1, ctx->comm, st));
+    NK(N.GroupEnd());
+    mo.haloVbase = rv; mo.haloMask = rm; mo.haloPrefix = rp;
+    CK(cudaEventRecord(ctx->ev[9], st));
+    if (info) {
+        info->nranks = R; info->rank = me; info->z_begin = G.lo[2]; info->z_end = G.hi[2];
+        info->vertex_offset = (int64_t)vOff; info->triangle_offset = (int64_t)tOff;
+        info->total_vertices = (int64_t)vTot; info->total_triangles = (int64_t)tTot;
+        info->stitched = 1;
+    }
+    return PSGPU_SUCCESS;
+}
+
+int polygonize_impl(psgpu_ctx* ctx, const psgpu_params* P, psgpu_mesh* out, bool forceFv, const HostSink* sink = nullptr, ShardCtl* shard = nullptr) {
     if (!ctx || !P || ctx->progQuads == 0) return PSGPU_PARAM_ERROR;
     CK(cudaSetDevice(ctx->device));
     cudaStream_t st = ctx->stream;
@@ -334,6 +460,11 @@ int polygonize_impl(psgpu_ctx* ctx, const psgpu_params* P, psgpu_mesh* out, bool
     int rc = fill_grid(ctx, P, G);
     if (rc != PSGPU_SUCCESS) { ctx->err = "bad grid parameters"; return rc; }
     G.forceFv = forceFv ? 1 : 0;
+    const bool stitch = shard && shard->stitch && ctx->nranks > 1;
+    if (stitch) {
+        if (P->output != PSGPU_OUT_INDEXED) { ctx->err = "sharded stitching needs PSGPU_OUT_INDEXED"; return PSGPU_PARAM_ERROR; }
+        G.zOwnLast = G.dims[2] - 1;  // only the lattice's last layer owns a closing z-plane
+    }
     if (P->output == PSGPU_OUT_INDEXED && P->coord_mode != PSGPU_COORD_GLOBAL) {
         ctx->err = "PSGPU_OUT_INDEXED needs PSGPU_COORD_GLOBAL (shared corners must be bit-identical across MPUs)";
         return PSGPU_PARAM_ERROR;
@@ -343,14 +474,20 @@ int polygonize_impl(psgpu_ctx* ctx, const psgpu_params* P, psgpu_mesh* out, bool
     S = psgpu_stats{};
     S.mpus_total = (int64_t)(G.hi[0] - G.lo[0]) * (G.hi[1] - G.lo[1]) * (G.hi[2] - G.lo[2]);
     S.program_quads = ctx->progQuads;
+    const bool colorExact = ctx->semantics == PSGPU_SEM_SIMD && P->want_colors;
+    rc = ensure_slab_program(ctx, G, colorExact);
+    if (rc != PSGPU_SUCCESS) return rc;
     CK(cudaEventRecord(ctx->ev[0], st));
     uint32_t maxLen = 0, poolUsed = 0;
-    rc = run_cull(ctx, G, P->cull, ctx->semantics == PSGPU_SEM_SIMD && P->want_colors, maxLen, poolUsed, launches);
-    if (rc != PSGPU_SUCCESS) return rc;
+    if (ctx->rootLen == 0) { ctx->nCand = 0; poolUsed = ctx->rootOff; }
+    else {
+        rc = run_cull(ctx, G, P->cull, colorExact, maxLen, poolUsed, launches);
+        if (rc != PSGPU_SUCCESS) return rc;
+    }
     CK(cudaEventRecord(ctx->ev[1], st));
     const int nCand = ctx->nCand;
     S.mpus_evaluated = nCand;
-    S.pruned_quads = (int64_t)poolUsed - ctx->progQuads;
+    S.pruned_quads = (int64_t)poolUsed - (ctx->rootOff + ctx->rootLen);
 
     psgpu_mesh M{};
     for (int a = 0; a < 3; a++) M.lattice[a] = G.dims[a];
@@ -403,6 +540,11 @@ int polygonize_impl(psgpu_ctx* ctx, const psgpu_params* P, psgpu_mesh* out, bool
             CK(cudaMemcpyAsync(ctx->mpuVbase.as<uint32_t>() + nMixed, ctx->vbase.as<uint32_t>() + nCand, 4, cudaMemcpyDeviceToDevice, st));
             CK(cudaMemcpyAsync(ctx->mpuTbase.as<uint32_t>() + nMixed, ctx->tbase.as<uint32_t>() + nCand, 4, cudaMemcpyDeviceToDevice, st));
         }
+        if (stitch) {
+            rc = shard_exchange(ctx, G, nV, nT, &fo, mo, shard->info);
+            if (rc != PSGPU_SUCCESS) return rc;
+            launches++;
+        }
         if (sink && ((int64_t)nV > sink->capV || (int64_t)nT > sink->capT)) {
             ctx->err = "host buffers too small";
             M.n_vertices = nV; M.n_triangles = nT;
@@ -440,7 +582,13 @@ int polygonize_impl(psgpu_ctx* ctx, const psgpu_params* P, psgpu_mesh* out, bool
             S.algorithmic_flops = (int64_t)acc[0]; S.prim_evals = (int64_t)acc[1]; S.vertex_eval_flops = (int64_t)acc[4];
         }
     } else {
-        CK(cudaEventRecord(ctx->ev[2], st)); CK(cudaEventRecord(ctx->ev[3], st)); CK(cudaEventRecord(ctx->ev[4], st));
+        CK(cudaEventRecord(ctx->ev[2], st));
+        if (stitch) {  // an empty slab still takes part in the collectives
+            MeshOutputs mo{};
+            rc = shard_exchange(ctx, G, 0u, 0u, nullptr, mo, shard->info);
+            if (rc != PSGPU_SUCCESS) return rc;
+        }
+        CK(cudaEventRecord(ctx->ev[3], st)); CK(cudaEventRecord(ctx->ev[4], st));
     }
     CK(cudaStreamSynchronize(st));
     if (streamed) CK(cudaStreamSynchronize(ctx->copyStream));
@@ -457,6 +605,17 @@ int polygonize_impl(psgpu_ctx* ctx, const psgpu_params* P, psgpu_mesh* out, bool
         cudaEventElapsedTime(&S.ms_tri, ctx->ev[3], ctx->ev[5]);
         cudaEventElapsedTime(&S.ms_vertex, ctx->ev[5], ctx->ev[6]);
         cudaEventElapsedTime(&S.ms_color, ctx->ev[6], ctx->ev[4]);
+    }
+    if (stitch) cudaEventElapsedTime(&S.ms_exchange, ctx->ev[8], ctx->ev[9]);
+    if (shard && shard->info) shard->info->ms_exchange = S.ms_exchange;
+    if (nMixed > 0 && P->output == PSGPU_OUT_INDEXED) {
+        // edges whose owner did not report the crossing (tri_kernel): never expected, never silent
+        CK(cudaMemcpy(&ctx->hostScalars[13], ctx->counters.as<uint32_t>() + 6, 4, cudaMemcpyDeviceToHost));
+        S.unresolved_edges = ctx->hostScalars[13];
+        if (S.unresolved_edges) {
+            ctx->err = "indexed mesh: " + std::to_string(S.unresolved_edges) + " shared edges were not found in their owner's crossing mask";
+            return PSGPU_ERROR_CUDA;
+        }
     }
     S.mpus_crossed = nMixed;
     const int evalsPerVertex = (P->root_mode == PSGPU_ROOT_FOURSAMPLE) ? 8 : 14;
@@ -480,6 +639,128 @@ int polygonize_impl(psgpu_ctx* ctx, const psgpu_params* P, psgpu_mesh* out, bool
 }  // namespace
 
 extern "C" int psgpu_polygonize(psgpu_ctx* ctx, const psgpu_params* params, psgpu_mesh* out) { return polygonize_impl(ctx, params, out, false); }
+
+// ---- multi-GPU: one context per rank, NCCL over NVLink --------------------------------------------------------------------------
+extern "C" int psgpu_comm_get_unique_id(void* id128) {
+    if (!id128) return PSGPU_PARAM_ERROR;
+    psgpu::NcclApi& N = psgpu::nccl_api();
+    if (!N.load()) return PSGPU_ERROR_NO_DEVICE;
+    psgpu::NcclApi::unique_id id;
+    if (N.GetUniqueId(&id) != 0) return PSGPU_ERROR_CUDA;
+    memcpy(id128, &id, sizeof(id));
+    return PSGPU_SUCCESS;
+}
+
+extern "C" int psgpu_comm_init(psgpu_ctx* ctx, int nranks, int rank, const void* id128) {
+    if (!ctx || !id128 || nranks < 1 || rank < 0 || rank >= nranks) return PSGPU_PARAM_ERROR;
+    psgpu::NcclApi& N = psgpu::nccl_api();
+    if (!N.load()) { ctx->err = "libnccl.so.2 not found"; return PSGPU_ERROR_NO_DEVICE; }
+    CK(cudaSetDevice(ctx->device));
+    if (ctx->comm) { N.CommDestroy(ctx->comm); ctx->comm = nullptr; }
+    psgpu::NcclApi::unique_id id;
+    memcpy(&id, id128, sizeof(id));
+    NK(N.CommInitRank(&ctx->comm, nranks, id, rank));
+    ctx->nranks = nranks; ctx->rank = rank;
+    return PSGPU_SUCCESS;
+}
+
+extern "C" int psgpu_comm_destroy(psgpu_ctx* ctx) {
+    if (!ctx) return PSGPU_PARAM_ERROR;
+    if (ctx->comm) { psgpu::nccl_api().CommDestroy(ctx->comm); ctx->comm = nullptr; }
+    ctx->nranks = 1; ctx->rank = 0;
+    return PSGPU_SUCCESS;
+}
+
+// [begin, end) MPU layers of `rank`: equal slabs, or - with one weight per layer - the cut points that balance the weight prefix
+// sum (parsip_b200/sharding.py: slab_bounds is the same rule; computed identically on every rank, no communication)
+extern "C" int psgpu_slab_bounds(int n_layers, int nranks, int rank, const float* layer_weights, int32_t* z_begin, int32_t* z_end) {
+    if (n_layers < 0 || nranks <= 0 || rank < 0 || rank >= nranks || !z_begin || !z_end) return PSGPU_PARAM_ERROR;
+    double total = 0.0;
+    if (layer_weights) for (int i = 0; i < n_layers; i++) total += layer_weights[i];
+    if (!layer_weights || !(total > 0.0)) {
+        const int base = n_layers / nranks, extra = n_layers % nranks;
+        *z_begin = rank * base + std::min(rank, extra);
+        *z_end = *z_begin + base + (rank < extra ? 1 : 0);
+        return PSGPU_SUCCESS;
+    }
+    std::vector<int> cuts(1, 0);
+    double acc = 0.0;
+    int layer = 0;
+    for (int r = 1; r < nranks; r++) {
+        const double target = total * r / nranks;
+        while (layer < n_layers && acc + 0.5 * layer_weights[layer] < target) { acc += layer_weights[layer]; layer++; }
+        cuts.push_back(layer);
+    }
+    cuts.push_back(n_layers);
+    *z_begin = cuts[rank]; *z_end = cuts[rank + 1];
+    return PSGPU_SUCCESS;
+}
+
+extern "C" int psgpu_polygonize_sharded(psgpu_ctx* ctx, const psgpu_params* params, psgpu_mesh* out, psgpu_shard* shard) {
+    if (!ctx || !params) return PSGPU_PARAM_ERROR;
+    if (shard) *shard = psgpu_shard{};
+    psgpu_params P = *params;
+    if (ctx->nranks > 1 && !ctx->comm) { ctx->err = "psgpu_comm_init first"; return PSGPU_PARAM_ERROR; }
+    if (P.z_end <= 0) {  // no explicit slab: equal shares of the MPU layers
+        int32_t nm[3];
+        psgpu_lattice_dims(P.cellsize, P.bbox_lo, P.bbox_hi, nm);
+        if (nm[2] < ctx->nranks) { ctx->err = "fewer MPU layers than ranks"; return PSGPU_PARAM_ERROR; }
+        psgpu_slab_bounds(nm[2], ctx->nranks, ctx->rank, nullptr, &P.z_begin, &P.z_end);
+    }
+    if (P.z_end <= P.z_begin) { ctx->err = "empty slab"; return PSGPU_PARAM_ERROR; }
+    ShardCtl sc{true, shard};
+    const int rc = polygonize_impl(ctx, &P, out, false, nullptr, &sc);
+    if (shard && ctx->nranks <= 1 && rc == PSGPU_SUCCESS) {
+        shard->nranks = 1; shard->rank = 0; shard->z_begin = P.z_begin; shard->z_end = P.z_end;
+        shard->total_vertices = ctx->last.n_vertices; shard->total_triangles = ctx->last.n_triangles;
+    }
+    return rc;
+}
+
+// Assembles the stitched mesh on `root`: DEVICE buffers of total_vertices * 3 floats (pos, nrm, col; NULL skips one) and
+// total_triangles * 3 indices, written at every rank's offset; other ranks pass NULL. Grouped ncclSend / ncclRecv over NVLink.
+extern "C" int psgpu_mesh_gather(psgpu_ctx* ctx, int root, float* pos, float* nrm, float* col, uint32_t* tri) {
+    if (!ctx || root < 0 || root >= ctx->nranks) return PSGPU_PARAM_ERROR;
+    if ((int)ctx->rankCounts.size() != 2 * ctx->nranks) { ctx->err = "psgpu_polygonize_sharded first"; return PSGPU_PARAM_ERROR; }
+    CK(cudaSetDevice(ctx->device));
+    cudaStream_t st = ctx->stream;
+    psgpu::NcclApi& N = psgpu::nccl_api();
+    const int R = ctx->nranks, me = ctx->rank;
+    const psgpu_mesh& M = ctx->last;
+    if (R == 1 || me == root) {
+        uint64_t vo = 0, to = 0;
+        if (R > 1) NK(N.GroupStart());
+        for (int r = 0; r < R; r++) {
+            const uint64_t nv = ctx->rankCounts.empty() ? (uint64_t)M.n_vertices : ctx->rankCounts[2 * r];
+            const uint64_t nt = ctx->rankCounts.empty() ? (uint64_t)M.n_triangles : ctx->rankCounts[2 * r + 1];
+            if (r == me) {
+                if (pos && nv) CK(cudaMemcpyAsync(pos + 3 * vo, M.pos, nv * 12, cudaMemcpyDeviceToDevice, st));
+                if (nrm && nv) CK(cudaMemcpyAsync(nrm + 3 * vo, M.nrm, nv * 12, cudaMemcpyDeviceToDevice, st));
+                if (col && nv) CK(cudaMemcpyAsync(col + 3 * vo, M.col, nv * 12, cudaMemcpyDeviceToDevice, st));
+                if (tri && nt) CK(cudaMemcpyAsync(tri + 3 * to, M.tri, nt * 12, cudaMemcpyDeviceToDevice, st));
+            } else {
+                if (pos && nv) NK(N.Recv(pos + 3 * vo, nv * 3, psgpu::NcclApi::kFloat32, r, ctx->comm, st));
+                if (nrm && nv) NK(N.Recv(nrm + 3 * vo, nv * 3, psgpu::NcclApi::kFloat32, r, ctx->comm, st));
+                if (col && nv) NK(N.Recv(col + 3 * vo, nv * 3, psgpu::NcclApi::kFloat32, r, ctx->comm, st));
+                if (tri && nt) NK(N.Recv(tri + 3 * to, nt * 3, psgpu::NcclApi::kUint32, r, ctx->comm, st));
+            }
+            vo += nv; to += nt;
+        }
+        if (R > 1) NK(N.GroupEnd());
+    } else {
+        // which arrays the root wants is part of the call contract: every rank passes the same NULL pattern through `pos/nrm/col/tri`
+        // being non-NULL on the root; the senders mirror it with the flags below (non-NULL = send)
+        const uint64_t nv = (uint64_t)M.n_vertices, nt = (uint64_t)M.n_triangles;
+        NK(N.GroupStart());
+        if (pos && nv) NK(N.Send(M.pos, nv * 3, psgpu::NcclApi::kFloat32, root, ctx->comm, st));
+        if (nrm && nv) NK(N.Send(M.nrm, nv * 3, psgpu::NcclApi::kFloat32, root, ctx->comm, st));
+        if (col && nv) NK(N.Send(M.col, nv * 3, psgpu::NcclApi::kFloat32, root, ctx->comm, st));
+        if (tri && nt) NK(N.Send(M.tri, nt * 3, psgpu::NcclApi::kUint32, root, ctx->comm, st));
+        NK(N.GroupEnd());
+    }
+    CK(cudaStreamSynchronize(st));
+    return PSGPU_SUCCESS;
+}
 
 extern "C" int psgpu_mesh_download(psgpu_ctx* ctx, float* pos, float* nrm, float* col, uint32_t* tri, int32_t* mpu_ijk, uint32_t* mpu_vbase,
                                    uint32_t* mpu_tbase) {

@@ -334,16 +334,37 @@ __global__ void __launch_bounds__(kThreads) tri_kernel(GridParams G, const Regio
                 else {
                     const int dI = (sx == 7 && ax != 0 && r.x != G.hi[0] - 1) ? 1 : 0;
                     const int dJ = (sy == 7 && ax != 1 && r.y != G.hi[1] - 1) ? 1 : 0;
-                    const int dK = (sz == 7 && ax != 2 && r.z != G.hi[2] - 1) ? 1 : 0;
+                    const int dK = (sz == 7 && ax != 2 && r.z != G.zOwnLast) ? 1 : 0;
                     if ((dI | dJ | dK) == 0) {
                         const int eb = (sx * 8 + sy * 64 + sz) * 3 + ax;
-                        vid = vbase + S.edgeP[eb >> 5] + __popc(S.edgeW[eb >> 5] & ((1u << (eb & 31)) - 1u));
+                        vid = G.vertexOffset + vbase + S.edgeP[eb >> 5] + __popc(S.edgeW[eb >> 5] & ((1u << (eb & 31)) - 1u));
                     } else {
                         sx -= 7 * dI; sy -= 7 * dJ; sz -= 7 * dK;
-                        const int32_t nc = candOfMpu[((size_t)(r.x + dI - G.lo[0]) * ny + (r.y + dJ - G.lo[1])) * nz + (r.z + dK - G.lo[2])];
                         const int eb = (sx * 8 + sy * 64 + sz) * 3 + ax;
-                        const uint32_t w = fo.edgeMask[(size_t)nc * 48 + (eb >> 5)];
-                        vid = mo.vbase[nc] + fo.edgePrefix[(size_t)nc * 48 + (eb >> 5)] + __popc(w & ((1u << (eb & 31)) - 1u));
+                        const uint32_t bit = 1u << (eb & 31);
+                        vid = 0u;
+                        bool found = false;
+                        if (r.z + dK >= G.hi[2]) {
+                            // the owner lives in the slab of the rank above: its first-layer table came over NVLink (context.cu)
+                            const size_t h = (size_t)(r.x + dI - G.lo[0]) * ny + (r.y + dJ - G.lo[1]);
+                            const uint32_t hb = mo.haloVbase ? mo.haloVbase[h] : 0xFFFFFFFFu;
+                            if (hb != 0xFFFFFFFFu) {
+                                const uint32_t w = mo.haloMask[h * 48 + (eb >> 5)];
+                                found = (w & bit) != 0u;
+                                vid = hb + mo.haloPrefix[h * 48 + (eb >> 5)] + __popc(w & (bit - 1u));
+                            }
+                        } else {
+                            const int32_t nc = candOfMpu[((size_t)(r.x + dI - G.lo[0]) * ny + (r.y + dJ - G.lo[1])) * nz + (r.z + dK - G.lo[2])];
+                            if (nc >= 0 && fo.tcount[nc] != 0u) {  // a culled / surface-free neighbour has no (or stale) masks
+                                const uint32_t w = fo.edgeMask[(size_t)nc * 48 + (eb >> 5)];
+                                found = (w & bit) != 0u;
+                                vid = G.vertexOffset + mo.vbase[nc] + fo.edgePrefix[(size_t)nc * 48 + (eb >> 5)] + __popc(w & (bit - 1u));
+                            }
+                        }
+                        // The owner must have seen the same crossing: shared corners are evaluated from the same lattice
+                        // coordinates by programs that differ only in operands that are exactly zero there. If it ever did
+                        // not, count it (psgpu_polygonize fails with the count) and keep the index in range.
+                        if (!found) { atomicAdd(&fo.counters[6], 1u); vid = G.vertexOffset; }
                     }
                 }
                 vid3[k] = vid;
@@ -477,6 +498,28 @@ __global__ void __launch_bounds__(kThreads) color_kernel(GridParams G, const Reg
 }
 
 }  // namespace
+
+// first-layer table this rank sends to the rank below (see tri_kernel): per (x, y) the GLOBAL vertex base of the MPU at the slab's
+// first z-layer and its crossing-edge mask / prefix, or 0xFFFFFFFF where that MPU has no surface
+__global__ void halo_build_kernel(GridParams G, const int32_t* __restrict__ candOfMpu, FieldOutputs fo, const uint32_t* __restrict__ vbase,
+                                  uint32_t* __restrict__ hVbase, uint32_t* __restrict__ hMask, uint16_t* __restrict__ hPrefix, int nxy) {
+    const int h = blockIdx.x * (blockDim.x / 32) + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+    if (h >= nxy) return;
+    const int nz = G.hi[2] - G.lo[2];
+    const int32_t c = candOfMpu[(size_t)h * nz];
+    const bool ok = c >= 0 && fo.tcount[c] != 0u;
+    if (lane == 0) hVbase[h] = ok ? G.vertexOffset + vbase[c] : 0xFFFFFFFFu;
+    for (int w = lane; w < 48; w += 32) {
+        hMask[(size_t)h * 48 + w] = ok ? fo.edgeMask[(size_t)c * 48 + w] : 0u;
+        hPrefix[(size_t)h * 48 + w] = ok ? fo.edgePrefix[(size_t)c * 48 + w] : (uint16_t)0;
+    }
+}
+
+void launch_halo_build(const GridParams& G, const int32_t* candOfMpu, const FieldOutputs& fo, const uint32_t* vbase, uint32_t* hVbase,
+                       uint32_t* hMask, uint16_t* hPrefix, int nxy, cudaStream_t st) {
+    if (nxy <= 0) return;
+    halo_build_kernel<<<(nxy + 3) / 4, 128, 0, st>>>(G, candOfMpu, fo, vbase, hVbase, hMask, hPrefix, nxy);
+}
 
 void launch_emit_kernels(const GridParams& G, const Region* cands, const float4* pool, const float* colorTab, const FieldOutputs& fo,
                          const MeshOutputs& mo, const int32_t* candOfMpu, int nMixed, uint32_t maxProgQuads, int numSMs, cudaStream_t st,

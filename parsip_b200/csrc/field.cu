@@ -146,7 +146,7 @@ __global__ void __launch_bounds__(512 / kPts, kPts == 4 ? 6 : (STRICT ? PSGPU_ST
             }
             if (mixed) {
                 // ---- crossing edges this MPU owns: per corner the x, y, z edge leaving it; bit 3*(8t + n) + axis of the edge mask
-                const bool lastX = (r.x == G.hi[0] - 1), lastY = (r.y == G.hi[1] - 1), lastZ = (r.z == G.hi[2] - 1);
+                const bool lastX = (r.x == G.hi[0] - 1), lastY = (r.y == G.hi[1] - 1), lastZ = (r.z == G.zOwnLast);
                 const bool perMpu = (G.output == PSGPU_OUT_MPU);
                 const bool ownX = perMpu || ci < 7 || lastX, ownY = perMpu || cj < 7 || lastY;
                 const uint32_t zmask = (perMpu || lastZ) ? 0xffu : 0x7fu;  // edges starting at ck = 7 belong to the next MPU in z
@@ -176,7 +176,7 @@ __global__ void __launch_bounds__(512 / kPts, kPts == 4 ? 6 : (STRICT ? PSGPU_ST
             atomicOr(&S.insideW[(kPts * t) >> 5], inb << ((kPts * t) & 31));
             __syncthreads();
             // ---- crossing edges this MPU owns: 3 bits per corner (x, y, z edge leaving it)
-            const bool lastX = (r.x == G.hi[0] - 1), lastY = (r.y == G.hi[1] - 1), lastZ = (r.z == G.hi[2] - 1);
+            const bool lastX = (r.x == G.hi[0] - 1), lastY = (r.y == G.hi[1] - 1), lastZ = (r.z == G.zOwnLast);
             const bool perMpu = (G.output == PSGPU_OUT_MPU);
             const bool ownX = perMpu || ci < 7 || lastX, ownY = perMpu || cj < 7 || lastY;
             uint32_t ebits = 0;

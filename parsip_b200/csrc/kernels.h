@@ -37,6 +37,11 @@ struct GridParams {
     int forceFv;         // parity hook: write the field cache of every candidate
     int hasWarps;        // the uploaded program contains warp instructions (picks the kernels compiled with them)
     float iso;
+    // z-slab stitching (psgpu_polygonize_sharded): the MPU layer whose closing z-plane this slab owns - its own last layer for a
+    // stand-alone slab, the lattice's last layer when the slabs of several ranks form ONE mesh (then only the last rank owns a
+    // closing plane and the others resolve those edges through the halo table of the rank above)
+    int zOwnLast;
+    uint32_t vertexOffset;  // added to every vertex id this rank writes into tri[] (global numbering across ranks)
 };
 
 // per-candidate outputs of the field kernel
@@ -57,6 +62,10 @@ struct MeshOutputs {
     const uint32_t* mixedIdx;  // [cand] rank among mixed candidates (PSGPU_OUT_MPU tables), may be null
     int32_t* mpuIjk; uint32_t* mpuVbase; uint32_t* mpuTbase;
     uint16_t* vperm;           // PSGPU_OUT_MPU: [vertex base + edge rank] -> reference-order local vertex id
+    // halo of the rank above (first MPU layer of its slab), indexed x * ny + y; null when this slab owns its closing plane
+    const uint32_t* haloVbase;   // GLOBAL vertex base of the MPU, 0xFFFFFFFF = no surface there
+    const uint32_t* haloMask;    // [.][48]
+    const uint16_t* haloPrefix;  // [.][48]
 };
 
 // cull.cu
@@ -73,6 +82,8 @@ void launch_prune_fused(const CullLevel& L, const Region* parents, int nParents,
 void launch_prune_compact(const CullLevel& L, const Region* parents, int nParents, const float4* scratch, const uint8_t* scratchFlag, uint32_t stride,
                           const uint32_t* childLen, const uint32_t* childOff, const uint32_t* childIdx, float4* outPool, uint8_t* outFlag,
                           uint32_t outBase, Region* children, int32_t* candOfMpu, cudaStream_t st);
+void launch_prune_slab(const float4* prog, const float* lo, const float* hi, float iso, int colorExact, float4* out, uint8_t* outFlag,
+                       uint32_t cap, uint32_t* lenOut, cudaStream_t st);
 void launch_prune_one(const float4* prog, const float* lo, const float* hi, int cullMode, float iso, int colorExact, float4* out, uint32_t cap,
                       uint32_t* lenOut, cudaStream_t st);
 size_t scan_temp_bytes(int n);
@@ -89,6 +100,8 @@ void launch_program_stats(const Region* cands, int nCand, const float4* pool, co
 float run_fp32_peak(int numSMs, cudaStream_t st, float* ms_out);
 
 // emit.cu
+void launch_halo_build(const GridParams& G, const int32_t* candOfMpu, const FieldOutputs& fo, const uint32_t* vbase, uint32_t* hVbase,
+                       uint32_t* hMask, uint16_t* hPrefix, int nxy, cudaStream_t st);
 void launch_emit_kernels(const GridParams& G, const Region* cands, const float4* pool, const float* colorTab, const FieldOutputs& fo,
                          const MeshOutputs& mo, const int32_t* candOfMpu, int nMixed, uint32_t maxProgQuads, int numSMs, cudaStream_t st,
                          cudaEvent_t evTriDone = nullptr, cudaEvent_t evVertexDone = nullptr);
