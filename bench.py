@@ -7,13 +7,14 @@
 A "step" is one full polygonization of the workload scene. Metric (BASELINE.json): MC cells/s = grid cells of
 the job / device time of the step (field evals/s, triangles/s and ms per polygonization ride along).
 
-  N = 1     BASELINE configs[1]: synthetic 1k point/line/cylinder blob scene at 512^3 cells
-  N = 8     BASELINE configs[3]: 10k-primitive blob scene at 1024^3, MPU lattice sharded in z-slabs
-  N = 2, 4  the same family in between (1250*N primitives, extent 13*N^(1/3), 512*N^(1/3) cells): weak scaling
+  N = 1        BASELINE configs[1]: synthetic 1k point/line/cylinder blob scene at 512^3 cells (the config the metric is quoted on)
+  N = 2, 4, 8  BASELINE configs[3]: 10k-primitive blob scene at 1024^3, MPU lattice sharded in z-slabs ("sharded over 2/4/8 B200"):
+               the SAME job on more GPUs; `strong_scaling` in the line relates it to the same job timed on one GPU in the same run
 
-GPU arm: the scene is linearized on the host, uploaded once, and every step runs psgpu_polygonize (device
-time from CUDA events on the library's own stream, `value`) - then, for `e2e`, re-linearize-free upload of the
-program from pinned host memory + psgpu_polygonize_host into pinned host buffers, timed by wall clock.
+GPU arm: the scene is linearized on the host, uploaded once, and every step runs psgpu_polygonize_sharded (at N = 1 that is
+psgpu_polygonize): cull -> field -> scans -> [count all-gather + boundary halo exchange over NCCL] -> emit, all on the library's
+stream between its own CUDA events - the SAME clock at every N, max over ranks (`value`). Then, for `e2e`, upload of the
+program from pinned host memory + polygonize + the rank's mesh share into pinned host buffers, timed by wall clock.
 Both arms run the SAME semantics (PS_SimdPoly: infinite lines, inside = f >= iso, 4-sample + lerp roots), so
 the meshes are comparable; `native` adds the numbers of the canonical mode (segments, bracketed root search).
 
@@ -41,11 +42,7 @@ sys.path.insert(0, ROOT)
 def workload(n_gpus: int) -> dict:
     if n_gpus <= 1:
         return dict(name="blob1k@512^3 (BASELINE configs[1])", prims=1000, extent=12.0, seed=2, cells=512)
-    if n_gpus == 8:
-        return dict(name="blob10k@1024^3 z-slab sharded (BASELINE configs[3])", prims=10000, extent=26.0, seed=4, cells=1024)
-    s = n_gpus ** (1.0 / 3.0)
-    return dict(name="blob%dk@%d^3 z-slab sharded (between configs[1] and configs[3])" % (1250 * n_gpus // 1000, round(512 * s)),
-                prims=1250 * n_gpus, extent=13.0 * s, seed=4, cells=int(round(512 * s)))
+    return dict(name="blob10k@1024^3 z-slab sharded (BASELINE configs[3])", prims=10000, extent=26.0, seed=4, cells=1024)
 
 
 def build_scene(w):
@@ -124,21 +121,43 @@ def cpu_polygonizer(root, bt, n_prims):
     return "port", sc, (lambda cs, b, e: sc.polygonize(cs, 0, b, e, keep_mesh=False)[1])
 
 
+def sample_blocks(dims, n_mpus_target, n_layers=6):
+    """A bounded, spread-out sample of the MPU lattice: up to n_layers z-layers at evenly spaced heights (not the dense middle only),
+    each restricted to a centred x-range so that the blocks hold about n_mpus_target MPUs together. Returns [(b, e)] index boxes."""
+    nx, ny, nz = dims
+    n_layers = max(1, min(n_layers, nz))
+    per_layer = max(1.0, n_mpus_target / n_layers)
+    wx = int(max(1, min(nx, round(per_layer / ny))))
+    x0 = (nx - wx) // 2
+    zs = sorted({int(round((i + 0.5) * nz / n_layers - 0.5)) for i in range(n_layers)})
+    return [([x0, 0, z], [x0 + wx, ny, z + 1]) for z in zs]
+
+
+def run_blocks(run, cs, blocks):
+    tot = dict(mpus=0, crossed=0, simd_evals=0, triangles=0, vertices=0)
+    t = time.perf_counter()
+    for b, e in blocks:
+        st = run(cs, b, e)
+        for k in tot:
+            tot[k] += st.get(k, 0)
+    return time.perf_counter() - t, tot
+
+
 def cpu_sample(run, cs, dims, budget_s):
-    """Times a z-slab sample of the lattice sized for about budget_s seconds. Returns (seconds, mpu layers, stats)."""
-    nz = dims[2]
-    mid = nz // 2
-    t = time.perf_counter()
-    st = run(cs, [0, 0, mid], [dims[0], dims[1], mid + 1])
-    t1 = time.perf_counter() - t
-    layers = int(max(1, min(nz, budget_s / max(t1, 1e-6))))
-    if layers == 1:
-        return t1, 1, st
-    b = max(0, mid - layers // 2)
-    e = min(nz, b + layers)
-    t = time.perf_counter()
-    st = run(cs, [0, 0, b], [dims[0], dims[1], e])
-    return time.perf_counter() - t, e - b, st
+    """Calibrates on a thin probe, then times a sample sized for about budget_s seconds. Returns (seconds, blocks, stats)."""
+    probe = sample_blocks(dims, max(64, dims[1]), n_layers=2)
+    t0, st0 = run_blocks(run, cs, probe)
+    per_mpu = t0 / max(1, st0["mpus"])
+    blocks = sample_blocks(dims, max(st0["mpus"], budget_s / max(per_mpu, 1e-9)))
+    sec, st = run_blocks(run, cs, blocks)
+    return sec, blocks, st
+
+
+def describe(blocks, dims, st, name=""):
+    zs = [b[2] for b, _ in blocks]
+    wx = blocks[0][1][0] - blocks[0][0][0]
+    return "%d z-layers spread over the lattice (z = %s of %d), x-range %d/%d MPUs, full y: %d MPUs, %d with surface%s" % (
+        len(blocks), ",".join(str(z) for z in zs), dims[2], wx, dims[0], st["mpus"], st["crossed"], (" of " + name) if name else "")
 
 
 def run_reference(args):
@@ -153,27 +172,23 @@ def run_reference(args):
     cs = scenes.cellsize_for(lo, hi, w["cells"])
     dims = [int(math.ceil(math.ceil(float(hi[a] - lo[a]) / cs) / 7.0)) for a in range(3)]
     cores = os.cpu_count() or 1
-    per_step = max(1.0, min(20.0, 150.0 / max(1, args.steps + args.warmup)))
-    # calibrate the sample once, then time K steps of it
-    t0, layers, st = cpu_sample(run, cs, dims, per_step)
-    mid = dims[2] // 2
-    b = max(0, mid - layers // 2)
-    e = min(dims[2], b + layers)
+    # bounded at every N: about 10 s of CPU work per step, and the whole --steps K --warmup W run within a few minutes
+    per_step = max(1.0, min(10.0, 180.0 / max(1, args.steps + args.warmup + 1)))
+    t0, blocks, st = cpu_sample(run, cs, dims, per_step)
     for _ in range(max(0, args.warmup - 1)):
-        run(cs, [0, 0, b], [dims[0], dims[1], e])
+        run_blocks(run, cs, blocks)
     times = []
     for _ in range(args.steps):
-        t = time.perf_counter()
-        st = run(cs, [0, 0, b], [dims[0], dims[1], e])
-        times.append(time.perf_counter() - t)
+        sec1, st = run_blocks(run, cs, blocks)
+        times.append(sec1)
     sec = float(np.sum(times))
-    cells = float(dims[0] * dims[1] * (e - b)) * 343.0 * args.steps
+    cells = float(st["mpus"]) * 343.0 * args.steps
     value = cells / sec
-    sample = "z-slab of %d/%d MPU layers (%d MPUs, %d with surface) of %s" % (e - b, dims[2], st["mpus"], st["crossed"], w["name"])
+    sample = describe(blocks, dims, st, w["name"])
     out = {
         "impl": "reference", "metric": "MC cells/s", "value": value, "unit": "cells/s", "n_gpus": args.gpus, "steps": args.steps,
-        "warmup": args.warmup, "ms_per_step": 1e3 * sec / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-        "dtype": "f32", "data": "synthetic",
+        "warmup": args.warmup, "ms_per_step": 1e3 * sec / args.steps, "higher_is_better": True, "scaling": "strong" if args.gpus > 1 else "weak",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": w["name"], "semantics": "PS_SimdPoly (infinite lines, f>=iso, 4-sample roots)", "cells": w["cells"],
                    "primitives": w["prims"], "cellsize": cs, "lattice_mpus": dims},
         "field_evals_per_s": st["simd_evals"] * 4.0 * args.steps / sec,
@@ -189,12 +204,85 @@ def run_reference(args):
 # ----------------------------------------------------------------------------------------------------------
 # GPU arm
 # ----------------------------------------------------------------------------------------------------------
+def layer_weights(flat, lo, cs, nz):
+    """Per-MPU-layer work estimate for the weighted slab cut (host, deterministic, identical on every rank): how many primitives'
+    supports (skeleton extent + the Wyvill radius 1) reach into each z-layer."""
+    side = 7.0 * cs
+    prim = flat["type"] < 16
+    z0 = np.minimum(flat["pos"][prim, 2], np.where(flat["type"][prim] == 1, flat["dir"][prim, 2], flat["pos"][prim, 2])) - 1.3
+    z1 = np.maximum(flat["pos"][prim, 2], np.where(flat["type"][prim] == 1, flat["dir"][prim, 2], flat["pos"][prim, 2])) + 1.3
+    w = np.zeros(nz, np.float64)
+    l0 = np.clip(np.floor((z0 - lo[2]) / side).astype(int), 0, nz - 1)
+    l1 = np.clip(np.floor((z1 - lo[2]) / side).astype(int), 0, nz - 1)
+    for a, b in zip(l0, l1):
+        w[a:b + 1] += 1.0
+    return (w + 0.05 * w.mean()).astype(np.float32)  # a floor: every layer costs its cull walk
+
+
+def measure_other_configs(ps, bt, scenes, ctx):
+    """BASELINE configs[0], [2] and [4] on this GPU, so that the driver-run line covers them (median of device-event times)."""
+    out = {}
+
+    def run(prog, prm, reps=9):
+        ctx.upload(prog)
+        ms, st, m = [], None, None
+        for _ in range(reps):
+            m = ctx.polygonize(prm, download=False)
+            st = ctx.stats()
+            ms.append(st["ms_total"])
+        return float(np.median(ms[3:])), st, m
+
+    root = bt.binarize(scenes.small())
+    flat = bt.flatten(root)
+    lo, hi = ps.prepare_bboxes(flat)
+    cs = scenes.cellsize_for(lo, hi, 128)
+    ms, st, m = run(ps.linearize(flat, ps.SEM_SIMD, 0), ps.Params.make(cs, lo, hi, root_mode=ps.ROOT_FOURSAMPLE))
+    d = ps.lattice_dims(cs, lo, hi)
+    out["configs[0] small@128^3 (PS_SimdPoly semantics)"] = {"ms": ms, "cells_per_s": d[0] * d[1] * d[2] * 343 / (ms * 1e-3), "vertices": m["n_vertices"],
+                                                             "triangles": m["n_triangles"], "stage_ms": {k: st[k] for k in ("ms_cull", "ms_field", "ms_tri", "ms_vertex", "ms_color")}}
+    for label, survey in (("configs[2] csgwarp@512^3, warp rates scaled to the group size (scenes.csgwarp default)", False),
+                          ("configs[2] csgwarp@512^3, SURVEY 8(d) warp rates as written (about the world origin)", True)):
+        flat = bt.flatten(scenes.csgwarp(survey_rates=survey))
+        if survey:
+            # twist angles of up to 10 radians about the world axes carry the surface anywhere within the groups' distance from the
+            # origin, far outside any box built from the unwarped primitives (the warp-box heuristic overflows): a fixed cube
+            lo, hi = np.full(3, -15.0, np.float32), np.full(3, 15.0, np.float32)
+        else:
+            lo, hi = ps.prepare_bboxes(flat)
+        cs = scenes.cellsize_for(lo, hi, 512)
+        ms, st, m = run(ps.linearize(flat, ps.SEM_SCALAR, ps.LIN_REASSOCIATE), ps.Params.make(cs, lo, hi), reps=7)
+        d = ps.lattice_dims(cs, lo, hi)
+        out[label] = {"ms": ms, "cells_per_s": d[0] * d[1] * d[2] * 343 / (ms * 1e-3), "mpus": st["mpus_total"], "evaluated": st["mpus_evaluated"],
+                      "crossed": st["mpus_crossed"], "vertices": m["n_vertices"], "triangles": m["n_triangles"],
+                      "stage_ms": {k: st[k] for k in ("ms_cull", "ms_field", "ms_tri", "ms_vertex", "ms_color")}}
+    # configs[4]: per frame = psgpu_linearize + psgpu_upload_program + psgpu_polygonize, wall clock (tree construction in Python excluded)
+    f0 = bt.flatten(scenes.anim_frame(0))
+    lo, hi = ps.prepare_bboxes(f0)
+    for f in (30, 60, 90):
+        l2, h2 = ps.prepare_bboxes(bt.flatten(scenes.anim_frame(f)))
+        lo, hi = np.minimum(lo, l2), np.maximum(hi, h2)
+    cs = scenes.cellsize_for(lo, hi, 256)
+    prm = ps.Params.make(cs, lo, hi)
+    frames, gpu_ms = [], []
+    for f in range(0, 120, 2):
+        flat = bt.flatten(scenes.anim_frame(f))
+        t0 = time.perf_counter()
+        prog = ps.linearize(flat, ps.SEM_SCALAR, ps.LIN_REASSOCIATE)
+        ctx.upload(prog)
+        ctx.polygonize(prm, download=False)
+        frames.append((time.perf_counter() - t0) * 1e3)
+        gpu_ms.append(ctx.stats()["ms_total"])
+    out["configs[4] anim@256^3, 60 frames, ms per frame (linearize + upload + polygonize, wall clock)"] = {
+        "ms_per_frame_median": float(np.median(frames[5:])), "ms_per_frame_p99": float(np.percentile(frames[5:], 99)), "gpu_ms_median": float(np.median(gpu_ms[5:]))}
+    return out
+
+
 def run_gpu(args):
     import torch
     import torch.distributed as dist
 
     import parsip_b200 as ps
-    from parsip_b200 import scenes, sharding
+    from parsip_b200 import scenes
 
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -210,10 +298,19 @@ def run_gpu(args):
     lo, hi = ps.prepare_bboxes(flat)
     cs = scenes.cellsize_for(lo, hi, w["cells"])
     dims = ps.lattice_dims(cs, lo, hi)
-    zb, ze = sharding.slab_bounds(dims[2], world, rank)
     ctx = ps.Context(local)
     prog = ps.linearize(flat, ps.SEM_SIMD, 0)
     ctx.upload(prog)
+    zb, ze = 0, dims[2]
+    if world > 1:
+        # the product's own multi-GPU path: NCCL communicator inside libpsgpu.so (the 128-byte id travels over torch.distributed),
+        # slabs balanced by a per-layer primitive histogram
+        idt = torch.zeros(128, dtype=torch.uint8, device="cuda")
+        if rank == 0:
+            idt.copy_(torch.frombuffer(bytearray(ps.comm_unique_id()), dtype=torch.uint8))
+        dist.broadcast(idt, 0)
+        ctx.comm_init(world, rank, idt.cpu().numpy().tobytes())
+        zb, ze = ps.slab_bounds(dims[2], world, rank, layer_weights(flat, lo, cs, dims[2]))
     mk = lambda **kw: ps.Params.make(cs, lo, hi, root_mode=ps.ROOT_FOURSAMPLE, coord_mode=ps.COORD_GLOBAL, output=ps.OUT_INDEXED,
                                      cull=ps.CULL_INTERVAL, z_begin=zb, z_end=ze, **kw)
     prm = mk()
@@ -224,72 +321,89 @@ def run_gpu(args):
             dist.barrier()
         torch.cuda.synchronize()
 
-    def exchange(nv, nt):
-        """per-rank vertex / triangle counts -> global offsets (NCCL all-gather over NVLink when world > 1)"""
-        if world == 1:
-            return (0, 0), (nv, nt)
-        return sharding.exchange_counts(nv, nt, torch.device("cuda", local))
-
-    # ---- device-resident steps: `value`
+    # ---- device-resident steps: `value`. One clock at every N: the library's CUDA events around cull .. emit on its own stream,
+    # which at N > 1 includes the NCCL count all-gather and the halo exchange (they run on that stream between the scans and emit).
     for _ in range(args.warmup):
-        m = ctx.polygonize(prm, download=False)
-        exchange(m["n_vertices"], m["n_triangles"])
+        m = ctx.polygonize_sharded(prm)
     sampler = ClockSampler(local)
     barrier()
     if rank == 0:
         sampler.start()
-    dev_ms, launches, stats_sum = 0.0, 0, None
-    field_ms = emit_ms = cull_ms = scan_ms = tri_ms = vertex_ms = color_ms = 0.0
+    keys = ("ms_total", "ms_cull", "ms_field", "ms_scan", "ms_exchange", "ms_emit", "ms_tri", "ms_vertex", "ms_color")
+    acc = {k: 0.0 for k in keys}
+    launches = 0
     for _ in range(args.steps):
         flush.fill_(1)  # L2 flush between steps (untimed)
-        torch.cuda.synchronize()
-        t = time.perf_counter()
-        m = ctx.polygonize(prm, download=False)
-        offs, tot = exchange(m["n_vertices"], m["n_triangles"])
-        wall = (time.perf_counter() - t) * 1e3
+        barrier()       # ranks start a step together: the exchange inside it waits for the slowest rank
+        m = ctx.polygonize_sharded(prm)
         st = ctx.stats()
-        # device time of the step = CUDA events on the library's launching stream (cull .. emit); the count exchange
-        # (16 B per rank) is added from its wall time when sharded
-        dev_ms += st["ms_total"] + (max(0.0, wall - st["ms_total"]) if world > 1 else 0.0)
-        field_ms += st["ms_field"]; emit_ms += st["ms_emit"]; cull_ms += st["ms_cull"]; scan_ms += st["ms_scan"]
-        tri_ms += st["ms_tri"]; vertex_ms += st["ms_vertex"]; color_ms += st["ms_color"]
+        for k in keys:
+            acc[k] += st[k]
         launches += st["gpu_launches"]
     barrier()
     clocks = sampler.stop() if rank == 0 else None
-    stc = ctx.polygonize(mk(collect_stats=1), download=False)
+    dev_ms = acc["ms_total"]
+    shard = m["shard"]
+    nv, nt = m["n_vertices"], m["n_triangles"]
+    ctx.polygonize_sharded(mk(collect_stats=1))
     st = ctx.stats()
 
-    # ---- end to end through the C ABI with HOST buffers: upload (pinned) + polygonize + mesh download (pinned)
-    nv, nt = m["n_vertices"], m["n_triangles"]
+    # ---- end to end through the C ABI with HOST buffers: upload (pinned) + polygonize + this rank's mesh share into pinned memory
     pin = lambda n: torch.empty((max(n, 1), 3), dtype=torch.float32, pin_memory=True).numpy()
     pos, nrm, col = pin(nv), pin(nv), pin(nv)
     tri = torch.empty((max(nt, 1), 3), dtype=torch.int32, pin_memory=True).numpy().view(np.uint32)
-    ctx.upload(prog); ctx.polygonize_host(prm, pos, nrm, col, tri)
+
+    def e2e_step():
+        ctx.upload(prog)
+        if world == 1:
+            ctx.polygonize_host(prm, pos, nrm, col, tri)  # copies overlap the emission kernels
+        else:
+            ctx.polygonize_sharded_host(prm, pos, nrm, col, tri)
+
+    e2e_step()
     barrier()
     e2e_s = 0.0
     for _ in range(args.steps):
         flush.fill_(1)
-        torch.cuda.synchronize()
+        barrier()
         t = time.perf_counter()
-        ctx.upload(prog)
-        mh = ctx.polygonize_host(prm, pos, nrm, col, tri)
-        exchange(mh["n_vertices"], mh["n_triangles"])
+        e2e_step()
         e2e_s += time.perf_counter() - t
     barrier()
 
-    # ---- canonical native mode (segments, bracketed root search), for information
+    # ---- the same job on ONE GPU, timed in the same run by rank 0 (strong-scaling reference at N > 1)
+    single_ms = None
+    if world > 1 and rank == 0:
+        one = ps.Context(local)
+        one.upload(prog)
+        whole = ps.Params.make(cs, lo, hi, root_mode=ps.ROOT_FOURSAMPLE, coord_mode=ps.COORD_GLOBAL, output=ps.OUT_INDEXED, cull=ps.CULL_INTERVAL)
+        ts = []
+        for _ in range(4):
+            one.polygonize(whole, download=False)
+            ts.append(one.stats()["ms_total"])
+        single_ms = float(np.median(ts[1:]))
+        one.close()
+    barrier()
+
+    # ---- canonical native mode (segments, bracketed root search): time, op counts and rooflines of its own kernels
     progN = ps.linearize(bt.flatten(root), ps.SEM_SCALAR, ps.LIN_REASSOCIATE)
     ctx.upload(progN)
     prmN = ps.Params.make(cs, lo, hi, z_begin=zb, z_end=ze)
-    ctx.polygonize(prmN, download=False)
-    nat_ms = 0.0
-    for _ in range(max(1, min(args.steps, 5))):
-        mn = ctx.polygonize(prmN, download=False)
-        nat_ms += ctx.stats()["ms_total"]
-    nat_ms /= max(1, min(args.steps, 5))
+    ctx.polygonize_sharded(prmN)
+    ctx.polygonize_sharded(prmN)
+    nkeys = ("ms_total", "ms_field", "ms_vertex", "ms_color", "ms_cull", "ms_tri")
+    nacc = {k: 0.0 for k in nkeys}
+    nrep = max(1, min(args.steps, 5))
+    for _ in range(nrep):
+        barrier()
+        mn = ctx.polygonize_sharded(prmN)
+        s2 = ctx.stats()
+        for k in nkeys:
+            nacc[k] += s2[k] / nrep
+    ctx.polygonize_sharded(ps.Params.make(cs, lo, hi, z_begin=zb, z_end=ze, collect_stats=1))
     stn = ctx.stats()
 
-    # ---- reduce over ranks: max time, summed work
+    # ---- reduce over ranks: max time, summed work, per-rank stage table
     def allmax(x):
         if world == 1:
             return x
@@ -300,6 +414,16 @@ def run_gpu(args):
             return x
         t = torch.tensor([x], dtype=torch.float64, device="cuda"); dist.all_reduce(t, op=dist.ReduceOp.SUM); return float(t[0])
 
+    def gather_rows(row):
+        t = torch.tensor(row, dtype=torch.float64, device="cuda")
+        if world == 1:
+            return [row]
+        out = [torch.empty_like(t) for _ in range(world)]
+        dist.all_gather(out, t)
+        return [[float(v) for v in o.cpu()] for o in out]
+
+    K = float(args.steps)
+    per_rank = gather_rows([zb, ze, st["mpus_evaluated"], st["mpus_crossed"], nv, nt] + [acc[k] / K for k in keys] + [e2e_s / K * 1e3])
     dev_ms_max = allmax(dev_ms)
     e2e_s_max = allmax(e2e_s)
     cells_total = float(dims[0] * dims[1] * dims[2]) * 343.0  # grid cells of the whole job
@@ -308,8 +432,7 @@ def run_gpu(args):
     launches_all = allsum(float(launches))
     h2d = prog.n_quads * 16 + prog.n_prims * 12
     d2h = nv * 36 + nt * 12
-    flops = float(st["algorithmic_flops"])
-    nat_ms_max = allmax(nat_ms)
+    nat_ms_max = allmax(nacc["ms_total"])
     if world > 1:
         dist.barrier()
     if rank != 0:
@@ -324,75 +447,148 @@ def run_gpu(args):
     # ---- rooflines, rank 0's launches (DESIGN.md section 5 states the per-unit figures):
     #   field_kernel / vertex_kernel / color_kernel  FP32 pipe: SURVEY 8(d) op counts of every MPU's pruned program x points evaluated
     #   tri_kernel                                   HBM: per surface MPU 2 KB field cache + 288 B edge masks read, 12 B per triangle written
-    K = float(args.steps)
-    traffic = {}
-    tp = os.path.join(ROOT, "profiles", "traffic.json")  # dram__bytes_read+write per launch from the committed ncu --set full capture
-    if os.path.exists(tp) and world == 1:
+    # `traffic` = dram__bytes_read + write per launch from this round's ncu --set full captures (profiles/traffic.json names the commit
+    # and the command; the N > 1 entry is rank 0's slab captured on one GPU)
+    traffic, traffic_src = {}, None
+    tp = os.path.join(ROOT, "profiles", "traffic.json")
+    if os.path.exists(tp):
         try:
-            traffic = json.load(open(tp)).get(w["name"], {})
+            tj = json.load(open(tp))
+            traffic = tj.get(w["name"] if world == 1 else w["name"] + " rank 0 of %d" % world, {})
+            traffic_src = tj.get("_source")
         except Exception:
             traffic = {}
     fp32_src = "FFMA-chain microbenchmark run in this process (MEASURED_PEAKS.json has no fp32 figure)"
 
-    def roof_fp32(name, fl, ms):
+    def roof_fp32(name, fl, ms, sem="PS_SimdPoly"):
         ach = fl / max(ms, 1e-9) / 1e9
-        return {"bound": "fp32", "kernel": name, "achieved": ach, "peak": fp32_tflops, "unit": "TFLOP/s", "frac": ach / fp32_tflops,
-                "traffic": traffic.get(name), "peak_source": fp32_src, "algorithmic_flops_per_launch": fl, "ms_per_launch": ms}
+        return {"bound": "fp32", "kernel": name, "semantics": sem, "achieved": ach, "peak": fp32_tflops, "unit": "TFLOP/s", "frac": ach / fp32_tflops,
+                "traffic": traffic.get(name) if sem == "PS_SimdPoly" else traffic.get(name + " native"), "peak_source": fp32_src,
+                "algorithmic_flops_per_launch": fl, "ms_per_launch": ms}
 
     def roof_hbm(name, by, ms):
         ach = by / max(ms, 1e-9) / 1e6
         return {"bound": "hbm", "kernel": name, "achieved": ach, "peak": peaks["hbm_gbs"], "unit": "GB/s", "frac": ach / peaks["hbm_gbs"],
                 "traffic": traffic.get(name), "peak_source": peak_src, "algorithmic_bytes_per_launch": by, "ms_per_launch": ms}
 
+    flops = float(st["algorithmic_flops"])
     vflops = float(st["vertex_eval_flops"])
     tri_bytes = float(st["mpus_crossed"]) * (2048 + 288 + 8) + nt * 12.0
-    roofs = [roof_fp32("field_kernel", flops, field_ms / K), roof_fp32("vertex_kernel", 8.0 * vflops, vertex_ms / K),
-             roof_fp32("color_kernel", vflops, color_ms / K), roof_hbm("tri_kernel", tri_bytes, tri_ms / K)]
+    roofs = [roof_fp32("field_kernel", flops, acc["ms_field"] / K), roof_fp32("vertex_kernel", 8.0 * vflops, acc["ms_vertex"] / K),
+             roof_fp32("color_kernel", vflops, acc["ms_color"] / K), roof_hbm("tri_kernel", tri_bytes, acc["ms_tri"] / K)]
     roofs.sort(key=lambda r: -r["ms_per_launch"])
     dominant, other = roofs[0], roofs[1:]
-    field_ms_r0, emit_ms_r0 = field_ms / K, emit_ms / K
+    # native semantics: 14 point evaluations per vertex (4 section rounds x ... see psgpu_stats.field_evals) - the vertex kernel's
+    # op count = evaluations per vertex x the per-vertex program cost
+    nat_roofs = [roof_fp32("field_kernel", float(stn["algorithmic_flops"]), nacc["ms_field"], "native"),
+                 roof_fp32("vertex_kernel", 20.0 * float(stn["vertex_eval_flops"]), nacc["ms_vertex"], "native"),
+                 roof_fp32("color_kernel", float(stn["vertex_eval_flops"]), nacc["ms_color"], "native")]
+    rank_cols = ["z_begin", "z_end", "mpus_evaluated", "mpus_crossed", "vertices", "triangles"] + list(keys) + ["e2e_ms"]
 
     out = {
         "metric": "MC cells/s", "value": value, "unit": "cells/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-        "ms_per_step": dev_ms_max / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
-        "data": "synthetic",
+        "ms_per_step": dev_ms_max / args.steps, "higher_is_better": True, "scaling": "strong" if world > 1 else "weak", "vs_baseline": None,
+        "dtype": "f32", "data": "synthetic",
         "config": {"workload": w["name"], "semantics": "PS_SimdPoly (infinite lines, f>=iso, 4-sample roots)", "cells": w["cells"],
-                   "primitives": w["prims"], "cellsize": cs, "lattice_mpus": list(dims), "sharding": "z-slabs of MPU layers, %d ranks" % world,
+                   "primitives": w["prims"], "cellsize": cs, "lattice_mpus": list(dims),
+                   "sharding": "z-slabs of MPU layers over %d ranks, cut by a per-layer primitive histogram; boundary vertices exist once "
+                               "(psgpu_polygonize_sharded)" % world if world > 1 else "single GPU",
                    "l2": "flushed between steps (256 MiB fill, untimed); a step's field caches + mesh also exceed L2",
-                   "cull": "interval", "output": "indexed mesh (global edge-id dedup)"},
-        "field_evals_per_s": evals * args.steps / sec / args.steps * 1.0 / 1.0,
-        "triangles_per_s": tris * args.steps / sec / args.steps * 1.0,
+                   "cull": "interval", "output": "indexed mesh (global edge-id dedup)",
+                   "timing": "library CUDA events cull..emit on its stream (incl. the NCCL exchange at N > 1), max over ranks, same at every N"},
+        "field_evals_per_s": evals / (dev_ms_max / args.steps * 1e-3),
+        "triangles_per_s": tris / (dev_ms_max / args.steps * 1e-3),
         "ms_per_polygonization": dev_ms_max / args.steps,
-        "mesh": {"vertices": int(verts), "triangles": int(tris)},
-        "stage_ms_rank0": {"cull": cull_ms / args.steps, "field": field_ms_r0, "scan": scan_ms / args.steps, "emit": emit_ms_r0,
-                           "tri": tri_ms / K, "vertex": vertex_ms / K, "color": color_ms / K},
+        "mesh": {"vertices": int(verts), "triangles": int(tris), "stitched_total_vertices": int(shard["total_vertices"] or verts)},
+        "stage_ms_rank0": {"cull": acc["ms_cull"] / K, "field": acc["ms_field"] / K, "scan": acc["ms_scan"] / K, "exchange": acc["ms_exchange"] / K,
+                           "emit": acc["ms_emit"] / K, "tri": acc["ms_tri"] / K, "vertex": acc["ms_vertex"] / K, "color": acc["ms_color"] / K},
+        "per_rank": {"columns": rank_cols, "rows": per_rank},
         "mpus_rank0": {"total": st["mpus_total"], "evaluated": st["mpus_evaluated"], "crossed": st["mpus_crossed"]},
         "e2e": {"value": cells_total * args.steps / e2e_s_max, "unit": "cells/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
                 "ms_per_step": 1e3 * e2e_s_max / args.steps},
         "gpu_launches": int(launches_all),
-        "roofline": dominant, "roofline_other": other,
-        "native": {"semantics": "CompactBlobTree (segments, f>iso), bracketed false-position roots", "ms_per_polygonization": nat_ms_max,
-                   "cells_per_s": cells_total / (nat_ms_max * 1e-3), "vertices": mn["n_vertices"], "triangles": mn["n_triangles"],
-                   "field_evals": stn["field_evals"]},
+        "roofline": dominant, "roofline_other": other, "traffic_source": traffic_src,
+        "native": {"semantics": "CompactBlobTree (segments, f>iso), bracketed section roots", "ms_per_polygonization": nat_ms_max,
+                   "cells_per_s": cells_total / (nat_ms_max * 1e-3), "vertices_rank0": mn["n_vertices"], "triangles_rank0": mn["n_triangles"],
+                   "stage_ms_rank0": {k[3:]: nacc[k] for k in nkeys}, "roofline": nat_roofs},
         "clocks": clocks,
     }
-    out["field_evals_per_s"] = evals / (dev_ms_max / args.steps * 1e-3)
-    out["triangles_per_s"] = tris / (dev_ms_max / args.steps * 1e-3)
+    if world > 1 and single_ms:
+        out["strong_scaling"] = {"single_gpu_ms_same_job_same_run": single_ms, "speedup": single_ms / (dev_ms_max / args.steps),
+                                 "efficiency": single_ms / (dev_ms_max / args.steps) / world}
 
-    # ---- CPU baseline beside it (N = 1 only): bounded sample of the same workload on the host cores
+    # ---- N = 1 only: the other BASELINE configs on this GPU, and the CPU baseline beside it with a mesh comparison
+    if world == 1:
+        try:
+            out["other_configs"] = measure_other_configs(ps, bt, scenes, ctx)
+        except Exception as e:  # never lose the headline line to a side measurement
+            out["other_configs"] = {"error": repr(e)}
     if world == 1 and not args.no_cpu_baseline:
         kind, sc, run = cpu_polygonizer(root, bt, w["prims"])
         rlo, rhi = sc.bbox()
         rcs = scenes.cellsize_for(rlo, rhi, w["cells"])
         rdims = [int(math.ceil(math.ceil(float(rhi[a] - rlo[a]) / rcs) / 7.0)) for a in range(3)]
-        tsec, layers, rst = cpu_sample(run, rcs, rdims, 12.0)
-        out["cpu_baseline"] = {"value": rdims[0] * rdims[1] * layers * 343.0 / tsec, "unit": "cells/s", "cores": os.cpu_count() or 1, "kind": kind,
-                               "sample": "z-slab of %d/%d MPU layers (%d MPUs, %d with surface), %.1f s" % (layers, rdims[2], rst["mpus"], rst["crossed"], tsec),
+        tsec, blocks, rst = cpu_sample(run, rcs, rdims, 12.0)
+        out["cpu_baseline"] = {"value": rst["mpus"] * 343.0 / tsec, "unit": "cells/s", "cores": os.cpu_count() or 1, "kind": kind,
+                               "sample": describe(blocks, rdims, rst) + ", %.1f s" % tsec,
                                "field_evals_per_s": rst["simd_evals"] * 4.0 / tsec, "triangles_per_s": rst["triangles"] / tsec}
+        try:
+            out["cpu_baseline"]["mesh_check"] = mesh_check(ps, ctx, prog, sc, kind, rcs, rdims, lo, hi, cs)
+        except Exception as e:
+            out["cpu_baseline"]["mesh_check"] = {"error": repr(e)}
     print(json.dumps(out))
     if world > 1:
         dist.destroy_process_group()
     return 0
+
+
+def mesh_check(ps, ctx, prog, sc, kind, rcs, rdims, lo, hi, cs):
+    """One MPU layer of the workload polygonized by the CPU arm and by the GPU in the reference's own output format (MPU-local
+    coordinates, per-MPU vertex order) and compared. `as_shipped`: the reference as it runs in the timed CPU arm (its depth>3
+    operator-box prune active); `op_boxes_padded`: the same build with that prune neutralised through the caller-owned
+    operator boxes - the configuration the GPU path reproduces byte for byte."""
+    import hashlib
+    if kind != "reference":
+        return {"skipped": "reference build absent"}
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import gpu_helpers as gh
+    z = rdims[2] // 2
+    ctx.upload(prog)
+    m = ctx.polygonize(ps.Params.make(cs, lo, hi, root_mode=ps.ROOT_FOURSAMPLE, coord_mode=ps.COORD_MPU_LOCAL, output=ps.OUT_MPU, z_begin=z, z_end=z + 1),
+                       allow_over_capacity=True)
+    pos, nrm, col, tri, ijk, counts = gh.lattice_ordered(m)
+    sha = lambda a: hashlib.sha256(np.ascontiguousarray(a).tobytes()).hexdigest()[:16]
+    res = {"layer": z, "gpu": {"mpus": int(len(ijk)), "vertices": int(len(pos)), "triangles": int(len(tri)), "pos_sha": sha(pos), "tri_sha": sha(tri)}}
+    def per_mpu(ijk_, counts_, pos_, tri_, col_):
+        vb = np.concatenate([[0], np.cumsum(counts_[:, 0])]).astype(np.int64)
+        tb = np.concatenate([[0], np.cumsum(counts_[:, 1])]).astype(np.int64)
+        return {tuple(int(v) for v in ijk_[i]): (pos_[vb[i]:vb[i + 1]], tri_[tb[i]:tb[i + 1]].astype(np.int64) - vb[i], col_[vb[i]:vb[i + 1]]) for i in range(len(ijk_))}
+
+    mine = per_mpu(ijk, counts, pos, tri, col)
+    for label, pad in (("as_shipped", False), ("op_boxes_padded", True)):
+        if pad:
+            sc.pad_op_boxes(1.0e6)
+        ret, r = sc.polygonize_stream(rcs, [0, 0, z], [rdims[0], rdims[1], z + 1], keep_mesh=True)
+        theirs = per_mpu(r["mpu_idx"], r["mpu_counts"].astype(np.int64), r["pos"], r["tri"], r["col"])
+        # The SIMD cylinder takes sqrt(|p|^2 - (p.d)^2) (PS_Polygonizer.cpp:1012-1039); for points on the axis the argument rounds
+        # negative, the reference's field is NaN there and _mm_max_ps / _mm_min_ps pass or drop it depending on operand order, which
+        # leaves a few MPUs with NaN vertices and spurious triangles in its output. The GPU evaluates those points as numbers
+        # (DESIGN.md, known divergences): such MPUs are counted and left out of the byte comparison.
+        nan_mpus = {k for k, (p_, _, _) in theirs.items() if not np.isfinite(p_).all()}
+        equal = differ = 0
+        for k, (p_, t_, c_) in theirs.items():
+            if k in nan_mpus:
+                continue
+            g_ = mine.get(k)
+            ok = g_ is not None and len(g_[0]) == len(p_) and len(g_[1]) == len(t_) and np.array_equal(g_[0].view(np.uint32), p_.view(np.uint32)) \
+                and np.array_equal(g_[1], t_) and np.array_equal(g_[2].view(np.uint32), c_.view(np.uint32))
+            equal += int(ok); differ += int(not ok)
+        extra = len(set(mine) - set(theirs))
+        res[label] = {"mpus": len(theirs), "vertices": int(len(r["pos"])), "triangles": int(len(r["tri"])), "pos_sha": sha(r["pos"]), "tri_sha": sha(r["tri"]),
+                      "mpus_byte_identical": equal, "mpus_differing": differ, "mpus_with_nan_vertices_in_reference": len(nan_mpus),
+                      "gpu_mpus_absent_from_reference": extra, "mesh_equal": bool(differ == 0 and extra == 0)}
+    res["mesh_equal"] = res["op_boxes_padded"]["mesh_equal"]
+    return res
 
 
 def main():

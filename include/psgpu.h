@@ -168,6 +168,9 @@ int psgpu_slab_bounds(int n_layers, int nranks, int rank, const float* layer_wei
  * counts and the boundary layer's vertex tables, and leaves a stitched share of ONE mesh on every rank (see psgpu_shard).
  * PSGPU_OUT_INDEXED + PSGPU_COORD_GLOBAL only. Without psgpu_comm_init it is psgpu_polygonize. */
 int psgpu_polygonize_sharded(psgpu_ctx* ctx, const psgpu_params* params, psgpu_mesh* out, psgpu_shard* shard);
+/* Same, with this rank's share copied into caller-provided HOST buffers while the emission kernels still run. */
+int psgpu_polygonize_sharded_host(psgpu_ctx* ctx, const psgpu_params* params, psgpu_mesh* out, psgpu_shard* shard, float* pos, float* nrm,
+                                  float* col, uint32_t* tri, int64_t cap_vertices, int64_t cap_triangles);
 /* Collective: gathers the shares into DEVICE buffers on `root` (3 * total_vertices floats each, 3 * total_triangles indices);
  * every rank passes the same set of non-NULL arguments (any valid non-NULL value on the senders means "send this array"). */
 int psgpu_mesh_gather(psgpu_ctx* ctx, int root, float* pos, float* nrm, float* col, uint32_t* tri);

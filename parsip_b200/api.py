@@ -22,7 +22,7 @@ EXPORTS = [
     "psgpu_program_info", "psgpu_program_copy", "psgpu_program_colors", "psgpu_prepare_bboxes", "psgpu_count_mpus", "psgpu_upload_program",
     "psgpu_polygonize", "psgpu_polygonize_host", "psgpu_mesh_download", "psgpu_mesh_map_host", "psgpu_field_eval", "psgpu_field_color_normal",
     "psgpu_tree_binarize", "psgpu_tree_view", "psgpu_tree_free", "psgpu_mpu_cache", "psgpu_mpu_caches_culled", "psgpu_prune_region", "psgpu_get_stats", "psgpu_measure_fp32_peak",
-    "psgpu_comm_get_unique_id", "psgpu_comm_init", "psgpu_comm_destroy", "psgpu_slab_bounds", "psgpu_polygonize_sharded", "psgpu_mesh_gather",
+    "psgpu_comm_get_unique_id", "psgpu_comm_init", "psgpu_comm_destroy", "psgpu_slab_bounds", "psgpu_polygonize_sharded", "psgpu_polygonize_sharded_host", "psgpu_mesh_gather",
 ]
 
 
@@ -143,6 +143,7 @@ def load_library():
     lib.psgpu_slab_bounds.argtypes = [C.c_int, C.c_int, C.c_int, vp, vp, vp]
     lib.psgpu_polygonize_sharded.argtypes = [vp, C.POINTER(Params), C.POINTER(_Mesh), C.POINTER(_Shard)]
     lib.psgpu_mesh_gather.argtypes = [vp, C.c_int, vp, vp, vp, vp]
+    lib.psgpu_polygonize_sharded_host.argtypes = [vp, C.POINTER(Params), C.POINTER(_Mesh), C.POINTER(_Shard), vp, vp, vp, vp, C.c_int64, C.c_int64]
     lib.psgpu_measure_fp32_peak.argtypes = [vp, vp, vp]
     _lib = lib
     return lib
@@ -365,6 +366,13 @@ class Context:
                         "psgpu_mesh_download")
             out.update(pos=pos, nrm=nrm, col=col, tri=tri)
         return out
+
+    def polygonize_sharded_host(self, params: Params, pos, nrm, col, tri) -> dict:
+        """psgpu_polygonize_sharded_host (collective): the rank's share lands in HOST buffers, copies overlapping the emission kernels."""
+        m, sh = _Mesh(), _Shard()
+        self._check(self.lib.psgpu_polygonize_sharded_host(self.h, C.byref(params), C.byref(m), C.byref(sh), pos.ctypes.data, nrm.ctypes.data,
+                                                           col.ctypes.data, tri.ctypes.data, pos.shape[0], tri.shape[0]), "psgpu_polygonize_sharded_host")
+        return dict(n_vertices=int(m.n_vertices), n_triangles=int(m.n_triangles), shard={f: getattr(sh, f) for f, _ in _Shard._fields_})
 
     def mesh_gather(self, root: int, pos_ptr: int, nrm_ptr: int, col_ptr: int, tri_ptr: int):
         """psgpu_mesh_gather (collective): device pointers on the root (ints, e.g. torch tensors' data_ptr()); any non-zero value on

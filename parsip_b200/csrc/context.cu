@@ -618,7 +618,8 @@ int polygonize_impl(psgpu_ctx* ctx, const psgpu_params* P, psgpu_mesh* out, bool
         }
     }
     S.mpus_crossed = nMixed;
-    const int evalsPerVertex = (P->root_mode == PSGPU_ROOT_FOURSAMPLE) ? 8 : 14;
+    // 4-sample: 4 root samples + 4 gradient samples; section search: 4 samples per round + 4; reference Newton: ~2 iterations of 5 + 4
+    const int evalsPerVertex = (P->root_mode == PSGPU_ROOT_FOURSAMPLE) ? 8 : (P->root_mode == PSGPU_ROOT_BISECT ? 4 * G.rootIters + 4 : 14);
     S.field_evals = (int64_t)nCand * 512 + (int64_t)nV * evalsPerVertex;
     S.gpu_launches = launches;
     M.n_vertices = nV; M.n_triangles = nT;
@@ -696,7 +697,7 @@ extern "C" int psgpu_slab_bounds(int n_layers, int nranks, int rank, const float
     return PSGPU_SUCCESS;
 }
 
-extern "C" int psgpu_polygonize_sharded(psgpu_ctx* ctx, const psgpu_params* params, psgpu_mesh* out, psgpu_shard* shard) {
+static int polygonize_sharded_impl(psgpu_ctx* ctx, const psgpu_params* params, psgpu_mesh* out, psgpu_shard* shard, const HostSink* sink) {
     if (!ctx || !params) return PSGPU_PARAM_ERROR;
     if (shard) *shard = psgpu_shard{};
     psgpu_params P = *params;
@@ -709,11 +710,25 @@ extern "C" int psgpu_polygonize_sharded(psgpu_ctx* ctx, const psgpu_params* para
     }
     if (P.z_end <= P.z_begin) { ctx->err = "empty slab"; return PSGPU_PARAM_ERROR; }
     ShardCtl sc{true, shard};
-    const int rc = polygonize_impl(ctx, &P, out, false, nullptr, &sc);
+    const int rc = polygonize_impl(ctx, &P, out, false, sink, &sc);
     if (shard && ctx->nranks <= 1 && rc == PSGPU_SUCCESS) {
         shard->nranks = 1; shard->rank = 0; shard->z_begin = P.z_begin; shard->z_end = P.z_end;
         shard->total_vertices = ctx->last.n_vertices; shard->total_triangles = ctx->last.n_triangles;
     }
+    return rc;
+}
+
+extern "C" int psgpu_polygonize_sharded(psgpu_ctx* ctx, const psgpu_params* params, psgpu_mesh* out, psgpu_shard* shard) {
+    return polygonize_sharded_impl(ctx, params, out, shard, nullptr);
+}
+
+// the same with this rank's share streamed into HOST buffers behind the emission kernels (like psgpu_polygonize_host)
+extern "C" int psgpu_polygonize_sharded_host(psgpu_ctx* ctx, const psgpu_params* params, psgpu_mesh* out, psgpu_shard* shard, float* pos,
+                                             float* nrm, float* col, uint32_t* tri, int64_t cap_vertices, int64_t cap_triangles) {
+    psgpu_mesh M{};
+    const HostSink sink{pos, nrm, col, tri, cap_vertices, cap_triangles};
+    const int rc = polygonize_sharded_impl(ctx, params, &M, shard, &sink);
+    if (out) *out = M;
     return rc;
 }
 

@@ -355,7 +355,7 @@ __global__ void __launch_bounds__(kThreads) tri_kernel(GridParams G, const Regio
                             }
                         } else {
                             const int32_t nc = candOfMpu[((size_t)(r.x + dI - G.lo[0]) * ny + (r.y + dJ - G.lo[1])) * nz + (r.z + dK - G.lo[2])];
-                            if (nc >= 0 && fo.tcount[nc] != 0u) {  // a culled / surface-free neighbour has no (or stale) masks
+                            if (nc >= 0) {  // a culled neighbour has no masks at all (index -1: the out-of-bounds read ADVICE r1 flagged)
                                 const uint32_t w = fo.edgeMask[(size_t)nc * 48 + (eb >> 5)];
                                 found = (w & bit) != 0u;
                                 vid = G.vertexOffset + mo.vbase[nc] + fo.edgePrefix[(size_t)nc * 48 + (eb >> 5)] + __popc(w & (bit - 1u));

@@ -81,10 +81,14 @@ def blob10k() -> bt.Node:
     return blobs(10000, 26.0, 4)
 
 
-def csgwarp(n_groups: int = 32, extent: float = 10.0, seed: int = 3) -> bt.Node:
+def csgwarp(n_groups: int = 32, extent: float = 10.0, seed: int = 3, survey_rates: bool = False) -> bt.Node:
     """S3 / config 3: 8 primitives per group, all six skeleton kinds,
     bend(taper(twist(dif(intersect(blend(a, b, c, d), e), blend(f, g)) ... h))) chains; identity
-    affines under warps."""
+    affines under warps.
+    Warp rates: the warps of the compact tree act about the WORLD origin (twist angle = k * coordinate, CompactBlobTree.cpp:1355-1385),
+    and the groups sit up to `extent` away from it, so SURVEY 8(d)'s rates (twist k in [0.2, 1], taper [-0.3, 0.3], bend [0.1, 0.5])
+    wind a group at distance 10 by up to 10 radians. The default divides them by `extent` (same angles per group as the survey's
+    numbers would give a group of unit size at the origin); survey_rates=True takes them as written."""
     rs = np.random.RandomState(seed)
     kinds = ("point", "line", "cylinder", "disc", "ring", "cube")
     groups = []
@@ -112,10 +116,11 @@ def csgwarp(n_groups: int = 32, extent: float = 10.0, seed: int = 3) -> bt.Node:
         carved = bt.Dif(bt.Intersect(body, bt.Blend(ps[4], ps[0], ps[1])), bt.Blend(ps[5], ps[6]))
         solid = bt.SmoothDif(bt.Union(carved, ps[7]), bt.Point(_f32(centre + rs.uniform(-0.6, 0.6, 3)),
                                                                 color=rs.uniform(0, 1, 3)))
-        w = bt.Twist(rs.uniform(0.2, 1.0) / extent, int(rs.randint(0, 3)), solid)
-        w = bt.Taper(rs.uniform(-0.3, 0.3) / extent, int(rs.randint(0, 2)), 2, w)
+        den = 1.0 if survey_rates else extent
+        w = bt.Twist(rs.uniform(0.2, 1.0) / den, int(rs.randint(0, 3)), solid)
+        w = bt.Taper(rs.uniform(-0.3, 0.3) / den, int(rs.randint(0, 2)), 2, w)
         y0 = float(centre[1])
-        w = bt.Bend(rs.uniform(0.1, 0.5) / extent, y0, y0 - 1.0, y0 + 1.0, w)
+        w = bt.Bend(rs.uniform(0.1, 0.5) / den, y0, y0 - 1.0, y0 + 1.0, w)
         groups.append(w)
     return bt.Union(*groups)
 
