@@ -204,19 +204,17 @@ def run_reference(args):
 # ----------------------------------------------------------------------------------------------------------
 # GPU arm
 # ----------------------------------------------------------------------------------------------------------
-def layer_weights(flat, lo, cs, nz):
-    """Per-MPU-layer work estimate for the weighted slab cut (host, deterministic, identical on every rank): how many primitives'
-    supports (skeleton extent + the Wyvill radius 1) reach into each z-layer."""
-    side = 7.0 * cs
-    prim = flat["type"] < 16
-    z0 = np.minimum(flat["pos"][prim, 2], np.where(flat["type"][prim] == 1, flat["dir"][prim, 2], flat["pos"][prim, 2])) - 1.3
-    z1 = np.maximum(flat["pos"][prim, 2], np.where(flat["type"][prim] == 1, flat["dir"][prim, 2], flat["pos"][prim, 2])) + 1.3
-    w = np.zeros(nz, np.float64)
-    l0 = np.clip(np.floor((z0 - lo[2]) / side).astype(int), 0, nz - 1)
-    l1 = np.clip(np.floor((z1 - lo[2]) / side).astype(int), 0, nz - 1)
-    for a, b in zip(l0, l1):
-        w[a:b + 1] += 1.0
-    return (w + 0.05 * w.mean()).astype(np.float32)  # a floor: every layer costs its cull walk
+def measured_layer_weights(ctx, nz, dist, world):
+    """Slab cut for the NEXT frames from what the last one cost: per MPU layer, MPUs evaluated and MPUs with surface (psgpu_layer_work),
+    summed over the ranks, weighted by the measured per-MPU stage costs (field ~ 1 per evaluated MPU, emission ~ 3 per surface MPU)."""
+    import torch
+    ev, cr = ctx.layer_work(nz)
+    t = torch.tensor(np.stack([ev, cr]).astype(np.float64), device="cuda")
+    if world > 1:
+        dist.all_reduce(t)
+    ev, cr = t.cpu().numpy()
+    w = ev + 3.0 * cr
+    return (w + 0.02 * max(w.mean(), 1.0)).astype(np.float32)
 
 
 def measure_other_configs(ps, bt, scenes, ctx):
@@ -304,16 +302,22 @@ def run_gpu(args):
     zb, ze = 0, dims[2]
     if world > 1:
         # the product's own multi-GPU path: NCCL communicator inside libpsgpu.so (the 128-byte id travels over torch.distributed),
-        # slabs balanced by a per-layer primitive histogram
+        # slabs cut from the measured per-layer work of a first frame
         idt = torch.zeros(128, dtype=torch.uint8, device="cuda")
         if rank == 0:
             idt.copy_(torch.frombuffer(bytearray(ps.comm_unique_id()), dtype=torch.uint8))
         dist.broadcast(idt, 0)
         ctx.comm_init(world, rank, idt.cpu().numpy().tobytes())
-        zb, ze = ps.slab_bounds(dims[2], world, rank, layer_weights(flat, lo, cs, dims[2]))
+        zb, ze = ps.slab_bounds(dims[2], world, rank)
     mk = lambda **kw: ps.Params.make(cs, lo, hi, root_mode=ps.ROOT_FOURSAMPLE, coord_mode=ps.COORD_GLOBAL, output=ps.OUT_INDEXED,
                                      cull=ps.CULL_INTERVAL, z_begin=zb, z_end=ze, **kw)
     prm = mk()
+    if world > 1:
+        # the first frame runs on equal slabs; the frames after it (the steady state that is timed) on slabs cut from its measured
+        # per-layer work - the re-polygonization / animation case (BASELINE configs[4]'s calling pattern on configs[3]'s job)
+        ctx.polygonize_sharded(prm)
+        zb, ze = ps.slab_bounds(dims[2], world, rank, measured_layer_weights(ctx, dims[2], dist, world))
+        prm = mk()
     flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
 
     def barrier():
@@ -491,7 +495,7 @@ def run_gpu(args):
         "dtype": "f32", "data": "synthetic",
         "config": {"workload": w["name"], "semantics": "PS_SimdPoly (infinite lines, f>=iso, 4-sample roots)", "cells": w["cells"],
                    "primitives": w["prims"], "cellsize": cs, "lattice_mpus": list(dims),
-                   "sharding": "z-slabs of MPU layers over %d ranks, cut by a per-layer primitive histogram; boundary vertices exist once "
+                   "sharding": "z-slabs of MPU layers over %d ranks, cut from the per-layer work measured on a first frame (psgpu_layer_work); boundary vertices exist once "
                                "(psgpu_polygonize_sharded)" % world if world > 1 else "single GPU",
                    "l2": "flushed between steps (256 MiB fill, untimed); a step's field caches + mesh also exceed L2",
                    "cull": "interval", "output": "indexed mesh (global edge-id dedup)",

@@ -164,6 +164,9 @@ int psgpu_comm_init(psgpu_ctx* ctx, int nranks, int rank, const void* id128);
 int psgpu_comm_destroy(psgpu_ctx* ctx);
 /* [z_begin, z_end) of `rank`: equal slabs (layer_weights == NULL) or balanced by one weight per MPU layer. */
 int psgpu_slab_bounds(int n_layers, int nranks, int rank, const float* layer_weights, int32_t* z_begin, int32_t* z_end);
+/* MPUs evaluated / MPUs with triangles per MPU layer of the global lattice in the LAST polygonize of this context (zero outside its
+ * slab). Summed over the ranks and weighted it feeds psgpu_slab_bounds for the next frame (re-polygonization, animation). */
+int psgpu_layer_work(psgpu_ctx* ctx, int32_t* evaluated, int32_t* crossed, int32_t n_layers);
 /* Collective over the communicator: polygonizes this rank's slab (params->z_begin/z_end, or an equal share if z_end <= 0), exchanges
  * counts and the boundary layer's vertex tables, and leaves a stitched share of ONE mesh on every rank (see psgpu_shard).
  * PSGPU_OUT_INDEXED + PSGPU_COORD_GLOBAL only. Without psgpu_comm_init it is psgpu_polygonize. */

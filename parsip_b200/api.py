@@ -22,7 +22,7 @@ EXPORTS = [
     "psgpu_program_info", "psgpu_program_copy", "psgpu_program_colors", "psgpu_prepare_bboxes", "psgpu_count_mpus", "psgpu_upload_program",
     "psgpu_polygonize", "psgpu_polygonize_host", "psgpu_mesh_download", "psgpu_mesh_map_host", "psgpu_field_eval", "psgpu_field_color_normal",
     "psgpu_tree_binarize", "psgpu_tree_view", "psgpu_tree_free", "psgpu_mpu_cache", "psgpu_mpu_caches_culled", "psgpu_prune_region", "psgpu_get_stats", "psgpu_measure_fp32_peak",
-    "psgpu_comm_get_unique_id", "psgpu_comm_init", "psgpu_comm_destroy", "psgpu_slab_bounds", "psgpu_polygonize_sharded", "psgpu_polygonize_sharded_host", "psgpu_mesh_gather",
+    "psgpu_comm_get_unique_id", "psgpu_comm_init", "psgpu_comm_destroy", "psgpu_slab_bounds", "psgpu_polygonize_sharded", "psgpu_polygonize_sharded_host", "psgpu_mesh_gather", "psgpu_layer_work",
 ]
 
 
@@ -143,6 +143,7 @@ def load_library():
     lib.psgpu_slab_bounds.argtypes = [C.c_int, C.c_int, C.c_int, vp, vp, vp]
     lib.psgpu_polygonize_sharded.argtypes = [vp, C.POINTER(Params), C.POINTER(_Mesh), C.POINTER(_Shard)]
     lib.psgpu_mesh_gather.argtypes = [vp, C.c_int, vp, vp, vp, vp]
+    lib.psgpu_layer_work.argtypes = [vp, vp, vp, C.c_int32]
     lib.psgpu_polygonize_sharded_host.argtypes = [vp, C.POINTER(Params), C.POINTER(_Mesh), C.POINTER(_Shard), vp, vp, vp, vp, C.c_int64, C.c_int64]
     lib.psgpu_measure_fp32_peak.argtypes = [vp, vp, vp]
     _lib = lib
@@ -366,6 +367,12 @@ class Context:
                         "psgpu_mesh_download")
             out.update(pos=pos, nrm=nrm, col=col, tri=tri)
         return out
+
+    def layer_work(self, n_layers: int):
+        """psgpu_layer_work: (evaluated, crossed) MPU counts per layer of the global lattice in the last polygonize of this context."""
+        ev, cr = np.zeros(n_layers, np.int32), np.zeros(n_layers, np.int32)
+        self._check(self.lib.psgpu_layer_work(self.h, ev.ctypes.data, cr.ctypes.data, int(n_layers)), "psgpu_layer_work")
+        return ev, cr
 
     def polygonize_sharded_host(self, params: Params, pos, nrm, col, tri) -> dict:
         """psgpu_polygonize_sharded_host (collective): the rank's share lands in HOST buffers, copies overlapping the emission kernels."""

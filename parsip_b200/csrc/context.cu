@@ -959,6 +959,36 @@ extern "C" int psgpu_prune_region(psgpu_ctx* ctx, const float* lo3, const float*
     return PSGPU_SUCCESS;
 }
 
+namespace {
+__global__ void layer_work_kernel(const psgpu::Region* __restrict__ cands, const uint32_t* __restrict__ tcount, int nCand, int nLayers,
+                                  int32_t* __restrict__ evaluated, int32_t* __restrict__ crossed) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= nCand) return;
+    const int z = cands[i].z;
+    if (z < 0 || z >= nLayers) return;
+    atomicAdd(&evaluated[z], 1);
+    if (tcount[i] != 0u) atomicAdd(&crossed[z], 1);
+}
+}  // namespace
+
+// Per-MPU-layer work of the LAST polygonize on this context (layers of the global lattice; zero outside the context's slab): MPUs
+// evaluated and MPUs that produced triangles. Summed over ranks it is the histogram psgpu_slab_bounds balances the next frame with.
+extern "C" int psgpu_layer_work(psgpu_ctx* ctx, int32_t* evaluated, int32_t* crossed, int32_t n_layers) {
+    if (!ctx || !evaluated || !crossed || n_layers <= 0) return PSGPU_PARAM_ERROR;
+    CK(cudaSetDevice(ctx->device));
+    cudaStream_t st = ctx->stream;
+    memset(evaluated, 0, sizeof(int32_t) * (size_t)n_layers); memset(crossed, 0, sizeof(int32_t) * (size_t)n_layers);
+    if (ctx->nCand <= 0) return PSGPU_SUCCESS;
+    CK(ctx->ptsF.reserve((size_t)n_layers * 8));
+    int32_t* d = ctx->ptsF.as<int32_t>();
+    CK(cudaMemsetAsync(d, 0, (size_t)n_layers * 8, st));
+    layer_work_kernel<<<(ctx->nCand + 255) / 256, 256, 0, st>>>(ctx->cands, ctx->tcount.as<uint32_t>(), ctx->nCand, n_layers, d, d + n_layers);
+    CK(cudaMemcpyAsync(evaluated, d, (size_t)n_layers * 4, cudaMemcpyDeviceToHost, st));
+    CK(cudaMemcpyAsync(crossed, d + n_layers, (size_t)n_layers * 4, cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
+    return PSGPU_SUCCESS;
+}
+
 extern "C" int psgpu_get_stats(const psgpu_ctx* ctx, psgpu_stats* out) {
     if (!ctx || !out) return PSGPU_PARAM_ERROR;
     *out = ctx->stats;
