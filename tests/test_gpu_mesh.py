@@ -381,3 +381,27 @@ def test_compat_mesh_vs_reference_as_shipped_delta(ctx, name):
           "points, reference vertices to this surface <= %.3f cell"
           % (name, differing, len(theirs), dv, ref["vertices"], int((~fin).sum()), dt, ref["triangles"], df.max(), int((df > 0).sum()), len(df), h))
     assert abs(dv) <= 0.02 * ref["vertices"] and abs(dt) <= 0.02 * ref["triangles"] and differing <= 0.25 * len(theirs)
+
+
+def test_q9_reference_mpu_reject_drops_surface_at_coarse_cells(ctx):
+    """SURVEY Q9, documented: the reference skips an MPU whose 8 corners all evaluate to exactly 0 (PS_Polygonizer.cpp:483-540). At
+    cellsize 0.2 an MPU is 1.4 wide, so a point primitive at its centre (support radius 1, iso radius 0.454) is invisible from the
+    corners (distance 1.21) and the reference loses the whole sphere; this path culls by per-MPU primitive lists and keeps it."""
+    cs = 0.2
+    a, b = bt.Point([0.0, 0.0, 0.0], (1, 0, 0)), bt.Point([1.596, 1.596, 1.596], (0, 1, 0))  # b sits at the centre of MPU (1, 1, 1)
+    root = bt.Blend(a, b)
+    _, soa, orc = scenes_small.simd_oracle(root)
+    ctx.upload(ps.linearize(bt.flatten(root), ps.SEM_SIMD, 0))
+    lo, hi = orc.bbox()
+    assert ps.lattice_dims(cs, lo, hi) == (2, 2, 2)
+    ret, ref = orc.polygonize(cs)
+    m = ctx.polygonize(compat_params(cs, lo, hi))
+    pos, nrm, col, tri, ijk, counts = gh.lattice_ordered(m)
+    ref_mpus = {tuple(k) for k in ref["mpu_idx"].tolist()}
+    gpu_mpus = {tuple(k) for k in ijk.tolist()}
+    assert (1, 1, 1) in gpu_mpus and (1, 1, 1) not in ref_mpus, (sorted(ref_mpus), sorted(gpu_mpus))
+    assert gpu_mpus - ref_mpus == {(1, 1, 1)} and m["n_triangles"] > ref["triangles"]
+    # what the reference dropped is real surface: the GPU's extra vertices lie on b's iso-sphere
+    extra = pos[np.concatenate([[0], np.cumsum(counts[:, 0])])[ijk.tolist().index([1, 1, 1])]:][:counts[ijk.tolist().index([1, 1, 1]), 0]]
+    r = np.linalg.norm(extra - np.array([1.596, 1.596, 1.596], np.float32), axis=1)
+    assert len(extra) > 20 and np.abs(r - 0.4542).max() < 0.02
