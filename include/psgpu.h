@@ -147,6 +147,20 @@ typedef struct psgpu_tree_buf psgpu_tree_buf;
 int psgpu_tree_binarize(const psgpu_tree* in, int split_always, int pad_with_null, psgpu_tree_buf** out, int32_t* n_converted);
 const psgpu_tree* psgpu_tree_view(const psgpu_tree_buf* buf);
 int psgpu_tree_free(psgpu_tree_buf* buf);
+/* CLayer::flattenTransformations (CLayerManager.cpp:604-624): pushes the transforms of n-ary operators down to the primitives and
+ * warps below them, composing scale / rotation / translation the way CAffineTransformation::add does (PS_AffineTransformation.h:
+ * 46-52: scales multiply, quaternions multiply, translations ADD). The tree must carry `srt`. Output: same topology, operators
+ * at identity, leaf srt + backward matrices rebuilt. The SIMD semantics require a flattened tree. */
+int psgpu_tree_flatten_transforms(const psgpu_tree* in, psgpu_tree_buf** out);
+/* Bounding boxes ("octrees") of all nodes as the scene API computes them: recompute = 0 CBlobNode::getOctree() on a fresh tree,
+ * recompute = 1 after CLayer::setOctreeFromBlobTree (CLayerManager.cpp:421-427, 626-645). lo3n / hi3n: 3 floats per node; the root's
+ * box is the grid domain the GUI polygonizes. */
+int psgpu_tree_octrees(const psgpu_tree* tree, int recompute, float* lo3n, float* hi3n);
+/* .scene files (INI, one [BLOBNODE id] section per node): reader = CLayer::recursive_ReadBlobNode (CLayerManager.cpp:684-800) incl.
+ * the SkeletonType spelling of the shipped Distrib/train_corrected.scene; writer = CBlobNode::saveScript (CBlobTree.cpp:40-118).
+ * root_id < 0: the first section of the file. */
+int psgpu_scene_load(const char* path, int root_id, psgpu_tree_buf** out);
+int psgpu_scene_save(const psgpu_tree* tree, const char* path);
 /* Grid-domain box of the tree the way PrepareBBoxes computes it (iso distance 0.4542 + 0.05 padding). */
 int psgpu_prepare_bboxes(const psgpu_tree* tree, float cellsize, float* lo3, float* hi3);
 uint32_t psgpu_count_mpus(float cellsize, const float* lo3, const float* hi3);

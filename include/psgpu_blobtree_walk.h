@@ -53,8 +53,8 @@ inline int node_type_from_reference(BlobNodeType t) {
 /* Owns the arrays a psgpu_tree points to. */
 struct FlatBlobTree {
     std::vector<int32_t> type, first_child, n_children, child, org_id;
-    std::vector<float> pos, dir, res, color, xform, oct_lo, oct_hi;
-    std::vector<uint8_t> has_xform;
+    std::vector<float> pos, dir, res, color, xform, oct_lo, oct_hi, srt;
+    std::vector<uint8_t> has_xform, has_srt;
     int unsupported_type;  /* reference BlobNodeType that stopped the walk, -1 if none */
 
     FlatBlobTree() : unsupported_type(-1) {}
@@ -79,7 +79,7 @@ struct FlatBlobTree {
         const size_t N = nodes.size();
         type.resize(N); first_child.resize(N); n_children.resize(N); org_id.resize(N); has_xform.resize(N);
         pos.assign(N * 3, 0.f); dir.assign(N * 3, 0.f); res.assign(N * 4, 0.f); color.assign(N * 3, 0.f);
-        xform.assign(N * 12, 0.f); oct_lo.assign(N * 3, 0.f); oct_hi.assign(N * 3, 0.f);
+        xform.assign(N * 12, 0.f); oct_lo.assign(N * 3, 0.f); oct_hi.assign(N * 3, 0.f); srt.assign(N * 10, 0.f); has_srt.assign(N, 1);
         for (size_t i = 0; i < N; i++) {
             CBlobNode* n = nodes[i];
             const int t = node_type_from_reference(n->getNodeType());
@@ -94,6 +94,12 @@ struct FlatBlobTree {
             has_xform[i] = back.isIdentity() ? 0 : 1;
             float row[4];
             for (int r = 0; r < 3; r++) { back.getRow(row, r); for (int c = 0; c < 4; c++) xform[i * 12 + r * 4 + c] = row[c]; }
+            {   // the transform as the scene API holds it (what flattenTransformations composes and saveScript writes)
+                const vec3f sc = n->getTransform().getScale(), tr = n->getTransform().getTranslate();
+                const vec4f ro = n->getTransform().getRotationVec4();
+                float* q = &srt[i * 10];
+                q[0] = sc.x; q[1] = sc.y; q[2] = sc.z; q[3] = ro.x; q[4] = ro.y; q[5] = ro.z; q[6] = ro.w; q[7] = tr.x; q[8] = tr.y; q[9] = tr.z;
+            }
             PS::COctree oct = n->getOctree();
             put3(oct_lo, i, oct.lower); put3(oct_hi, i, oct.upper);
             if (PSGPU_IS_PRIM(t)) {
@@ -117,17 +123,18 @@ struct FlatBlobTree {
     }
 
     psgpu_tree view() const {
-        psgpu_tree t;
+        psgpu_tree t = psgpu_tree();
         t.n_nodes = (int32_t)type.size(); t.root = 0;
         t.type = type.data(); t.first_child = first_child.data(); t.n_children = n_children.data(); t.child = child.data();
         t.pos = pos.data(); t.dir = dir.data(); t.res = res.data(); t.color = color.data();
         t.xform = xform.data(); t.has_xform = has_xform.data();
+        t.srt = srt.data(); t.has_srt = has_srt.data(); t.node_id = org_id.data();
         return t;
     }
 
     void clear() {
         type.clear(); first_child.clear(); n_children.clear(); child.clear(); org_id.clear();
-        pos.clear(); dir.clear(); res.clear(); color.clear(); xform.clear(); oct_lo.clear(); oct_hi.clear(); has_xform.clear();
+        pos.clear(); dir.clear(); res.clear(); color.clear(); xform.clear(); oct_lo.clear(); oct_hi.clear(); has_xform.clear(); srt.clear(); has_srt.clear();
         unsupported_type = -1;
     }
 

@@ -66,6 +66,12 @@ typedef struct psgpu_tree {
     const float* color;         /* [n_nodes*3] primitive diffuse colour */
     const float* xform;         /* [n_nodes*12] backward (world->local) 3x4 row-major; NULL = all identity */
     const uint8_t* has_xform;   /* [n_nodes] 0 = identity; NULL = all identity */
+    /* optional (NULL = absent): the scene API's own transform parametrisation, CAffineTransformation = scale xyz, rotation
+     * quaternion xyzw, translate xyz (PS_FrameWork/include/PS_AffineTransformation.h). Needed by psgpu_tree_flatten_transforms
+     * (the reference composes these triples, not matrices) and written / read by the .scene I/O. */
+    const float* srt;           /* [n_nodes*10] */
+    const uint8_t* has_srt;     /* [n_nodes] */
+    const int32_t* node_id;     /* [n_nodes] CBlobNode::getID() (the BLOBNODE section numbers of a .scene file); NULL = index */
 } psgpu_tree;
 
 #ifdef __cplusplus

@@ -143,6 +143,9 @@ void cref_walk_copy(const cref_h* h, int32_t* type, int32_t* first_child, int32_
     memcpy(color, f.color.data(), N * 12); memcpy(xform, f.xform.data(), N * 48); memcpy(has_xform, f.has_xform.data(), N);
     memcpy(oct_lo, f.oct_lo.data(), N * 12); memcpy(oct_hi, f.oct_hi.data(), N * 12);
 }
+void cref_walk_srt(const cref_h* h, float* srt10n, int32_t* ids) {
+    memcpy(srt10n, h->flat.srt.data(), h->flat.srt.size() * 4); memcpy(ids, h->flat.org_id.data(), h->flat.org_id.size() * 4);
+}
 
 void cref_octree(const cref_h* h, float* lo3, float* hi3) {
     COctree o = h->root->getOctree();
@@ -185,6 +188,59 @@ void cref_newton(cref_h* h, int64_t n, const float* p1, const float* p2, const f
 /* the scene API's own recursive evaluation, CBlobNode::fieldValue (PS_BlobTree/include/CBlobTree.h) */
 void cref_scene_field(cref_h* h, int64_t n, const float* xyz, float* out) {
     for (int64_t i = 0; i < n; i++) out[i] = h->root->fieldValue(vec3f(xyz[3 * i], xyz[3 * i + 1], xyz[3 * i + 2]));
+}
+
+/* ---- pre-linearization passes and .scene output with the reference's own classes. The recursions below restate
+ * CLayer::recursive_FlattenTransformations / recursive_RecomputeAllOctrees (ParsipHaptics/include/CLayerManager.cpp:604-645; that
+ * file needs Qt) around the reference's CAffineTransformation::add, CMatrix and COctree, which do the arithmetic. */
+static void ref_flatten(CBlobNode* node, const CAffineTransformation& transformBranch) {
+    if (node == NULL) return;
+    if (node->isOperator() && (!node->isUnary())) {
+        CAffineTransformation t = transformBranch;
+        t.add(node->getTransform());
+        node->getTransform().init();
+        for (size_t i = 0; i < node->countChildren(); i++) ref_flatten(node->getChild(i), t);
+    } else {
+        CAffineTransformation t = transformBranch;
+        t.add(node->getTransform());
+        node->getTransform().set(t);
+    }
+}
+
+static void ref_recompute_octrees(CBlobNode* node, const CMatrix& mtxBranch) {
+    if (node == NULL) return;
+    CMatrix mtxCurrent = mtxBranch;
+    mtxCurrent.multiply(node->getTransform().getForwardMatrix());
+    if (node->isOperator()) {
+        for (size_t i = 0; i < node->countChildren(); i++) ref_recompute_octrees(node->getChild(i), mtxCurrent);
+        node->computeOctree();
+    } else {
+        COctree oct = node->computeOctree();
+        oct.transform(mtxCurrent);
+        node->setOctree(oct.lower, oct.upper);
+    }
+}
+
+void cref_flatten_transforms(cref_h* h) {
+    CAffineTransformation t;
+    ref_flatten(h->root, t);
+    h->convert_rc = h->cpt->convert(h->root);
+    h->walk_rc = h->flat.walk(h->root);
+}
+
+void cref_recompute_octrees(cref_h* h) {
+    CMatrix m;
+    ref_recompute_octrees(h->root, m);
+    h->convert_rc = h->cpt->convert(h->root);
+    h->walk_rc = h->flat.walk(h->root);
+}
+
+/* CBlobNode::saveScript (recursive, PS_BlobTree/include/CBlobTree.cpp:40-118 + the node classes) into an INI file */
+int cref_save_scene(cref_h* h, const char* path) {
+    CSketchConfig* cfg = new CSketchConfig(DAnsiStr(path), CAppConfig::fmWrite);
+    const bool ok = h->root->saveScript(cfg);
+    delete cfg;
+    return ok ? 1 : 0;
 }
 
 /* CParsipOptimized::setup + run (CPolyParsipOptimized.cpp:330-410) on a caller-chosen box */

@@ -218,6 +218,7 @@ class _Tree(C.Structure):
         ("n_children", C.POINTER(C.c_int32)), ("child", C.POINTER(C.c_int32)),
         ("pos", C.POINTER(C.c_float)), ("dir", C.POINTER(C.c_float)), ("res", C.POINTER(C.c_float)),
         ("color", C.POINTER(C.c_float)), ("xform", C.POINTER(C.c_float)), ("has_xform", C.POINTER(C.c_uint8)),
+        ("srt", C.POINTER(C.c_float)), ("has_srt", C.POINTER(C.c_uint8)), ("node_id", C.POINTER(C.c_int32)),
     ]
 
 
@@ -491,6 +492,10 @@ def _load_compactref():
     lib.cref_result_counts.argtypes = [vp, vp]
     lib.cref_result_copy.argtypes = [vp] * 7
     lib.cref_export_mesh.argtypes = [vp] * 6
+    lib.cref_walk_srt.argtypes = [vp, vp, vp]
+    lib.cref_flatten_transforms.argtypes = [vp]
+    lib.cref_recompute_octrees.argtypes = [vp]
+    lib.cref_save_scene.argtypes = [vp, C.c_char_p]
     _clib = lib
     return lib
 
@@ -536,7 +541,22 @@ class CompactRef:
                    has_xform=np.zeros(N, np.uint8), oct_lo=np.zeros((N, 3), np.float32), oct_hi=np.zeros((N, 3), np.float32))
         self.lib.cref_walk_copy(self.h, *(out[k].ctypes.data for k in ("type", "first_child", "n_children", "child", "pos", "dir", "res",
                                                                         "color", "xform", "has_xform", "oct_lo", "oct_hi")))
+        out["srt"], out["node_id"] = np.zeros((N, 10), np.float32), np.zeros(N, np.int32)
+        self.lib.cref_walk_srt(self.h, out["srt"].ctypes.data, out["node_id"].ctypes.data)
+        out["has_srt"] = np.ones(N, np.uint8)
         return out
+
+    def flatten_transforms(self):
+        """CLayer::recursive_FlattenTransformations with the reference's CAffineTransformation::add, in place on the CBlobNode tree."""
+        self.lib.cref_flatten_transforms(self.h)
+
+    def recompute_octrees(self):
+        """CLayer::recursive_RecomputeAllOctrees with the reference's CMatrix / COctree, in place."""
+        self.lib.cref_recompute_octrees(self.h)
+
+    def save_scene(self, path):
+        """CBlobNode::saveScript of the root (the reference's own .scene writer)."""
+        return self.lib.cref_save_scene(self.h, os.fsencode(path))
 
     def octree(self):
         lo, hi = np.zeros(3, np.float32), np.zeros(3, np.float32)

@@ -21,7 +21,7 @@ EXPORTS = [
     "psgpu_create", "psgpu_destroy", "psgpu_last_error", "psgpu_device_count", "psgpu_linearize", "psgpu_program_free",
     "psgpu_program_info", "psgpu_program_copy", "psgpu_program_colors", "psgpu_prepare_bboxes", "psgpu_count_mpus", "psgpu_upload_program",
     "psgpu_polygonize", "psgpu_polygonize_host", "psgpu_mesh_download", "psgpu_mesh_map_host", "psgpu_field_eval", "psgpu_field_color_normal",
-    "psgpu_tree_binarize", "psgpu_tree_view", "psgpu_tree_free", "psgpu_mpu_cache", "psgpu_mpu_caches_culled", "psgpu_prune_region", "psgpu_get_stats", "psgpu_measure_fp32_peak",
+    "psgpu_tree_binarize", "psgpu_tree_view", "psgpu_tree_free", "psgpu_tree_flatten_transforms", "psgpu_tree_octrees", "psgpu_scene_load", "psgpu_scene_save", "psgpu_mpu_cache", "psgpu_mpu_caches_culled", "psgpu_prune_region", "psgpu_get_stats", "psgpu_measure_fp32_peak",
     "psgpu_comm_get_unique_id", "psgpu_comm_init", "psgpu_comm_destroy", "psgpu_slab_bounds", "psgpu_polygonize_sharded", "psgpu_polygonize_sharded_host", "psgpu_mesh_gather", "psgpu_layer_work",
 ]
 
@@ -39,6 +39,7 @@ class _Tree(C.Structure):
         ("n_children", C.POINTER(C.c_int32)), ("child", C.POINTER(C.c_int32)),
         ("pos", C.POINTER(C.c_float)), ("dir", C.POINTER(C.c_float)), ("res", C.POINTER(C.c_float)),
         ("color", C.POINTER(C.c_float)), ("xform", C.POINTER(C.c_float)), ("has_xform", C.POINTER(C.c_uint8)),
+        ("srt", C.POINTER(C.c_float)), ("has_srt", C.POINTER(C.c_uint8)), ("node_id", C.POINTER(C.c_int32)),
     ]
 
 
@@ -131,6 +132,10 @@ def load_library():
     lib.psgpu_tree_view.restype = vp
     lib.psgpu_tree_view.argtypes = [vp]
     lib.psgpu_tree_free.argtypes = [vp]
+    lib.psgpu_tree_flatten_transforms.argtypes = [vp, vp]
+    lib.psgpu_tree_octrees.argtypes = [vp, C.c_int, vp, vp]
+    lib.psgpu_scene_load.argtypes = [C.c_char_p, C.c_int, vp]
+    lib.psgpu_scene_save.argtypes = [vp, C.c_char_p]
     lib.psgpu_field_eval.argtypes = [vp, vp, C.c_int64, vp]
     lib.psgpu_field_color_normal.argtypes = [vp, vp, C.c_int64, vp, vp, vp]
     lib.psgpu_mpu_cache.argtypes = [vp, C.POINTER(Params), vp, vp, vp]
@@ -159,6 +164,12 @@ def _tree_struct(flat: dict):
     t = _Tree(flat["n_nodes"], flat["root"], p(k["type"], C.c_int32), p(k["first_child"], C.c_int32), p(k["n_children"], C.c_int32),
               p(k["child"], C.c_int32), p(k["pos"], C.c_float), p(k["dir"], C.c_float), p(k["res"], C.c_float),
               p(k["color"], C.c_float), p(k["xform"], C.c_float), p(k["has_xform"], C.c_uint8))
+    if "srt" in k and "has_srt" in k:
+        k["srt"], k["has_srt"] = np.ascontiguousarray(k["srt"], np.float32), np.ascontiguousarray(k["has_srt"], np.uint8)
+        t.srt, t.has_srt = p(k["srt"], C.c_float), p(k["has_srt"], C.c_uint8)
+    if "node_id" in k:
+        k["node_id"] = np.ascontiguousarray(k["node_id"], np.int32)
+        t.node_id = p(k["node_id"], C.c_int32)
     return t, k
 
 
@@ -248,6 +259,74 @@ def slab_bounds(n_layers: int, nranks: int, rank: int, weights=None):
     if rc != SUCCESS:
         raise PsGpuError(rc, "psgpu_slab_bounds")
     return int(b.value), int(e.value)
+
+
+def _tree_dict(lib, h) -> dict:
+    """numpy copy of a library-owned psgpu_tree_buf"""
+    v = C.cast(lib.psgpu_tree_view(h), C.POINTER(_Tree)).contents
+    N = v.n_nodes
+    arr = lambda ptr, n, dt: np.ctypeslib.as_array(ptr, shape=(n,)).astype(dt).copy() if n else np.zeros(0, dt)
+    nk = arr(v.n_children, N, np.int32)
+    fc = arr(v.first_child, N, np.int32)
+    nchild = max(1, int((fc + nk).max()) if N else 1)
+    out = dict(n_nodes=N, root=v.root, type=arr(v.type, N, np.int32), first_child=fc, n_children=nk,
+               child=arr(v.child, nchild, np.int32), pos=arr(v.pos, N * 3, np.float32).reshape(N, 3),
+               dir=arr(v.dir, N * 3, np.float32).reshape(N, 3), res=arr(v.res, N * 4, np.float32).reshape(N, 4),
+               color=arr(v.color, N * 3, np.float32).reshape(N, 3), xform=arr(v.xform, N * 12, np.float32).reshape(N, 12),
+               has_xform=arr(v.has_xform, N, np.uint8))
+    if v.srt:
+        out["srt"] = arr(v.srt, N * 10, np.float32).reshape(N, 10)
+        out["has_srt"] = arr(v.has_srt, N, np.uint8) if v.has_srt else np.ones(N, np.uint8)
+    if v.node_id:
+        out["node_id"] = arr(v.node_id, N, np.int32)
+    return out
+
+
+def flatten_transforms(flat: dict) -> dict:
+    """psgpu_tree_flatten_transforms (CLayer::flattenTransformations); the tree must carry srt / has_srt."""
+    lib = load_library()
+    t, keep = _tree_struct(flat)
+    h = C.c_void_p()
+    rc = lib.psgpu_tree_flatten_transforms(C.byref(t), C.byref(h))
+    if rc != SUCCESS:
+        raise PsGpuError(rc, "psgpu_tree_flatten_transforms")
+    try:
+        return _tree_dict(lib, h)
+    finally:
+        lib.psgpu_tree_free(h)
+
+
+def tree_octrees(flat: dict, recompute: bool = False):
+    """psgpu_tree_octrees: (lo, hi) boxes of all nodes as the scene API computes them; [root] is the grid domain."""
+    lib = load_library()
+    t, keep = _tree_struct(flat)
+    N = flat["n_nodes"]
+    lo, hi = np.zeros((N, 3), np.float32), np.zeros((N, 3), np.float32)
+    rc = lib.psgpu_tree_octrees(C.byref(t), int(recompute), lo.ctypes.data, hi.ctypes.data)
+    if rc != SUCCESS:
+        raise PsGpuError(rc, "psgpu_tree_octrees")
+    return lo, hi
+
+
+def scene_load(path: str, root_id: int = -1) -> dict:
+    """psgpu_scene_load: a .scene file as a flat tree (with srt and node ids)."""
+    lib = load_library()
+    h = C.c_void_p()
+    rc = lib.psgpu_scene_load(os.fsencode(path), int(root_id), C.byref(h))
+    if rc != SUCCESS:
+        raise PsGpuError(rc, "psgpu_scene_load " + path)
+    try:
+        return _tree_dict(lib, h)
+    finally:
+        lib.psgpu_tree_free(h)
+
+
+def scene_save(flat: dict, path: str):
+    lib = load_library()
+    t, keep = _tree_struct(flat)
+    rc = lib.psgpu_scene_save(C.byref(t), os.fsencode(path))
+    if rc != SUCCESS:
+        raise PsGpuError(rc, "psgpu_scene_save " + path)
 
 
 def count_mpus(cellsize, lo, hi) -> int:

@@ -75,7 +75,7 @@ struct FlatTree {
     std::vector<int32_t> type, first, nk, child;
     std::vector<float> pos, dir, res, color, xform;
     std::vector<uint8_t> hasxf;
-    psgpu_tree t;
+    psgpu_tree t{};
 };
 
 int buildTree(const SOABlobPrims& P, const SOABlobPrimMatrices& M, const SOABlobOps& O, FlatTree& F) {

@@ -898,18 +898,12 @@ extern "C" int psgpu_mpu_cache(psgpu_ctx* ctx, const psgpu_params* params, const
     fo.edgeMask = ctx->edgeMask.as<uint32_t>(); fo.edgePrefix = ctx->edgePrefix.as<uint16_t>();
     fo.mixedList = ctx->mixedList.as<uint32_t>(); fo.counters = ctx->counters.as<uint32_t>();
     psgpu::launch_field_kernel(G, ctx->regionsA.as<psgpu::Region>(), 1, ctx->pool.as<float4>(), fo, ctx->progQuads, ctx->hasWarps, ctx->numSMs, st);
+    CK(ctx->ptsCol.reserve(512));
+    psgpu::launch_cube_cases(G, ctx->fv.as<float>(), ctx->ptsCol.as<uint8_t>(), st);  // the device classifier, not a host re-statement
     CK(cudaMemcpyAsync(fv512, ctx->fv.p, 2048, cudaMemcpyDeviceToHost, st));
+    CK(cudaMemcpyAsync(case343, ctx->ptsCol.p, 343, cudaMemcpyDeviceToHost, st));
     CK(cudaStreamSynchronize(st));
     CK(cudaGetLastError());
-    for (int i = 0; i < 7; i++) for (int j = 0; j < 7; j++) for (int k = 0; k < 7; k++) {
-        int cfg = 0;
-        for (int b = 0; b < 8; b++) {
-            const float f = fv512[(i + ((b >> 2) & 1)) * 8 + (j + ((b >> 1) & 1)) * 64 + (k + (b & 1))];
-            const bool in = G.insideGE ? (f >= G.iso) : (f > G.iso);
-            if (in) cfg |= 1 << b;
-        }
-        case343[i * 49 + j * 7 + k] = (uint8_t)cfg;
-    }
     return PSGPU_SUCCESS;
 }
 

@@ -515,6 +515,23 @@ __global__ void halo_build_kernel(GridParams G, const int32_t* __restrict__ cand
     }
 }
 
+// parity hook (psgpu_mpu_cache): the cube cases of ONE MPU from its field cache, by the classifier the emission kernels use
+// (inside bits as bytes, cell_case) - so the hook checks the device classification, not a host re-statement of it
+__global__ void cube_cases_kernel(GridParams G, const float* __restrict__ fv, uint8_t* __restrict__ case343) {
+    __shared__ uint8_t B[64];
+    const int t = threadIdx.x;  // 64 threads: one z-column each
+    uint32_t inb = 0;
+    for (int n = 0; n < 8; n++) inb |= (is_inside(G, fv[t * 8 + n]) ? 1u : 0u) << n;
+    B[t] = (uint8_t)inb;
+    __syncthreads();
+    for (int c = t; c < 343; c += 64) {
+        const int x = c / 49, y = (c - x * 49) / 7, z = c - x * 49 - y * 7;
+        case343[c] = (uint8_t)cell_case(B, x, y, z);
+    }
+}
+
+void launch_cube_cases(const GridParams& G, const float* fv, uint8_t* case343, cudaStream_t st) { cube_cases_kernel<<<1, 64, 0, st>>>(G, fv, case343); }
+
 void launch_halo_build(const GridParams& G, const int32_t* candOfMpu, const FieldOutputs& fo, const uint32_t* vbase, uint32_t* hVbase,
                        uint32_t* hMask, uint16_t* hPrefix, int nxy, cudaStream_t st) {
     if (nxy <= 0) return;

@@ -100,6 +100,7 @@ void launch_program_stats(const Region* cands, int nCand, const float4* pool, co
 float run_fp32_peak(int numSMs, cudaStream_t st, float* ms_out);
 
 // emit.cu
+void launch_cube_cases(const GridParams& G, const float* fv, uint8_t* case343, cudaStream_t st);
 void launch_halo_build(const GridParams& G, const int32_t* candOfMpu, const FieldOutputs& fo, const uint32_t* vbase, uint32_t* hVbase,
                        uint32_t* hMask, uint16_t* hPrefix, int nxy, cudaStream_t st);
 void launch_emit_kernels(const GridParams& G, const Region* cands, const float4* pool, const float* colorTab, const FieldOutputs& fo,

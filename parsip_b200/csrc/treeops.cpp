@@ -15,14 +15,7 @@
 
 #include "../../include/psgpu.h"
 
-struct psgpu_tree_buf {
-    std::vector<int32_t> type, first, nk, child;
-    std::vector<float> pos, dir, res, color, xform;
-    std::vector<uint8_t> hasxf;
-    std::vector<std::vector<int32_t>> kids;  // while building
-    psgpu_tree view;
-    int converted = 0;
-};
+#include "tree_buf.h"
 
 namespace {
 
@@ -132,8 +125,7 @@ extern "C" int psgpu_tree_binarize(const psgpu_tree* in, int split_always, int p
     }
     if (out->child.empty()) out->child.push_back(0);
     out->kids.clear(); out->kids.shrink_to_fit();
-    out->view = psgpu_tree{N, 0, out->type.data(), out->first.data(), out->nk.data(), out->child.data(), out->pos.data(), out->dir.data(),
-                           out->res.data(), out->color.data(), out->xform.data(), out->hasxf.data()};
+    out->finish(0);
     if (n_converted) *n_converted = out->converted;
     *outp = out;
     return PSGPU_SUCCESS;

@@ -10,7 +10,7 @@ import numpy as np
 import pytest
 
 import gpu_helpers as gh
-from test_compactref import COLOR_UNPINNED, FIELD_FLOOR, NAMES, golden, golden_tree
+from test_compactref import COLOR_UNPINNED, FIELD_FLOOR, GOLDEN_NAMES as NAMES, golden, golden_tree
 import parsip_b200 as ps
 
 pytestmark = pytest.mark.gpu
@@ -127,3 +127,47 @@ def test_native_mesh_vs_reference_mesh_hausdorff(ctx, name):
     assert h < 0.75, h  # corner-collapsed vertices: up to ~sqrt(3)/2 cell off the edge crossing they stand for
     print("%s: native residual vs reference field max %.2e; reference vertices to native surface: max %.3f cell (reference Newton residual %.1e)"
           % (name, res.max(), h, ref_res))
+
+
+def test_train_model_counts_vs_reference_run(ctx):
+    """The reference's one real model at the cell size of its recorded runs (Distrib/ParsipHaptics_Release.csv:2: 0.13, 146 352 faces,
+    82 370 vertices with the older 16^3-MPU build). tools/gen_golden.py repeated that run with the reference's own code as built here
+    (8^3 MPUs, GUI domain from setOctreeFromBlobTree) and stored its counts; the GPU in the same mode (Newton roots, per-MPU vertices)
+    must reproduce the triangle count of every MPU the reference kept, the native mesh the same faces with shared vertices."""
+    g = golden("train")
+    upload(ctx, g)
+    lo, hi, cs = g["gui_lo"], g["gui_hi"], float(g["gui_cellsize"])
+    m = ctx.polygonize(ps.Params.make(cs, lo, hi, root_mode=ps.ROOT_NEWTON_REF, coord_mode=ps.COORD_MPU_LOCAL, output=ps.OUT_MPU), allow_over_capacity=True)
+    ref_t, ref_v = int(g["gui_triangles"]), int(g["gui_vertices"])
+    # the reference's octree filter may drop surface MPUs (Q12); never the other way round
+    assert m["n_triangles"] >= ref_t and (m["n_triangles"] - ref_t) <= 0.02 * ref_t, (m["n_triangles"], ref_t)
+    assert abs(m["n_vertices"] - ref_v) <= 0.02 * ref_v, (m["n_vertices"], ref_v)
+    assert abs(m["n_triangles"] - 146352) <= 0.02 * 146352  # and the recorded run, loosely (other MPU size, same cells)
+    nat = ctx.polygonize(ps.Params.make(cs, lo, hi))
+    assert nat["n_triangles"] == m["n_triangles"] and nat["n_vertices"] < m["n_vertices"]
+    print("train @0.13: reference build %d triangles / %d vertices, recorded 146352 / 82370; GPU Newton mode %d / %d, native %d / %d"
+          % (ref_t, ref_v, m["n_triangles"], m["n_vertices"], nat["n_triangles"], nat["n_vertices"]))
+
+
+def test_parsipcmd_cli_on_a_scene_file(ctx, tmp_path):
+    """parsip_b200/parsipcmd (the ParsipCmd role of BASELINE configs[0]): .scene file -> flatten -> octree domain -> polygonize; its
+    counts must equal the library called directly on the same tree and domain."""
+    import subprocess
+    g = golden("train")
+    tree = golden_tree(g)
+    tree["srt"], tree["has_srt"], tree["node_id"] = g["tree_srt"], np.ones(int(g["n_nodes"]), np.uint8), g["tree_node_id"]
+    path = str(tmp_path / "train.scene")
+    ps.scene_save(tree, path)
+    exe = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "parsip_b200", "parsipcmd")
+    r = subprocess.run([exe, path, "0.13", "--reps", "3", "--obj", str(tmp_path / "train.obj")], capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stdout + r.stderr
+    row = r.stdout.strip().splitlines()[-1].split(",")
+    faces, verts = int(row[10]), int(row[11])
+    t2 = ps.flatten_transforms(ps.scene_load(path))
+    lo, hi = ps.tree_octrees(t2, True)
+    ctx.upload(ps.linearize(t2, ps.SEM_SCALAR, ps.LIN_REASSOCIATE))
+    m = ctx.polygonize(ps.Params.make(0.13, lo[0], hi[0]))
+    assert (faces, verts) == (m["n_triangles"], m["n_vertices"]) and int(row[1]) == 95
+    assert abs(faces - 146352) <= 0.02 * 146352  # ParsipHaptics_Release.csv:2, loosely (%f scene precision, other MPU size)
+    lines = open(tmp_path / "train.obj").read().splitlines()
+    assert sum(l.startswith("v ") for l in lines) == verts and sum(l.startswith("f ") for l in lines) == faces

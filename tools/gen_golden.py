@@ -68,10 +68,23 @@ SCALAR_CELLS = 36
 WALK_KEYS = ("type", "first_child", "n_children", "child", "pos", "dir", "res", "color", "xform", "has_xform", "oct_lo", "oct_hi")
 
 
+TRAIN_SCENE = "/root/reference/Parsip100/Distrib/train_corrected.scene"
+
+
+def train_flat():
+    """The reference's one real model (Distrib/train_corrected.scene, 95 primitives), read by the product's .scene reader and put
+    through the GUI's flattenTransformations - the tree CLayer hands to its polygonizers."""
+    import parsip_b200 as ps
+    return ps.flatten_transforms(ps.scene_load(TRAIN_SCENE))
+
+
 def main_scalar():
     out = os.path.join(ROOT, "tests", "golden")
-    for name, mk in scenes_small.COMPACTREF_SCENES.items():
-        ref = CompactRef(bt.flatten(mk()))
+    todo = [(name, (lambda mk=mk: bt.flatten(mk()))) for name, mk in scenes_small.COMPACTREF_SCENES.items()]
+    if os.path.exists(TRAIN_SCENE):
+        todo.append(("train", train_flat))
+    for name, mk_flat in todo:
+        ref = CompactRef(mk_flat())
         assert ref.convert_rc >= 0 and ref.walk_rc == 0, (name, ref.convert_rc, ref.walk_rc)
         w = ref.walk()
         lo, hi = ref.octree()
@@ -90,6 +103,16 @@ def main_scalar():
         m = ref.polygonize(lo, hi, float(cs), nthreads=1)
         ok, em = ref.export_mesh()
         assert ok and em["vertices"] == m["vertices"] and em["triangles"] == m["triangles"]
+        extra = {}
+        if name == "train":
+            # the run the reference recorded (Distrib/ParsipHaptics_Release.csv:2: cell size 0.13, 146 352 faces / 82 370 vertices with its
+            # older 16^3 MPUs) repeated with today's 8^3 build on the GUI's domain (setOctreeFromBlobTree): counts only
+            ref.recompute_octrees()
+            glo, ghi = ref.octree()
+            big = ref.polygonize(glo, ghi, 0.13, nthreads=0)
+            extra = dict(gui_lo=glo, gui_hi=ghi, gui_cellsize=np.float32(0.13), gui_mpus=np.int64(big["mpus"]), gui_vertices=np.int64(big["vertices"]),
+                         gui_triangles=np.int64(big["triangles"]))
+            print("train @0.13 on", glo, ghi, "->", big["mpus"], "MPUs", big["vertices"], "vertices", big["triangles"], "triangles")
         np.savez_compressed(
             os.path.join(out, "scalar_%s.npz" % name),
             n_nodes=np.int32(w["n_nodes"]), **{"tree_" + k: w[k] for k in WALK_KEYS},
@@ -97,7 +120,8 @@ def main_scalar():
             scene_field=ref.scene_field(pts), newton_p1=cand[cross], newton_p2=p2[cross], newton_f1=f1[cross], newton_f2=f2[cross],
             newton_root=root, newton_field=fr, newton_evals=ev, cellsize=cs, mesh_mpus=np.int64(m["mpus"]),
             mesh_field_evals=np.int64(m["field_evals"]), mesh_origin=m["mpu_origin"], mesh_counts=m["mpu_counts"], mesh_pos=m["pos"],
-            mesh_nrm=m["nrm"], mesh_col=m["col"], mesh_tri=m["tri"], export_pos_sha=sha(em["pos"]), export_tri_sha=sha(em["tri"]))
+            mesh_nrm=m["nrm"], mesh_col=m["col"], mesh_tri=m["tri"], export_pos_sha=sha(em["pos"]), export_tri_sha=sha(em["tri"]),
+            tree_srt=w["srt"], tree_node_id=w["node_id"], **extra)
         print("scalar", name, "prims", ref.n_prims, "ops", ref.n_ops, "surface pts", int((f > 0.5).sum()), "newton edges", len(cross),
               "mesh", m["mpus"], m["vertices"], m["triangles"])
 
