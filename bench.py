@@ -272,7 +272,61 @@ def measure_other_configs(ps, bt, scenes, ctx):
         gpu_ms.append(ctx.stats()["ms_total"])
     out["configs[4] anim@256^3, 60 frames, ms per frame (linearize + upload + polygonize, wall clock)"] = {
         "ms_per_frame_median": float(np.median(frames[5:])), "ms_per_frame_p99": float(np.percentile(frames[5:], 99)), "gpu_ms_median": float(np.median(gpu_ms[5:]))}
+    out.update(measure_train(ps, ctx))
     return out
+
+
+TRAIN_GOLDEN = os.path.join(ROOT, "tests", "golden", "scalar_train.npz")
+TRAIN_KEYS = ("type", "first_child", "n_children", "child", "pos", "dir", "res", "color", "xform", "has_xform", "oct_lo", "oct_hi")
+
+
+def train_tree():
+    """The reference's one real model (Distrib/train_corrected.scene: 95 primitives, 95 operators, the scene its only recorded timings
+    are on) as the committed fixture carries it: the flat tree read back from the reference's CBlobNode objects, and the GUI's domain."""
+    g = np.load(TRAIN_GOLDEN)
+    t = {k: g["tree_" + k] for k in TRAIN_KEYS}
+    t["n_nodes"], t["root"] = int(g["n_nodes"]), 0
+    t["srt"], t["has_srt"], t["node_id"] = g["tree_srt"], np.ones(int(g["n_nodes"]), np.uint8), g["tree_node_id"]
+    return t, g
+
+
+def measure_train(ps, ctx):
+    """Scalar-path workload of the reference's recorded runs (ParsipHaptics_Release.csv: cell size 0.13; 0.53 / 0.14 s on 1 / 4 cores of
+    the authors' 2.66 GHz quad-core, 146 352 faces): native indexed mesh and the reference-Newton per-MPU mode."""
+    if not os.path.exists(TRAIN_GOLDEN):
+        return {}
+    t, g = train_tree()
+    ctx.upload(ps.linearize(t, ps.SEM_SCALAR, ps.LIN_REASSOCIATE))
+    lo, hi, cs = g["gui_lo"], g["gui_hi"], float(g["gui_cellsize"])
+    res = {}
+    for label, kw in (("native", {}), ("reference_newton_per_mpu", dict(root_mode=ps.ROOT_NEWTON_REF, coord_mode=ps.COORD_MPU_LOCAL, output=ps.OUT_MPU))):
+        ms, m = [], None
+        for _ in range(9):
+            m = ctx.polygonize(ps.Params.make(cs, lo, hi, **kw), download=False, allow_over_capacity=bool(kw))
+            ms.append(ctx.stats()["ms_total"])
+        res[label] = {"ms": float(np.median(ms[3:])), "vertices": m["n_vertices"], "triangles": m["n_triangles"]}
+    res["recorded_by_the_reference"] = {"s_1_core": 0.53, "s_4_cores": 0.14, "triangles": 146352, "vertices": 82370,
+                                        "source": "Distrib/ParsipHaptics_Release.csv:2-17 (older 16^3-MPU build, Intel quad-core 2.66 GHz)"}
+    res["reference_build_counts_in_fixture"] = {"triangles": int(g["gui_triangles"]), "vertices": int(g["gui_vertices"])}
+    return {"train_corrected.scene @ cell size 0.13 (scalar path, CParsipOptimized's recorded workload)": res}
+
+
+def train_reference_cpu():
+    """The reference's OWN scalar polygonizer (oracle/_ref/libcompactref.so: CParsipOptimized + COMPACTBLOBTREE compiled unmodified) on the
+    train model at 0.13 with every host thread: best of 3 wall-clock runs of setup + run."""
+    from oracle import pyoracle
+    if not (os.path.exists(TRAIN_GOLDEN) and os.path.exists(os.path.join(ROOT, "oracle", "_ref", "libcompactref.so"))):
+        return None
+    t, g = train_tree()
+    ref = pyoracle.CompactRef(t)
+    ref.recompute_octrees()  # CLayer::setOctreeFromBlobTree, as the GUI does before polygonizing
+    best, m = 1e9, None
+    for _ in range(3):
+        t0 = time.perf_counter()
+        m = ref.polygonize(g["gui_lo"], g["gui_hi"], float(g["gui_cellsize"]), nthreads=0)
+        best = min(best, time.perf_counter() - t0)
+    return {"ms": best * 1e3, "threads": os.cpu_count() or 1, "triangles": m["triangles"], "vertices": m["vertices"], "mpus_with_surface": m["mpus"],
+            "kind": "reference (CParsipOptimized::run compiled from the reference's sources, TBB replaced by the thread-pool shim; includes the result copy-out)"}
 
 
 def run_gpu(args):
@@ -536,6 +590,10 @@ def run_gpu(args):
         out["cpu_baseline"] = {"value": rst["mpus"] * 343.0 / tsec, "unit": "cells/s", "cores": os.cpu_count() or 1, "kind": kind,
                                "sample": describe(blocks, rdims, rst) + ", %.1f s" % tsec,
                                "field_evals_per_s": rst["simd_evals"] * 4.0 / tsec, "triangles_per_s": rst["triangles"] / tsec}
+        try:
+            out["cpu_baseline"]["train_scene_cell_0.13"] = train_reference_cpu()
+        except Exception as e:
+            out["cpu_baseline"]["train_scene_cell_0.13"] = {"error": repr(e)}
         try:
             out["cpu_baseline"]["mesh_check"] = mesh_check(ps, ctx, prog, sc, kind, rcs, rdims, lo, hi, cs)
         except Exception as e:
