@@ -140,6 +140,12 @@ void PrintThreadResults(int ctAttempts, U32* lpThreadProcessed = 0, U32* lpThrea
 int FieldValues(const SOABlobPrims& blobPrims, const SOABlobPrimMatrices& blobPrimMatrices, const SOABlobOps& blobOps, const float* xyz, int n,
                 float* outField);
 
+// FieldComputer::computeRootNewtonRaphson (PS_Polygonizer.h:311-314, .cpp:1625-1681) for n point pairs at once: p1 / p2 are 3 floats per
+// pair, fp1 / fp2 their field values; per pair the root, the field there and the member's return value ((rounds) * 4 field evaluations).
+int RootsNewtonRaphson(const SOABlobPrims& blobPrims, const SOABlobPrimMatrices& blobPrimMatrices, const SOABlobOps& blobOps, const float* p1,
+                       const float* p2, const float* fp1, const float* fp2, int n, float* outRoot, float* outField, int* outEvals,
+                       float target_field, int iterations);
+
 }  // namespace SIMDPOLY
 }  // namespace PS
 

@@ -14,6 +14,8 @@
  *   psgpu_field_eval         <- FieldComputer::fieldValue          PS_SimdPoly/include/PS_Polygonizer.cpp:1184-1376
  *                               COMPACTBLOBTREE::fieldvalue        ParsipHaptics/include/CompactBlobTree.cpp:476-487
  *   psgpu_field_color_normal <- FieldComputer::fieldValueAndColor + normal   PS_Polygonizer.cpp:1378-1622
+ *   psgpu_newton_roots       <- FieldComputer::computeRootNewtonRaphson   PS_SimdPoly/include/PS_Polygonizer.cpp:1625-1681
+ *                               ComputeRootNewtonRaphsonVEC4       ParsipHaptics/include/CompactBlobTree.cpp:1581-1622
  *   psgpu_get_stats          <- PrintThreadResults / MPUSTATS      PS_SimdPoly/include/PS_Polygonizer.cpp:414-428
  *
  * Conventions: every function returns an int status (PSGPU_SUCCESS == 1, errors negative, the
@@ -208,6 +210,12 @@ int psgpu_mesh_map_host(psgpu_ctx* ctx, const float** pos, const float** nrm, co
 /* Parity hooks: field (and colour / normal) at arbitrary HOST points with the full, unculled program. */
 int psgpu_field_eval(psgpu_ctx* ctx, const float* xyz, int64_t n, float* f_out);
 int psgpu_field_color_normal(psgpu_ctx* ctx, const float* xyz, int64_t n, float* f, float* col, float* nrm);
+/* Shrink-wrap Newton root search between n HOST point pairs (p1, p2: 3 floats each; f1, f2: their field values) with the full program, in
+ * the uploaded program's semantics: PSGPU_SEM_SIMD = FieldComputer::computeRootNewtonRaphson (public in the reference, not called by its
+ * Polygonize), PSGPU_SEM_SCALAR = ComputeRootNewtonRaphsonVEC4 (what CParsipOptimized places vertices with). Outputs per pair: root (3
+ * floats), the field there, and the reference's return value (field evaluations spent, (rounds) * 4; -1 if iterations <= 0). */
+int psgpu_newton_roots(psgpu_ctx* ctx, const float* p1, const float* p2, const float* f1, const float* f2, int64_t n, float target_field,
+                       int iterations, float* root_out, float* field_out, int32_t* evals_out);
 /* Field cache (fv[i*8 + j*64 + k]) and cube cases (cell i*49 + j*7 + k) of one MPU, for parity tests. */
 int psgpu_mpu_cache(psgpu_ctx* ctx, const psgpu_params* params, const int32_t* ijk, float* fv512, uint8_t* case343);
 /* Parity hook: runs cull + field for `params` and returns the lattice index and the 512-value field cache of EVERY evaluated

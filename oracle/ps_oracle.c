@@ -537,6 +537,38 @@ static void simd_normal(const pso_simd* s, simd_scratch* w, float x, float y, fl
     n[0] = nx * inv; n[1] = ny * inv; n[2] = nz * inv;
 }
 
+/* FieldComputer::computeRootNewtonRaphson, SP/PS_Polygonizer.cpp:1625-1681, with gradient() :1576-1596: every operand is a point
+ * broadcast to all lanes, lane 0 is returned. The field at the start point is the caller's fp1 / fp2, not re-evaluated. */
+void pso_simd_newton(const pso_simd* s, int64_t n, const float* p1, const float* p2, const float* fp1, const float* fp2,
+                     float target, int iterations, float* root, float* root_field, int32_t* evals) {
+    simd_scratch w;
+    scratch_init(s, &w);
+    const float delta = 0.001f; /* FIELDVALUE_EPSILON, SP/PS_Polygonizer.h:60 */
+    const float deltaInv = 1.0f / delta;
+    for (int64_t k = 0; k < n; k++) {
+        if (iterations <= 0) { evals[k] = -1; continue; }
+        float x, y, z, field;
+        if (fabsf(fp1[k] - target) < fabsf(fp2[k] - target)) { x = p1[k * 3]; y = p1[k * 3 + 1]; z = p1[k * 3 + 2]; field = fp1[k]; }
+        else { x = p2[k * 3]; y = p2[k * 3 + 1]; z = p2[k * 3 + 2]; field = fp2[k]; }
+        int i = 0;
+        for (i = 0; i < iterations; i++) {
+            float dX = simd_field_bcast(s, &w, x + delta, y, z);
+            float dY = simd_field_bcast(s, &w, x, y + delta, z);
+            float dZ = simd_field_bcast(s, &w, x, y, z + delta);
+            float gx = (dX - field) * deltaInv, gy = (dY - field) * deltaInv, gz = (dZ - field) * deltaInv;
+            float den = gx * gx; den = den + gy * gy; den = den + gz * gz;
+            float g = (target - field) / den;
+            x = x + gx * g; y = y + gy * g; z = z + gz * g;
+            field = simd_field_bcast(s, &w, x, y, z);
+            if (fabsf(field - target) < delta) break;
+        }
+        root[k * 3] = x; root[k * 3 + 1] = y; root[k * 3 + 2] = z;
+        root_field[k] = field;
+        evals[k] = (i + 1) * 4;
+    }
+    scratch_free(&w);
+}
+
 void pso_simd_field(const pso_simd* s, int64_t n, const float* xyz, float* out) {
     simd_scratch w;
     scratch_init(s, &w);

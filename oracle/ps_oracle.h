@@ -64,6 +64,8 @@ void pso_simd_get_op_boxes(const pso_simd* s, float* out6);
 void pso_simd_pad_op_boxes(pso_simd* s, float pad);
 uint32_t pso_count_mpus(float cellsize, const float* lo, const float* hi);
 void pso_simd_field(const pso_simd* s, int64_t n, const float* xyz, float* out);
+void pso_simd_newton(const pso_simd* s, int64_t n, const float* p1, const float* p2, const float* fp1, const float* fp2,
+                     float target, int iterations, float* root, float* root_field, int32_t* evals);
 void pso_simd_field_color_normal(const pso_simd* s, int64_t n, const float* xyz, float* f, float* col, float* nrm);
 /* field cache (z contiguous: fv[i*8 + j*64 + k]) and cube cases (cell i*49 + j*7 + k) of one MPU */
 void pso_simd_mpu_cache(const pso_simd* s, float cellsize, const int32_t* ijk, float* fv512, uint8_t* case343);

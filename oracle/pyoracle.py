@@ -68,6 +68,8 @@ def _load_ref(path):
     lib.psref_count_mpus.argtypes = [C.c_void_p, C.c_float]
     lib.psref_field.argtypes = [C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p]
     lib.psref_field_color_normal.argtypes = [C.c_void_p, C.c_int64] + [C.c_void_p] * 4
+    if hasattr(lib, "psref_newton"):
+        lib.psref_newton.argtypes = [C.c_void_p, C.c_int64] + [C.c_void_p] * 4 + [C.c_float, C.c_int] + [C.c_void_p] * 3
     lib.psref_polygonize.argtypes = [C.c_void_p, C.c_float, C.c_void_p]
     lib.psref_mpu_info.argtypes = [C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p]
     lib.psref_mpu_copy.argtypes = [C.c_void_p, C.c_uint32] + [C.c_void_p] * 4
@@ -150,6 +152,17 @@ class RefScene:
         out = np.zeros(len(xyz), np.float32)
         self.lib.psref_field(self.h, len(xyz), xyz.ctypes.data, out.ctypes.data)
         return out
+
+    def newton(self, p1, p2, f1, f2, target=0.5, iterations=8):
+        """FieldComputer::computeRootNewtonRaphson per point pair: (root, field at the root, the member's return value)."""
+        p1 = np.ascontiguousarray(p1, np.float32).reshape(-1, 3)
+        p2 = np.ascontiguousarray(p2, np.float32).reshape(-1, 3)
+        f1, f2 = np.ascontiguousarray(f1, np.float32), np.ascontiguousarray(f2, np.float32)
+        n = len(p1)
+        root, fr, ev = np.zeros((n, 3), np.float32), np.zeros(n, np.float32), np.zeros(n, np.int32)
+        self.lib.psref_newton(self.h, n, p1.ctypes.data, p2.ctypes.data, f1.ctypes.data, f2.ctypes.data, float(target), int(iterations),
+                    root.ctypes.data, fr.ctypes.data, ev.ctypes.data)
+        return root, fr, ev
 
     def field_color_normal(self, xyz):
         xyz = np.ascontiguousarray(xyz, np.float32).reshape(-1, 3)
@@ -258,6 +271,7 @@ def _load_oracle():
     lib.pso_count_mpus.argtypes = [C.c_float, vp, vp]
     lib.pso_simd_field.argtypes = [vp, C.c_int64, vp, vp]
     lib.pso_simd_field_color_normal.argtypes = [vp, C.c_int64, vp, vp, vp, vp]
+    lib.pso_simd_newton.argtypes = [vp, C.c_int64, vp, vp, vp, vp, C.c_float, C.c_int, vp, vp, vp]
     lib.pso_simd_mpu_cache.argtypes = [vp, C.c_float, vp, vp, vp]
     lib.pso_simd_polygonize.argtypes = [vp, C.c_float, C.c_int, vp, vp, C.c_int, vp]
     lib.pso_simd_result_counts.argtypes = [vp, vp]
@@ -350,6 +364,17 @@ class SimdOracle:
         out = np.zeros(len(xyz), np.float32)
         self.lib.pso_simd_field(self.h, len(xyz), xyz.ctypes.data, out.ctypes.data)
         return out
+
+    def newton(self, p1, p2, f1, f2, target=0.5, iterations=8):
+        """FieldComputer::computeRootNewtonRaphson per point pair: (root, field at the root, the member's return value)."""
+        p1 = np.ascontiguousarray(p1, np.float32).reshape(-1, 3)
+        p2 = np.ascontiguousarray(p2, np.float32).reshape(-1, 3)
+        f1, f2 = np.ascontiguousarray(f1, np.float32), np.ascontiguousarray(f2, np.float32)
+        n = len(p1)
+        root, fr, ev = np.zeros((n, 3), np.float32), np.zeros(n, np.float32), np.zeros(n, np.int32)
+        self.lib.pso_simd_newton(self.h, n, p1.ctypes.data, p2.ctypes.data, f1.ctypes.data, f2.ctypes.data, float(target), int(iterations),
+                    root.ctypes.data, fr.ctypes.data, ev.ctypes.data)
+        return root, fr, ev
 
     def field_color_normal(self, xyz):
         xyz = np.ascontiguousarray(xyz, np.float32).reshape(-1, 3)

@@ -235,6 +235,19 @@ void psref_field_color_normal(psref_scene* s, int64_t n, const float* xyz, float
     }
 }
 
+// FieldComputer::computeRootNewtonRaphson (PS_Polygonizer.cpp:1625-1681), called as declared; evals = its return value.
+void psref_newton(psref_scene* s, int64_t n, const float* p1, const float* p2, const float* fp1, const float* fp2, float target,
+                  int iterations, float* root, float* root_field, int32_t* evals) {
+    FieldComputer* fc = get_fc(s);
+    for (int64_t i = 0; i < n; i++) {
+        svec3f a(p1[i*3], p1[i*3+1], p1[i*3+2]), b(p2[i*3], p2[i*3+1], p2[i*3+2]), out(0.0f, 0.0f, 0.0f);
+        float of = 0.0f;
+        evals[i] = fc->computeRootNewtonRaphson(a, b, fp1[i], fp2[i], out, of, target, iterations);
+        root[i*3] = out.x; root[i*3+1] = out.y; root[i*3+2] = out.z;
+        root_field[i] = of;
+    }
+}
+
 // The reference's Polygonize (PS_Polygonizer.cpp:315-385), whole grid, into its own PolyMPUs.
 // stats: [0] ctMPUs [1] MPUs with triangles [2] vertices [3] triangles [4] sum ctFieldEvals (SIMD evals)
 int psref_polygonize(psref_scene* s, float cellsize, int64_t* stats) {

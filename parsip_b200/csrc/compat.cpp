@@ -341,6 +341,14 @@ int FieldValues(const SOABlobPrims& P, const SOABlobPrimMatrices& M, const SOABl
     return psgpu_field_eval(g_ctx, xyz, n, outField);
 }
 
+int RootsNewtonRaphson(const SOABlobPrims& P, const SOABlobPrimMatrices& M, const SOABlobOps& O, const float* p1, const float* p2, const float* fp1,
+                       const float* fp2, int n, float* outRoot, float* outField, int* outEvals, float target_field, int iterations) {
+    std::lock_guard<std::mutex> guard(g_lock);
+    int rc = uploadScene(P, M, O);
+    if (rc != RET_SUCCESS) return rc;
+    return psgpu_newton_roots(g_ctx, p1, p2, fp1, fp2, n, target_field, iterations, outRoot, outField, outEvals);
+}
+
 }  // namespace SIMDPOLY
 }  // namespace PS
 

@@ -878,6 +878,30 @@ extern "C" int psgpu_field_color_normal(psgpu_ctx* ctx, const float* xyz, int64_
     return PSGPU_SUCCESS;
 }
 
+extern "C" int psgpu_newton_roots(psgpu_ctx* ctx, const float* p1, const float* p2, const float* f1, const float* f2, int64_t n, float target_field,
+                                  int iterations, float* root_out, float* field_out, int32_t* evals_out) {
+    if (!ctx || !p1 || !p2 || !f1 || !f2 || !root_out || !field_out || !evals_out || n < 0 || ctx->progQuads == 0) return PSGPU_PARAM_ERROR;
+    if (n == 0) return PSGPU_SUCCESS;
+    CK(cudaSetDevice(ctx->device));
+    cudaStream_t st = ctx->stream;
+    // in: p1 | p2 | f1 | f2 (8 floats per pair); out: root | field | evals (5 words per pair)
+    CK(ctx->ptsIn.reserve((size_t)n * 32)); CK(ctx->ptsNrm.reserve((size_t)n * 20));
+    float* in = ctx->ptsIn.as<float>();
+    float* out = ctx->ptsNrm.as<float>();
+    CK(cudaMemcpyAsync(in, p1, (size_t)n * 12, cudaMemcpyHostToDevice, st));
+    CK(cudaMemcpyAsync(in + n * 3, p2, (size_t)n * 12, cudaMemcpyHostToDevice, st));
+    CK(cudaMemcpyAsync(in + n * 6, f1, (size_t)n * 4, cudaMemcpyHostToDevice, st));
+    CK(cudaMemcpyAsync(in + n * 7, f2, (size_t)n * 4, cudaMemcpyHostToDevice, st));
+    psgpu::launch_points_newton(ctx->pool.as<float4>(), in, in + n * 3, in + n * 6, in + n * 7, n, target_field, iterations, out, out + n * 3,
+                                reinterpret_cast<int32_t*>(out + n * 4), ctx->semantics, st);
+    CK(cudaMemcpyAsync(root_out, out, (size_t)n * 12, cudaMemcpyDeviceToHost, st));
+    CK(cudaMemcpyAsync(field_out, out + n * 3, (size_t)n * 4, cudaMemcpyDeviceToHost, st));
+    CK(cudaMemcpyAsync(evals_out, out + n * 4, (size_t)n * 4, cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
+    CK(cudaGetLastError());
+    return PSGPU_SUCCESS;
+}
+
 extern "C" int psgpu_mpu_cache(psgpu_ctx* ctx, const psgpu_params* params, const int32_t* ijk, float* fv512, uint8_t* case343) {
     if (!ctx || !params || !ijk || !fv512 || !case343) return PSGPU_PARAM_ERROR;
     CK(cudaSetDevice(ctx->device));

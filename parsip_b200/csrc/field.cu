@@ -288,6 +288,51 @@ __global__ void __launch_bounds__(128) points_fcn_kernel(const float4* __restric
     }
 }
 
+// Shrink-wrap Newton root between two points, one edge per thread, in the uploaded program's semantics:
+//  STRICT  FieldComputer::computeRootNewtonRaphson (PS_SimdPoly/include/PS_Polygonizer.cpp:1625-1681): starts at the end whose field is
+//          nearer the target and CARRIES that field value; gradient() by forward differences (:1576-1596); g = (t - f) / |grad|^2
+//  else    ComputeRootNewtonRaphsonVEC4 (ParsipHaptics/include/CompactBlobTree.cpp:1581-1622): field re-evaluated with the gradient,
+//          g = 1 / (|grad|^2 + f^2) (its vec4 dot includes the field lane)
+// evals = (i + 1) * 4 with i the loop counter at exit (iterations + 1 rounds reported when the loop runs out), as both return it.
+template <bool STRICT>
+__global__ void __launch_bounds__(128) points_newton_kernel(const float4* __restrict__ prog, const float* __restrict__ p1, const float* __restrict__ p2,
+                                                            const float* __restrict__ f1, const float* __restrict__ f2, int64_t n, float target,
+                                                            int iterations, float* __restrict__ root, float* __restrict__ rootField,
+                                                            int32_t* __restrict__ evals, int sem) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t j = i < n ? i : n - 1;
+    const bool first = fabsf(f1[j] - target) < fabsf(f2[j] - target);
+    const float* s = first ? p1 : p2;
+    float x = s[j * 3], y = s[j * 3 + 1], z = s[j * 3 + 2];
+    float field = first ? f1[j] : f2[j];
+    const float eps = PS_FIELDVALUE_EPSILON, inv = 1.0f / PS_FIELDVALUE_EPSILON;
+    int it = 0;
+    for (; it < iterations; it++) {
+        float X[4] = {x, __fadd_rn(x, eps), x, x}, Y[4] = {y, y, __fadd_rn(y, eps), y}, Z[4] = {z, z, z, __fadd_rn(z, eps)}, F[4];
+        eval_program<4, false, STRICT>(prog, X, Y, Z, F, nullptr, nullptr, sem);
+        if (!STRICT) field = F[0];
+        const float gx = __fmul_rn(__fsub_rn(F[1], field), inv), gy = __fmul_rn(__fsub_rn(F[2], field), inv), gz = __fmul_rn(__fsub_rn(F[3], field), inv);
+        const float d = __fsub_rn(target, field);
+        const float gg = __fadd_rn(__fadd_rn(__fmul_rn(gx, gx), __fmul_rn(gy, gy)), __fmul_rn(gz, gz));
+        if (STRICT) {
+            const float g = __fdiv_rn(d, gg);
+            x = __fadd_rn(x, __fmul_rn(gx, g)); y = __fadd_rn(y, __fmul_rn(gy, g)); z = __fadd_rn(z, __fmul_rn(gz, g));
+        } else {
+            const float g = __fdiv_rn(1.0f, __fadd_rn(gg, __fmul_rn(field, field)));
+            x = __fadd_rn(x, __fmul_rn(__fmul_rn(d, gx), g)); y = __fadd_rn(y, __fmul_rn(__fmul_rn(d, gy), g)); z = __fadd_rn(z, __fmul_rn(__fmul_rn(d, gz), g));
+        }
+        float X1[1] = {x}, Y1[1] = {y}, Z1[1] = {z}, F1[1];
+        eval_program<1, false, STRICT>(prog, X1, Y1, Z1, F1, nullptr, nullptr, sem);
+        field = F1[0];
+        if (fabsf(__fsub_rn(field, target)) < eps) break;
+    }
+    if (i < n) {
+        root[i * 3] = x; root[i * 3 + 1] = y; root[i * 3 + 2] = z;
+        rootField[i] = field;
+        evals[i] = iterations <= 0 ? -1 : (it + 1) * 4;
+    }
+}
+
 // exact SURVEY 8(d) bookkeeping over the final per-MPU programs: acc[0] += 512 * flops, acc[1] += 512 * prims,
 // acc[2] += quads, acc[3] += 512 (corner evaluations)
 __global__ void program_stats_kernel(const Region* __restrict__ cands, int nCand, const float4* __restrict__ pool,
@@ -382,6 +427,14 @@ void launch_points_field_color_normal(const float4* prog, const float* colorTab,
     if (n <= 0) return;
     if (sem == PSGPU_SEM_SIMD) points_fcn_kernel<true><<<(unsigned)((n + 127) / 128), 128, 0, st>>>(prog, colorTab, xyz, n, f, col, nrm, sem);
     else points_fcn_kernel<false><<<(unsigned)((n + 127) / 128), 128, 0, st>>>(prog, colorTab, xyz, n, f, col, nrm, sem);
+}
+
+void launch_points_newton(const float4* prog, const float* p1, const float* p2, const float* f1, const float* f2, int64_t n, float target, int iterations,
+                          float* root, float* rootField, int32_t* evals, int sem, cudaStream_t st) {
+    if (n <= 0) return;
+    const unsigned grid = (unsigned)((n + 127) / 128);
+    if (sem == PSGPU_SEM_SIMD) points_newton_kernel<true><<<grid, 128, 0, st>>>(prog, p1, p2, f1, f2, n, target, iterations, root, rootField, evals, sem);
+    else points_newton_kernel<false><<<grid, 128, 0, st>>>(prog, p1, p2, f1, f2, n, target, iterations, root, rootField, evals, sem);
 }
 
 void launch_program_stats(const Region* cands, int nCand, const float4* pool, const uint32_t* vcount, unsigned long long* acc, cudaStream_t st) {

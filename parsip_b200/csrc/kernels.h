@@ -94,6 +94,8 @@ int field_kernel_smem_bytes(uint32_t maxProgQuads, uint32_t* progCapQuads);
 void launch_field_kernel(const GridParams& G, const Region* cands, int nCand, const float4* pool, const FieldOutputs& out, uint32_t maxProgQuads,
                          bool hasWarps, int numSMs, cudaStream_t st);
 void launch_points_field(const float4* prog, const float* xyz, int64_t n, float* f, int sem, cudaStream_t st);
+void launch_points_newton(const float4* prog, const float* p1, const float* p2, const float* f1, const float* f2, int64_t n, float target, int iterations,
+                          float* root, float* rootField, int32_t* evals, int sem, cudaStream_t st);
 void launch_points_field_color_normal(const float4* prog, const float* colorTab, const float* xyz, int64_t n, float* f, float* col, float* nrm,
                                       int sem, cudaStream_t st);
 void launch_program_stats(const Region* cands, int nCand, const float4* pool, const uint32_t* tcount, unsigned long long* acc, cudaStream_t st);

@@ -112,6 +112,10 @@ void fac_get_boxes(const fac_scene* s, float* prim6, float* op6) {
 uint32_t fac_count_mpus(const fac_scene* s, float cellsize) { return CountMPUNeeded(cellsize, s->prims.bboxLo, s->prims.bboxHi); }
 
 int fac_field(fac_scene* s, int n, const float* xyz, float* out) { return FieldValues(s->prims, s->primMats, s->ops, xyz, n, out); }
+int fac_newton(fac_scene* s, int n, const float* p1, const float* p2, const float* f1, const float* f2, float target, int iters, float* root, float* field,
+               int* evals) {
+    return RootsNewtonRaphson(s->prims, s->primMats, s->ops, p1, p2, f1, f2, n, root, field, evals, target, iters);
+}
 
 // stats: ctMPUs, crossed, vertices, triangles
 int fac_polygonize(fac_scene* s, float cellsize, int64_t* stats) {

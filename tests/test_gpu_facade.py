@@ -38,6 +38,7 @@ def _lib():
     l.fac_count_mpus.restype = C.c_uint32
     l.fac_count_mpus.argtypes = [C.c_void_p, C.c_float]
     l.fac_field.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]
+    l.fac_newton.argtypes = [C.c_void_p, C.c_int] + [C.c_void_p] * 4 + [C.c_float, C.c_int] + [C.c_void_p] * 3
     l.fac_polygonize.argtypes = [C.c_void_p, C.c_float, C.c_void_p]
     l.fac_mesh_concat.argtypes = [C.c_void_p] * 6
     l.fac_simdpoly_run.argtypes = [C.c_void_p, C.c_float, C.c_void_p]
@@ -88,6 +89,15 @@ def test_facade_polygonize_fills_polympus_like_the_reference(lib, name):
         assert lib.fac_field(sc.h, len(pts), pts.ctypes.data, f.ctypes.data) == 1
         if name not in RSQRT_SCENES:
             assert np.array_equal(bits(f), bits(g["field_bcast"]))
+        # FieldComputer::computeRootNewtonRaphson through the facade (a20)
+        gn = np.load(os.path.join(GOLD, "simd_newton.npz"))
+        k = name + "_padded_"
+        p1, p2, f1, f2 = (np.ascontiguousarray(gn[k + q], np.float32) for q in ("p1", "p2", "f1", "f2"))
+        root, fr, ev = np.zeros((len(p1), 3), np.float32), np.zeros(len(p1), np.float32), np.zeros(len(p1), np.int32)
+        assert lib.fac_newton(sc.h, len(p1), p1.ctypes.data, p2.ctypes.data, f1.ctypes.data, f2.ctypes.data, 0.5, 8, root.ctypes.data, fr.ctypes.data,
+                              ev.ctypes.data) == 1
+        if name not in RSQRT_SCENES:
+            assert np.array_equal(bits(root), bits(gn[k + "root8"])) and np.array_equal(ev, gn[k + "evals8"])
         st = np.zeros(4, np.int64)
         assert lib.fac_polygonize(sc.h, cs, st.ctypes.data) == 1
         assert int(st[0]) == int(g["n_mpus"])

@@ -54,6 +54,24 @@ def test_field_bit_identical_to_reference_golden(ctx, name):
 
 
 @pytest.mark.parametrize("name", sorted(scenes_small.SIMD_SCENES))
+def test_newton_roots_bit_identical_to_reference_golden(ctx, name):
+    """psgpu_newton_roots in PS_SimdPoly semantics = FieldComputer::computeRootNewtonRaphson (a20), against the roots the reference's own
+    member returned (tests/golden/simd_newton.npz): same iterates bit for bit, same return value."""
+    g = np.load(os.path.join(GOLD, "simd_newton.npz"))
+    _, orc = simd_setup(ctx, name)
+    k = name + "_padded_"
+    for iters in (8, 2):
+        root, fr, ev = ctx.newton_roots(g[k + "p1"], g[k + "p2"], g[k + "f1"], g[k + "f2"], 0.5, iters)
+        if name in RSQRT_SCENES:
+            ro, fo, eo = orc.newton(g[k + "p1"], g[k + "p2"], g[k + "f1"], g[k + "f2"], 0.5, iters)
+            assert np.array_equal(bits(root), bits(ro)) and np.array_equal(ev, eo)  # bit-identical to the exact-rsqrt oracle
+            continue
+        assert np.array_equal(ev, g[k + "evals%d" % iters])
+        assert np.array_equal(bits(root), bits(g[k + "root%d" % iters])) and np.array_equal(bits(fr), bits(g[k + "field%d" % iters]))
+    assert ctx.newton_roots(g[k + "p1"][:3], g[k + "p2"][:3], g[k + "f1"][:3], g[k + "f2"][:3], 0.5, 0)[2].tolist() == [-1, -1, -1]
+
+
+@pytest.mark.parametrize("name", sorted(scenes_small.SIMD_SCENES))
 def test_field_color_normal_vs_oracle(ctx, name):
     _, orc = simd_setup(ctx, name)
     lo, hi = orc.bbox()

@@ -132,3 +132,22 @@ def test_scalar_oracle_agrees_with_simd_oracle_where_semantics_coincide():
     pts = np.random.RandomState(9).uniform(lo, hi, (20000, 3)).astype(np.float32)
     a, b = o.field(pts), so.field(pts)
     assert np.abs(a - b).max() < 2e-6
+
+
+@pytest.mark.parametrize("name", sorted(scenes_small.SIMD_SCENES))
+@pytest.mark.parametrize("variant", ["asis", "padded"])
+def test_oracle_newton_matches_golden(name, variant):
+    """FieldComputer::computeRootNewtonRaphson (SURVEY 8 a20; PS_Polygonizer.cpp:1625-1681): the restatement against roots the reference's
+    own member returned (tools/gen_golden.py main_simd_newton), 8 and 2 iterations (the latter mostly runs out: return value (n+1)*4)."""
+    g = np.load(os.path.join(GOLD, "simd_newton.npz"))
+    _, soa, o = scenes_small.simd_oracle(scenes_small.SIMD_SCENES[name](), pad_op_boxes=(variant == "padded"))
+    k = "%s_%s_" % (name, variant)
+    for iters in (8, 2):
+        root, fr, ev = o.newton(g[k + "p1"], g[k + "p2"], g[k + "f1"], g[k + "f2"], 0.5, iters)
+        if name in RSQRT_SCENES:  # 12-bit rsqrt in the reference's disc / ring distances (Q7): the roots agree to the field tolerance
+            assert np.abs(root - g[k + "root%d" % iters]).max() < 5e-3
+            continue
+        assert np.array_equal(ev, g[k + "evals%d" % iters])
+        assert np.array_equal(root.view(np.uint32), g[k + "root%d" % iters].view(np.uint32))
+        assert np.array_equal(fr.view(np.uint32), g[k + "field%d" % iters].view(np.uint32))
+    assert o.newton(g[k + "p1"][:2], g[k + "p2"][:2], g[k + "f1"][:2], g[k + "f2"][:2], 0.5, 0)[2].tolist() == [-1, -1]

@@ -64,6 +64,34 @@ def main():
             print(name, "padded" if padded else "asis", st)
 
 
+def main_simd_newton():
+    """FieldComputer::computeRootNewtonRaphson (PS_Polygonizer.cpp:1625-1681; public, not called by Polygonize) on lattice-style crossing
+    edges, with the reference's own and with padded operator boxes -> tests/golden/simd_newton.npz"""
+    out, rec = os.path.join(ROOT, "tests", "golden"), {}
+    for name, mk in scenes_small.SIMD_SCENES.items():
+        soa = bt.to_binary_soa(bt.binarize(mk()))
+        for padded in (False, True):
+            ref = RefScene(soa)
+            ref.prepare_bboxes(0.05)
+            lo, hi = ref.bbox()
+            if padded:
+                ref.pad_op_boxes(1.0e6)
+            rs = np.random.RandomState(44)
+            cs = np.float32(scenes.cellsize_for(lo, hi, CELLS[name]))
+            cand = rs.uniform(lo, hi, (40000, 3)).astype(np.float32)
+            p2 = cand.copy()
+            p2[np.arange(len(cand)), rs.randint(0, 3, len(cand))] += cs
+            f1, f2 = ref.field_color_normal(cand)[0], ref.field_color_normal(p2)[0]  # broadcast evaluation, as the root finder's own
+            cross = np.nonzero((f1 > 0.5) != (f2 > 0.5))[0][:300]
+            k = "%s_%s_" % (name, "padded" if padded else "asis")
+            rec[k + "p1"], rec[k + "p2"], rec[k + "f1"], rec[k + "f2"] = cand[cross], p2[cross], f1[cross], f2[cross]
+            for iters in (8, 2):
+                root, fr, ev = ref.newton(cand[cross], p2[cross], f1[cross], f2[cross], 0.5, iters)
+                rec[k + "root%d" % iters], rec[k + "field%d" % iters], rec[k + "evals%d" % iters] = root, fr, ev
+            print("simd newton", k, len(cross), "edges, evals histogram", np.bincount(rec[k + "evals8"] // 4))
+    np.savez_compressed(os.path.join(out, "simd_newton.npz"), **rec)
+
+
 SCALAR_CELLS = 36
 WALK_KEYS = ("type", "first_child", "n_children", "child", "pos", "dir", "res", "color", "xform", "has_xform", "oct_lo", "oct_hi")
 
@@ -130,5 +158,7 @@ if __name__ == "__main__":
     what = sys.argv[1] if len(sys.argv) > 1 else "all"
     if what in ("all", "simd"):
         main()
+    if what in ("all", "simd", "simd_newton"):
+        main_simd_newton()
     if what in ("all", "scalar"):
         main_scalar()
