@@ -10,6 +10,8 @@
 
 #include "PS_SimdPolyCompat.h"
 #include "psgpu_blobtree_walk.h"
+#include "PS_FrameWork/include/PS_MeshVV.h"
+#include "psgpu_meshvv_export.h"
 
 #include <cstring>
 
@@ -62,6 +64,47 @@ int bnp_run(void* cblobnode_root, float cellsize, int64_t* stats4) {
     }
     delete sp;
     return rc;
+}
+
+/* f4: CBlobNode* -> walker -> scalar-semantics program -> GPU polygonize (reference-Newton per-MPU output or the native indexed mesh)
+ * -> psgpu::export_mesh into a reference CMeshVV. Two-call protocol: arrays NULL = counts only. counts2 = {vertices, faces}. */
+int bnp_export_mesh(void* cblobnode_root, const float* lo3, const float* hi3, float cellsize, int per_mpu, int64_t* counts2, float* pos, float* nrm,
+                    float* col4, uint32_t* faces) {
+    static PS::CMeshVV* mesh = 0;
+    if (!pos) {
+        psgpu::FlatBlobTree flat;
+        if (flat.walk(reinterpret_cast<CBlobNode*>(cblobnode_root)) != 0) return -1;
+        const psgpu_tree t = flat.view();
+        psgpu_program* prog = 0;
+        if (psgpu_linearize(&t, PSGPU_SEM_SCALAR, PSGPU_LIN_REASSOCIATE, &prog) != PSGPU_SUCCESS) return -2;
+        psgpu_ctx* ctx = 0;
+        if (psgpu_create(0, &ctx) != PSGPU_SUCCESS) { psgpu_program_free(prog); return -3; }
+        int rc = psgpu_upload_program(ctx, prog);
+        psgpu_params P;
+        memset(&P, 0, sizeof(P));
+        P.cellsize = cellsize;
+        for (int a = 0; a < 3; a++) { P.bbox_lo[a] = lo3[a]; P.bbox_hi[a] = hi3[a]; }
+        P.root_mode = per_mpu ? PSGPU_ROOT_NEWTON_REF : PSGPU_ROOT_BISECT;
+        P.coord_mode = per_mpu ? PSGPU_COORD_MPU_LOCAL : PSGPU_COORD_GLOBAL;
+        P.output = per_mpu ? PSGPU_OUT_MPU : PSGPU_OUT_INDEXED;
+        P.cull = PSGPU_CULL_INTERVAL;
+        P.want_colors = P.want_normals = 1;
+        psgpu_mesh M;
+        if (rc == PSGPU_SUCCESS) rc = psgpu_polygonize(ctx, &P, &M);
+        delete mesh;
+        mesh = new PS::CMeshVV();
+        const bool ok = rc == PSGPU_SUCCESS && psgpu::export_mesh(ctx, M, mesh);
+        psgpu_destroy(ctx);
+        psgpu_program_free(prog);
+        counts2[0] = mesh->countVertices(); counts2[1] = mesh->countFaces();
+        return ok ? 1 : 0;
+    }
+    if (!mesh) return -1;
+    memcpy(pos, mesh->m_lstVertices.data(), mesh->m_lstVertices.size() * 4);
+    memcpy(nrm, mesh->m_lstNormals.data(), mesh->m_lstNormals.size() * 4);
+    memcpy(col4, mesh->m_lstColors.data(), mesh->m_lstColors.size() * 4);
+    memcpy(faces, mesh->m_lstFaces.data(), mesh->m_lstFaces.size() * 4);
+    return 1;
 }
 
 }  // extern "C"

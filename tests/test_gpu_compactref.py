@@ -193,3 +193,44 @@ def test_parsipcmd_cli_on_a_scene_file(ctx, tmp_path):
     assert abs(faces - 146352) <= 0.02 * 146352  # ParsipHaptics_Release.csv:2, loosely (%f scene precision, other MPU size)
     lines = open(tmp_path / "train.obj").read().splitlines()
     assert sum(l.startswith("v ") for l in lines) == verts and sum(l.startswith("f ") for l in lines) == faces
+
+
+def test_export_mesh_into_the_reference_cmeshvv(ctx):
+    """include/psgpu_meshvv_export.h compiled against the reference's CMeshVV declaration (oracle/_ref/libblobnode_probe.so,
+    tests/facade/blobnode_probe.cpp): CBlobNode* -> walker -> GPU polygonize -> psgpu::export_mesh, against (1) the same mesh fetched
+    through the C ABI and rebased the way CMeshVV::appendFrom does, and (2) CParsipOptimized::exportMesh of the reference build."""
+    import ctypes as C
+    from oracle import pyoracle
+    from parsip_b200 import blobtree as bt
+    import scenes_small
+    probe = os.path.join(os.path.dirname(pyoracle.compactref_lib_path()), "libblobnode_probe.so")
+    if not (os.path.exists(probe) and os.path.exists(pyoracle.compactref_lib_path())):
+        pytest.skip("oracle/_ref reference builds not present")
+    lib = C.CDLL(probe)
+    lib.bnp_export_mesh.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_float, C.c_int] + [C.c_void_p] * 5
+    cref = pyoracle._load_compactref()
+    cref.cref_root.restype, cref.cref_root.argtypes = C.c_void_p, [C.c_void_p]
+    ref = pyoracle.CompactRef(bt.flatten(scenes_small.COMPACTREF_SCENES["blob"]()))
+    g = golden("blob")
+    lo, hi, cs = np.ascontiguousarray(g["bbox_lo"], np.float32), np.ascontiguousarray(g["bbox_hi"], np.float32), float(g["cellsize"])
+    rm = ref.polygonize(lo, hi, cs, nthreads=2)
+    ok, rex = ref.export_mesh()
+    assert ok and rex["triangles"] == rm["triangles"]
+    upload(ctx, g)
+    for per_mpu in (1, 0):
+        cnt = np.zeros(2, np.int64)
+        assert lib.bnp_export_mesh(cref.cref_root(ref.h), lo.ctypes.data, hi.ctypes.data, cs, per_mpu, cnt.ctypes.data, None, None, None, None) == 1
+        nv, nt = int(cnt[0]), int(cnt[1])
+        pos, nrm, col, tri = np.zeros((nv, 3), np.float32), np.zeros((nv, 3), np.float32), np.zeros((nv, 4), np.float32), np.zeros((nt, 3), np.uint32)
+        assert lib.bnp_export_mesh(None, None, None, cs, per_mpu, cnt.ctypes.data, pos.ctypes.data, nrm.ctypes.data, col.ctypes.data, tri.ctypes.data) == 1
+        kw = dict(root_mode=ps.ROOT_NEWTON_REF, coord_mode=ps.COORD_MPU_LOCAL, output=ps.OUT_MPU) if per_mpu else {}
+        m = ctx.polygonize(ps.Params.make(cs, lo, hi, **kw))
+        assert (nv, nt) == (m["n_vertices"], m["n_triangles"])
+        want = m["tri"].astype(np.int64)
+        if per_mpu:
+            vb, tb = m["mpu_vbase"].astype(np.int64), m["mpu_tbase"].astype(np.int64)
+            want = want + np.repeat(vb[:-1], np.diff(tb))[:, None]
+        assert np.array_equal(tri.astype(np.int64), want) and tri.max() < nv
+        assert np.array_equal(pos, m["pos"]) and np.array_equal(nrm, m["nrm"]) and np.array_equal(col[:, :3], m["col"]) and (col[:, 3] == 1).all()
+        if per_mpu:  # the reference's own export of the same scene: same faces where its octree filter kept the MPU (Q12), never more
+            assert nt >= rex["triangles"] and nt - rex["triangles"] <= 0.02 * nt, (nt, rex["triangles"])
