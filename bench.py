@@ -356,7 +356,7 @@ def run_gpu(args):
     zb, ze = 0, dims[2]
     if world > 1:
         # the product's own multi-GPU path: NCCL communicator inside libpsgpu.so (the 128-byte id travels over torch.distributed),
-        # slabs cut from the measured per-layer work of a first frame
+        # slabs cut from the measured per-layer work of a first frame, then refined from measured times
         idt = torch.zeros(128, dtype=torch.uint8, device="cuda")
         if rank == 0:
             idt.copy_(torch.frombuffer(bytearray(ps.comm_unique_id()), dtype=torch.uint8))
@@ -370,8 +370,25 @@ def run_gpu(args):
         # the first frame runs on equal slabs; the frames after it (the steady state that is timed) on slabs cut from its measured
         # per-layer work - the re-polygonization / animation case (BASELINE configs[4]'s calling pattern on configs[3]'s job)
         ctx.polygonize_sharded(prm)
-        zb, ze = ps.slab_bounds(dims[2], world, rank, measured_layer_weights(ctx, dims[2], dist, world))
+        wl = measured_layer_weights(ctx, dims[2], dist, world)
+        zb, ze = ps.slab_bounds(dims[2], world, rank, wl)
         prm = mk()
+        # ... and twice more from the ranks' MEASURED times (a rank's own time - cull .. emit without the wait inside the exchange - spread over
+        # its layers in proportion to their work counts): what an application re-polygonizing every frame does with psgpu_get_stats
+        for _ in range(2):
+            for _ in range(2):  # the first frame after a re-cut grows buffers; the second is representative
+                ctx.polygonize_sharded(prm)
+            st = ctx.stats()
+            mine = torch.tensor([st["ms_total"] - st["ms_exchange"], float(zb), float(ze)], dtype=torch.float64, device="cuda")
+            allr = [torch.zeros_like(mine) for _ in range(world)]
+            dist.all_gather(allr, mine)
+            cost = np.zeros(dims[2], np.float64)
+            for t_r, b_r, e_r in (a.cpu().numpy() for a in allr):
+                sl = slice(int(b_r), int(e_r))
+                cost[sl] = t_r * wl[sl] / max(float(wl[sl].sum()), 1e-9)
+            wl = (cost + 1e-3 * cost.mean()).astype(np.float32)
+            zb, ze = ps.slab_bounds(dims[2], world, rank, wl)
+            prm = mk()
     flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
 
     def barrier():
@@ -549,7 +566,7 @@ def run_gpu(args):
         "dtype": "f32", "data": "synthetic",
         "config": {"workload": w["name"], "semantics": "PS_SimdPoly (infinite lines, f>=iso, 4-sample roots)", "cells": w["cells"],
                    "primitives": w["prims"], "cellsize": cs, "lattice_mpus": list(dims),
-                   "sharding": "z-slabs of MPU layers over %d ranks, cut from the per-layer work measured on a first frame (psgpu_layer_work); boundary vertices exist once "
+                   "sharding": "z-slabs of MPU layers over %d ranks, cut from the per-layer work measured on a first frame (psgpu_layer_work) and refined twice from the measured per-rank times (psgpu_get_stats); boundary vertices exist once "
                                "(psgpu_polygonize_sharded)" % world if world > 1 else "single GPU",
                    "l2": "flushed between steps (256 MiB fill, untimed); a step's field caches + mesh also exceed L2",
                    "cull": "interval", "output": "indexed mesh (global edge-id dedup)",

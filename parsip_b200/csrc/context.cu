@@ -63,7 +63,7 @@ struct psgpu_ctx {
     // cull scratch
     DevBuf regionsA, regionsB, childLen, childOff, childFlag, childIdx, scanTemp, candOfMpu, scalars, cullScratch, cullScratchFlag;
     // field outputs
-    DevBuf fv, vcount, tcount, vbase, tbase, edgeMask, edgePrefix, mixedList, mixedFlag, mixedIdx, counters, statsAcc;
+    DevBuf fv, inside, vcount, tcount, vbase, tbase, edgeMask, edgePrefix, mixedList, mixedFlag, mixedIdx, counters, statsAcc;
     // mesh
     DevBuf pos, nrm, col, tri, mpuIjk, mpuVbase, mpuTbase, vperm;
     DevBuf ptsIn, ptsF, ptsCol, ptsNrm;
@@ -126,7 +126,7 @@ extern "C" int psgpu_destroy(psgpu_ctx* ctx) {
     cudaSetDevice(ctx->device);
     cudaStreamSynchronize(ctx->stream);
     DevBuf* all[] = {&ctx->pool, &ctx->qflag, &ctx->colors, &ctx->regionsA, &ctx->regionsB, &ctx->childLen, &ctx->childOff, &ctx->childFlag, &ctx->childIdx,
-                     &ctx->scanTemp, &ctx->candOfMpu, &ctx->scalars, &ctx->cullScratch, &ctx->cullScratchFlag, &ctx->fv, &ctx->vcount, &ctx->tcount, &ctx->vbase, &ctx->tbase,
+                     &ctx->scanTemp, &ctx->candOfMpu, &ctx->scalars, &ctx->cullScratch, &ctx->cullScratchFlag, &ctx->fv, &ctx->inside, &ctx->vcount, &ctx->tcount, &ctx->vbase, &ctx->tbase,
                      &ctx->edgeMask, &ctx->edgePrefix, &ctx->mixedList, &ctx->mixedFlag, &ctx->mixedIdx, &ctx->counters, &ctx->statsAcc,
                      &ctx->pos, &ctx->nrm, &ctx->col, &ctx->tri, &ctx->mpuIjk, &ctx->mpuVbase, &ctx->mpuTbase, &ctx->vperm, &ctx->ptsIn, &ctx->ptsF,
                      &ctx->ptsCol, &ctx->ptsNrm, &ctx->shardCounts, &ctx->haloSend, &ctx->haloRecv};
@@ -280,10 +280,15 @@ int run_cull(psgpu_ctx* ctx, const GridParams& G, int cullMode, bool colorExact,
         // coarse levels (few regions, long programs): ONE warp-cooperative walk per region into scratch slots, compacted after the scans;
         // the scratch bound keeps 10k-primitive trees within ~1 GB
         const size_t scratchQuads = (size_t)n * parentMaxLen;
-        const bool fused = prune_level_is_fused(nParents) && scratchQuads <= ((size_t)64 << 20) && !getenv("PSGPU_CULL_TWO_PASS");
+        // The thread-per-MPU level too when it is the last one, its slots fit 4 GB and the program has warps: there a walk is dominated by
+        // the warp-box arithmetic and walking twice costs more than the slot copy (csgwarp@512^3: cull 1.34 -> 1.22 ms); for warp-free
+        // programs count + emit stays (blob1k@512^3: 0.67 vs 0.70 ms fused). No flags at the last level: the field kernel never reads them.
+        const bool warpLevel = prune_level_is_fused(nParents);
+        const bool fused = !getenv("PSGPU_CULL_TWO_PASS") &&
+                           (warpLevel ? scratchQuads <= ((size_t)64 << 20) : (last && ctx->hasWarps && scratchQuads <= ((size_t)256 << 20)));
         uint32_t* levelMax = ctx->scalars.as<uint32_t>() + 1 + lv;
         if (fused) {
-            CK(ctx->cullScratch.reserve(scratchQuads * 16)); CK(ctx->cullScratchFlag.reserve(scratchQuads));
+            CK(ctx->cullScratch.reserve(scratchQuads * 16)); CK(ctx->cullScratchFlag.reserve(warpLevel ? scratchQuads : 16));
             CK(cudaMemsetAsync(levelMax, 0, 4, st));
             // few regions with a long program (the top level): a whole CTA per region instead of a warp
             const char* ctaMin = getenv("PSGPU_CULL_CTA_MINLEN");
@@ -495,7 +500,7 @@ int polygonize_impl(psgpu_ctx* ctx, const psgpu_params* P, psgpu_mesh* out, bool
     bool streamed = false;
     if (nCand > 0) {
         const size_t n1 = (size_t)nCand + 1;
-        CK(ctx->fv.reserve((size_t)nCand * 2048));
+        CK(ctx->fv.reserve((size_t)nCand * 2048)); CK(ctx->inside.reserve((size_t)nCand * 64));
         CK(ctx->vcount.reserve(n1 * 4)); CK(ctx->tcount.reserve(n1 * 4)); CK(ctx->vbase.reserve(n1 * 4)); CK(ctx->tbase.reserve(n1 * 4));
         CK(ctx->edgeMask.reserve((size_t)nCand * 192)); CK(ctx->edgePrefix.reserve((size_t)nCand * 96));
         CK(ctx->mixedList.reserve((size_t)nCand * 4));
@@ -504,7 +509,7 @@ int polygonize_impl(psgpu_ctx* ctx, const psgpu_params* P, psgpu_mesh* out, bool
         CK(cudaMemsetAsync(ctx->vcount.as<uint32_t>() + nCand, 0, 4, st));
         CK(cudaMemsetAsync(ctx->tcount.as<uint32_t>() + nCand, 0, 4, st));
         FieldOutputs fo;
-        fo.fv = ctx->fv.as<float4>(); fo.vcount = ctx->vcount.as<uint32_t>(); fo.tcount = ctx->tcount.as<uint32_t>();
+        fo.fv = ctx->fv.as<float4>(); fo.inside = ctx->inside.as<uint32_t>(); fo.vcount = ctx->vcount.as<uint32_t>(); fo.tcount = ctx->tcount.as<uint32_t>();
         fo.edgeMask = ctx->edgeMask.as<uint32_t>(); fo.edgePrefix = ctx->edgePrefix.as<uint16_t>();
         fo.mixedList = ctx->mixedList.as<uint32_t>(); fo.counters = ctx->counters.as<uint32_t>();
         launch_field_kernel(G, ctx->cands, nCand, ctx->pool.as<float4>(), fo, maxLen, ctx->hasWarps, ctx->numSMs, st);
@@ -914,11 +919,11 @@ extern "C" int psgpu_mpu_cache(psgpu_ctx* ctx, const psgpu_params* params, const
     psgpu::Region r{ijk[0], ijk[1], ijk[2], 0u, ctx->progQuads};
     CK(ctx->regionsA.reserve(sizeof(r)));
     CK(cudaMemcpyAsync(ctx->regionsA.p, &r, sizeof(r), cudaMemcpyHostToDevice, st));
-    CK(ctx->fv.reserve(2048)); CK(ctx->vcount.reserve(8)); CK(ctx->tcount.reserve(8));
+    CK(ctx->fv.reserve(2048)); CK(ctx->inside.reserve(64)); CK(ctx->vcount.reserve(8)); CK(ctx->tcount.reserve(8));
     CK(ctx->edgeMask.reserve(192)); CK(ctx->edgePrefix.reserve(96)); CK(ctx->mixedList.reserve(4)); CK(ctx->counters.reserve(64));
     CK(cudaMemsetAsync(ctx->counters.p, 0, 64, st));
     psgpu::FieldOutputs fo;
-    fo.fv = ctx->fv.as<float4>(); fo.vcount = ctx->vcount.as<uint32_t>(); fo.tcount = ctx->tcount.as<uint32_t>();
+    fo.fv = ctx->fv.as<float4>(); fo.inside = ctx->inside.as<uint32_t>(); fo.vcount = ctx->vcount.as<uint32_t>(); fo.tcount = ctx->tcount.as<uint32_t>();
     fo.edgeMask = ctx->edgeMask.as<uint32_t>(); fo.edgePrefix = ctx->edgePrefix.as<uint16_t>();
     fo.mixedList = ctx->mixedList.as<uint32_t>(); fo.counters = ctx->counters.as<uint32_t>();
     psgpu::launch_field_kernel(G, ctx->regionsA.as<psgpu::Region>(), 1, ctx->pool.as<float4>(), fo, ctx->progQuads, ctx->hasWarps, ctx->numSMs, st);

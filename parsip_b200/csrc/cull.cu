@@ -83,6 +83,24 @@ __global__ void __launch_bounds__(128) prune_emit_kernel(CullLevel L, const Regi
     publish_child(L, coord, off, len, childIdx[tid], children, candOfMpu, maxLen);
 }
 
+// single-walk variant of the thread-per-MPU level: emit into a private scratch slot, compacted after the scans (one walk instead of
+// count + emit; the slot stride is the longest parent program)
+__global__ void __launch_bounds__(128) prune_fused_thread_kernel(CullLevel L, const Region* __restrict__ parents, int nParents,
+                                                                 const float4* __restrict__ pool, float4* __restrict__ scratch, uint32_t stride,
+                                                                 uint32_t* __restrict__ childLen, uint32_t* __restrict__ maxLen) {
+    const int tid = blockIdx.x * blockDim.x + threadIdx.x;
+    if (tid >= nParents * 64) return;
+    const Region parent = parents[tid >> 6];
+    int coord[3];
+    Box3 box;
+    uint32_t len = 0;
+    if (child_region(L, parent, tid & 63, coord, box))
+        len = prune_walk<true>(pool + parent.off, box, L.cullMode, L.iso, scratch + (size_t)tid * stride, L.colorExact != 0, stride, nullptr);
+    if (len > stride) len = 0xFFFFFFFFu;  // cannot happen (emitted <= source); poisons the total so the host notices
+    childLen[tid] = len;
+    if (len) atomicMax(maxLen, len);
+}
+
 // ---- warp-cooperative pruning --------------------------------------------------------------------------------------
 // The coarse levels have few regions and long parent programs (level 0 walks the whole BlobTree), so one thread per region
 // is bound by the latency of ~1000 dependent primitive bounds (ncu r01b: 0.7 ms per pass on 4 CTAs). Here a WARP prunes one
@@ -136,9 +154,14 @@ __device__ uint32_t prune_walk_warp(const float4* __restrict__ src, const uint8_
             if (lane >= o) incl += v;
         }
         const uint32_t entMask = __ballot_sync(FULL, isEntry);
+        // "PUSH <all-zero primitive>" whose union (OPC_COMBINE, CMB_MAX, no colour-scale marker) is the very next surviving
+        // instruction: the culled blend group of a union of blends. Found here by all lanes; lane 0 then steps over the pair (below).
+        const uint32_t above = entMask & ~((2u << lane) - 1u);
+        const uint32_t hdrNext = __shfl_sync(FULL, hdr, above ? (__ffs((int)above) - 1) : lane);
+        const bool zeroPair = isEntry && isPrim && pz && PS_HDR_CMB(hdr) == CMB_PUSH && above != 0u && ps_is_plain_union(hdrNext, colorExact);
         if (isEntry) {
             CoopEntry e;
-            e.pc = p | (pz ? 0x80000000u : 0u); e.za = zaTotal + incl - zs; e.flo = flo; e.fhi = fhi;
+            e.pc = p | (pz ? 0x80000000u : 0u) | (zeroPair ? 0x40000000u : 0u); e.za = zaTotal + incl - zs; e.flo = flo; e.fhi = fhi;
             ent[__popc(entMask & ((1u << lane) - 1u))] = e;
         }
         zaTotal += __shfl_sync(FULL, incl, 31);
@@ -148,9 +171,14 @@ __device__ uint32_t prune_walk_warp(const float4* __restrict__ src, const uint8_
             const int n = __popc(entMask);
             for (int i = 0; i < n; i++) {
                 const CoopEntry e = ent[i];
-                const uint32_t pc = e.pc & 0x7FFFFFFFu;
+                const uint32_t pc = e.pc & 0x3FFFFFFFu;
                 P.skipped_scale(e.za - zaPrev);
                 zaPrev = e.za;
+                if ((e.pc & 0x40000000u) && P.zero_union_is_noop()) {  // max(T, 0) with T >= 0 or T all-zero: nothing to emit, no state to change
+                    zaPrev = ent[i + 1].za;  // scale steps owed between the two belong to the zero entry: dropped
+                    i++;
+                    continue;
+                }
                 const float4 h0 = src[pc];
                 const uint32_t h = __float_as_uint(h0.x), o = PS_HDR_OPC(h);
                 if (o == OPC_END) { endSeen = 1; break; }
@@ -320,13 +348,27 @@ __device__ uint32_t prune_walk_cta(const float4* __restrict__ src, const uint8_t
         }
         zaTotal += ztot;
         __syncthreads();
+        {   // culled blend group of a union of blends (see prune_walk_warp): flagged by all threads, stepped over by thread 0
+            bool zeroPair = false;
+            if ((uint32_t)tid + 1u < etot) {
+                const uint32_t h1 = __float_as_uint(S.ent[tid].h0.x), h2 = __float_as_uint(S.ent[tid + 1].h0.x);
+                zeroPair = (S.ent[tid].pc >> 31) != 0u && PS_HDR_OPC(h1) < OPC_FIRST_NONPRIM && PS_HDR_CMB(h1) == CMB_PUSH && ps_is_plain_union(h2, colorExact);
+            }
+            if (zeroPair) S.ent[tid].pc |= 0x40000000u;
+        }
+        __syncthreads();
         if (tid == 0) {
             uint32_t endSeen = 0;
             for (uint32_t i = 0; i < etot; i++) {
                 const CtaEntry e = S.ent[i];
-                const uint32_t pc = e.pc & 0x7FFFFFFFu;
+                const uint32_t pc = e.pc & 0x3FFFFFFFu;
                 P.skipped_scale(e.za - zaPrev);
                 zaPrev = e.za;
+                if ((e.pc & 0x40000000u) && P.zero_union_is_noop()) {
+                    zaPrev = S.ent[i + 1].za;
+                    i++;
+                    continue;
+                }
                 const uint32_t h = __float_as_uint(e.h0.x), o = PS_HDR_OPC(h);
                 if (o == OPC_END) { endSeen = 1; break; }
                 if (o < OPC_FIRST_NONPRIM) {
@@ -495,6 +537,10 @@ void launch_prune_fused(const CullLevel& L, const Region* parents, int nParents,
     const int n = nParents * 64;
     if (ctaPerRegion) {
         prune_fused_cta_kernel<<<n, kCtaWarps * 32, 0, st>>>(L, parents, nParents, pool, qflag, scratch, scratchFlag, stride, childLen, maxLen);
+        return;
+    }
+    if (!use_warp_walk(nParents)) {
+        prune_fused_thread_kernel<<<(n + 127) / 128, 128, 0, st>>>(L, parents, nParents, pool, scratch, stride, childLen, maxLen);
         return;
     }
     prune_fused_warp_kernel<<<(n + kCoopWarps - 1) / kCoopWarps, kCoopWarps * 32, 0, st>>>(L, parents, nParents, pool, qflag, scratch, scratchFlag, stride,

@@ -236,7 +236,9 @@ struct Pruner {
     // copies instruction (pc, q0) with a possibly rewritten header
     __device__ void copy(uint32_t pc, const float4 q0, uint32_t newHdr, int nq) {
         const uint32_t o = PS_HDR_OPC(newHdr);
-        if (o < OPC_FIRST_NONPRIM || o == OPC_COMBINE) { lastHdrPos = emit; lastHdrVal = newHdr; lastHdrQuad = make_float4(__uint_as_float(newHdr), q0.y, q0.z, q0.w); }
+        // (a PRE count - program.h - scales the primitive's own colour before the combine: later steps owed to the ENTRY must not be
+        //  added to it, they go to an explicit OPC_CSCALE quad)
+        if ((o < OPC_FIRST_NONPRIM || o == OPC_COMBINE) && !PS_HDR_PRE(newHdr)) { lastHdrPos = emit; lastHdrVal = newHdr; lastHdrQuad = make_float4(__uint_as_float(newHdr), q0.y, q0.z, q0.w); }
         else lastHdrPos = 0xFFFFFFFFu;
         put(make_float4(__uint_as_float(newHdr), q0.y, q0.z, q0.w), true);
         for (int i = 1; i < nq; i++) put(src[pc + i], false);
@@ -305,6 +307,9 @@ struct Pruner {
         } else if (cmb == CMB_ADD) cscale(1);
         if (!bzero[t]) cscale(PS_HDR_CSC(hdr));
     }
+    // "PUSH <all-zero primitive>; OPC_COMBINE(CMB_MAX, no marker)" leaves emit, stack and markers untouched when the entry below is
+    // all-zero (0 max 0) or cannot be negative (max(T, 0) = T): what step_prim + step_op would conclude, decided in a few instructions
+    __device__ __forceinline__ bool zero_union_is_noop() const { return sp >= 0 && (bzero[sp] || blo[sp] >= 0.f); }
     // "PUSH <all-zero primitive>; OPC_COMBINE" with nothing fed in between, in one step: what step_prim + step_op would do,
     // without the stack round trip (the cooperative walks of cull.cu meet this pair once per culled blend group)
     __device__ __forceinline__ void step_zero_operand(uint32_t combineHdr) {
@@ -425,6 +430,15 @@ struct Pruner {
         return emit;
     }
 };
+
+// OPC_COMBINE header of a union that carries no colour-scale marker (or markers do not matter in this pass)
+__device__ __forceinline__ bool ps_is_plain_union(uint32_t hdr, bool colorExact) {
+#ifdef PSGPU_NO_ZEROPAIR  // A/B switch
+    return false;
+#else
+    return PS_HDR_OPC(hdr) == OPC_COMBINE && PS_HDR_CMB(hdr) == CMB_MAX && (!colorExact || PS_HDR_CSC(hdr) == 0u);
+#endif
+}
 
 // does this opcode change the region box of the walk (so that bounds of later primitives depend on it)?
 __device__ __forceinline__ bool ps_changes_box(uint32_t opc) { return opc >= OPC_TWIST && opc <= OPC_POPPOINT; }

@@ -210,16 +210,7 @@ __global__ void __launch_bounds__(kThreads) tri_kernel(GridParams G, const Regio
             S.edgeW[32 + lane] = fo.edgeMask[(size_t)cand * 48 + 32 + lane];
             S.edgeP[32 + lane] = fo.edgePrefix[(size_t)cand * 48 + 32 + lane];
         }
-#pragma unroll
-        for (int q = 0; q < 4; q++) {  // 512 inside bits from the field cache: float4 t covers bits 4t .. 4t+3
-            const float4 f4 = fo.fv[(size_t)cand * 128 + q * 32 + lane];
-            uint32_t v = (is_inside(G, f4.x) ? 1u : 0u) | (is_inside(G, f4.y) ? 2u : 0u) | (is_inside(G, f4.z) ? 4u : 0u) | (is_inside(G, f4.w) ? 8u : 0u);
-            v <<= (lane & 7) * 4;
-            v |= __shfl_xor_sync(0xffffffffu, v, 1);
-            v |= __shfl_xor_sync(0xffffffffu, v, 2);
-            v |= __shfl_xor_sync(0xffffffffu, v, 4);
-            if ((lane & 7) == 0) S.insideW[q * 4 + (lane >> 3)] = v;
-        }
+        if (lane < 16) S.insideW[lane] = fo.inside[(size_t)cand * 16 + lane];  // 512 inside bits, as field_kernel classified them
         __syncwarp();
 
         // ---- cube cases of this lane's cells, triangle count

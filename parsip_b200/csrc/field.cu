@@ -237,6 +237,8 @@ __global__ void __launch_bounds__(512 / kPts, kPts == 4 ? 6 : (STRICT ? PSGPU_ST
         if (G.forceFv || nT > 0) {
 #pragma unroll
             for (int q = 0; q < kPts / 4; q++) out.fv[(size_t)item * 128 + t * (kPts / 4) + q] = reinterpret_cast<float4*>(S.fv)[t * (kPts / 4) + q];
+            // the 64 bytes tri_kernel builds its cube cases from (it used to re-derive them from the 2 KB field cache)
+            if (nT > 0 && t < 16) out.inside[(size_t)item * 16 + t] = S.insideW[t];
         }
         if (t == 0) {
             out.vcount[item] = (nT > 0) ? nV : 0u;

@@ -51,6 +51,7 @@ struct FieldOutputs {
     uint32_t* tcount;      // [cand]
     uint32_t* edgeMask;    // [cand][48] crossing-edge bits, bit e = (i*8 + j*64 + k)*3 + axis
     uint16_t* edgePrefix;  // [cand][48] exclusive popcount prefix
+    uint32_t* inside;      // [cand][16] inside bits of the 512 corners (bit i*8 + j*64 + k), written for candidates with triangles
     uint32_t* mixedList;   // candidates with triangles (arrival order)
     uint32_t* counters;    // [0] field work counter, [1] mixed count, [2] over-capacity MPUs, [3] tri work counter, [4] vertex work counter
 };
