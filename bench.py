@@ -342,7 +342,20 @@ def run_gpu(args):
     if world != args.gpus and world > 1:
         raise SystemExit("WORLD_SIZE %d != --gpus %d" % (world, args.gpus))
     torch.cuda.set_device(local)
+    affinity_note = "unchanged"
     if world > 1:
+        # host threads and the pinned buffers they first touch next to the rank's GPU (NVML's ideal CPU set for the device)
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            h = pynvml.nvmlDeviceGetHandleByIndex(local)
+            words = pynvml.nvmlDeviceGetCpuAffinity(h, (os.cpu_count() + 63) // 64)
+            cpus = {64 * i + b for i, w in enumerate(words) for b in range(64) if (int(w) >> b) & 1} & set(os.sched_getaffinity(0))
+            if cpus:
+                os.sched_setaffinity(0, cpus)
+                affinity_note = "NVML ideal set of GPU %d: %d cpus (%d..%d)" % (local, len(cpus), min(cpus), max(cpus))
+        except Exception as e:
+            affinity_note = "unchanged (%r)" % (e,)
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     w = workload(world)
     root, bt = build_scene(w)
@@ -446,6 +459,44 @@ def run_gpu(args):
         e2e_s += time.perf_counter() - t
     barrier()
 
+    def gather_rows(row):
+        t = torch.tensor(row, dtype=torch.float64, device="cuda")
+        if world == 1:
+            return [row]
+        out = [torch.empty_like(t) for _ in range(world)]
+        dist.all_gather(out, t)
+        return [[float(v) for v in o.cpu()] for o in out]
+
+    # ---- what the host link gives each rank (N > 1): 256 MiB device -> pinned host, all ranks at once and one rank at a time. Explains
+    # the e2e figure at N = 8, where every rank pulls its share of the mesh through the same host at the same moment.
+    d2h_probe = None
+    if world > 1:
+        nb = 256 << 20
+        dsrc = torch.empty(nb, dtype=torch.uint8, device="cuda")
+        hdst = torch.empty(nb, dtype=torch.uint8, pin_memory=True)
+
+        def copy_ms():
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            hdst.copy_(dsrc, non_blocking=True)
+            e1.record()
+            e1.synchronize()
+            return e0.elapsed_time(e1)
+
+        copy_ms()
+        barrier()
+        together = copy_ms()
+        alone = 0.0
+        for r in range(world):
+            barrier()
+            if r == rank:
+                alone = copy_ms()
+        barrier()
+        rows = gather_rows([nb / together * 1e-6, nb / alone * 1e-6])
+        d2h_probe = {"bytes": nb, "GBps_all_ranks_at_once": [round(r[0], 1) for r in rows], "GBps_one_rank_at_a_time": [round(r[1], 1) for r in rows],
+                     "cpu_affinity": affinity_note}
+        del dsrc, hdst
+
     # ---- the same job on ONE GPU, timed in the same run by rank 0 (strong-scaling reference at N > 1)
     single_ms = None
     if world > 1 and rank == 0:
@@ -488,14 +539,6 @@ def run_gpu(args):
         if world == 1:
             return x
         t = torch.tensor([x], dtype=torch.float64, device="cuda"); dist.all_reduce(t, op=dist.ReduceOp.SUM); return float(t[0])
-
-    def gather_rows(row):
-        t = torch.tensor(row, dtype=torch.float64, device="cuda")
-        if world == 1:
-            return [row]
-        out = [torch.empty_like(t) for _ in range(world)]
-        dist.all_gather(out, t)
-        return [[float(v) for v in o.cpu()] for o in out]
 
     K = float(args.steps)
     per_rank = gather_rows([zb, ze, st["mpus_evaluated"], st["mpus_crossed"], nv, nt] + [acc[k] / K for k in keys] + [e2e_s / K * 1e3])
@@ -588,6 +631,8 @@ def run_gpu(args):
                    "stage_ms_rank0": {k[3:]: nacc[k] for k in nkeys}, "roofline": nat_roofs},
         "clocks": clocks,
     }
+    if d2h_probe:
+        out["d2h_probe"] = d2h_probe
     if world > 1 and single_ms:
         out["strong_scaling"] = {"single_gpu_ms_same_job_same_run": single_ms, "speedup": single_ms / (dev_ms_max / args.steps),
                                  "efficiency": single_ms / (dev_ms_max / args.steps) / world}

@@ -292,7 +292,8 @@ int run_cull(psgpu_ctx* ctx, const GridParams& G, int cullMode, bool colorExact,
             CK(cudaMemsetAsync(levelMax, 0, 4, st));
             // few regions with a long program (the top level): a whole CTA per region instead of a warp
             const char* ctaMin = getenv("PSGPU_CULL_CTA_MINLEN");
-            const bool ctaPerRegion = n <= 4096 && parentMaxLen >= (uint32_t)(ctaMin ? atoi(ctaMin) : 1024);
+            const char* ctaMaxN = getenv("PSGPU_CULL_CTA_MAXN");
+            const bool ctaPerRegion = n <= (ctaMaxN ? atoi(ctaMaxN) : 4096) && parentMaxLen >= (uint32_t)(ctaMin ? atoi(ctaMin) : 1024);
             launch_prune_fused(L, cur->as<Region>(), nParents, ctx->pool.as<float4>(), ctx->qflag.as<uint8_t>(), ctx->cullScratch.as<float4>(),
                                ctx->cullScratchFlag.as<uint8_t>(), parentMaxLen, ctx->childLen.as<uint32_t>(), levelMax, ctaPerRegion, st);
         } else
@@ -379,7 +380,7 @@ int ensure_slab_program(psgpu_ctx* ctx, const GridParams& G, bool colorExact) {
         CK(ctx->pool.reserve(((size_t)ctx->progQuads * 2 + 16) * 16, true, st));
         CK(ctx->qflag.reserve((size_t)ctx->progQuads * 2 + 16, true, st));
         CK(ctx->scalars.reserve(64));
-        launch_prune_slab(ctx->pool.as<float4>(), lo, hi, PS_ISO_VALUE, colorExact ? 1 : 0, ctx->pool.as<float4>() + ctx->progQuads,
+        launch_prune_slab(ctx->pool.as<float4>(), ctx->qflag.as<uint8_t>(), ctx->progQuads, lo, hi, PS_ISO_VALUE, colorExact ? 1 : 0, ctx->pool.as<float4>() + ctx->progQuads,
                           ctx->qflag.as<uint8_t>() + ctx->progQuads, cap, ctx->scalars.as<uint32_t>() + 12, st);
         CK(cudaMemcpyAsync(&ctx->hostScalars[12], ctx->scalars.as<uint32_t>() + 12, 4, cudaMemcpyDeviceToHost, st));
         CK(cudaStreamSynchronize(st));

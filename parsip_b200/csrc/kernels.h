@@ -83,8 +83,8 @@ void launch_prune_fused(const CullLevel& L, const Region* parents, int nParents,
 void launch_prune_compact(const CullLevel& L, const Region* parents, int nParents, const float4* scratch, const uint8_t* scratchFlag, uint32_t stride,
                           const uint32_t* childLen, const uint32_t* childOff, const uint32_t* childIdx, float4* outPool, uint8_t* outFlag,
                           uint32_t outBase, Region* children, int32_t* candOfMpu, cudaStream_t st);
-void launch_prune_slab(const float4* prog, const float* lo, const float* hi, float iso, int colorExact, float4* out, uint8_t* outFlag,
-                       uint32_t cap, uint32_t* lenOut, cudaStream_t st);
+void launch_prune_slab(const float4* prog, const uint8_t* progFlag, uint32_t progLen, const float* lo, const float* hi, float iso, int colorExact,
+                       float4* out, uint8_t* outFlag, uint32_t cap, uint32_t* lenOut, cudaStream_t st);
 void launch_prune_one(const float4* prog, const float* lo, const float* hi, int cullMode, float iso, int colorExact, float4* out, uint32_t cap,
                       uint32_t* lenOut, cudaStream_t st);
 size_t scan_temp_bytes(int n);

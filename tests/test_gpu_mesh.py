@@ -405,3 +405,45 @@ def test_q9_reference_mpu_reject_drops_surface_at_coarse_cells(ctx):
     extra = pos[np.concatenate([[0], np.cumsum(counts[:, 0])])[ijk.tolist().index([1, 1, 1])]:][:counts[ijk.tolist().index([1, 1, 1]), 0]]
     r = np.linalg.norm(extra - np.array([1.596, 1.596, 1.596], np.float32), axis=1)
     assert len(extra) > 20 and np.abs(r - 0.4542).max() < 0.02
+
+
+@pytest.mark.parametrize("sem", ["simd", "native"])
+def test_slab_program_of_a_long_tree_gives_the_whole_mesh(ctx, sem):
+    """A slab of a program of >= 2048 quads is polygonized from the program pruned once against the slab's box (context.cu:
+    ensure_slab_program -> prune_slab_kernel, the CTA-cooperative walk). 1 600 primitives in 80 blend groups, 3 slabs: the union of
+    the slab meshes - positions, and in PS_SimdPoly semantics the exact colours with their culling-order scale steps - must be the
+    whole mesh, bit for bit; PSGPU_NO_SLAB_PROGRAM (every slab walks the full program) must give the same slabs."""
+    root = scenes.blobs(1600, 13.0, 5)
+    simd = sem == "simd"
+    flat = bt.flatten(bt.binarize(root)) if simd else bt.flatten(root)
+    lo, hi = ps.prepare_bboxes(bt.flatten(bt.binarize(root)))
+    cs = scenes.cellsize_for(lo, hi, 160)
+    prog = ps.linearize(flat, ps.SEM_SIMD, 0) if simd else ps.linearize(flat, ps.SEM_SCALAR, ps.LIN_REASSOCIATE)
+    assert prog.n_quads >= 2048
+    ctx.upload(prog)
+    kw = dict(root_mode=ps.ROOT_FOURSAMPLE) if simd else {}
+    nz = ps.lattice_dims(cs, lo, hi)[2]
+
+    def soup(m):  # positions (+ colours in the STRICT semantics; the FMA colour blend of the native mode rounds with the pruned program's
+        idx = m["tri"].astype(np.int64)  # form: 1-ulp differences on ~1e-4 of the vertices, with or without the slab program)
+        rows = m["pos"][idx].reshape(-1, 9)
+        if simd:
+            rows = np.concatenate([rows, m["col"][idx].reshape(-1, 9)], axis=1)
+        rows = np.ascontiguousarray(rows, np.float32).view(np.uint32)
+        return rows[np.lexsort(rows.T[::-1])]
+
+    whole = soup(ctx.polygonize(ps.Params.make(cs, lo, hi, **kw)))
+    assert len(whole) > 100_000
+    for env in (None, "1"):
+        if env:
+            os.environ["PSGPU_NO_SLAB_PROGRAM"] = env
+        try:
+            parts = []
+            for r in range(3):
+                zb, ze = sharding.slab_bounds(nz, 3, r)
+                parts.append(soup(ctx.polygonize(ps.Params.make(cs, lo, hi, z_begin=zb, z_end=ze, **kw))))
+        finally:
+            os.environ.pop("PSGPU_NO_SLAB_PROGRAM", None)
+        got = np.concatenate(parts)
+        got = got[np.lexsort(got.T[::-1])]
+        assert got.shape == whole.shape and np.array_equal(got, whole), "slab meshes differ from the whole mesh (slab program %s)" % ("off" if env else "on")
