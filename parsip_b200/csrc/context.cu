@@ -572,8 +572,10 @@ int polygonize_impl(psgpu_ctx* ctx, const psgpu_params* P, psgpu_mesh* out, bool
             if (sink->tri && nT) CK(cudaMemcpyAsync(sink->tri, ctx->tri.p, (size_t)nT * 12, cudaMemcpyDeviceToHost, cs));
             CK(cudaStreamWaitEvent(cs, ctx->ev[6], 0));
             if (sink->pos && nV) CK(cudaMemcpyAsync(sink->pos, ctx->pos.p, (size_t)nV * 12, cudaMemcpyDeviceToHost, cs));
-            if (sink->nrm && nV && P->want_normals) CK(cudaMemcpyAsync(sink->nrm, ctx->nrm.p, (size_t)nV * 12, cudaMemcpyDeviceToHost, cs));
+            const bool nrmLate = normals_in_color_pass(G);  // then the colour pass writes them
+            if (sink->nrm && nV && P->want_normals && !nrmLate) CK(cudaMemcpyAsync(sink->nrm, ctx->nrm.p, (size_t)nV * 12, cudaMemcpyDeviceToHost, cs));
             CK(cudaStreamWaitEvent(cs, ctx->ev[4], 0));
+            if (sink->nrm && nV && P->want_normals && nrmLate) CK(cudaMemcpyAsync(sink->nrm, ctx->nrm.p, (size_t)nV * 12, cudaMemcpyDeviceToHost, cs));
             if (sink->col && nV && P->want_colors) CK(cudaMemcpyAsync(sink->col, ctx->col.p, (size_t)nV * 12, cudaMemcpyDeviceToHost, cs));
             streamed = true;
         }

@@ -460,7 +460,10 @@ __global__ void __launch_bounds__(kThreads, 6) vertex_kernel(GridParams G, const
 
 // colour walk at the final vertex positions (fieldValueAndColor, PS_Polygonizer.cpp:1378-1551 / baseColorOp,
 // CompactBlobTree.cpp:1124-1294): one vertex per lane, the 1-wide coloured interpreter
-template <bool STRICT, bool SMEM, bool WARPS>
+// NRM: the same walk 4 wide over (p, p + dx, p + dy, p + dz) - colour at p plus the forward-difference normal vertex_kernel would
+// otherwise spend its second interpreter pass on (vertex_at): the primitive decode, the colour blends and the scale steps dominate
+// this kernel, three more field lanes ride along for a fraction of a separate pass.
+template <bool STRICT, bool SMEM, bool WARPS, bool NRM>
 __global__ void __launch_bounds__(kThreads) color_kernel(GridParams G, const Region* __restrict__ cands, const float4* __restrict__ pool,
                                                          const float* __restrict__ colorTab, FieldOutputs fo, MeshOutputs mo, int nMixed,
                                                          uint32_t sliceQuads) {
@@ -478,8 +481,21 @@ __global__ void __launch_bounds__(kThreads) color_kernel(GridParams G, const Reg
         const float4* prog = SMEM ? slice : pool + r.off;
         for (uint32_t rk = lane; rk < nV; rk += 32) {
             const size_t vo = (size_t)(vbase + rk) * 3;
-            float X[1] = {mo.pos[vo]}, Y[1] = {mo.pos[vo + 1]}, Z[1] = {mo.pos[vo + 2]}, F[1], rgb[3];
-            eval_program<1, true, STRICT, SMEM, WARPS>(prog, X, Y, Z, F, rgb, colorTab, G.sem);
+            float rgb[3];
+            if (NRM) {
+                const float px = mo.pos[vo], py = mo.pos[vo + 1], pz = mo.pos[vo + 2], dl = PS_NORMAL_DELTA;
+                float X[4] = {px, px + dl, px, px}, Y[4] = {py, py, py + dl, py}, Z[4] = {pz, pz, pz, pz + dl}, F[4];
+                eval_program<4, true, STRICT, SMEM, WARPS>(prog, X, Y, Z, F, rgb, colorTab, G.sem);
+                const float dinv = -1.0f / dl;  // as vertex_at
+                float nx = (F[1] - F[0]) * dinv, nyv = (F[2] - F[0]) * dinv, nzv = (F[3] - F[0]) * dinv;
+                const float l2 = nx * nx + nyv * nyv + nzv * nzv;
+                if (l2 > 0.f) { const float il = rsqrtf(l2); nx *= il; nyv *= il; nzv *= il; }
+                else if (G.sem == PSGPU_SEM_SCALAR) { nx = nyv = nzv = 1.0f; }
+                mo.nrm[vo] = nx; mo.nrm[vo + 1] = nyv; mo.nrm[vo + 2] = nzv;
+            } else {
+                float X[1] = {mo.pos[vo]}, Y[1] = {mo.pos[vo + 1]}, Z[1] = {mo.pos[vo + 2]}, F[1];
+                eval_program<1, true, STRICT, SMEM, WARPS>(prog, X, Y, Z, F, rgb, colorTab, G.sem);
+            }
             mo.col[vo] = rgb[0]; mo.col[vo + 1] = rgb[1]; mo.col[vo + 2] = rgb[2];
         }
         int nxt = 0;
@@ -529,6 +545,11 @@ void launch_halo_build(const GridParams& G, const int32_t* candOfMpu, const Fiel
     halo_build_kernel<<<(nxy + 3) / 4, 128, 0, st>>>(G, candOfMpu, fo, vbase, hVbase, hMask, hPrefix, nxy);
 }
 
+// PS_SimdPoly semantics with colours and normals wanted: the normal comes out of the colour pass (color_kernel<.., NRM>)
+bool normals_in_color_pass(const GridParams& G) {
+    return G.sem == PSGPU_SEM_SIMD && G.wantColors && G.wantNormals && !getenv("PSGPU_SEPARATE_NORMAL_PASS");
+}
+
 void launch_emit_kernels(const GridParams& G, const Region* cands, const float4* pool, const float* colorTab, const FieldOutputs& fo,
                          const MeshOutputs& mo, const int32_t* candOfMpu, int nMixed, uint32_t maxProgQuads, int numSMs, cudaStream_t st,
                          cudaEvent_t evTriDone, cudaEvent_t evVertexDone) {
@@ -565,13 +586,17 @@ void launch_emit_kernels(const GridParams& G, const Region* cands, const float4*
     if (perSM < 1) perSM = 1;
     int grid = numSMs * perSM;
     if (grid > need) grid = need;
-    k<<<grid, kThreads, smem, st>>>(G, cands, pool, fo, mo, nMixed, slice);
+    const bool nrmInColor = normals_in_color_pass(G);
+    GridParams Gv = G;
+    if (nrmInColor) Gv.wantNormals = 0;  // vertex_kernel places the vertex only
+    k<<<grid, kThreads, smem, st>>>(Gv, cands, pool, fo, mo, nMixed, slice);
     if (evVertexDone) cudaEventRecord(evVertexDone, st);
     if (G.wantColors) {
         using ColorT = void (*)(GridParams, const Region*, const float4*, const float*, FieldOutputs, MeshOutputs, int, uint32_t);
-        const ColorT kc = strict ? (smemOk ? color_kernel<true, true, false> : color_kernel<true, false, false>)
-                          : warps ? (smemOk ? color_kernel<false, true, true> : color_kernel<false, false, true>)
-                                  : (smemOk ? color_kernel<false, true, false> : color_kernel<false, false, false>);
+        const ColorT kc = nrmInColor ? (smemOk ? color_kernel<true, true, false, true> : color_kernel<true, false, false, true>)
+                          : strict ? (smemOk ? color_kernel<true, true, false, false> : color_kernel<true, false, false, false>)
+                          : warps ? (smemOk ? color_kernel<false, true, true, false> : color_kernel<false, false, true, false>)
+                                  : (smemOk ? color_kernel<false, true, false, false> : color_kernel<false, false, false, false>);
         perSM = 0;
         cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSM, kc, kThreads, smem);
         if (perSM < 1) perSM = 1;

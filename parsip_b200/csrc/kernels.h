@@ -106,6 +106,7 @@ float run_fp32_peak(int numSMs, cudaStream_t st, float* ms_out);
 void launch_cube_cases(const GridParams& G, const float* fv, uint8_t* case343, cudaStream_t st);
 void launch_halo_build(const GridParams& G, const int32_t* candOfMpu, const FieldOutputs& fo, const uint32_t* vbase, uint32_t* hVbase,
                        uint32_t* hMask, uint16_t* hPrefix, int nxy, cudaStream_t st);
+bool normals_in_color_pass(const GridParams& G);
 void launch_emit_kernels(const GridParams& G, const Region* cands, const float4* pool, const float* colorTab, const FieldOutputs& fo,
                          const MeshOutputs& mo, const int32_t* candOfMpu, int nMixed, uint32_t maxProgQuads, int numSMs, cudaStream_t st,
                          cudaEvent_t evTriDone = nullptr, cudaEvent_t evVertexDone = nullptr);
