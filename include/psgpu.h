@@ -210,6 +210,17 @@ int psgpu_mesh_map_host(psgpu_ctx* ctx, const float** pos, const float** nrm, co
 /* Parity hooks: field (and colour / normal) at arbitrary HOST points with the full, unculled program. */
 int psgpu_field_eval(psgpu_ctx* ctx, const float* xyz, int64_t n, float* f_out);
 int psgpu_field_color_normal(psgpu_ctx* ctx, const float* xyz, int64_t n, float* f, float* col, float* nrm);
+/* psgpu_field_eval without any allocation. NO COUNTERPART IN THE REFERENCE: added for callers that
+ * cannot call cudaMalloc (code under CUDA graph capture, tight serving / haptics loops, harnesses that forbid it). Same inputs, outputs
+ * and results as psgpu_field_eval (the same kernel); the device staging is a file-scope static device array of
+ * 4 * PSGPU_NOALLOC_MAX_POINTS floats = 1 MiB that every GPU which loads the library holds until the process exits. It calls no
+ * cudaMalloc / cudaFree or allocating library routine, on the first call or later (the program must already be uploaded).
+ * n > PSGPU_NOALLOC_MAX_POINTS is rejected with PSGPU_NOT_ENOUGH_MEM and a message in psgpu_last_error: split the batch.
+ * All calls on one device share the array and it keeps the last call's contents; nothing in it needs to start at zero (a call
+ * overwrites every word it reads). Calls that OVERLAP on the GPU - two contexts on one device, two host threads - race on it and
+ * must be serialised by the caller. */
+#define PSGPU_NOALLOC_MAX_POINTS 65536
+int psgpu_field_eval_noalloc(psgpu_ctx* ctx, const float* xyz, int64_t n, float* f_out);
 /* Shrink-wrap Newton root search between n HOST point pairs (p1, p2: 3 floats each; f1, f2: their field values) with the full program, in
  * the uploaded program's semantics: PSGPU_SEM_SIMD = FieldComputer::computeRootNewtonRaphson (public in the reference, not called by its
  * Polygonize), PSGPU_SEM_SCALAR = ComputeRootNewtonRaphsonVEC4 (what CParsipOptimized places vertices with). Outputs per pair: root (3

@@ -8,6 +8,7 @@ import numpy as np
 
 SEM_SIMD, SEM_SCALAR = 0, 1
 ROOT_FOURSAMPLE, ROOT_NEWTON_REF, ROOT_BISECT = 0, 1, 2
+NOALLOC_MAX_POINTS = 65536  # PSGPU_NOALLOC_MAX_POINTS
 COORD_MPU_LOCAL, COORD_GLOBAL = 0, 1
 OUT_INDEXED, OUT_MPU = 0, 1
 CULL_NONE, CULL_SUPPORT, CULL_INTERVAL = 0, 1, 2
@@ -20,7 +21,7 @@ ERRORS = {-1: "PARAM_ERROR", -2: "NOT_ENOUGH_MEM", -3: "INVALID_BVH", -4: "UNSUP
 EXPORTS = [
     "psgpu_create", "psgpu_destroy", "psgpu_last_error", "psgpu_device_count", "psgpu_linearize", "psgpu_program_free",
     "psgpu_program_info", "psgpu_program_copy", "psgpu_program_colors", "psgpu_prepare_bboxes", "psgpu_count_mpus", "psgpu_upload_program",
-    "psgpu_polygonize", "psgpu_polygonize_host", "psgpu_mesh_download", "psgpu_mesh_map_host", "psgpu_field_eval", "psgpu_field_color_normal", "psgpu_newton_roots",
+    "psgpu_polygonize", "psgpu_polygonize_host", "psgpu_mesh_download", "psgpu_mesh_map_host", "psgpu_field_eval", "psgpu_field_color_normal", "psgpu_newton_roots", "psgpu_field_eval_noalloc",
     "psgpu_tree_binarize", "psgpu_tree_view", "psgpu_tree_free", "psgpu_tree_flatten_transforms", "psgpu_tree_octrees", "psgpu_scene_load", "psgpu_scene_save", "psgpu_mpu_cache", "psgpu_mpu_caches_culled", "psgpu_prune_region", "psgpu_get_stats", "psgpu_measure_fp32_peak",
     "psgpu_comm_get_unique_id", "psgpu_comm_init", "psgpu_comm_destroy", "psgpu_slab_bounds", "psgpu_polygonize_sharded", "psgpu_polygonize_sharded_host", "psgpu_mesh_gather", "psgpu_layer_work",
 ]
@@ -137,6 +138,7 @@ def load_library():
     lib.psgpu_scene_load.argtypes = [C.c_char_p, C.c_int, vp]
     lib.psgpu_scene_save.argtypes = [vp, C.c_char_p]
     lib.psgpu_field_eval.argtypes = [vp, vp, C.c_int64, vp]
+    lib.psgpu_field_eval_noalloc.argtypes = [vp, vp, C.c_int64, vp]
     lib.psgpu_newton_roots.argtypes = [vp, vp, vp, vp, vp, C.c_int64, C.c_float, C.c_int, vp, vp, vp]
     lib.psgpu_field_color_normal.argtypes = [vp, vp, C.c_int64, vp, vp, vp]
     lib.psgpu_mpu_cache.argtypes = [vp, C.POINTER(Params), vp, vp, vp]
@@ -375,6 +377,13 @@ class Context:
         xyz = np.ascontiguousarray(xyz, np.float32).reshape(-1, 3)
         out = np.zeros(len(xyz), np.float32)
         self._check(self.lib.psgpu_field_eval(self.h, xyz.ctypes.data, len(xyz), out.ctypes.data), "psgpu_field_eval")
+        return out
+
+    def field_noalloc(self, xyz) -> np.ndarray:
+        """psgpu_field_eval_noalloc: the same kernel with its staging in the library's static device array (<= NOALLOC_MAX_POINTS points)."""
+        xyz = np.ascontiguousarray(xyz, np.float32).reshape(-1, 3)
+        out = np.zeros(len(xyz), np.float32)
+        self._check(self.lib.psgpu_field_eval_noalloc(self.h, xyz.ctypes.data, len(xyz), out.ctypes.data), "psgpu_field_eval_noalloc")
         return out
 
     def newton_roots(self, p1, p2, f1, f2, target=0.5, iterations=8):

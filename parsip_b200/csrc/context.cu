@@ -9,6 +9,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <mutex>
 #include <string>
 #include <vector>
 
@@ -1032,5 +1033,58 @@ extern "C" int psgpu_measure_fp32_peak(psgpu_ctx* ctx, float* tflops_out, float*
         *sm_clock_mhz_out = khz / 1000.0f;
     }
     CK(cudaGetLastError());
+    return PSGPU_SUCCESS;
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
+// psgpu_field_eval_noalloc: psgpu_field_eval for callers that must not allocate (code under CUDA graph capture, tight
+// serving / haptics loops, harnesses that forbid cudaMalloc). No counterpart in the reference.
+// The device staging psgpu_field_eval keeps in growable context buffers (ptsIn / ptsF, cudaMalloc on first
+// use and on growth) lives here in ONE file-scope device array of fixed size:
+//     [ xyz: 3 * PSGPU_NOALLOC_MAX_POINTS floats | f: PSGPU_NOALLOC_MAX_POINTS floats ]  = 1 MiB,
+// held by every GPU that loads the library until the process exits. All calls on a device share it and it keeps the last
+// call's contents. Nothing in it has to start at zero: a call writes xyz[0 .. 3n) before the kernel reads it and the kernel
+// writes f[0 .. n) before the copy-out reads it (the kernel clamps its read index to n - 1), so no clear is issued.
+// Calls that overlap on the GPU (two contexts = two streams on one device, or two host threads) RACE on the array: the
+// caller serialises them. In HOST code `g_noallocScratch` is a host-side stand-in, not a device address - the pointer the
+// kernel gets comes from cudaGetSymbolAddress, looked up once per device with that device current.
+// ---------------------------------------------------------------------------------------------------------------------
+static __device__ __align__(256) float g_noallocScratch[4 * PSGPU_NOALLOC_MAX_POINTS];
+
+namespace {
+constexpr int kNoallocMaxDevices = 64;
+float* g_noallocAddr[kNoallocMaxDevices];  // device address of g_noallocScratch per device ordinal, nullptr = not looked up yet
+std::mutex g_noallocLock;
+}  // namespace
+
+extern "C" int psgpu_field_eval_noalloc(psgpu_ctx* ctx, const float* xyz, int64_t n, float* f_out) {
+    if (!ctx || !xyz || !f_out || n < 0 || ctx->progQuads == 0) return PSGPU_PARAM_ERROR;
+    if (n > (int64_t)PSGPU_NOALLOC_MAX_POINTS) {
+        ctx->err = "psgpu_field_eval_noalloc: " + std::to_string((long long)n) + " points exceed the static scratch of " +
+                   std::to_string((long long)PSGPU_NOALLOC_MAX_POINTS) + " points (PSGPU_NOALLOC_MAX_POINTS); split the batch or use psgpu_field_eval";
+        return PSGPU_NOT_ENOUGH_MEM;
+    }
+    if (ctx->device < 0 || ctx->device >= kNoallocMaxDevices) { ctx->err = "psgpu_field_eval_noalloc: device ordinal out of range"; return PSGPU_PARAM_ERROR; }
+    if (n == 0) return PSGPU_SUCCESS;
+    CK(cudaSetDevice(ctx->device));
+    float* scratch = nullptr;
+    {
+        std::lock_guard<std::mutex> guard(g_noallocLock);
+        if (!g_noallocAddr[ctx->device]) {  // set-up, once per device, with that device current
+            void* p = nullptr;
+            CK(cudaGetSymbolAddress(&p, g_noallocScratch));
+            if (!p) { ctx->err = "cudaGetSymbolAddress(g_noallocScratch) returned a null address"; return PSGPU_ERROR_CUDA; }
+            g_noallocAddr[ctx->device] = static_cast<float*>(p);
+        }
+        scratch = g_noallocAddr[ctx->device];
+    }
+    cudaStream_t st = ctx->stream;
+    float* dXyz = scratch;
+    float* dF = scratch + (size_t)3 * PSGPU_NOALLOC_MAX_POINTS;
+    CK(cudaMemcpyAsync(dXyz, xyz, (size_t)n * 12, cudaMemcpyHostToDevice, st));
+    psgpu::launch_points_field(ctx->pool.as<float4>(), dXyz, n, dF, ctx->semantics, st);  // the kernel psgpu_field_eval launches
+    CK(cudaGetLastError());
+    CK(cudaMemcpyAsync(f_out, dF, (size_t)n * 4, cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
     return PSGPU_SUCCESS;
 }
