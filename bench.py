@@ -592,8 +592,12 @@ def run_gpu(args):
     flops = float(st["algorithmic_flops"])
     vflops = float(st["vertex_eval_flops"])
     tri_bytes = float(st["mpus_crossed"]) * (2048 + 288 + 8) + nt * 12.0
-    roofs = [roof_fp32("field_kernel", flops, acc["ms_field"] / K), roof_fp32("vertex_kernel", 8.0 * vflops, acc["ms_vertex"] / K),
-             roof_fp32("color_kernel", vflops, acc["ms_color"] / K), roof_hbm("tri_kernel", tri_bytes, acc["ms_tri"] / K)]
+    # per vertex the reference spends 4 root samples, then fieldValueAndColor (1) + normal (3 more samples): 8 evaluations of the MPU's
+    # program. vertex_kernel does the first 4; color_kernel<.., NRM> the other 4 in one 4-wide coloured walk (emit.cu:
+    # normals_in_color_pass). With PSGPU_SEPARATE_NORMAL_PASS the normal samples go back to vertex_kernel (8) and the colour walk is 1-wide.
+    v_evals, c_evals = (8.0, 1.0) if os.environ.get("PSGPU_SEPARATE_NORMAL_PASS") else (4.0, 4.0)
+    roofs = [roof_fp32("field_kernel", flops, acc["ms_field"] / K), roof_fp32("vertex_kernel", v_evals * vflops, acc["ms_vertex"] / K),
+             roof_fp32("color_kernel", c_evals * vflops, acc["ms_color"] / K), roof_hbm("tri_kernel", tri_bytes, acc["ms_tri"] / K)]
     roofs.sort(key=lambda r: -r["ms_per_launch"])
     dominant, other = roofs[0], roofs[1:]
     # native semantics: 14 point evaluations per vertex (4 section rounds x ... see psgpu_stats.field_evals) - the vertex kernel's

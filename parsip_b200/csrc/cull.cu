@@ -278,7 +278,7 @@ struct CtaWalkSmem {
     float box[6];
 };
 
-template <bool EMIT>
+template <bool EMIT, bool FINE = false>
 __device__ uint32_t prune_walk_cta(const float4* __restrict__ src, const uint8_t* __restrict__ sflag, uint32_t srcLen, const Box3& region,
                                    int cullMode, float iso, float4* __restrict__ dst, uint8_t* dflag, bool colorExact, uint32_t limit,
                                    CtaWalkSmem& S) {
@@ -319,7 +319,7 @@ __device__ uint32_t prune_walk_cta(const float4* __restrict__ src, const uint8_t
         float flo = 0.f, fhi = 0.f;
         uint32_t scale = 0;
         if (active && opc != OPC_END && opc < OPC_FIRST_NONPRIM) {
-            pz = prim_bound(hdr, q0, src + p + 1, box, flo, fhi);
+            pz = FINE ? prim_bound_tiled(hdr, q0, src + p + 1, box, flo, fhi, false) : prim_bound(hdr, q0, src + p + 1, box, flo, fhi);  // <= 64 tiles: with the exact box test finer ones drop nothing more and cost 7 ms per upload
             skip = Pruner<EMIT>::skippable(hdr, pz, scale);
         }
         const bool isEntry = active && !skip;
@@ -485,7 +485,7 @@ __global__ void __launch_bounds__(kCtaWarps * 32) prune_slab_kernel(const float4
                                                                     Box3 box, float iso, int colorExact, float4* __restrict__ out,
                                                                     uint8_t* __restrict__ outFlag, uint32_t cap, uint32_t* __restrict__ lenOut) {
     __shared__ CtaWalkSmem S;
-    const uint32_t len = prune_walk_cta<true>(prog, progFlag, progLen, box, PSGPU_CULL_SUPPORT, iso, out, outFlag, colorExact != 0, cap, S);
+    const uint32_t len = prune_walk_cta<true, true>(prog, progFlag, progLen, box, PSGPU_CULL_SUPPORT, iso, out, outFlag, colorExact != 0, cap, S);
     if (threadIdx.x == 0) *lenOut = len;
 }
 

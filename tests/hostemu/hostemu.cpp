@@ -66,9 +66,11 @@ uint32_t hostemu_prune(const float* quads, const float* lo3, const float* hi3, i
     const float4* prog = reinterpret_cast<const float4*>(quads);
     Box3 b;
     for (int a = 0; a < 3; a++) { b.lo[a] = lo3[a]; b.hi[a] = hi3[a]; }
-    const uint32_t len = prune_walk<false>(prog, b, cullMode, iso, nullptr, colorExact != 0);
+    const bool fine = (colorExact & 2) != 0;  // bit 1: the slab prune's fine tiling of elongated boxes (cull_walk.cuh: prim_bound)
+    colorExact &= 1;
+    const uint32_t len = prune_walk<false>(prog, b, cullMode, iso, nullptr, colorExact != 0, 0xFFFFFFFFu, nullptr, fine);
     if (len == 0 || len > outCapQuads || !out) return len;
-    const uint32_t len2 = prune_walk<true>(prog, b, cullMode, iso, reinterpret_cast<float4*>(out), colorExact != 0, len);
+    const uint32_t len2 = prune_walk<true>(prog, b, cullMode, iso, reinterpret_cast<float4*>(out), colorExact != 0, len, nullptr, fine);
     if (len2 != len) return 0xFFFFFFFFu;  // the measuring and the emitting pass must agree
     return len;
 }

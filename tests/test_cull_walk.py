@@ -156,3 +156,27 @@ def test_simd_colour_rule_survives_two_pruning_levels():
             assert np.array_equal(col[on].view(np.uint32), full_c[on].view(np.uint32))
             checked += int(on.sum())
     assert checked > 1000
+
+
+@pytest.mark.parametrize("sem", ["simd", "scalar"])
+def test_slab_prune_with_tiled_bounds_is_exact_and_tighter(sem):
+    """The one-off prune of a program against a rank's z-slab (context.cu: ensure_slab_program) covers the elongated slab box with a grid
+    of balls and tests every primitive's exact support box (cull_walk.cuh: prim_bound_tiled, prim_outside_box) - one ball around a
+    146 x 146 x 18-MPU slab reaches across the whole model and drops nothing. The slab program must give bit-identical fields at every
+    point of the slab, and be much shorter than the single-ball prune."""
+    from parsip_b200 import scenes
+    root = scenes.blobs(1200, 12.0, 9)
+    simd = sem == "simd"
+    flat = bt.flatten(bt.binarize(root)) if simd else bt.flatten(root)
+    quads = (ps.linearize(flat, ps.SEM_SIMD, 0) if simd else ps.linearize(flat, ps.SEM_SCALAR, ps.LIN_REASSOCIATE)).quads()
+    lo, hi = ps.prepare_bboxes(bt.flatten(bt.binarize(root)))
+    rs = np.random.RandomState(4)
+    semc = ps.SEM_SIMD if simd else ps.SEM_SCALAR
+    for z0, z1 in ((lo[2], lo[2] + 1.5), (5.0, 6.2), (hi[2] - 2.0, hi[2])):
+        a, b = np.array([lo[0], lo[1], z0], np.float32), np.array([hi[0], hi[1], z1], np.float32)
+        ball = emu.prune(quads, a, b, ps.CULL_SUPPORT, ISO, 1 if simd else 0)
+        tiled = emu.prune(quads, a, b, ps.CULL_SUPPORT, ISO, (1 if simd else 0) | 2)
+        assert tiled is not None and len(tiled) < 0.6 * len(ball), (len(tiled), len(ball))
+        pts = rs.uniform(a, b, (20000, 3)).astype(np.float32)
+        pts[:4000, 2] = np.where(rs.rand(4000) < 0.5, a[2], b[2])  # the slab's own boundary planes
+        assert np.array_equal(emu.field(quads, pts, semc).view(np.uint32), emu.field(tiled, pts, semc).view(np.uint32))
