@@ -58,6 +58,7 @@ struct psgpu_ctx {
     int nPrims = 0;
     int semantics = PSGPU_SEM_SCALAR;
     bool hasWarps = false;  // the program uses the point stack (warps / operator matrices)
+    bool nonNeg = false;    // no difference operator anywhere in the program: every value on the stack is >= 0
     DevBuf pool;      // float4: [full program | level 0 programs | level 1 programs | ...]
     DevBuf qflag;     // one byte per pool quad: 1 = first quad of an instruction (read by the warp-cooperative pruning passes)
     DevBuf colors;
@@ -180,6 +181,19 @@ extern "C" int psgpu_upload_program(psgpu_ctx* ctx, const psgpu_program* p) {
     ctx->nPrims = p->nPrims;
     ctx->semantics = p->semantics;
     ctx->hasWarps = p->maxPointStack > 0;
+    {   // differences (min(a, 1 - b), a * (1 - b) and their reversed forms) are the only operators that can leave a negative value
+        bool neg = false;
+        const uint32_t* w = p->words.data();
+        const size_t nq = p->words.size() / 4;
+        for (size_t pc = 0; pc < nq;) {
+            const uint32_t hdr = w[pc * 4], opc = PS_HDR_OPC(hdr), cmb = PS_HDR_CMB(hdr);
+            if (opc == OPC_END) break;
+            if ((opc < OPC_FIRST_NONPRIM || opc == OPC_COMBINE) && (cmb == CMB_DIF || cmb == CMB_SDIF || cmb == CMB_RDIF || cmb == CMB_RSDIF)) neg = true;
+            if (opc == OPC_DIF0 || opc == OPC_RICCI_SIMD) neg = true;  // fast_pow's quotient changes sign beyond its pole
+            pc += (size_t)ps_instr_quads(hdr);
+        }
+        ctx->nonNeg = !neg;
+    }
     return PSGPU_SUCCESS;
 }
 
@@ -219,7 +233,7 @@ int run_cull(psgpu_ctx* ctx, const GridParams& G, int cullMode, bool colorExact,
     CK(ctx->candOfMpu.reserve(nMpu * 4));
     CullLevel L;
     for (int a = 0; a < 3; a++) { L.lo[a] = G.lo[a]; L.hi[a] = G.hi[a]; L.gridLo[a] = G.gridLo[a]; }
-    L.mpuSide = G.mpuSide; L.cullMode = cullMode; L.iso = G.iso; L.childSize = 1; L.colorExact = colorExact ? 1 : 0;
+    L.mpuSide = G.mpuSide; L.cullMode = cullMode; L.iso = G.iso; L.childSize = 1; L.colorExact = colorExact ? 1 : 0; L.nonNeg = ctx->nonNeg ? 1 : 0;
     poolUsed = ctx->rootOff + ctx->rootLen;  // [full program | slab program] stay; the levels are rebuilt behind them
     if (cullMode == PSGPU_CULL_NONE) {
         if (nMpu > (size_t)1 << 30) { ctx->err = "lattice too large"; return PSGPU_NOT_ENOUGH_MEM; }

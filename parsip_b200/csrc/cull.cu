@@ -113,7 +113,7 @@ struct __align__(16) CoopEntry { uint32_t pc; uint32_t za; float flo, fhi; };  /
 template <bool EMIT>
 __device__ uint32_t prune_walk_warp(const float4* __restrict__ src, const uint8_t* __restrict__ sflag, uint32_t srcLen, const Box3& region,
                                     int cullMode, float iso, float4* __restrict__ dst, uint8_t* dflag, bool colorExact, uint32_t limit,
-                                    CoopEntry* ent) {
+                                    CoopEntry* ent, bool nonNeg = false) {
     const int lane = threadIdx.x & 31;
     const uint32_t FULL = 0xffffffffu;
     Pruner<EMIT> P;
@@ -143,7 +143,7 @@ __device__ uint32_t prune_walk_warp(const float4* __restrict__ src, const uint8_
         uint32_t scale = 0;
         if (active && opc != OPC_END && opc < OPC_FIRST_NONPRIM) {
             pz = prim_bound(hdr, q0, src + p + 1, box, flo, fhi);
-            skip = Pruner<EMIT>::skippable(hdr, pz, scale);
+            skip = Pruner<EMIT>::skippable(hdr, pz, scale, nonNeg);
         }
         const bool isEntry = active && !skip;
         const uint32_t zs = (active && skip) ? scale : 0u;
@@ -213,7 +213,7 @@ __global__ void __launch_bounds__(kCoopWarps * 32) prune_count_warp_kernel(CullL
     uint32_t len = 0;
     if (child_region(L, parent, gw & 63, coord, box))
         len = prune_walk_warp<false>(pool + parent.off, qflag + parent.off, parent.len, box, L.cullMode, L.iso, nullptr, nullptr, L.colorExact != 0,
-                                     0xFFFFFFFFu, sEnt[threadIdx.x >> 5]);
+                                     0xFFFFFFFFu, sEnt[threadIdx.x >> 5], L.nonNeg != 0);
     if ((threadIdx.x & 31) == 0) childLen[gw] = len;
 }
 
@@ -234,7 +234,7 @@ __global__ void __launch_bounds__(kCoopWarps * 32) prune_emit_warp_kernel(CullLe
     child_region(L, parent, gw & 63, coord, box);
     const uint32_t off = outBase + childOff[gw];
     prune_walk_warp<true>(pool + parent.off, qflag + parent.off, parent.len, box, L.cullMode, L.iso, outPool + off, outFlag ? outFlag + off : nullptr,
-                          L.colorExact != 0, len, sEnt[threadIdx.x >> 5]);
+                          L.colorExact != 0, len, sEnt[threadIdx.x >> 5], L.nonNeg != 0);
     if ((threadIdx.x & 31) == 0) publish_child(L, coord, off, len, childIdx[gw], children, candOfMpu, maxLen);
 }
 
@@ -254,7 +254,7 @@ __global__ void __launch_bounds__(kCoopWarps * 32) prune_fused_warp_kernel(CullL
     uint32_t len = 0;
     if (child_region(L, parent, gw & 63, coord, box))
         len = prune_walk_warp<true>(pool + parent.off, qflag + parent.off, parent.len, box, L.cullMode, L.iso, scratch + (size_t)gw * stride,
-                                    scratchFlag + (size_t)gw * stride, L.colorExact != 0, stride, sEnt[threadIdx.x >> 5]);
+                                    scratchFlag + (size_t)gw * stride, L.colorExact != 0, stride, sEnt[threadIdx.x >> 5], L.nonNeg != 0);
     if ((threadIdx.x & 31) == 0) {
         if (len > stride) len = 0xFFFFFFFFu;  // cannot happen (emitted <= source); poisons the total so the host notices
         childLen[gw] = len;
@@ -281,7 +281,7 @@ struct CtaWalkSmem {
 template <bool EMIT, bool FINE = false>
 __device__ uint32_t prune_walk_cta(const float4* __restrict__ src, const uint8_t* __restrict__ sflag, uint32_t srcLen, const Box3& region,
                                    int cullMode, float iso, float4* __restrict__ dst, uint8_t* dflag, bool colorExact, uint32_t limit,
-                                   CtaWalkSmem& S) {
+                                   CtaWalkSmem& S, bool nonNeg = false) {
     const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
     const uint32_t FULL = 0xffffffffu, NONE = 0xffffffffu;
     Pruner<EMIT> P;
@@ -320,7 +320,7 @@ __device__ uint32_t prune_walk_cta(const float4* __restrict__ src, const uint8_t
         uint32_t scale = 0;
         if (active && opc != OPC_END && opc < OPC_FIRST_NONPRIM) {
             pz = FINE ? prim_bound_tiled(hdr, q0, src + p + 1, box, flo, fhi, false) : prim_bound(hdr, q0, src + p + 1, box, flo, fhi);  // <= 64 tiles: with the exact box test finer ones drop nothing more and cost 7 ms per upload
-            skip = Pruner<EMIT>::skippable(hdr, pz, scale);
+            skip = Pruner<EMIT>::skippable(hdr, pz, scale, nonNeg);
         }
         const bool isEntry = active && !skip;
         const uint32_t zs = (active && skip) ? scale : 0u;
@@ -417,7 +417,7 @@ __global__ void __launch_bounds__(kCtaWarps * 32) prune_fused_cta_kernel(CullLev
     uint32_t len = 0;
     if (child_region(L, parent, gw & 63, coord, box))  // uniform over the CTA
         len = prune_walk_cta<true>(pool + parent.off, qflag + parent.off, parent.len, box, L.cullMode, L.iso, scratch + (size_t)gw * stride,
-                                   scratchFlag + (size_t)gw * stride, L.colorExact != 0, stride, S);
+                                   scratchFlag + (size_t)gw * stride, L.colorExact != 0, stride, S, L.nonNeg != 0);
     if (threadIdx.x == 0) {
         if (len > stride) len = 0xFFFFFFFFu;
         childLen[gw] = len;

@@ -274,6 +274,7 @@ __device__ __noinline__ bool prim_bound_tiled(uint32_t hdr, const float4 q0, con
 }
 
 __device__ __forceinline__ void bound_combine(uint32_t cmb, float& lo, float& hi, float vlo, float vhi) {
+    const bool nonNegIn = lo >= 0.f && vlo >= 0.f && (cmb == CMB_ADD || cmb == CMB_RADD || cmb == CMB_MAX || cmb == CMB_MIN);
     switch (cmb) {
     case CMB_ADD: case CMB_RADD: lo += vlo; hi += vhi; break;
     case CMB_MAX: lo = fmaxf(lo, vlo); hi = fmaxf(hi, vhi); break;
@@ -293,6 +294,9 @@ __device__ __forceinline__ void bound_combine(uint32_t cmb, float& lo, float& hi
     }
     const float e = 2e-6f * (fabsf(lo) + fabsf(hi)) + 1e-7f;
     lo -= e; hi += e;
+    // sums, maxima and minima of non-negative values are non-negative in floating point too: without this a sum with lower bound 0 went
+    // to -1e-7 and the next all-zero union operand left a useless `max(top, 0)` instruction in the pruned program (3 % of them)
+    if (nonNegIn) lo = fmaxf(lo, 0.f);
 }
 
 // Prunes a program against a region box. EMIT = false only measures. finish() returns the pruned length in quads including
@@ -381,9 +385,12 @@ struct Pruner {
     }
     // true for an all-zero primitive the caller may skip instead of feeding it to step_prim: 0 added to / smooth-subtracted
     // from the top changes nothing but the colour weights; `scale` = the colour-scale steps to pass to skipped_scale
-    __device__ static __forceinline__ bool skippable(uint32_t hdr, bool pz, uint32_t& scale) {
+    // nonNeg (the program has no difference operators, so no value on the stack can be negative - context.cu sets it at upload): an
+    // all-zero union operand, max(top, 0), is skippable too. Unions of one-primitive groups are most of a pruned blob program
+    // (the peephole of step_op folds `PUSH p; COMBINE max` into `p (max)`), and at the next finer level most of them are zero.
+    __device__ static __forceinline__ bool skippable(uint32_t hdr, bool pz, uint32_t& scale, bool nonNeg = false) {
         const uint32_t cmb = PS_HDR_CMB(hdr);
-        if (!pz || (cmb != CMB_ADD && cmb != CMB_SDIF)) return false;
+        if (!pz || (cmb != CMB_ADD && cmb != CMB_SDIF && !(nonNeg && cmb == CMB_MAX))) return false;
         scale = (cmb == CMB_ADD ? 1u : 0u) + (PS_HDR_PRE(hdr) ? 0u : PS_HDR_CSC(hdr));  // a PRE count scaled the dropped primitive's own colour
         return true;
     }
@@ -504,7 +511,7 @@ struct Pruner {
                 copy(pc, q0, hdr, nq);
                 const float e = q0.y;
                 const float a = powf(fmaxf(blo[sp], 0.f), e), b = powf(fmaxf(bhi[sp], 0.f), e);
-                blo[sp] = fminf(a, b) * 0.9999f - 1e-7f; bhi[sp] = fmaxf(a, b) * 1.0001f + 1e-7f;
+                blo[sp] = fmaxf(fminf(a, b) * 0.9999f - 1e-7f, 0.f); bhi[sp] = fmaxf(a, b) * 1.0001f + 1e-7f;  // a power of a clamped base is >= 0
                 if (!(blo[sp] == blo[sp]) || !(bhi[sp] == bhi[sp])) { blo[sp] = -3.0e38f; bhi[sp] = 3.0e38f; }
             }
         } break;

@@ -23,6 +23,7 @@ struct CullLevel {
     int cullMode;
     float iso;
     int colorExact;      // PS_SimdPoly semantics with colours wanted: blends keep OPC_CSCALE markers (program.h)
+    int nonNeg;          // the program has no difference operators: no stack value can be negative (cull_walk.cuh: skippable)
 };
 
 struct GridParams {
