@@ -484,8 +484,19 @@ __global__ void __launch_bounds__(kThreads) color_kernel(GridParams G, const Reg
             float rgb[3];
             if (NRM) {
                 const float px = mo.pos[vo], py = mo.pos[vo + 1], pz = mo.pos[vo + 2], dl = PS_NORMAL_DELTA;
-                float X[4] = {px, px + dl, px, px}, Y[4] = {py, py, py + dl, py}, Z[4] = {pz, pz, pz, pz + dl}, F[4];
-                eval_program<4, true, STRICT, SMEM, WARPS>(prog, X, Y, Z, F, rgb, colorTab, G.sem);
+                float F[4];
+                if constexpr (STRICT) {  // the packed-pair walk with the colour rules on point 0 (interp_packed.cuh), same bits
+                    PairPts<2, false> P;
+                    P.x[0] = pk(px, px + dl); P.x[1] = pk(px, px);
+                    P.y[0] = pk(py, py); P.y[1] = pk(py + dl, py);
+                    P.z[0] = pk(pz, pz); P.z[1] = pk(pz, pz + dl);
+                    F2 FP[2];
+                    eval_program_packed<2, false, SMEM, true>(prog, P, FP, rgb, colorTab);
+                    up(FP[0], F[0], F[1]); up(FP[1], F[2], F[3]);
+                } else {
+                    float X[4] = {px, px + dl, px, px}, Y[4] = {py, py, py + dl, py}, Z[4] = {pz, pz, pz, pz + dl};
+                    eval_program<4, true, STRICT, SMEM, WARPS>(prog, X, Y, Z, F, rgb, colorTab, G.sem);
+                }
                 const float dinv = -1.0f / dl;  // as vertex_at
                 float nx = (F[1] - F[0]) * dinv, nyv = (F[2] - F[0]) * dinv, nzv = (F[3] - F[0]) * dinv;
                 const float l2 = nx * nx + nyv * nyv + nzv * nzv;

@@ -60,6 +60,22 @@ void hostemu_field_packed(const float* quads, const float* xyz, int64_t n, float
     }
 }
 
+// the packed walk WITH colour (color_kernel<.., NRM>): per point p the 4 samples (p, p + dx, p + dy, p + dz) of the normal pass, colour at p;
+// f4[4*i .. 4*i+3] = the four fields, col[3*i ..] = the colour
+void hostemu_field_color_packed(const float* quads, const float* colorTab, const float* xyz, int64_t n, float delta, float* f4, float* col) {
+    const float4* prog = reinterpret_cast<const float4*>(quads);
+    for (int64_t i = 0; i < n; i++) {
+        const float px = xyz[i * 3], py = xyz[i * 3 + 1], pz = xyz[i * 3 + 2];
+        PairPts<2, false> P;
+        P.x[0] = pk(px, px + delta); P.x[1] = pk(px, px);
+        P.y[0] = pk(py, py); P.y[1] = pk(py + delta, py);
+        P.z[0] = pk(pz, pz); P.z[1] = pk(pz, pz + delta);
+        F2 F[2];
+        eval_program_packed<2, false, false, true>(prog, P, F, col + i * 3, colorTab);
+        up(F[0], f4[i * 4], f4[i * 4 + 1]); up(F[1], f4[i * 4 + 2], f4[i * 4 + 3]);
+    }
+}
+
 // prunes the program against the box; returns the pruned length in quads (0 = region needs no evaluation)
 uint32_t hostemu_prune(const float* quads, const float* lo3, const float* hi3, int cullMode, float iso, float* out, uint32_t outCapQuads,
                        int colorExact) {

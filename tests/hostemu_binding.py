@@ -18,6 +18,7 @@ def lib():
         l.hostemu_field_color.argtypes = [vp, vp, vp, C.c_int64, vp, vp, C.c_int]
         l.hostemu_field_packed_columns.argtypes = [vp, vp, vp, C.c_int64, vp]
         l.hostemu_field_packed.argtypes = [vp, vp, C.c_int64, vp]
+        l.hostemu_field_color_packed.argtypes = [vp, vp, vp, C.c_int64, C.c_float, vp, vp]
         l.hostemu_prune.restype = C.c_uint32
         l.hostemu_prune.argtypes = [vp, vp, vp, C.c_int, C.c_float, vp, C.c_uint32, C.c_int]
         _lib = l
@@ -50,6 +51,16 @@ def field_packed(quads, xyz) -> np.ndarray:
     out = np.zeros(len(xyz), np.float32)
     lib().hostemu_field_packed(quads.ctypes.data, xyz.ctypes.data, len(xyz), out.ctypes.data)
     return out
+
+
+def field_color_packed(quads, colors, xyz, delta=1e-3):
+    """packed PS_SimdPoly walk with colour: fields at (p, p+dx, p+dy, p+dz) and the colour at p"""
+    quads = np.ascontiguousarray(quads, np.uint32)
+    colors = np.ascontiguousarray(colors, np.float32)
+    xyz = np.ascontiguousarray(xyz, np.float32).reshape(-1, 3)
+    f4, col = np.zeros((len(xyz), 4), np.float32), np.zeros((len(xyz), 3), np.float32)
+    lib().hostemu_field_color_packed(quads.ctypes.data, colors.ctypes.data, xyz.ctypes.data, len(xyz), float(delta), f4.ctypes.data, col.ctypes.data)
+    return f4, col
 
 
 def field_color(quads, colors, xyz, sem):

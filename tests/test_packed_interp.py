@@ -81,3 +81,46 @@ def test_packed_division_matches_ieee_on_random_lines():
     quads = ps.linearize(bt.flatten(bt.binarize(root)), ps.SEM_SIMD, 0).quads()
     pts = rs.uniform(-3, 3, (20000, 3)).astype(np.float32)
     assert np.array_equal(_bits(emu.field_packed(quads, pts)), _bits(emu.field(quads, pts, ps.SEM_SIMD)))
+
+
+@pytest.mark.parametrize("name", sorted(scenes_small.SIMD_SCENES))
+def test_packed_walk_with_colour_equals_scalar_strict(name):
+    """eval_program_packed<.., COLOR> (the colour + normal pass of color_kernel<.., NRM>): fields at (p, p+dx, p+dy, p+dz) and the colour
+    at p against the scalar STRICT walk - on the full program and on pruned ones, whose colour-scale markers (OPC_CSCALE, header counts,
+    PRE-counted folded groups) only exist after culling."""
+    root = bt.binarize(scenes_small.SIMD_SCENES[name]())
+    flat = bt.flatten(root)
+    prog = ps.linearize(flat, ps.SEM_SIMD, 0)
+    quads, colors = prog.quads(), prog.colors()
+    lo, hi = ps.prepare_bboxes(flat)
+    rs = np.random.RandomState(6)
+    dl = np.float32(1e-3)
+
+    def check(q, pts):
+        f4, col = emu.field_color_packed(q, colors, pts, dl)
+        for k, off in enumerate(([0, 0, 0], [dl, 0, 0], [0, dl, 0], [0, 0, dl])):
+            assert np.array_equal(_bits(f4[:, k]), _bits(emu.field(q, (pts + np.float32(off)).astype(np.float32), ps.SEM_SIMD)))
+        fr, cr = emu.field_color(q, colors, pts, ps.SEM_SIMD)
+        assert np.array_equal(_bits(f4[:, 0]), _bits(fr)) and np.array_equal(_bits(col), _bits(cr)), np.abs(col - cr).max()
+        return fr
+
+    f = check(quads, rs.uniform(lo, hi, (3000, 3)).astype(np.float32))
+    assert (f > 0.3).sum() > 50
+    pruned = 0
+    for _ in range(60):  # pruned twice, as the hierarchy does (exact colours: markers ride on headers, fold into PRE counts, overflow into quads)
+        a = rs.uniform(lo, hi - 0.6, 3).astype(np.float32)
+        big = emu.prune(quads, a, a + np.float32(0.6), ps.CULL_INTERVAL, 0.5, True)
+        if big is None:
+            continue
+        b = (a + rs.uniform(0, 0.45, 3)).astype(np.float32)
+        small = emu.prune(big, b, b + np.float32(0.15), ps.CULL_INTERVAL, 0.5, True)
+        if small is None:
+            continue
+        pruned += 1
+        pts = rs.uniform(b, b + np.float32(0.149), (64, 3)).astype(np.float32)  # + delta stays inside the box's pad? compare like with like:
+        f4, col = emu.field_color_packed(small, colors, pts, dl)
+        fr, cr = emu.field_color(small, colors, pts, ps.SEM_SIMD)
+        assert np.array_equal(_bits(f4[:, 0]), _bits(fr)) and np.array_equal(_bits(col), _bits(cr))
+        fq, cq = emu.field_color(quads, colors, pts, ps.SEM_SIMD)  # and the pruned colour is the full program's colour
+        assert np.array_equal(_bits(col), _bits(cq))
+    assert pruned >= 5
