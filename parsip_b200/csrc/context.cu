@@ -87,6 +87,7 @@ struct psgpu_ctx {
     // slab program: the uploaded program pruned once against this rank's slab box, cached behind the full program in the pool
     struct SlabProg { bool valid = false; int zb = 0, ze = 0; float lo[3] = {0, 0, 0}, side = 0.f; int nx = 0, ny = 0; int colorExact = 0; uint32_t len = 0; } slab;
     uint32_t rootOff = 0, rootLen = 0;  // program the cull hierarchy starts from in the current polygonize
+    int polysSinceUpload = 0;           // polygonize calls since the last psgpu_upload_program (ensure_slab_program)
 };
 
 #define CK(call)                                                                                              \
@@ -178,6 +179,7 @@ extern "C" int psgpu_upload_program(psgpu_ctx* ctx, const psgpu_program* p) {
     CK(cudaStreamSynchronize(ctx->stream));
     ctx->progQuads = (uint32_t)(p->words.size() / 4);
     ctx->slab.valid = false;
+    ctx->polysSinceUpload = 0;
     ctx->nPrims = p->nPrims;
     ctx->semantics = p->semantics;
     ctx->hasWarps = p->maxPointStack > 0;
@@ -373,14 +375,18 @@ struct HostSink {
 
 // The uploaded program pruned ONCE against the slab's box (support culling, colour markers as the levels leave them): with R
 // ranks every rank's hierarchy then walks ~1/R of the primitives instead of all of them at its top level (SCALE_r01: cull 0.64 ms
-// at N = 1 but 1.30 ms per rank at N = 8). A single-thread walk of the whole program - milliseconds for 10k primitives - so it is
-// a plan-time cost like the upload: cached behind the full program until the program or the slab changes, and only taken for
+// at N = 1 but 1.30 ms per rank at N = 8). One CTA-cooperative walk of the whole program (prune_slab_kernel) - milliseconds for 10k
+// primitives - so it is a plan-time cost like the upload: cached behind the full program until the program or the slab changes, and only taken for
 // programs long enough to pay back (>= 2048 quads) on a slab that is a proper part of the lattice.
 int ensure_slab_program(psgpu_ctx* ctx, const GridParams& G, bool colorExact) {
     ctx->rootOff = 0; ctx->rootLen = ctx->progQuads;
     const bool partial = (G.hi[2] - G.lo[2]) < G.dims[2];
     if (!partial || ctx->progQuads < 2048 || getenv("PSGPU_NO_SLAB_PROGRAM")) { ctx->slab.valid = false; return PSGPU_SUCCESS; }
     psgpu_ctx::SlabProg& S = ctx->slab;
+    // The prune is a plan-time cost (4 ms for a rank's eighth of blob10k) that saves ~0.1 ms of culling per polygonize: it is only
+    // built once the uploaded program has proved to be REUSED - from its third polygonize on. A caller that uploads a new program for
+    // every frame (animation, the end-to-end path of bench.py) never pays it; PSGPU_SLAB_PROGRAM_NOW=1 builds it at once.
+    if (++ctx->polysSinceUpload < 3 && !S.valid && !getenv("PSGPU_SLAB_PROGRAM_NOW")) return PSGPU_SUCCESS;
     const bool hit = S.valid && S.zb == G.lo[2] && S.ze == G.hi[2] && S.side == G.mpuSide && S.nx == G.dims[0] && S.ny == G.dims[1] &&
                      S.lo[0] == G.gridLo[0] && S.lo[1] == G.gridLo[1] && S.lo[2] == G.gridLo[2] && S.colorExact == (colorExact ? 1 : 0);
     if (!hit) {

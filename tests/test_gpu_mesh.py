@@ -435,8 +435,8 @@ def test_slab_program_of_a_long_tree_gives_the_whole_mesh(ctx, sem):
     whole = soup(ctx.polygonize(ps.Params.make(cs, lo, hi, **kw)))
     assert len(whole) > 100_000
     for env in (None, "1"):
-        if env:
-            os.environ["PSGPU_NO_SLAB_PROGRAM"] = env
+        # the slab program is built lazily (third polygonize after an upload) unless asked for at once
+        os.environ["PSGPU_NO_SLAB_PROGRAM" if env else "PSGPU_SLAB_PROGRAM_NOW"] = "1"
         try:
             parts = []
             for r in range(3):
@@ -444,6 +444,7 @@ def test_slab_program_of_a_long_tree_gives_the_whole_mesh(ctx, sem):
                 parts.append(soup(ctx.polygonize(ps.Params.make(cs, lo, hi, z_begin=zb, z_end=ze, **kw))))
         finally:
             os.environ.pop("PSGPU_NO_SLAB_PROGRAM", None)
+            os.environ.pop("PSGPU_SLAB_PROGRAM_NOW", None)
         got = np.concatenate(parts)
         got = got[np.lexsort(got.T[::-1])]
         assert got.shape == whole.shape and np.array_equal(got, whole), "slab meshes differ from the whole mesh (slab program %s)" % ("off" if env else "on")
