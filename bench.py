@@ -591,7 +591,9 @@ def run_gpu(args):
 
     flops = float(st["algorithmic_flops"])
     vflops = float(st["vertex_eval_flops"])
-    tri_bytes = float(st["mpus_crossed"]) * (2048 + 288 + 8) + nt * 12.0
+    # per surface MPU: 64 B inside mask + 288 B edge mask / prefix + 8 B bases read; per triangle 12 B written (until r02b
+    # the kernel re-derived the inside mask from the 2 048 B field cache, which counted here)
+    tri_bytes = float(st["mpus_crossed"]) * (64 + 288 + 8) + nt * 12.0
     # per vertex the reference spends 4 root samples, then fieldValueAndColor (1) + normal (3 more samples): 8 evaluations of the MPU's
     # program. vertex_kernel does the first 4; color_kernel<.., NRM> the other 4 in one 4-wide coloured walk (emit.cu:
     # normals_in_color_pass). With PSGPU_SEPARATE_NORMAL_PASS the normal samples go back to vertex_kernel (8) and the colour walk is 1-wide.
