@@ -548,8 +548,9 @@ def run_gpu(args):
     evals = allsum(float(st["field_evals"]))
     tris = allsum(float(nt)); verts = allsum(float(nv))
     launches_all = allsum(float(launches))
-    h2d = prog.n_quads * 16 + prog.n_prims * 12
-    d2h = nv * 36 + nt * 12
+    # whole-job bytes per step, like `value`: every rank uploads the program and pulls its own share of the mesh
+    h2d = (prog.n_quads * 16 + prog.n_prims * 12) * world
+    d2h = verts * 36 + tris * 12
     nat_ms_max = allmax(nacc["ms_total"])
     if world > 1:
         dist.barrier()
