@@ -58,6 +58,14 @@ typedef struct psgpu_program psgpu_program; /* host-side linearized BlobTree */
 #define PSGPU_LIN_FULL_AFFINE 2 /* PSGPU_SEM_SCALAR: apply an operator's whole backward matrix. Default (0) reproduces the compact
                                    tree, whose vec4 w lane is 0 at the root and below warps, so an operator's translation column
                                    only acts directly below another operator matrix (CompactBlobTree.cpp:685-694) */
+#define PSGPU_LIN_AS_SHIPPED 4  /* PSGPU_SEM_SIMD: reproduce the reference's prune of operators deeper than 3 levels
+                                   (PS_Polygonizer.cpp:1228-1252): such an operator evaluates to 0 for a SIMD packet of which no
+                                   point lies inside its box's x-, y- OR z-slab. Needs psgpu_tree.op_box_lo / op_box_hi = the operator
+                                   boxes PrepareBBoxes computed (PS_Polygonizer.cpp:238-307; boxes padded by 0.504 although the field's
+                                   support is 1, so contributions of up to 0.0135 vanish). Field values, positions and indices then equal
+                                   the shipped reference's; its COLOURS where the prune fires come from uninitialised stack arrays
+                                   (:1384-1385) and are not reproducible. Default (0): every contribution is kept. Binary trees without
+                                   warps only; programs get one 3-quad instruction per deep operator. */
 
 typedef struct psgpu_params {
     float cellsize;

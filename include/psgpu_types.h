@@ -72,6 +72,10 @@ typedef struct psgpu_tree {
     const float* srt;           /* [n_nodes*10] */
     const uint8_t* has_srt;     /* [n_nodes] */
     const int32_t* node_id;     /* [n_nodes] CBlobNode::getID() (the BLOBNODE section numbers of a .scene file); NULL = index */
+    /* optional (NULL = absent), read by PSGPU_LIN_AS_SHIPPED only: operator boxes as the reference's PrepareBBoxes leaves them in
+     * SOABlobOps.vBoxLo / vBoxHi (PS_SimdPoly/include/PS_Polygonizer.cpp:238-307); entries of primitives are ignored */
+    const float* op_box_lo;     /* [n_nodes*3] */
+    const float* op_box_hi;     /* [n_nodes*3] */
 } psgpu_tree;
 
 #ifdef __cplusplus

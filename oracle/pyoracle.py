@@ -232,6 +232,7 @@ class _Tree(C.Structure):
         ("pos", C.POINTER(C.c_float)), ("dir", C.POINTER(C.c_float)), ("res", C.POINTER(C.c_float)),
         ("color", C.POINTER(C.c_float)), ("xform", C.POINTER(C.c_float)), ("has_xform", C.POINTER(C.c_uint8)),
         ("srt", C.POINTER(C.c_float)), ("has_srt", C.POINTER(C.c_uint8)), ("node_id", C.POINTER(C.c_int32)),
+        ("op_box_lo", C.POINTER(C.c_float)), ("op_box_hi", C.POINTER(C.c_float)),
     ]
 
 

@@ -9,5 +9,5 @@ from . import blobtree, scenes, sharding  # noqa: F401
 from .api import (  # noqa: F401
     PsGpuError, Context, Program, Params, linearize, prepare_bboxes, binarize_tree, count_mpus, lattice_dims, lib_path, load_library, comm_unique_id, slab_bounds, flatten_transforms, tree_octrees, scene_load, scene_save,
     SEM_SIMD, SEM_SCALAR, ROOT_FOURSAMPLE, ROOT_NEWTON_REF, ROOT_BISECT, COORD_MPU_LOCAL, COORD_GLOBAL,
-    OUT_INDEXED, OUT_MPU, CULL_NONE, CULL_SUPPORT, CULL_INTERVAL, LIN_REASSOCIATE,
+    OUT_INDEXED, OUT_MPU, CULL_NONE, CULL_SUPPORT, CULL_INTERVAL, LIN_REASSOCIATE, LIN_FULL_AFFINE, LIN_AS_SHIPPED, NOALLOC_MAX_POINTS,
 )

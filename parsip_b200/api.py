@@ -13,6 +13,7 @@ COORD_MPU_LOCAL, COORD_GLOBAL = 0, 1
 OUT_INDEXED, OUT_MPU = 0, 1
 CULL_NONE, CULL_SUPPORT, CULL_INTERVAL = 0, 1, 2
 LIN_REASSOCIATE = 1
+LIN_FULL_AFFINE, LIN_AS_SHIPPED = 2, 4
 
 SUCCESS = 1
 ERRORS = {-1: "PARAM_ERROR", -2: "NOT_ENOUGH_MEM", -3: "INVALID_BVH", -4: "UNSUPPORTED_NODE", -5: "CUDA", -6: "NO_DEVICE"}
@@ -41,6 +42,7 @@ class _Tree(C.Structure):
         ("pos", C.POINTER(C.c_float)), ("dir", C.POINTER(C.c_float)), ("res", C.POINTER(C.c_float)),
         ("color", C.POINTER(C.c_float)), ("xform", C.POINTER(C.c_float)), ("has_xform", C.POINTER(C.c_uint8)),
         ("srt", C.POINTER(C.c_float)), ("has_srt", C.POINTER(C.c_uint8)), ("node_id", C.POINTER(C.c_int32)),
+        ("op_box_lo", C.POINTER(C.c_float)), ("op_box_hi", C.POINTER(C.c_float)),
     ]
 
 
@@ -173,6 +175,9 @@ def _tree_struct(flat: dict):
     if "node_id" in k:
         k["node_id"] = np.ascontiguousarray(k["node_id"], np.int32)
         t.node_id = p(k["node_id"], C.c_int32)
+    if "op_box_lo" in k and "op_box_hi" in k:  # PSGPU_LIN_AS_SHIPPED: the operator boxes of the reference's PrepareBBoxes
+        k["op_box_lo"], k["op_box_hi"] = np.ascontiguousarray(k["op_box_lo"], np.float32), np.ascontiguousarray(k["op_box_hi"], np.float32)
+        t.op_box_lo, t.op_box_hi = p(k["op_box_lo"], C.c_float), p(k["op_box_hi"], C.c_float)
     return t, k
 
 

@@ -5,6 +5,7 @@
 #include <cmath>
 #include <cstdio>
 #include <cstring>
+#include <cstdlib>
 #include <algorithm>
 #include <atomic>
 #include <chrono>
@@ -75,6 +76,7 @@ struct FlatTree {
     std::vector<int32_t> type, first, nk, child;
     std::vector<float> pos, dir, res, color, xform;
     std::vector<uint8_t> hasxf;
+    std::vector<float> boxLo, boxHi;  // the caller's operator boxes (SOABlobOps.vBox*, written by PrepareBBoxes)
     psgpu_tree t{};
 };
 
@@ -88,7 +90,10 @@ int buildTree(const SOABlobPrims& P, const SOABlobPrimMatrices& M, const SOABlob
     F.type.assign(n, 0); F.first.assign(n, 0); F.nk.assign(n, 0);
     F.pos.assign((size_t)n * 3, 0.f); F.dir.assign((size_t)n * 3, 0.f); F.res.assign((size_t)n * 4, 0.f); F.color.assign((size_t)n * 3, 0.f);
     F.xform.assign((size_t)n * 12, 0.f); F.hasxf.assign(n, 0);
+    F.boxLo.assign((size_t)n * 3, 0.f); F.boxHi.assign((size_t)n * 3, 0.f);
     for (int i = 0; i < nO; i++) {
+        F.boxLo[i * 3] = O.vBoxLoX[i]; F.boxLo[i * 3 + 1] = O.vBoxLoY[i]; F.boxLo[i * 3 + 2] = O.vBoxLoZ[i];
+        F.boxHi[i * 3] = O.vBoxHiX[i]; F.boxHi[i * 3 + 1] = O.vBoxHiY[i]; F.boxHi[i * 3 + 2] = O.vBoxHiZ[i];
         const int ty = typeFromRef(O.opType[i]);
         if (ty < 0) return RET_INVALID_BVH;
         F.type[i] = ty;
@@ -126,8 +131,11 @@ int buildTree(const SOABlobPrims& P, const SOABlobPrimMatrices& M, const SOABlob
     F.t.type = F.type.data(); F.t.first_child = F.first.data(); F.t.n_children = F.nk.data(); F.t.child = F.child.data();
     F.t.pos = F.pos.data(); F.t.dir = F.dir.data(); F.t.res = F.res.data(); F.t.color = F.color.data();
     F.t.xform = F.xform.data(); F.t.has_xform = F.hasxf.data();
+    F.t.op_box_lo = F.boxLo.data(); F.t.op_box_hi = F.boxHi.data();
     return RET_SUCCESS;
 }
+
+inline int nOpsOf(const SOABlobOps& O) { return (int)O.ctOps; }
 
 int ensureCtx() {
     if (g_ctx) return RET_SUCCESS;
@@ -141,9 +149,13 @@ int uploadScene(const SOABlobPrims& P, const SOABlobPrimMatrices& M, const SOABl
     rc = ensureCtx();
     if (rc != RET_SUCCESS) return rc;
     psgpu_program* prog = nullptr;
-    // exact association of the binary tree is kept (no PSGPU_LIN_REASSOCIATE): with <= 128 nodes the stack fits
-    rc = psgpu_linearize(&F.t, PSGPU_SEM_SIMD, 0, &prog);
-    if (rc == PSGPU_NOT_ENOUGH_MEM) rc = psgpu_linearize(&F.t, PSGPU_SEM_SIMD, PSGPU_LIN_REASSOCIATE, &prog);
+    // exact association of the binary tree is kept (no PSGPU_LIN_REASSOCIATE): with <= 128 nodes the stack fits.
+    // PSGPU_FACADE_AS_SHIPPED=1: also the reference's prune of operators deeper than 3 levels by the caller's operator boxes
+    // (PSGPU_LIN_AS_SHIPPED, psgpu.h) - field values, positions and indices of the SHIPPED reference; default: every contribution kept
+    const char* shipped = getenv("PSGPU_FACADE_AS_SHIPPED");
+    const int base = (shipped && atoi(shipped) != 0 && nOpsOf(O) > 0) ? PSGPU_LIN_AS_SHIPPED : 0;
+    rc = psgpu_linearize(&F.t, PSGPU_SEM_SIMD, base, &prog);
+    if (rc == PSGPU_NOT_ENOUGH_MEM && base == 0) rc = psgpu_linearize(&F.t, PSGPU_SEM_SIMD, PSGPU_LIN_REASSOCIATE, &prog);
     if (rc != RET_SUCCESS) return rc;
     rc = psgpu_upload_program(g_ctx, prog);
     psgpu_program_free(prog);

@@ -59,6 +59,7 @@ struct psgpu_ctx {
     int semantics = PSGPU_SEM_SCALAR;
     bool hasWarps = false;  // the program uses the point stack (warps / operator matrices)
     bool nonNeg = false;    // no difference operator anywhere in the program: every value on the stack is >= 0
+    bool hasMasks = false;  // the program contains OPC_BOXMASK (linearized with PSGPU_LIN_AS_SHIPPED)
     DevBuf pool;      // float4: [full program | level 0 programs | level 1 programs | ...]
     DevBuf qflag;     // one byte per pool quad: 1 = first quad of an instruction (read by the warp-cooperative pruning passes)
     DevBuf colors;
@@ -184,17 +185,19 @@ extern "C" int psgpu_upload_program(psgpu_ctx* ctx, const psgpu_program* p) {
     ctx->semantics = p->semantics;
     ctx->hasWarps = p->maxPointStack > 0;
     {   // differences (min(a, 1 - b), a * (1 - b) and their reversed forms) are the only operators that can leave a negative value
-        bool neg = false;
+        bool neg = false, masks = false;
         const uint32_t* w = p->words.data();
         const size_t nq = p->words.size() / 4;
         for (size_t pc = 0; pc < nq;) {
             const uint32_t hdr = w[pc * 4], opc = PS_HDR_OPC(hdr), cmb = PS_HDR_CMB(hdr);
             if (opc == OPC_END) break;
             if ((opc < OPC_FIRST_NONPRIM || opc == OPC_COMBINE) && (cmb == CMB_DIF || cmb == CMB_SDIF || cmb == CMB_RDIF || cmb == CMB_RSDIF)) neg = true;
+            if (opc == OPC_BOXMASK) masks = true;
             if (opc == OPC_DIF0 || opc == OPC_RICCI_SIMD) neg = true;  // fast_pow's quotient changes sign beyond its pole
             pc += (size_t)ps_instr_quads(hdr);
         }
         ctx->nonNeg = !neg;
+        ctx->hasMasks = masks;
     }
     return PSGPU_SUCCESS;
 }
@@ -215,6 +218,7 @@ int fill_grid(psgpu_ctx* ctx, const psgpu_params* P, GridParams& G) {
     }
     G.cellsize = P->cellsize;
     G.hasWarps = ctx->hasWarps ? 1 : 0;
+    G.hasMasks = ctx->hasMasks ? 1 : 0;
     G.mpuSide = P->cellsize * (float)PS_CELLS_PER_MPU;
     G.coordMode = P->coord_mode; G.sem = ctx->semantics; G.output = P->output; G.rootMode = P->root_mode;
     G.rootIters = P->root_iterations > 0 ? P->root_iterations : (P->root_mode == PSGPU_ROOT_NEWTON_REF ? 8 : 4);

@@ -532,6 +532,9 @@ struct Pruner {
                 if (!(e > 0.f) || !(blo[t] == blo[t]) || !(bhi[t] == bhi[t]) || b0 < 0.f) { blo[t] = -3.0e38f; bhi[t] = 3.0e38f; }
             }
         } break;
+        case OPC_BOXMASK: {  // top, or 0 where the reference's deep-operator prune fires (program.h): an all-zero entry stays all-zero
+            if (!bzero[sp]) { copy(pc, q0, hdr, nq); blo[sp] = fminf(blo[sp], 0.f); bhi[sp] = fmaxf(bhi[sp], 0.f); }
+        } break;
         case OPC_CLAMP1: {
             if (!bzero[sp]) { copy(pc, q0, hdr, nq); bhi[sp] = fminf(bhi[sp], 1.0f); blo[sp] = fminf(blo[sp], 1.0f); }
         } break;

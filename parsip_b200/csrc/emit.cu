@@ -37,17 +37,20 @@ __device__ __forceinline__ EdgePos edge_endpoints(const GridParams& G, const Reg
     return E;
 }
 
+// In the STRICT (PS_SimdPoly) instantiations of this file the WARPS parameter - meaningless there, the SIMD path ignores warps - selects the
+// variants that know OPC_BOXMASK (programs linearized with PSGPU_LIN_AS_SHIPPED; GridParams.hasMasks).
 // ONE out-of-line copy of the plain 4-wide interpreter per kernel: the root search and the normal both call it (inlining it
 // at every call site multiplied the hot code past the instruction caches)
 template <bool STRICT, bool SMEM, bool WARPS>
-__device__ __noinline__ void eval4(const float4* prog, const float (&X)[4], const float (&Y)[4], const float (&Z)[4], float (&F)[4], int sem) {
+__device__ __noinline__ void eval4(const float4* prog, const float (&X)[4], const float (&Y)[4], const float (&Z)[4], float (&F)[4], int sem,
+                                   bool packet4 = false) {  // packet4: the 4 points are ONE SIMD call of the reference (OPC_BOXMASK, program.h)
     if constexpr (STRICT) {  // PS_SimdPoly semantics: packed-pair arithmetic (interp_packed.cuh), same bits
         PairPts<2, false> P;
         P.x[0] = pk(X[0], X[1]); P.x[1] = pk(X[2], X[3]);
         P.y[0] = pk(Y[0], Y[1]); P.y[1] = pk(Y[2], Y[3]);
         P.z[0] = pk(Z[0], Z[1]); P.z[1] = pk(Z[2], Z[3]);
         F2 FP[2];
-        eval_program_packed<2, false, SMEM>(prog, P, FP);
+        eval_program_packed<2, false, SMEM, false, WARPS>(prog, P, FP, nullptr, nullptr, packet4);  // STRICT: WARPS stands for MASKS
         up(FP[0], F[0], F[1]); up(FP[1], F[2], F[3]);
     } else
         eval_program<4, false, STRICT, SMEM, WARPS>(prog, X, Y, Z, F, nullptr, nullptr, sem);
@@ -67,7 +70,7 @@ __device__ void root_foursample(const GridParams& G, const float4* prog, const E
         Y[l] = (E.axis == 1) ? moved : E.e1[1];
         Z[l] = (E.axis == 2) ? moved : E.e1[2];
     }
-    eval4<STRICT, SMEM, WARPS>(prog, X, Y, Z, F, G.sem);
+    eval4<STRICT, SMEM, WARPS>(prog, X, Y, Z, F, G.sem, true);
     const bool state = is_inside(G, F[0]);
     // first lane whose flag differs from lane 0, else the last one (cpp:748-755)
     const int interval = (is_inside(G, F[1]) != state) ? 1 : ((is_inside(G, F[2]) != state) ? 2 : 3);
@@ -491,7 +494,7 @@ __global__ void __launch_bounds__(kThreads) color_kernel(GridParams G, const Reg
                     P.y[0] = pk(py, py); P.y[1] = pk(py + dl, py);
                     P.z[0] = pk(pz, pz); P.z[1] = pk(pz, pz + dl);
                     F2 FP[2];
-                    eval_program_packed<2, false, SMEM, true>(prog, P, FP, rgb, colorTab);
+                    eval_program_packed<2, false, SMEM, true, WARPS>(prog, P, FP, rgb, colorTab);  // STRICT: WARPS stands for MASKS
                     up(FP[0], F[0], F[1]); up(FP[1], F[2], F[3]);
                 } else {
                     float X[4] = {px, px + dl, px, px}, Y[4] = {py, py, py + dl, py}, Z[4] = {pz, pz, pz, pz + dl};
@@ -584,7 +587,9 @@ void launch_emit_kernels(const GridParams& G, const Region* cands, const float4*
     using KernelT = void (*)(GridParams, const Region*, const float4*, FieldOutputs, MeshOutputs, int, uint32_t);
     KernelT k;
     const bool warps = !strict && G.hasWarps != 0;
-#define PS_PICK(ROOT) (strict ? (smemOk ? vertex_kernel<true, ROOT, true, false> : vertex_kernel<true, ROOT, false, false>) \
+    const bool masks = strict && G.hasMasks != 0;
+#define PS_PICK(ROOT) (strict ? (masks ? (smemOk ? vertex_kernel<true, ROOT, true, true> : vertex_kernel<true, ROOT, false, true>) \
+                                       : (smemOk ? vertex_kernel<true, ROOT, true, false> : vertex_kernel<true, ROOT, false, false>)) \
                        : warps ? (smemOk ? vertex_kernel<false, ROOT, true, true> : vertex_kernel<false, ROOT, false, true>) \
                                : (smemOk ? vertex_kernel<false, ROOT, true, false> : vertex_kernel<false, ROOT, false, false>))
     if (G.rootMode == PSGPU_ROOT_FOURSAMPLE) k = PS_PICK(PSGPU_ROOT_FOURSAMPLE);
@@ -604,7 +609,8 @@ void launch_emit_kernels(const GridParams& G, const Region* cands, const float4*
     if (evVertexDone) cudaEventRecord(evVertexDone, st);
     if (G.wantColors) {
         using ColorT = void (*)(GridParams, const Region*, const float4*, const float*, FieldOutputs, MeshOutputs, int, uint32_t);
-        const ColorT kc = nrmInColor ? (smemOk ? color_kernel<true, true, false, true> : color_kernel<true, false, false, true>)
+        const ColorT kc = nrmInColor ? (masks ? (smemOk ? color_kernel<true, true, true, true> : color_kernel<true, false, true, true>)
+                                              : (smemOk ? color_kernel<true, true, false, true> : color_kernel<true, false, false, true>))
                           : strict ? (smemOk ? color_kernel<true, true, false, false> : color_kernel<true, false, false, false>)
                           : warps ? (smemOk ? color_kernel<false, true, true, false> : color_kernel<false, false, true, false>)
                                   : (smemOk ? color_kernel<false, true, false, false> : color_kernel<false, false, false, false>);

@@ -47,7 +47,7 @@ struct __align__(16) FieldSmemHeader {
 
 // STAGED: every candidate list fits the staging buffers (the host checks the longest one) and is interpreted from shared memory;
 // the unstaged variant (brute-force mode, very long lists) reads the lists from global memory. One interpreter copy per kernel.
-template <bool STRICT, bool STAGED, int kPts>
+template <bool STRICT, bool STAGED, int kPts, bool MASKS = false>
 __global__ void __launch_bounds__(512 / kPts, kPts == 4 ? 6 : (STRICT ? PSGPU_STRICT_CTAS : 16)) field_kernel(GridParams G, const Region* __restrict__ cands, int nCand,
                                                          const float4* __restrict__ pool, FieldOutputs out, uint32_t capQuads) {
     extern __shared__ __align__(16) unsigned char smemRaw[];
@@ -116,7 +116,7 @@ __global__ void __launch_bounds__(512 / kPts, kPts == 4 ? 6 : (STRICT ? PSGPU_ST
 #pragma unroll
             for (int n = 0; n < kPts / 2; n++) P.z[n] = pk(Z[2 * n], Z[2 * n + 1]);
             F2 FP[kPts / 2];
-            eval_program_packed<kPts / 2, true, STAGED>(STAGED ? progBuf + (size_t)stage * capQuads : pool + r.off, P, FP);
+            eval_program_packed<kPts / 2, true, STAGED, false, MASKS>(STAGED ? progBuf + (size_t)stage * capQuads : pool + r.off, P, FP, nullptr, nullptr, true);  // packets of 4 z-corners
 #pragma unroll
             for (int n = 0; n < kPts / 2; n++) up(FP[n], F[2 * n], F[2 * n + 1]);
         } else
@@ -404,7 +404,8 @@ void launch_field_kernel(const GridParams& G, const Region* cands, int nCand, co
     const bool four = !strict && hasWarps;
     using KernelT = void (*)(GridParams, const Region*, int, const float4*, FieldOutputs, uint32_t);
     KernelT k;
-    if (strict) k = staged ? field_kernel<true, true, 8> : field_kernel<true, false, 8>;
+    if (strict && G.hasMasks) k = staged ? field_kernel<true, true, 8, true> : field_kernel<true, false, 8, true>;  // PSGPU_LIN_AS_SHIPPED programs
+    else if (strict) k = staged ? field_kernel<true, true, 8> : field_kernel<true, false, 8>;
     else if (four) k = staged ? field_kernel<false, true, 4> : field_kernel<false, false, 4>;
     else k = staged ? field_kernel<false, true, 8> : field_kernel<false, false, 8>;
     const int threads = four ? 128 : 64;

@@ -541,6 +541,14 @@ __device__ void eval_program(const float4* __restrict__ prog, const float (&X)[N
         case OPC_CSCALE: if (STRICT) {
             if (COLOR) color_scale(top[0], tc, __float_as_uint(q0.y));
         } break;
+        case OPC_BOXMASK: if (STRICT) {  // every point is a packet of its own here (broadcast evaluations; program.h)
+            const float4 lo = prog[pc + 1], hi = prog[pc + 2];
+#pragma unroll
+            for (int n = 0; n < N; n++) {
+                const bool in = (x[n] >= lo.x && hi.x >= x[n]) || (y[n] >= lo.y && hi.y >= y[n]) || (z[n] >= lo.z && hi.z >= z[n]);
+                if (!in) top[n] = 0.0f;
+            }
+        } break;
         case OPC_CLAMP1: {
 #pragma unroll
             for (int n = 0; n < N; n++) top[n] = fminf(top[n], 1.0f);

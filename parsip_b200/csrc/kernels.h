@@ -37,6 +37,7 @@ struct GridParams {
     int wantColors, wantNormals;
     int forceFv;         // parity hook: write the field cache of every candidate
     int hasWarps;        // the uploaded program contains warp instructions (picks the kernels compiled with them)
+    int hasMasks;        // the program contains OPC_BOXMASK (PSGPU_LIN_AS_SHIPPED): kernels compiled with the mask routine
     float iso;
     // z-slab stitching (psgpu_polygonize_sharded): the MPU layer whose closing z-plane this slab owns - its own last layer for a
     // stand-alone slab, the lattice's last layer when the slabs of several ranks form ONE mesh (then only the last rank owns a

@@ -152,6 +152,7 @@ struct Emitter {
             int c = t->child[t->first_child[n] + i];
             bool assoc = (type == PSGPU_OP_UNION || type == PSGPU_OP_INTERSECT) ||
                          (type == PSGPU_OP_BLEND && (flags & PSGPU_LIN_REASSOCIATE));
+            if (asShipped()) assoc = false;  // every operator keeps its own value on the stack: it may be masked (OPC_BOXMASK)
             if (assoc && t->type[c] == type && !hasXf(c) && t->n_children[c] > 0) gatherKids(c, type, out);
             else out.push_back(c);
         }
@@ -180,8 +181,32 @@ struct Emitter {
         instanceDepth--;
     }
 
+    bool asShipped() const { return semantics == PSGPU_SEM_SIMD && (flags & PSGPU_LIN_AS_SHIPPED) != 0; }
+    int opDepth = -1;  // depth of the operator being emitted in the reference's traversal (root operator = 0)
+    // the reference's prune of an operator deeper than 3 levels (PS_Polygonizer.cpp:1228-1252): its value, alone on the stack top, is
+    // masked by its box. Bottom-up masking gives what the reference's top-down skip gives: a pruned ancestor's 0 overrides its sub-tree
+    void boxMask(int n) {
+        quad(PS_HDR(OPC_BOXMASK, 0, false, 0));
+        quadf(t->op_box_lo[n * 3], t->op_box_lo[n * 3 + 1], t->op_box_lo[n * 3 + 2], 0.f);
+        quadf(t->op_box_hi[n * 3], t->op_box_hi[n * 3 + 1], t->op_box_hi[n * 3 + 2], 0.f);
+        p->nInstr++;
+    }
+
     // Emits the sub-tree `n`; its value meets the current stack top with `cmb` (CMB_PUSH: new entry).
     void emit(int n, uint32_t cmb, int w = 0) {
+        if (err != PSGPU_SUCCESS) return;
+        const int type = t->type[n];
+        if (asShipped() && !PSGPU_IS_PRIM(type)) {
+            if (PSGPU_IS_WARP(type) || cmb != CMB_PUSH) { err = PSGPU_ERROR_UNSUPPORTED_NODE; msg = "PSGPU_LIN_AS_SHIPPED: binary operators without warps only"; return; }
+            opDepth++;
+            emitOp(n, cmb, w);
+            if (err == PSGPU_SUCCESS && opDepth > 3) boxMask(n);
+            opDepth--;
+            return;
+        }
+        emitOp(n, cmb, w);
+    }
+    void emitOp(int n, uint32_t cmb, int w) {
         if (err != PSGPU_SUCCESS) return;
         const int type = t->type[n];
         if (type == PSGPU_PRIM_INSTANCE) { emitInstance(n, cmb); return; }
@@ -276,6 +301,12 @@ extern "C" int psgpu_linearize(const psgpu_tree* tree, int semantics, int flags,
     psgpu_program* p = new psgpu_program();
     p->semantics = semantics;
     Emitter e{tree, semantics, flags, p};
+    if (semantics == PSGPU_SEM_SIMD && (flags & PSGPU_LIN_AS_SHIPPED) && (!tree->op_box_lo || !tree->op_box_hi)) {
+        fprintf(stderr, "psgpu_linearize: PSGPU_LIN_AS_SHIPPED needs psgpu_tree.op_box_lo / op_box_hi\n");
+        delete p;
+        *out = nullptr;
+        return PSGPU_PARAM_ERROR;
+    }
     e.emit(tree->root, CMB_PUSH);
     if (e.err == PSGPU_SUCCESS && p->maxValueStack > PS_MAX_VALUE_STACK) {
         e.err = PSGPU_NOT_ENOUGH_MEM;

@@ -49,6 +49,11 @@ enum PsOpcode : uint32_t {
     OPC_CSCALE = 21,     // {h, n}         colour *= (2*(0.5+top)-1), n times; field untouched. Left by the culling pass where a
                          //                blend lost an all-zero operand: the PS_SimdPoly colour rule 2*f_L*c_L + 2*f_R*c_R is
                          //                unnormalised (PS_Polygonizer.cpp:1475-1487), so the surviving operand's colour keeps its weight
+    OPC_BOXMASK = 22,    // {h}{lo.xyz, 0}{hi.xyz, 0}   PS_SimdPoly semantics linearized with PSGPU_LIN_AS_SHIPPED only: top = 0 for a PACKET of
+                         //                points of which none lies inside the box's x-slab OR y-slab OR z-slab - the reference's prune of
+                         //                operators deeper than 3 levels (PS_Polygonizer.cpp:1228-1252). A packet = the points
+                         //                the reference evaluates in one SIMD call: 4 z-consecutive corners in the grid phase, the 4 root
+                         //                samples of an edge, a single point everywhere else
     OPC_TWIST = 24,      // {h, k, axis}                 push point; warp
     OPC_TAPER = 25,      // {h, k, along, taper}
     OPC_BEND = 26,       // {h, k, y0, left}{right, 1/k, 0, 0}
@@ -92,8 +97,8 @@ __host__ __device__
 #endif
 static inline int ps_base_quads(uint32_t opc) {
     // 2 bits per opcode (quads - 1), opcodes 0..15 in the first word and 16..31 in the second: a shift and a mask instead of a
-    // compare chain in the interpreters' decode path. SEGMENT, LINE_INF, CUBE, DISC, RING, BEND = 2; CYLINDER = 3; AFFINE = 4.
-    const uint32_t k = (opc < 16u) ? 0x00045650u : 0x03100000u;  // QUADRIC (9) = 2
+    // compare chain in the interpreters' decode path. SEGMENT, LINE_INF, CUBE, DISC, RING, BEND = 2; CYLINDER, BOXMASK = 3; AFFINE = 4.
+    const uint32_t k = (opc < 16u) ? 0x00045650u : 0x03102000u;  // QUADRIC (9) = 2; BOXMASK (22) = 3
     return 1 + (int)((k >> (2u * (opc & 15u))) & 3u);
 }
 #if defined(__CUDACC__)

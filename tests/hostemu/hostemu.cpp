@@ -40,7 +40,7 @@ void hostemu_field_packed_columns(const float* quads, const float* xy, const flo
         P.x[0] = xy[c * 2]; P.y[0] = xy[c * 2 + 1];
         for (int i = 0; i < 4; i++) P.z[i] = pk(z[c * 8 + 2 * i], z[c * 8 + 2 * i + 1]);
         F2 F[4];
-        eval_program_packed<4, true, false>(prog, P, F);
+        eval_program_packed<4, true, false>(prog, P, F, nullptr, nullptr, true);
         for (int i = 0; i < 4; i++) up(F[i], f[c * 8 + 2 * i], f[c * 8 + 2 * i + 1]);
     }
 }
@@ -55,7 +55,7 @@ void hostemu_field_packed(const float* quads, const float* xyz, int64_t n, float
             P.x[i] = pk(a[0], a[3]); P.y[i] = pk(a[1], a[4]); P.z[i] = pk(a[2], a[5]);
         }
         F2 F[2];
-        eval_program_packed<2, false, false>(prog, P, F);
+        eval_program_packed<2, false, false>(prog, P, F, nullptr, nullptr, true);  // the 4 points = one SIMD packet of the reference
         for (int i = 0; i < 2; i++) up(F[i], f[b + 2 * i], f[b + 2 * i + 1]);
     }
 }

@@ -122,3 +122,17 @@ def simd_oracle(root, pad_op_boxes=True):
     if pad_op_boxes:
         o.pad_op_boxes(1.0e6)  # infinite lines (Q1) reach beyond any finite box
     return b, soa, o
+
+
+def with_op_boxes(flat, op_boxes):
+    """flat tree + the operator boxes of the reference's PrepareBBoxes (oracle / RefScene .op_boxes(): one [lo xyz, hi xyz] row per
+    operator in pre-order, the order blobtree.flatten numbers nodes in) as psgpu_tree.op_box_lo / op_box_hi for PSGPU_LIN_AS_SHIPPED."""
+    import numpy as np
+    is_op = flat["type"] >= 16
+    assert int(is_op.sum()) == len(op_boxes)
+    out = dict(flat)
+    out["op_box_lo"] = np.zeros((flat["n_nodes"], 3), np.float32)
+    out["op_box_hi"] = np.zeros((flat["n_nodes"], 3), np.float32)
+    out["op_box_lo"][is_op] = np.asarray(op_boxes, np.float32)[:, :3]
+    out["op_box_hi"][is_op] = np.asarray(op_boxes, np.float32)[:, 3:]
+    return out

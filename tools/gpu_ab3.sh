@@ -4,8 +4,7 @@ import sys,ast
 d=ast.literal_eval(sys.stdin.read().split('} ')[0]+'}')
 print({k:d[k] for k in ('mpus_evaluated','pruned_quads','ms_cull','ms_field','ms_tri','ms_vertex','ms_color','ms_total')})"; }
 run "A=1" ""
-run "A=1" "--slab=0/8"
+run "A=1" ""
+run "A=1" "--native"
 run "A=1" "--slab=3/8"
-run "PSGPU_NO_SLAB_PROGRAM=1" "--slab=3/8"
-python tools/time_upload.py
 python -m pytest tests -m gpu -q -x 2>&1 | tail -3
