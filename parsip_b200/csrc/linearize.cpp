@@ -7,6 +7,7 @@
 // (PS_SimdPoly/include/PS_Polygonizer.cpp:55-309, 388-412), which are host-only in the reference too.
 #include <cmath>
 #include <cstdio>
+#include <algorithm>
 #include <cstring>
 #include <string>
 #include <vector>
@@ -182,6 +183,24 @@ struct Emitter {
     }
 
     bool asShipped() const { return semantics == PSGPU_SEM_SIMD && (flags & PSGPU_LIN_AS_SHIPPED) != 0; }
+    std::vector<int> heightMemo;
+    int height(int n) {  // of the operator tree below n (primitives: 0); iterative, chains can be thousands of links deep
+        if (heightMemo.empty()) heightMemo.assign((size_t)t->n_nodes, -1);
+        if (heightMemo[n] >= 0) return heightMemo[n];
+        std::vector<int> st{n};
+        while (!st.empty()) {
+            const int v = st.back();
+            bool ready = true;
+            int h = 0;
+            for (int i = 0; i < t->n_children[v]; i++) {
+                const int c = t->child[t->first_child[v] + i];
+                if (heightMemo[c] < 0) { if (ready) ready = false; st.push_back(c); }
+                else h = std::max(h, heightMemo[c] + 1);
+            }
+            if (ready) { heightMemo[v] = PSGPU_IS_PRIM(t->type[v]) ? 0 : h; st.pop_back(); }
+        }
+        return heightMemo[n];
+    }
     int opDepth = -1;  // depth of the operator being emitted in the reference's traversal (root operator = 0)
     // the reference's prune of an operator deeper than 3 levels (PS_Polygonizer.cpp:1228-1252): its value, alone on the stack top, is
     // masked by its box. Bottom-up masking gives what the reference's top-down skip gives: a pruned ancestor's 0 overrides its sub-tree
@@ -277,6 +296,18 @@ struct Emitter {
                 // one per chain link, and bit-identical (IEEE add / max / min commute; the differences have reverse codes).
                 emit(kids[1], CMB_PUSH, w);
                 emitPrim(kids[0], x == CMB_DIF ? (uint32_t)CMB_RDIF : (x == CMB_SDIF ? (uint32_t)CMB_RSDIF : x));
+                for (int i = 0; i < pops; i++) { quad(PS_HDR(OPC_POPPOINT, 0, false, 0)); p->nInstr++; pdepth--; }
+                combine(cmb);
+                return;
+            }
+            if (asShipped() && kids.size() == 2 && !PSGPU_IS_PRIM(t->type[kids[0]]) && !PSGPU_IS_PRIM(t->type[kids[1]]) &&
+                height(kids[1]) > height(kids[0])) {
+                // op(sub-tree, taller sub-tree): nothing is gathered in this mode, so a right-leaning chain of operators (what
+                // ConvertToBinaryTree makes of an n-ary union) would keep one stack entry per link. The taller side goes first and the
+                // combine takes its reverse code (same operands, same bits): a chain needs two entries.
+                emit(kids[1], CMB_PUSH, w);
+                emit(kids[0], CMB_PUSH, w);
+                combine(x == CMB_DIF ? (uint32_t)CMB_RDIF : (x == CMB_SDIF ? (uint32_t)CMB_RSDIF : x));
                 for (int i = 0; i < pops; i++) { quad(PS_HDR(OPC_POPPOINT, 0, false, 0)); p->nInstr++; pdepth--; }
                 combine(cmb);
                 return;
