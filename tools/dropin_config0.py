@@ -39,6 +39,7 @@ def timed(fn):
 ref_ms, ref_best, (ret, rst) = timed(lambda: ref.polygonize(cs))
 assert ret == 1, ret
 asis = dict(vertices=rst["vertices"], triangles=rst["triangles"])
+apos, anrm, acol, atri = ref.mesh(rst)  # the SHIPPED reference's mesh (its own operator boxes)
 # as-is the reference's depth>3 operator-box prune zeroes small field values near box corners (boxes padded by 0.504, support 1.0:
 # SURVEY Q8), which moves a few dozen vertices; the byte comparison is against the same build with that prune neutralised
 ref.pad_op_boxes(1.0e6)
@@ -61,6 +62,22 @@ same = dict(counts=(int(st[0]), nv, nt) == (rst["mpus"], rst["vertices"], rst["t
             pos=bool(np.array_equal(pos.view(np.uint32), rpos.view(np.uint32))), tri=bool(np.array_equal(tri, rtri)),
             col=bool(np.array_equal(col.view(np.uint32), rcol.view(np.uint32))),
             nrm_max_abs=float(np.nanmax(np.abs(nrm - rnrm))) if nv else 0.0)
+# ... and the facade in the shipped reference's own semantics (PSGPU_FACADE_AS_SHIPPED=1: its depth > 3 operator prune reproduced from the
+# caller's operator boxes) against the UNMODIFIED, unpadded reference run above: positions and indices (colours are uninitialised reads there)
+os.environ["PSGPU_FACADE_AS_SHIPPED"] = "1"
+sc2 = tf.Scene(lib, soa)
+assert lib.fac_prepare_bboxes(sc2.h, 0.05) == 1
+st2 = np.zeros(4, np.int64)
+ship_ms, _, ret2 = timed(lambda: lib.fac_polygonize(sc2.h, C.c_float(cs), st2.ctypes.data))
+assert ret2 == 1, ret2
+nv2, nt2 = int(st2[2]), int(st2[3])
+pos2, nrm2, col2 = (np.zeros((nv2, 3), np.float32) for _ in range(3))
+tri2 = np.zeros((nt2, 3), np.uint32)
+lib.fac_mesh_concat(sc2.h, pos2.ctypes.data, nrm2.ctypes.data, col2.ctypes.data, tri2.ctypes.data, None)
+eqf = lambda a, b: a.shape == b.shape and bool(((a.view(np.uint32) == b.view(np.uint32)) | (np.isnan(a) & np.isnan(b))).all())
+same_shipped = dict(counts=(nv2, nt2) == (asis["vertices"], asis["triangles"]), pos=eqf(pos2, apos), tri=bool(np.array_equal(tri2, atri)), ms_median=ship_ms)
+os.environ.pop("PSGPU_FACADE_AS_SHIPPED")
+sc2.close()
 n_cells = rst["mpus"] * 343
 print(json.dumps({
     "config": "configs[0] small@128^3 through Polygonize(cellsize, prims, mats, ops, PolyMPUs&), host buffers both sides",
@@ -69,5 +86,5 @@ print(json.dumps({
                   "ms_best": ref_best, "cells_per_s": n_cells / (ref_ms * 1e-3), "as_is_counts": asis, "ms_median_op_boxes_padded": pad_ms},
     "facade": {"build": "libpsgpu.so behind PS_SimdPolyCompat.h", "ms_median": fac_ms, "ms_best": fac_best,
                "cells_per_s": n_cells / (fac_ms * 1e-3), "includes": "SoA -> tree, linearize, upload, cull, field, MC, D2H, PolyMPUs fill"},
-    "speedup_median": ref_ms / fac_ms, "same_output": same}))
+    "speedup_median": ref_ms / fac_ms, "same_output": same, "same_output_as_shipped_mode_vs_unpadded_reference": same_shipped}))
 sc.close()
