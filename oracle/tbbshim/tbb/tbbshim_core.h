@@ -9,6 +9,7 @@
 #define TBBSHIM_CORE_H
 #include <atomic>
 #include <chrono>
+#include <condition_variable>
 #include <cstdlib>
 #include <cstring>   // real TBB headers pull these in transitively; the 2011-era reference relies on it
 #include <cstdio>
@@ -34,6 +35,62 @@ inline int num_threads() {
     unsigned hc = std::thread::hardware_concurrency();
     return hc ? (int)hc : 1;
 }
+// A warm worker pool, like the arena real TBB keeps between parallel algorithms (the first version of this shim created and joined
+// its pthreads in every parallel_for, which charged thread start-up - 256 MB stacks - to every Polygonize of the reference).
+// run(n, fn, arg): n workers call fn(arg) concurrently, the caller waits. Workers are created on demand and never exit.
+class Pool {
+public:
+    static Pool& get() { static Pool* p = new Pool(); return *p; }  // leaked on purpose: workers outlive static destruction
+    static bool& in_worker() { static thread_local bool w = false; return w; }
+    void run(int n, void (*fn)(void*), void* arg) {
+        if (n <= 0) return;
+        if (in_worker()) { fn(arg); return; }  // nested parallelism: serial (the reference does not nest)
+        std::lock_guard<std::mutex> one(m_callers);  // one parallel algorithm at a time
+        std::unique_lock<std::mutex> lk(m_m);
+        while ((int)m_threads.size() < n) {
+            pthread_attr_t attr; pthread_attr_init(&attr);
+            pthread_attr_setstacksize(&attr, (size_t)256 << 20);  // widened reference builds keep MAX_TREE_NODES-sized scratch arrays on the stack
+            Arg* a = new Arg{this, (int)m_threads.size()};
+            pthread_t t;
+            if (pthread_create(&t, &attr, &Pool::worker, a) != 0) { delete a; pthread_attr_destroy(&attr); break; }
+            pthread_attr_destroy(&attr);
+            m_threads.push_back(t);
+        }
+        if ((int)m_threads.size() < n) n = (int)m_threads.size();
+        if (n == 0) { lk.unlock(); fn(arg); return; }
+        m_fn = fn; m_arg = arg; m_want = n; m_running = n; m_epoch++;
+        m_work.notify_all();
+        m_done.wait(lk, [this] { return m_running == 0; });
+    }
+private:
+    struct Arg { Pool* pool; int idx; };
+    static void* worker(void* p) {
+        Arg* a = (Arg*)p;
+        Pool* P = a->pool;
+        const int idx = a->idx;
+        delete a;
+        in_worker() = true;
+        unsigned long long seen = 0;
+        std::unique_lock<std::mutex> lk(P->m_m);
+        for (;;) {
+            P->m_work.wait(lk, [&] { return P->m_epoch != seen; });
+            seen = P->m_epoch;
+            if (idx >= P->m_want) continue;
+            void (*fn)(void*) = P->m_fn; void* arg = P->m_arg;
+            lk.unlock();
+            fn(arg);
+            lk.lock();
+            if (--P->m_running == 0) P->m_done.notify_all();
+        }
+        return 0;
+    }
+    std::mutex m_m, m_callers;
+    std::condition_variable m_work, m_done;
+    std::vector<pthread_t> m_threads;
+    void (*m_fn)(void*) = 0; void* m_arg = 0;
+    int m_want = 0, m_running = 0;
+    unsigned long long m_epoch = 0;
+};
 }  // namespace shim
 
 class task_scheduler_observer {
@@ -88,7 +145,7 @@ void parallel_for(const Range& range, const Body& body) {
                  std::vector<task_scheduler_observer*>* obs; };
     Ctx ctx = { &range, &body, &next, chunk, n, &obs };
     struct Run {
-        static void* go(void* p) {
+        static void go(void* p) {
             Ctx* c = (Ctx*)p;
             for (size_t i = 0; i < c->obs->size(); i++) (*c->obs)[i]->on_scheduler_entry(true);
             for (;;) {
@@ -98,15 +155,9 @@ void parallel_for(const Range& range, const Body& body) {
                 Range sub(c->range->begin() + b, c->range->begin() + e);
                 (*c->body)(sub);
             }
-            return 0;
         }
     };
-    // big stacks: widened reference builds keep MAX_TREE_NODES-sized scratch arrays on the stack
-    pthread_attr_t attr; pthread_attr_init(&attr); pthread_attr_setstacksize(&attr, (size_t)256 << 20);
-    std::vector<pthread_t> th((size_t)nt);
-    for (int t = 0; t < nt; t++) pthread_create(&th[(size_t)t], &attr, Run::go, &ctx);
-    for (int t = 0; t < nt; t++) pthread_join(th[(size_t)t], 0);
-    pthread_attr_destroy(&attr);
+    shim::Pool::get().run(nt, &Run::go, &ctx);
 }
 template <typename Range, typename Body, typename Part>
 void parallel_for(const Range& range, const Body& body, const Part&) { parallel_for(range, body); }
