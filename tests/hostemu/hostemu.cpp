@@ -40,7 +40,7 @@ void hostemu_field_packed_columns(const float* quads, const float* xy, const flo
         P.x[0] = xy[c * 2]; P.y[0] = xy[c * 2 + 1];
         for (int i = 0; i < 4; i++) P.z[i] = pk(z[c * 8 + 2 * i], z[c * 8 + 2 * i + 1]);
         F2 F[4];
-        eval_program_packed<4, true, false>(prog, P, F, nullptr, nullptr, true);
+        eval_program_packed<4, true, false, false, true>(prog, P, F, nullptr, nullptr, true);
         for (int i = 0; i < 4; i++) up(F[i], f[c * 8 + 2 * i], f[c * 8 + 2 * i + 1]);
     }
 }
@@ -55,7 +55,7 @@ void hostemu_field_packed(const float* quads, const float* xyz, int64_t n, float
             P.x[i] = pk(a[0], a[3]); P.y[i] = pk(a[1], a[4]); P.z[i] = pk(a[2], a[5]);
         }
         F2 F[2];
-        eval_program_packed<2, false, false>(prog, P, F, nullptr, nullptr, true);  // the 4 points = one SIMD packet of the reference
+        eval_program_packed<2, false, false, false, true>(prog, P, F, nullptr, nullptr, true);  // the 4 points = one SIMD packet of the reference
         for (int i = 0; i < 2; i++) up(F[i], f[b + 2 * i], f[b + 2 * i + 1]);
     }
 }
@@ -71,7 +71,7 @@ void hostemu_field_color_packed(const float* quads, const float* colorTab, const
         P.y[0] = pk(py, py); P.y[1] = pk(py + delta, py);
         P.z[0] = pk(pz, pz); P.z[1] = pk(pz, pz + delta);
         F2 F[2];
-        eval_program_packed<2, false, false, true>(prog, P, F, col + i * 3, colorTab);
+        eval_program_packed<2, false, false, true, true>(prog, P, F, col + i * 3, colorTab);
         up(F[0], f4[i * 4], f4[i * 4 + 1]); up(F[1], f4[i * 4 + 2], f4[i * 4 + 3]);
     }
 }
