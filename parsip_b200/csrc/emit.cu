@@ -159,6 +159,8 @@ struct TriWarpSmem {
     uint32_t edgeW[48];
     uint16_t edgeP[48];
     uint16_t edgeVid[1536];  // PSGPU_OUT_MPU: reference-order local vertex id per edge bit
+    int32_t nbCand[8];       // candidate index of the neighbour MPU at (+dI, +dJ, +dK), slot dI | dJ << 1 | dK << 2; -1 = culled / outside
+    uint32_t nbVbase[8];     // ... and its vertex base: read once per MPU, not once per shared edge behind a dependent load
 };
 
 __device__ __forceinline__ uint32_t warp_excl_scan(uint32_t v, uint32_t& total) {
@@ -214,6 +216,14 @@ __global__ void __launch_bounds__(kThreads) tri_kernel(GridParams G, const Regio
             S.edgeP[32 + lane] = fo.edgePrefix[(size_t)cand * 48 + 32 + lane];
         }
         if (lane < 16) S.insideW[lane] = fo.inside[(size_t)cand * 16 + lane];  // 512 inside bits, as field_kernel classified them
+        if (lane >= 16 && lane < 24 && !perMpu) {
+            const int q = lane - 16, nx_ = r.x + (q & 1), ny_ = r.y + ((q >> 1) & 1), nz_ = r.z + (q >> 2);
+            int32_t nc = -1;
+            if (q != 0 && nx_ < G.hi[0] && ny_ < G.hi[1] && nz_ < G.hi[2])
+                nc = candOfMpu[((size_t)(nx_ - G.lo[0]) * ny + (ny_ - G.lo[1])) * nz + (nz_ - G.lo[2])];
+            S.nbCand[q] = nc;
+            S.nbVbase[q] = (nc >= 0) ? mo.vbase[nc] : 0u;
+        }
         __syncwarp();
 
         // ---- cube cases of this lane's cells, triangle count
@@ -348,11 +358,12 @@ __global__ void __launch_bounds__(kThreads) tri_kernel(GridParams G, const Regio
                                 vid = hb + mo.haloPrefix[h * 48 + (eb >> 5)] + __popc(w & (bit - 1u));
                             }
                         } else {
-                            const int32_t nc = candOfMpu[((size_t)(r.x + dI - G.lo[0]) * ny + (r.y + dJ - G.lo[1])) * nz + (r.z + dK - G.lo[2])];
+                            const int q = dI | (dJ << 1) | (dK << 2);
+                            const int32_t nc = S.nbCand[q];
                             if (nc >= 0) {  // a culled neighbour has no masks at all (index -1: the out-of-bounds read ADVICE r1 flagged)
                                 const uint32_t w = fo.edgeMask[(size_t)nc * 48 + (eb >> 5)];
                                 found = (w & bit) != 0u;
-                                vid = G.vertexOffset + mo.vbase[nc] + fo.edgePrefix[(size_t)nc * 48 + (eb >> 5)] + __popc(w & (bit - 1u));
+                                vid = G.vertexOffset + S.nbVbase[q] + fo.edgePrefix[(size_t)nc * 48 + (eb >> 5)] + __popc(w & (bit - 1u));
                             }
                         }
                         // The owner must have seen the same crossing: shared corners are evaluated from the same lattice
