@@ -29,6 +29,7 @@ else:
     ctx.upload(ps.linearize(flat_bin, ps.SEM_SIMD, 0))
     prm = ps.Params.make(cs, lo, hi, root_mode=ps.ROOT_FOURSAMPLE)
 if slab:
+    os.environ.setdefault("PSGPU_SLAB_PROGRAM_NOW", "1")  # the steady state of a sharded run: the slab program exists from the third frame on
     from parsip_b200 import sharding
     prm.z_begin, prm.z_end = sharding.slab_bounds(ps.lattice_dims(cs, lo, hi)[2], slab[1], slab[0])
 for i in range(3):
