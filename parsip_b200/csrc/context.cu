@@ -304,7 +304,7 @@ int run_cull(psgpu_ctx* ctx, const GridParams& G, int cullMode, bool colorExact,
         // The thread-per-MPU level too when it is the last one, its slots fit 4 GB and the program has warps: there a walk is dominated by
         // the warp-box arithmetic and walking twice costs more than the slot copy (csgwarp@512^3: cull 1.34 -> 1.22 ms); for warp-free
         // programs count + emit stays (blob1k@512^3: 0.67 vs 0.70 ms fused). No flags at the last level: the field kernel never reads them.
-        const bool warpLevel = prune_level_is_fused(nParents);
+        const bool warpLevel = prune_level_is_fused(L, nParents);
         const bool fused = !getenv("PSGPU_CULL_TWO_PASS") &&
                            (warpLevel ? scratchQuads <= ((size_t)64 << 20) : (last && ctx->hasWarps && scratchQuads <= ((size_t)256 << 20)));
         uint32_t* levelMax = ctx->scalars.as<uint32_t>() + 1 + lv;

@@ -510,12 +510,16 @@ void launch_all_mpus(const CullLevel& L, Region* out, uint32_t fullLen, int32_t*
 }
 
 // regions per level below which a warp per region pays (few regions, long parent programs)
-static bool use_warp_walk(int nParents) { return nParents * 64 <= 16384; }
+// A coarse level (regions of several MPUs, long parent programs) takes a warp per region up to 65 536 regions; the last level (single MPUs,
+// short programs: 190 000 of them on blob1k@512^3, where a warp each measured 1.57 ms against 0.61 ms) only when it is small.
+// (One threshold for both was a cliff: a rank's slab that touches THREE layers of 16^3 regions instead of two has 300 x 64 = 19 200 regions
+// at the 4^3 level, fell back to a thread per region there and culled in 1.9 ms instead of 1.3 ms.)
+static bool use_warp_walk(const CullLevel& L, int nParents) { return (long long)nParents * 64 <= (L.childSize == 1 ? 16384 : 65536); }
 
 void launch_prune_count(const CullLevel& L, const Region* parents, int nParents, const float4* pool, const uint8_t* qflag, uint32_t* childLen,
                         cudaStream_t st) {
     const int n = nParents * 64;
-    if (use_warp_walk(nParents)) prune_count_warp_kernel<<<(n + kCoopWarps - 1) / kCoopWarps, kCoopWarps * 32, 0, st>>>(L, parents, nParents, pool, qflag, childLen);
+    if (use_warp_walk(L, nParents)) prune_count_warp_kernel<<<(n + kCoopWarps - 1) / kCoopWarps, kCoopWarps * 32, 0, st>>>(L, parents, nParents, pool, qflag, childLen);
     else prune_count_kernel<<<(n + 127) / 128, 128, 0, st>>>(L, parents, nParents, pool, childLen);
 }
 
@@ -525,7 +529,7 @@ void launch_prune_emit(const CullLevel& L, const Region* parents, int nParents, 
                        const uint32_t* childOff, const uint32_t* childIdx, float4* outPool, uint8_t* outFlag, uint32_t outBase, Region* children,
                        int32_t* candOfMpu, uint32_t* maxLen, cudaStream_t st) {
     const int n = nParents * 64;
-    if (use_warp_walk(nParents))
+    if (use_warp_walk(L, nParents))
         prune_emit_warp_kernel<<<(n + kCoopWarps - 1) / kCoopWarps, kCoopWarps * 32, 0, st>>>(L, parents, nParents, pool, qflag, childLen, childOff, childIdx,
                                                                                              outPool, outFlag, outBase, children, candOfMpu, maxLen);
     else
@@ -533,7 +537,7 @@ void launch_prune_emit(const CullLevel& L, const Region* parents, int nParents, 
                                                            candOfMpu, maxLen);
 }
 
-bool prune_level_is_fused(int nParents) { return use_warp_walk(nParents); }
+bool prune_level_is_fused(const CullLevel& L, int nParents) { return use_warp_walk(L, nParents); }
 
 void launch_prune_fused(const CullLevel& L, const Region* parents, int nParents, const float4* pool, const uint8_t* qflag, float4* scratch,
                         uint8_t* scratchFlag, uint32_t stride, uint32_t* childLen, uint32_t* maxLen, bool ctaPerRegion, cudaStream_t st) {
@@ -542,7 +546,7 @@ void launch_prune_fused(const CullLevel& L, const Region* parents, int nParents,
         prune_fused_cta_kernel<<<n, kCtaWarps * 32, 0, st>>>(L, parents, nParents, pool, qflag, scratch, scratchFlag, stride, childLen, maxLen);
         return;
     }
-    if (!use_warp_walk(nParents)) {
+    if (!use_warp_walk(L, nParents)) {
         prune_fused_thread_kernel<<<(n + 127) / 128, 128, 0, st>>>(L, parents, nParents, pool, scratch, stride, childLen, maxLen);
         return;
     }

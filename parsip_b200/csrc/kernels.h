@@ -79,7 +79,7 @@ void launch_flags(const uint32_t* len, uint32_t* flag, int n, cudaStream_t st);
 void launch_prune_emit(const CullLevel& L, const Region* parents, int nParents, const float4* pool, const uint8_t* qflag, const uint32_t* childLen,
                        const uint32_t* childOff, const uint32_t* childIdx, float4* outPool, uint8_t* outFlag, uint32_t outBase, Region* children,
                        int32_t* candOfMpu, uint32_t* maxLen, cudaStream_t st);
-bool prune_level_is_fused(int nParents);
+bool prune_level_is_fused(const CullLevel& L, int nParents);
 void launch_prune_fused(const CullLevel& L, const Region* parents, int nParents, const float4* pool, const uint8_t* qflag, float4* scratch,
                         uint8_t* scratchFlag, uint32_t stride, uint32_t* childLen, uint32_t* maxLen, bool ctaPerRegion, cudaStream_t st);
 void launch_prune_compact(const CullLevel& L, const Region* parents, int nParents, const float4* scratch, const uint8_t* scratchFlag, uint32_t stride,

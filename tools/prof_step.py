@@ -15,6 +15,12 @@ for a in sys.argv[1:]:
     if a.startswith("--slab="):
         slab = tuple(int(v) for v in a.split("=")[1].split("/"))
         cells = 1024
+zrange = None  # --zrange=a,b : an explicit slab of MPU layers of blob10k@1024^3
+for a in sys.argv[1:]:
+    if a.startswith("--zrange="):
+        zrange = tuple(int(v) for v in a.split("=")[1].split(","))
+        slab = (0, 1)
+        cells = 1024
 csgwarp = "--csgwarp" in sys.argv  # BASELINE configs[2], native semantics only (the SIMD path ignores warps)
 root = scenes.csgwarp() if csgwarp else (scenes.blob10k() if slab else scenes.blob1k())
 native = native or csgwarp
@@ -31,7 +37,7 @@ else:
 if slab:
     os.environ.setdefault("PSGPU_SLAB_PROGRAM_NOW", "1")  # the steady state of a sharded run: the slab program exists from the third frame on
     from parsip_b200 import sharding
-    prm.z_begin, prm.z_end = sharding.slab_bounds(ps.lattice_dims(cs, lo, hi)[2], slab[1], slab[0])
+    prm.z_begin, prm.z_end = zrange if zrange else sharding.slab_bounds(ps.lattice_dims(cs, lo, hi)[2], slab[1], slab[0])
 for i in range(3):
     m = ctx.polygonize(prm, download=False)
     st = ctx.stats()
