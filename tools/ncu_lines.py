@@ -1,10 +1,11 @@
 """Development aid: per-SOURCE-LINE totals of an ncu capture. `ncu --page source --csv` prints SASS rows only; this joins them with the line
 table of the cubin (nvdisasm -g) by instruction offset.
-    python tools/ncu_lines.py <report.ncu-rep> <kernel regex> <cubin> [top N]"""
+    python tools/ncu_lines.py <report.ncu-rep> <kernel regex> <cubin> [top N] [regex of the mangled name]"""
 import csv, io, re, subprocess, sys, collections
 
 rep, kern, cubin = sys.argv[1:4]
 top = int(sys.argv[4]) if len(sys.argv) > 4 else 40
+mangled_re = sys.argv[5] if len(sys.argv) > 5 else kern  # the cubin's section names are mangled: give their regex if it differs
 out = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv", "--kernel-name", "regex:" + kern], capture_output=True, text=True).stdout
 rows = list(csv.reader(io.StringIO(out)))
 hi = [i for i, r in enumerate(rows) if r and r[0] == "Address"][0]
@@ -22,7 +23,7 @@ dis = subprocess.run(["nvdisasm", "-g", cubin], capture_output=True, text=True).
 mangled = None
 fn = re.search(r"(\w+)\(", name.split("::")[-1] if "::" in name else name)
 short = kern.split("|")[0]
-start = [i for i, l in enumerate(dis) if l.startswith(".text.") and re.search(kern, l)][0]
+start = [i for i, l in enumerate(dis) if l.startswith(".text.") and re.search(mangled_re, l)][0]
 line_of, cur = {}, None
 for l in dis[start + 1:]:
     if l.startswith("//-----") or l.startswith("\t.section"):
