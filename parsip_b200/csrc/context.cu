@@ -308,9 +308,9 @@ int run_cull(psgpu_ctx* ctx, const GridParams& G, int cullMode, bool colorExact,
         const bool fused = !getenv("PSGPU_CULL_TWO_PASS") &&
                            (warpLevel ? scratchQuads <= ((size_t)64 << 20) : (last && ctx->hasWarps && scratchQuads <= ((size_t)256 << 20)));
         uint32_t* levelMax = ctx->scalars.as<uint32_t>() + 1 + lv;
+        CK(cudaMemsetAsync(levelMax, 0, 4, st));
         if (fused) {
             CK(ctx->cullScratch.reserve(scratchQuads * 16)); CK(ctx->cullScratchFlag.reserve(warpLevel ? scratchQuads : 16));
-            CK(cudaMemsetAsync(levelMax, 0, 4, st));
             // few regions with a long program (the top level): a whole CTA per region instead of a warp
             const char* ctaMin = getenv("PSGPU_CULL_CTA_MINLEN");
             const char* ctaMaxN = getenv("PSGPU_CULL_CTA_MAXN");
@@ -319,13 +319,15 @@ int run_cull(psgpu_ctx* ctx, const GridParams& G, int cullMode, bool colorExact,
                                ctx->cullScratchFlag.as<uint8_t>(), parentMaxLen, ctx->childLen.as<uint32_t>(), levelMax, ctaPerRegion, st);
         } else
             launch_prune_count(L, cur->as<Region>(), nParents, ctx->pool.as<float4>(), ctx->qflag.as<uint8_t>(), ctx->childLen.as<uint32_t>(), st);
-        launch_flags(ctx->childLen.as<uint32_t>(), ctx->childFlag.as<uint32_t>(), n + 1, st);
+        // (two-pass levels: the longest pruned program is known once the lengths are - it comes back with the scan totals below, and
+        //  the emit pass and the field kernel follow without another host round trip)
+        launch_flags(ctx->childLen.as<uint32_t>(), ctx->childFlag.as<uint32_t>(), n + 1, st, fused ? nullptr : levelMax);
         exclusive_scan_u32(ctx->scanTemp.p, tb, ctx->childLen.as<uint32_t>(), ctx->childOff.as<uint32_t>(), n + 1, st);
         exclusive_scan_u32(ctx->scanTemp.p, tb, ctx->childFlag.as<uint32_t>(), ctx->childIdx.as<uint32_t>(), n + 1, st);
         launches += 4;
         CK(cudaMemcpyAsync(&ctx->hostScalars[0], ctx->childOff.as<uint32_t>() + n, 4, cudaMemcpyDeviceToHost, st));
         CK(cudaMemcpyAsync(&ctx->hostScalars[1], ctx->childIdx.as<uint32_t>() + n, 4, cudaMemcpyDeviceToHost, st));
-        if (fused) CK(cudaMemcpyAsync(&ctx->hostScalars[3], levelMax, 4, cudaMemcpyDeviceToHost, st));
+        CK(cudaMemcpyAsync(&ctx->hostScalars[3], levelMax, 4, cudaMemcpyDeviceToHost, st));
         CK(cudaStreamSynchronize(st));
         const uint32_t totalQuads = ctx->hostScalars[0], nChildren = ctx->hostScalars[1];
         if (fused && ctx->hostScalars[3] > parentMaxLen) { ctx->err = "pruned program longer than its parent"; return PSGPU_ERROR_CUDA; }
@@ -352,15 +354,12 @@ int run_cull(psgpu_ctx* ctx, const GridParams& G, int cullMode, bool colorExact,
         poolUsed += totalQuads;
         std::swap(cur, nxt);
         nParents = (int)nChildren;
+        if (last) maxLen = ctx->hostScalars[3];
         if (nParents == 0) break;
     }
     ctx->cands = cur->as<Region>();
     ctx->nCand = nParents;
-    if (nParents > 0) {
-        CK(cudaMemcpyAsync(&ctx->hostScalars[2], ctx->scalars.p, 4, cudaMemcpyDeviceToHost, st));
-        CK(cudaStreamSynchronize(st));
-        maxLen = ctx->hostScalars[2];
-    }
+    if (nParents == 0) maxLen = 0;
     return PSGPU_SUCCESS;
 }
 

@@ -452,9 +452,16 @@ __global__ void __launch_bounds__(kCoopWarps * 32) prune_compact_kernel(CullLeve
     }
 }
 
-__global__ void flag_kernel(const uint32_t* __restrict__ len, uint32_t* __restrict__ flag, int n) {
+// flag[i] = (len[i] != 0); maxOut (optional): the longest length, so that the host learns it in the read-back it makes for the scans
+// anyway instead of waiting for the emit pass to report it
+__global__ void flag_kernel(const uint32_t* __restrict__ len, uint32_t* __restrict__ flag, int n, uint32_t* __restrict__ maxOut) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < n) flag[i] = len[i] ? 1u : 0u;
+    const uint32_t v = i < n ? len[i] : 0u;
+    if (i < n) flag[i] = v ? 1u : 0u;
+    if (maxOut) {
+        const uint32_t m = __reduce_max_sync(0xFFFFFFFFu, v);
+        if ((threadIdx.x & 31) == 0 && m) atomicMax(maxOut, m);
+    }
 }
 
 // PSGPU_CULL_NONE: every MPU of the slab is a candidate running the full program
@@ -523,7 +530,9 @@ void launch_prune_count(const CullLevel& L, const Region* parents, int nParents,
     else prune_count_kernel<<<(n + 127) / 128, 128, 0, st>>>(L, parents, nParents, pool, childLen);
 }
 
-void launch_flags(const uint32_t* len, uint32_t* flag, int n, cudaStream_t st) { flag_kernel<<<(n + 255) / 256, 256, 0, st>>>(len, flag, n); }
+void launch_flags(const uint32_t* len, uint32_t* flag, int n, cudaStream_t st, uint32_t* maxOut) {
+    flag_kernel<<<(n + 255) / 256, 256, 0, st>>>(len, flag, n, maxOut);
+}
 
 void launch_prune_emit(const CullLevel& L, const Region* parents, int nParents, const float4* pool, const uint8_t* qflag, const uint32_t* childLen,
                        const uint32_t* childOff, const uint32_t* childIdx, float4* outPool, uint8_t* outFlag, uint32_t outBase, Region* children,
