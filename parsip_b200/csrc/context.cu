@@ -287,6 +287,7 @@ int run_cull(psgpu_ctx* ctx, const GridParams& G, int cullMode, bool colorExact,
     CK(cudaMemcpyAsync(cur->p, top.data(), top.size() * sizeof(Region), cudaMemcpyHostToDevice, st));
     int nParents = (int)top.size();
     CK(ctx->scalars.reserve(64));
+    CK(cudaMemsetAsync(ctx->scalars.p, 0, 64, st));  // [0] longest candidate program (two-pass emit), [1 + level] the levels' maxima
     maxLen = 0;
     uint32_t parentMaxLen = ctx->rootLen;  // longest program among the current level's parents
     for (size_t lv = 0; lv < sizes.size(); lv++) {
@@ -297,7 +298,6 @@ int run_cull(psgpu_ctx* ctx, const GridParams& G, int cullMode, bool colorExact,
         CK(ctx->childFlag.reserve((size_t)(n + 1) * 4)); CK(ctx->childIdx.reserve((size_t)(n + 1) * 4));
         const size_t tb = scan_temp_bytes(n + 1);
         CK(ctx->scanTemp.reserve(tb));
-        CK(cudaMemsetAsync(ctx->childLen.as<uint32_t>() + n, 0, 4, st));
         // coarse levels (few regions, long programs): ONE warp-cooperative walk per region into scratch slots, compacted after the scans;
         // the scratch bound keeps 10k-primitive trees within ~1 GB
         const size_t scratchQuads = (size_t)n * parentMaxLen;
@@ -308,7 +308,6 @@ int run_cull(psgpu_ctx* ctx, const GridParams& G, int cullMode, bool colorExact,
         const bool fused = !getenv("PSGPU_CULL_TWO_PASS") &&
                            (warpLevel ? scratchQuads <= ((size_t)64 << 20) : (last && ctx->hasWarps && scratchQuads <= ((size_t)256 << 20)));
         uint32_t* levelMax = ctx->scalars.as<uint32_t>() + 1 + lv;
-        CK(cudaMemsetAsync(levelMax, 0, 4, st));
         if (fused) {
             CK(ctx->cullScratch.reserve(scratchQuads * 16)); CK(ctx->cullScratchFlag.reserve(warpLevel ? scratchQuads : 16));
             // few regions with a long program (the top level): a whole CTA per region instead of a warp
@@ -321,7 +320,7 @@ int run_cull(psgpu_ctx* ctx, const GridParams& G, int cullMode, bool colorExact,
             launch_prune_count(L, cur->as<Region>(), nParents, ctx->pool.as<float4>(), ctx->qflag.as<uint8_t>(), ctx->childLen.as<uint32_t>(), st);
         // (two-pass levels: the longest pruned program is known once the lengths are - it comes back with the scan totals below, and
         //  the emit pass and the field kernel follow without another host round trip)
-        launch_flags(ctx->childLen.as<uint32_t>(), ctx->childFlag.as<uint32_t>(), n + 1, st, fused ? nullptr : levelMax);
+        launch_flags(ctx->childLen.as<uint32_t>(), ctx->childFlag.as<uint32_t>(), n + 1, st, fused ? nullptr : levelMax, true);  // closes childLen[n] = 0
         exclusive_scan_u32(ctx->scanTemp.p, tb, ctx->childLen.as<uint32_t>(), ctx->childOff.as<uint32_t>(), n + 1, st);
         exclusive_scan_u32(ctx->scanTemp.p, tb, ctx->childFlag.as<uint32_t>(), ctx->childIdx.as<uint32_t>(), n + 1, st);
         launches += 4;
@@ -335,7 +334,6 @@ int run_cull(psgpu_ctx* ctx, const GridParams& G, int cullMode, bool colorExact,
         CK(ctx->pool.reserve(((size_t)poolUsed + totalQuads + 16) * 16, true, st));
         CK(ctx->qflag.reserve((size_t)poolUsed + totalQuads + 16, true, st));
         CK(nxt->reserve(std::max((size_t)nChildren, (size_t)1) * sizeof(Region)));
-        if (last) CK(cudaMemsetAsync(ctx->scalars.p, 0, 4, st));
         if (nChildren > 0 && fused) {
             launch_prune_compact(L, cur->as<Region>(), nParents, ctx->cullScratch.as<float4>(), ctx->cullScratchFlag.as<uint8_t>(), parentMaxLen,
                                  ctx->childLen.as<uint32_t>(), ctx->childOff.as<uint32_t>(), ctx->childIdx.as<uint32_t>(), ctx->pool.as<float4>(),
@@ -531,8 +529,7 @@ int polygonize_impl(psgpu_ctx* ctx, const psgpu_params* P, psgpu_mesh* out, bool
         CK(ctx->mixedList.reserve((size_t)nCand * 4));
         CK(ctx->counters.reserve(64));
         CK(cudaMemsetAsync(ctx->counters.p, 0, 64, st));
-        CK(cudaMemsetAsync(ctx->vcount.as<uint32_t>() + nCand, 0, 4, st));
-        CK(cudaMemsetAsync(ctx->tcount.as<uint32_t>() + nCand, 0, 4, st));
+        // (the closing entries vcount[nCand] = tcount[nCand] = 0 of the scans below are written by field_kernel)
         FieldOutputs fo;
         fo.fv = ctx->fv.as<float4>(); fo.inside = ctx->inside.as<uint32_t>(); fo.vcount = ctx->vcount.as<uint32_t>(); fo.tcount = ctx->tcount.as<uint32_t>();
         fo.edgeMask = ctx->edgeMask.as<uint32_t>(); fo.edgePrefix = ctx->edgePrefix.as<uint16_t>();

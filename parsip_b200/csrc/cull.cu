@@ -454,9 +454,12 @@ __global__ void __launch_bounds__(kCoopWarps * 32) prune_compact_kernel(CullLeve
 
 // flag[i] = (len[i] != 0); maxOut (optional): the longest length, so that the host learns it in the read-back it makes for the scans
 // anyway instead of waiting for the emit pass to report it
-__global__ void flag_kernel(const uint32_t* __restrict__ len, uint32_t* __restrict__ flag, int n, uint32_t* __restrict__ maxOut) {
+// closeLen: element n - 1 of `len` is the closing entry of the scans that follow (the exclusive scan's last output is the total): it is
+// set to 0 here instead of by a memset of its own
+__global__ void flag_kernel(uint32_t* len, uint32_t* __restrict__ flag, int n, uint32_t* __restrict__ maxOut, int closeLen) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    const uint32_t v = i < n ? len[i] : 0u;
+    uint32_t v = i < n ? len[i] : 0u;
+    if (closeLen && i == n - 1) { v = 0u; len[i] = 0u; }
     if (i < n) flag[i] = v ? 1u : 0u;
     if (maxOut) {
         const uint32_t m = __reduce_max_sync(0xFFFFFFFFu, v);
@@ -530,8 +533,8 @@ void launch_prune_count(const CullLevel& L, const Region* parents, int nParents,
     else prune_count_kernel<<<(n + 127) / 128, 128, 0, st>>>(L, parents, nParents, pool, childLen);
 }
 
-void launch_flags(const uint32_t* len, uint32_t* flag, int n, cudaStream_t st, uint32_t* maxOut) {
-    flag_kernel<<<(n + 255) / 256, 256, 0, st>>>(len, flag, n, maxOut);
+void launch_flags(uint32_t* len, uint32_t* flag, int n, cudaStream_t st, uint32_t* maxOut, bool closeLen) {
+    flag_kernel<<<(n + 255) / 256, 256, 0, st>>>(len, flag, n, maxOut, closeLen ? 1 : 0);
 }
 
 void launch_prune_emit(const CullLevel& L, const Region* parents, int nParents, const float4* pool, const uint8_t* qflag, const uint32_t* childLen,

@@ -61,6 +61,7 @@ __global__ void __launch_bounds__(512 / kPts, kPts == 4 ? 6 : (STRICT ? PSGPU_ST
         mbar_init(&S.bar[0], 1);
         mbar_init(&S.bar[1], 1);
         fence_mbar_init();
+        if (blockIdx.x == 0) { out.vcount[nCand] = 0u; out.tcount[nCand] = 0u; }  // closing entries of the exclusive scans that follow
     }
     for (int i = t; i < 256; i += kThreads) {
         S.nTri[i] = c_nTri[i];

@@ -75,7 +75,7 @@ struct MeshOutputs {
 void launch_all_mpus(const CullLevel& L, Region* out, uint32_t fullLen, int32_t* candOfMpu, int n, cudaStream_t st);
 void launch_prune_count(const CullLevel& L, const Region* parents, int nParents, const float4* pool, const uint8_t* qflag, uint32_t* childLen,
                         cudaStream_t st);
-void launch_flags(const uint32_t* len, uint32_t* flag, int n, cudaStream_t st, uint32_t* maxOut = nullptr);
+void launch_flags(uint32_t* len, uint32_t* flag, int n, cudaStream_t st, uint32_t* maxOut = nullptr, bool closeLen = false);
 void launch_prune_emit(const CullLevel& L, const Region* parents, int nParents, const float4* pool, const uint8_t* qflag, const uint32_t* childLen,
                        const uint32_t* childOff, const uint32_t* childIdx, float4* outPool, uint8_t* outFlag, uint32_t outBase, Region* children,
                        int32_t* candOfMpu, uint32_t* maxLen, cudaStream_t st);
