@@ -64,7 +64,7 @@ struct psgpu_ctx {
     DevBuf qflag;     // one byte per pool quad: 1 = first quad of an instruction (read by the warp-cooperative pruning passes)
     DevBuf colors;
     // cull scratch
-    DevBuf regionsA, regionsB, childLen, childOff, childFlag, childIdx, scanTemp, candOfMpu, scalars, cullScratch, cullScratchFlag;
+    DevBuf regionsA, regionsB, childLen, childOff, childIdx, scanTemp, candOfMpu, scalars, cullScratch, cullScratchFlag;
     // field outputs
     DevBuf fv, inside, vcount, tcount, vbase, tbase, edgeMask, edgePrefix, mixedList, mixedFlag, mixedIdx, counters, statsAcc;
     // mesh
@@ -129,7 +129,7 @@ extern "C" int psgpu_destroy(psgpu_ctx* ctx) {
     if (!ctx) return PSGPU_PARAM_ERROR;
     cudaSetDevice(ctx->device);
     cudaStreamSynchronize(ctx->stream);
-    DevBuf* all[] = {&ctx->pool, &ctx->qflag, &ctx->colors, &ctx->regionsA, &ctx->regionsB, &ctx->childLen, &ctx->childOff, &ctx->childFlag, &ctx->childIdx,
+    DevBuf* all[] = {&ctx->pool, &ctx->qflag, &ctx->colors, &ctx->regionsA, &ctx->regionsB, &ctx->childLen, &ctx->childOff, &ctx->childIdx,
                      &ctx->scanTemp, &ctx->candOfMpu, &ctx->scalars, &ctx->cullScratch, &ctx->cullScratchFlag, &ctx->fv, &ctx->inside, &ctx->vcount, &ctx->tcount, &ctx->vbase, &ctx->tbase,
                      &ctx->edgeMask, &ctx->edgePrefix, &ctx->mixedList, &ctx->mixedFlag, &ctx->mixedIdx, &ctx->counters, &ctx->statsAcc,
                      &ctx->pos, &ctx->nrm, &ctx->col, &ctx->tri, &ctx->mpuIjk, &ctx->mpuVbase, &ctx->mpuTbase, &ctx->vperm, &ctx->ptsIn, &ctx->ptsF,
@@ -295,7 +295,7 @@ int run_cull(psgpu_ctx* ctx, const GridParams& G, int cullMode, bool colorExact,
         const bool last = (lv + 1 == sizes.size());
         const int n = nParents * 64;
         CK(ctx->childLen.reserve((size_t)(n + 1) * 4)); CK(ctx->childOff.reserve((size_t)(n + 1) * 4));
-        CK(ctx->childFlag.reserve((size_t)(n + 1) * 4)); CK(ctx->childIdx.reserve((size_t)(n + 1) * 4));
+        CK(ctx->childIdx.reserve((size_t)(n + 1) * 4));
         const size_t tb = scan_temp_bytes(n + 1);
         CK(ctx->scanTemp.reserve(tb));
         // coarse levels (few regions, long programs): ONE warp-cooperative walk per region into scratch slots, compacted after the scans;
@@ -317,13 +317,12 @@ int run_cull(psgpu_ctx* ctx, const GridParams& G, int cullMode, bool colorExact,
             launch_prune_fused(L, cur->as<Region>(), nParents, ctx->pool.as<float4>(), ctx->qflag.as<uint8_t>(), ctx->cullScratch.as<float4>(),
                                ctx->cullScratchFlag.as<uint8_t>(), parentMaxLen, ctx->childLen.as<uint32_t>(), levelMax, ctaPerRegion, st);
         } else
-            launch_prune_count(L, cur->as<Region>(), nParents, ctx->pool.as<float4>(), ctx->qflag.as<uint8_t>(), ctx->childLen.as<uint32_t>(), st);
+            launch_prune_count(L, cur->as<Region>(), nParents, ctx->pool.as<float4>(), ctx->qflag.as<uint8_t>(), ctx->childLen.as<uint32_t>(), levelMax, st);
         // (two-pass levels: the longest pruned program is known once the lengths are - it comes back with the scan totals below, and
         //  the emit pass and the field kernel follow without another host round trip)
-        launch_flags(ctx->childLen.as<uint32_t>(), ctx->childFlag.as<uint32_t>(), n + 1, st, fused ? nullptr : levelMax, true);  // closes childLen[n] = 0
-        exclusive_scan_u32(ctx->scanTemp.p, tb, ctx->childLen.as<uint32_t>(), ctx->childOff.as<uint32_t>(), n + 1, st);
-        exclusive_scan_u32(ctx->scanTemp.p, tb, ctx->childFlag.as<uint32_t>(), ctx->childIdx.as<uint32_t>(), n + 1, st);
-        launches += 4;
+        // pool offsets (sums of the lengths) and compacted indices (sums of the flags length != 0) of the children in one scan
+        exclusive_scan_pair(ctx->scanTemp.p, tb, ctx->childLen.as<uint32_t>(), nullptr, ctx->childOff.as<uint32_t>(), ctx->childIdx.as<uint32_t>(), n, st);
+        launches += 2;
         CK(cudaMemcpyAsync(&ctx->hostScalars[0], ctx->childOff.as<uint32_t>() + n, 4, cudaMemcpyDeviceToHost, st));
         CK(cudaMemcpyAsync(&ctx->hostScalars[1], ctx->childIdx.as<uint32_t>() + n, 4, cudaMemcpyDeviceToHost, st));
         CK(cudaMemcpyAsync(&ctx->hostScalars[3], levelMax, 4, cudaMemcpyDeviceToHost, st));
@@ -539,9 +538,8 @@ int polygonize_impl(psgpu_ctx* ctx, const psgpu_params* P, psgpu_mesh* out, bool
         CK(cudaEventRecord(ctx->ev[2], st));
         const size_t tb = scan_temp_bytes((int)n1);
         CK(ctx->scanTemp.reserve(tb));
-        exclusive_scan_u32(ctx->scanTemp.p, tb, fo.vcount, ctx->vbase.as<uint32_t>(), (int)n1, st);
-        exclusive_scan_u32(ctx->scanTemp.p, tb, fo.tcount, ctx->tbase.as<uint32_t>(), (int)n1, st);
-        launches += 2;
+        exclusive_scan_pair(ctx->scanTemp.p, tb, fo.vcount, fo.tcount, ctx->vbase.as<uint32_t>(), ctx->tbase.as<uint32_t>(), nCand, st);  // both bases in one scan
+        launches += 1;
         CK(cudaMemcpyAsync(&ctx->hostScalars[4], ctx->vbase.as<uint32_t>() + nCand, 4, cudaMemcpyDeviceToHost, st));
         CK(cudaMemcpyAsync(&ctx->hostScalars[5], ctx->tbase.as<uint32_t>() + nCand, 4, cudaMemcpyDeviceToHost, st));
         CK(cudaMemcpyAsync(&ctx->hostScalars[6], ctx->counters.as<uint32_t>(), 16, cudaMemcpyDeviceToHost, st));

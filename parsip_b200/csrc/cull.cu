@@ -10,6 +10,11 @@
 // (zero-folding rules of SURVEY Q16), and - PSGPU_CULL_INTERVAL - a region is dropped when interval bounds of
 // the field over the region exclude the iso value (no surface can cross it).
 #include <cub/device/device_scan.cuh>
+#include <thrust/iterator/counting_iterator.h>
+#include <thrust/iterator/transform_iterator.h>
+#include <thrust/iterator/transform_output_iterator.h>
+#include <thrust/iterator/zip_iterator.h>
+#include <thrust/tuple.h>
 
 #include "cull_walk.cuh"
 #include "kernels.h"
@@ -52,7 +57,8 @@ __device__ __forceinline__ void publish_child(const CullLevel& L, const int (&co
 }
 
 __global__ void __launch_bounds__(128) prune_count_kernel(CullLevel L, const Region* __restrict__ parents, int nParents,
-                                                          const float4* __restrict__ pool, uint32_t* __restrict__ childLen) {
+                                                          const float4* __restrict__ pool, uint32_t* __restrict__ childLen,
+                                                          uint32_t* __restrict__ maxLen) {
     const int tid = blockIdx.x * blockDim.x + threadIdx.x;
     if (tid >= nParents * 64) return;
     const Region parent = parents[tid >> 6];
@@ -62,6 +68,10 @@ __global__ void __launch_bounds__(128) prune_count_kernel(CullLevel L, const Reg
     if (child_region(L, parent, tid & 63, coord, box))
         len = prune_walk<false>(pool + parent.off, box, L.cullMode, L.iso, nullptr, L.colorExact != 0);
     childLen[tid] = len;
+    // the longest pruned program of the level (the host reads it back with the scan totals): one atomic per warp
+    const uint32_t act = __activemask();
+    const uint32_t m = __reduce_max_sync(act, len);
+    if (m && (threadIdx.x & 31) == __ffs((int)act) - 1) atomicMax(maxLen, m);
 }
 
 __global__ void __launch_bounds__(128) prune_emit_kernel(CullLevel L, const Region* __restrict__ parents, int nParents,
@@ -203,7 +213,7 @@ __device__ uint32_t prune_walk_warp(const float4* __restrict__ src, const uint8_
 
 __global__ void __launch_bounds__(kCoopWarps * 32) prune_count_warp_kernel(CullLevel L, const Region* __restrict__ parents, int nParents,
                                                                            const float4* __restrict__ pool, const uint8_t* __restrict__ qflag,
-                                                                           uint32_t* __restrict__ childLen) {
+                                                                           uint32_t* __restrict__ childLen, uint32_t* __restrict__ maxLen) {
     __shared__ CoopEntry sEnt[kCoopWarps][32];
     const int gw = blockIdx.x * kCoopWarps + (threadIdx.x >> 5);
     if (gw >= nParents * 64) return;
@@ -214,7 +224,10 @@ __global__ void __launch_bounds__(kCoopWarps * 32) prune_count_warp_kernel(CullL
     if (child_region(L, parent, gw & 63, coord, box))
         len = prune_walk_warp<false>(pool + parent.off, qflag + parent.off, parent.len, box, L.cullMode, L.iso, nullptr, nullptr, L.colorExact != 0,
                                      0xFFFFFFFFu, sEnt[threadIdx.x >> 5], L.nonNeg != 0);
-    if ((threadIdx.x & 31) == 0) childLen[gw] = len;
+    if ((threadIdx.x & 31) == 0) {
+        childLen[gw] = len;
+        if (len) atomicMax(maxLen, len);
+    }
 }
 
 __global__ void __launch_bounds__(kCoopWarps * 32) prune_emit_warp_kernel(CullLevel L, const Region* __restrict__ parents, int nParents,
@@ -452,19 +465,9 @@ __global__ void __launch_bounds__(kCoopWarps * 32) prune_compact_kernel(CullLeve
     }
 }
 
-// flag[i] = (len[i] != 0); maxOut (optional): the longest length, so that the host learns it in the read-back it makes for the scans
-// anyway instead of waiting for the emit pass to report it
-// closeLen: element n - 1 of `len` is the closing entry of the scans that follow (the exclusive scan's last output is the total): it is
-// set to 0 here instead of by a memset of its own
-__global__ void flag_kernel(uint32_t* len, uint32_t* __restrict__ flag, int n, uint32_t* __restrict__ maxOut, int closeLen) {
+__global__ void flag_kernel(const uint32_t* __restrict__ len, uint32_t* __restrict__ flag, int n) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    uint32_t v = i < n ? len[i] : 0u;
-    if (closeLen && i == n - 1) { v = 0u; len[i] = 0u; }
-    if (i < n) flag[i] = v ? 1u : 0u;
-    if (maxOut) {
-        const uint32_t m = __reduce_max_sync(0xFFFFFFFFu, v);
-        if ((threadIdx.x & 31) == 0 && m) atomicMax(maxOut, m);
-    }
+    if (i < n) flag[i] = len[i] ? 1u : 0u;
 }
 
 // PSGPU_CULL_NONE: every MPU of the slab is a candidate running the full program
@@ -527,15 +530,14 @@ void launch_all_mpus(const CullLevel& L, Region* out, uint32_t fullLen, int32_t*
 static bool use_warp_walk(const CullLevel& L, int nParents) { return (long long)nParents * 64 <= (L.childSize == 1 ? 16384 : 65536); }
 
 void launch_prune_count(const CullLevel& L, const Region* parents, int nParents, const float4* pool, const uint8_t* qflag, uint32_t* childLen,
-                        cudaStream_t st) {
+                        uint32_t* maxLen, cudaStream_t st) {
     const int n = nParents * 64;
-    if (use_warp_walk(L, nParents)) prune_count_warp_kernel<<<(n + kCoopWarps - 1) / kCoopWarps, kCoopWarps * 32, 0, st>>>(L, parents, nParents, pool, qflag, childLen);
-    else prune_count_kernel<<<(n + 127) / 128, 128, 0, st>>>(L, parents, nParents, pool, childLen);
+    if (use_warp_walk(L, nParents))
+        prune_count_warp_kernel<<<(n + kCoopWarps - 1) / kCoopWarps, kCoopWarps * 32, 0, st>>>(L, parents, nParents, pool, qflag, childLen, maxLen);
+    else prune_count_kernel<<<(n + 127) / 128, 128, 0, st>>>(L, parents, nParents, pool, childLen, maxLen);
 }
 
-void launch_flags(uint32_t* len, uint32_t* flag, int n, cudaStream_t st, uint32_t* maxOut, bool closeLen) {
-    flag_kernel<<<(n + 255) / 256, 256, 0, st>>>(len, flag, n, maxOut, closeLen ? 1 : 0);
-}
+void launch_flags(const uint32_t* len, uint32_t* flag, int n, cudaStream_t st) { flag_kernel<<<(n + 255) / 256, 256, 0, st>>>(len, flag, n); }
 
 void launch_prune_emit(const CullLevel& L, const Region* parents, int nParents, const float4* pool, const uint8_t* qflag, const uint32_t* childLen,
                        const uint32_t* childOff, const uint32_t* childIdx, float4* outPool, uint8_t* outFlag, uint32_t outBase, Region* children,
@@ -574,10 +576,44 @@ void launch_prune_compact(const CullLevel& L, const Region* parents, int nParent
                                                                                        childIdx, outPool, outFlag, outBase, children, candOfMpu);
 }
 
+// ---- two exclusive sums in one pass: the pair (a[i], b[i]) travels as one 64-bit value (neither total reaches 2^32: the callers
+// check the totals they read back), the results are split into two arrays again on the way out. n real elements; element n, the
+// closing entry whose scan output is the total, is a constant 0 of the input iterator - nothing to memset. b == nullptr: b[i] = (a[i] != 0),
+// i.e. the offsets AND the compacted indices of the non-empty entries from one array of lengths.
+namespace {
+struct PairIn {
+    const uint32_t* a;
+    const uint32_t* b;
+    int n;
+    __host__ __device__ unsigned long long operator()(int i) const {
+        if (i >= n) return 0ull;
+        const uint32_t x = a[i];
+        const uint32_t y = b ? b[i] : (x ? 1u : 0u);
+        return (unsigned long long)x | ((unsigned long long)y << 32);
+    }
+};
+struct PairOut {
+    __host__ __device__ thrust::tuple<uint32_t, uint32_t> operator()(unsigned long long v) const {
+        return thrust::make_tuple((uint32_t)v, (uint32_t)(v >> 32));
+    }
+};
+using PairInIt = thrust::transform_iterator<PairIn, thrust::counting_iterator<int>>;
+using PairOutIt = thrust::transform_output_iterator<PairOut, thrust::zip_iterator<thrust::tuple<uint32_t*, uint32_t*>>>;
+}  // namespace
+
 size_t scan_temp_bytes(int n) {
-    size_t bytes = 0;
+    size_t bytes = 0, pair = 0;
     cub::DeviceScan::ExclusiveSum(nullptr, bytes, (const uint32_t*)nullptr, (uint32_t*)nullptr, n);
-    return bytes;
+    PairInIt in(thrust::counting_iterator<int>(0), PairIn{nullptr, nullptr, 0});
+    PairOutIt out(thrust::make_zip_iterator(thrust::make_tuple((uint32_t*)nullptr, (uint32_t*)nullptr)), PairOut{});
+    cub::DeviceScan::ExclusiveSum(nullptr, pair, in, out, n);
+    return bytes > pair ? bytes : pair;
+}
+
+void exclusive_scan_pair(void* temp, size_t tempBytes, const uint32_t* a, const uint32_t* b, uint32_t* outA, uint32_t* outB, int n, cudaStream_t st) {
+    PairInIt in(thrust::counting_iterator<int>(0), PairIn{a, b, n});
+    PairOutIt out(thrust::make_zip_iterator(thrust::make_tuple(outA, outB)), PairOut{});
+    cub::DeviceScan::ExclusiveSum(temp, tempBytes, in, out, n + 1, st);
 }
 
 void exclusive_scan_u32(void* temp, size_t tempBytes, const uint32_t* in, uint32_t* out, int n, cudaStream_t st) {

@@ -74,8 +74,8 @@ struct MeshOutputs {
 // cull.cu
 void launch_all_mpus(const CullLevel& L, Region* out, uint32_t fullLen, int32_t* candOfMpu, int n, cudaStream_t st);
 void launch_prune_count(const CullLevel& L, const Region* parents, int nParents, const float4* pool, const uint8_t* qflag, uint32_t* childLen,
-                        cudaStream_t st);
-void launch_flags(uint32_t* len, uint32_t* flag, int n, cudaStream_t st, uint32_t* maxOut = nullptr, bool closeLen = false);
+                        uint32_t* maxLen, cudaStream_t st);
+void launch_flags(const uint32_t* len, uint32_t* flag, int n, cudaStream_t st);
 void launch_prune_emit(const CullLevel& L, const Region* parents, int nParents, const float4* pool, const uint8_t* qflag, const uint32_t* childLen,
                        const uint32_t* childOff, const uint32_t* childIdx, float4* outPool, uint8_t* outFlag, uint32_t outBase, Region* children,
                        int32_t* candOfMpu, uint32_t* maxLen, cudaStream_t st);
@@ -91,6 +91,8 @@ void launch_prune_one(const float4* prog, const float* lo, const float* hi, int 
                       uint32_t* lenOut, cudaStream_t st);
 size_t scan_temp_bytes(int n);
 void exclusive_scan_u32(void* temp, size_t tempBytes, const uint32_t* in, uint32_t* out, int n, cudaStream_t st);
+// outA / outB[0..n] = exclusive sums of a[0..n) and of b[0..n) (b == nullptr: of the flags a[i] != 0) in ONE pass; entry n = the totals
+void exclusive_scan_pair(void* temp, size_t tempBytes, const uint32_t* a, const uint32_t* b, uint32_t* outA, uint32_t* outB, int n, cudaStream_t st);
 
 // field.cu
 int field_kernel_smem_bytes(uint32_t maxProgQuads, uint32_t* progCapQuads);
