@@ -110,7 +110,8 @@ typedef struct psgpu_stats {
     float ms_cull, ms_field, ms_scan, ms_emit, ms_total; /* CUDA-event times of the last polygonize */
     int64_t gpu_launches;     /* kernels launched by the last polygonize */
     float ms_tri, ms_vertex, ms_color; /* the three kernels inside ms_emit */
-    float ms_exchange;                 /* psgpu_polygonize_sharded: count all-gather + halo send/recv (inside ms_total) */
+    float ms_exchange;                 /* psgpu_polygonize_sharded: what the compute stream waited for the count all-gather + halo send/recv
+                                          (they run on a stream of their own beside the vertex / colour kernels; inside ms_total) */
     int64_t vertex_eval_flops; /* collect_stats: sum over surface MPUs of vertices x SURVEY 8(d) op count of the MPU's pruned program,
                                   i.e. the algorithmic work of ONE field evaluation per vertex (a vertex costs 8: 4 root samples,
                                   4 gradient samples; its colour walk 1 more) */
@@ -127,7 +128,7 @@ typedef struct psgpu_shard {
     int32_t z_begin, z_end;          /* MPU layers of this rank */
     int64_t vertex_offset, triangle_offset;
     int64_t total_vertices, total_triangles;
-    float ms_exchange;               /* count all-gather + halo exchange, CUDA events on the context's stream */
+    float ms_exchange;               /* what the compute stream waited for the count all-gather + halo exchange (CUDA events) */
     int32_t stitched;                /* 1: boundary vertices exist once and tri[] is globally indexed */
 } psgpu_shard;
 

@@ -52,6 +52,7 @@ struct psgpu_ctx {
     int numSMs = 148;
     cudaStream_t stream = nullptr;
     cudaStream_t copyStream = nullptr;  // device -> host mesh copies that overlap the emission kernels (psgpu_polygonize_host)
+    cudaStream_t commStream = nullptr;  // NCCL exchange of a stitched run, beside the vertex / colour kernels (highest priority)
     std::string err;
     // program
     uint32_t progQuads = 0;
@@ -70,7 +71,8 @@ struct psgpu_ctx {
     // mesh
     DevBuf pos, nrm, col, tri, mpuIjk, mpuVbase, mpuTbase, vperm;
     DevBuf ptsIn, ptsF, ptsCol, ptsNrm;
-    uint32_t* hostScalars = nullptr;  // pinned readback
+    uint32_t* hostScalars = nullptr;  // pinned readback; [20 ..) = the ranks' {vertices, triangles} of a stitched run
+    static constexpr int kHostScalars = 1024;
     void* hostStage = nullptr;        // pinned upload staging (program + colours)
     size_t hostStageCap = 0;
     void* hostMesh = nullptr;         // pinned arena behind psgpu_mesh_map_host
@@ -117,9 +119,14 @@ extern "C" int psgpu_create(int device, psgpu_ctx** out) {
     cudaDeviceGetAttribute(&ctx->numSMs, cudaDevAttrMultiProcessorCount, device);
     if (cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking) != cudaSuccess) { delete ctx; return PSGPU_ERROR_CUDA; }
     if (cudaStreamCreateWithFlags(&ctx->copyStream, cudaStreamNonBlocking) != cudaSuccess) { delete ctx; return PSGPU_ERROR_CUDA; }
+    {
+        int prLo = 0, prHi = 0;
+        cudaDeviceGetStreamPriorityRange(&prLo, &prHi);
+        if (cudaStreamCreateWithPriority(&ctx->commStream, cudaStreamNonBlocking, prHi) != cudaSuccess) { delete ctx; return PSGPU_ERROR_CUDA; }
+    }
     bool ok = true;
     for (auto& e : ctx->ev) { e = nullptr; ok = ok && cudaEventCreate(&e) == cudaSuccess; }
-    ok = ok && cudaMallocHost(&ctx->hostScalars, 64 * sizeof(uint32_t)) == cudaSuccess;
+    ok = ok && cudaMallocHost(&ctx->hostScalars, psgpu_ctx::kHostScalars * sizeof(uint32_t)) == cudaSuccess;
     if (!ok) { psgpu_destroy(ctx); return PSGPU_ERROR_CUDA; }
     *out = ctx;
     return PSGPU_SUCCESS;
@@ -141,6 +148,7 @@ extern "C" int psgpu_destroy(psgpu_ctx* ctx) {
     if (ctx->hostStage) cudaFreeHost(ctx->hostStage);
     if (ctx->hostMesh) cudaFreeHost(ctx->hostMesh);
     cudaStreamDestroy(ctx->copyStream);
+    if (ctx->commStream) cudaStreamDestroy(ctx->commStream);
     cudaStreamDestroy(ctx->stream);
     delete ctx;
     return PSGPU_SUCCESS;
@@ -227,6 +235,7 @@ int fill_grid(psgpu_ctx* ctx, const psgpu_params* P, GridParams& G) {
     G.forceFv = 0;
     G.zOwnLast = G.hi[2] - 1;
     G.vertexOffset = 0u;
+    G.haloVertexOffset = 0u;
     G.iso = (P->iso > 0.f) ? P->iso : PS_ISO_VALUE;
     return PSGPU_SUCCESS;
 }
@@ -422,33 +431,29 @@ struct ShardCtl {
     psgpu_shard* info;
 };
 
-// Count exchange + halo exchange of a stitched z-slab run, on the context's stream between the scans and the emission kernels:
+// Count exchange + halo exchange of a stitched z-slab run, on the context's COMMUNICATION stream, enqueued once the scans are through
+// and before the vertex / colour kernels are launched on the compute stream - those need nothing from the other ranks, so a rank that
+// reaches this point early computes while it waits for its neighbours instead of idling in the collective:
 //   1. ncclAllGather of {vertices, triangles} (16 bytes per rank) -> every rank's global vertex / triangle offset;
-//   2. every rank but the first sends the table of its FIRST MPU layer (global vertex base + crossing-edge mask / prefix per MPU)
+//   2. every rank but the first sends the table of its FIRST MPU layer (rank-local vertex base + crossing-edge mask / prefix per MPU)
 //      to the rank below, which resolves the edges of its closing z-plane through it (tri_kernel) - the lower-z rank does not emit
 //      those vertices, so the ranks' meshes concatenate to the single-GPU mesh (same vertex count, same triangle soup).
-int shard_exchange(psgpu_ctx* ctx, GridParams& G, uint32_t nV, uint32_t nT, const FieldOutputs* fo, MeshOutputs& mo, psgpu_shard* info) {
+// shard_exchange_finish waits for both (host side: the offsets become kernel parameters of tri_kernel) and leaves ev[9] for the
+// compute stream to wait on.
+int shard_exchange_begin(psgpu_ctx* ctx, const GridParams& G, uint32_t nV, uint32_t nT, const FieldOutputs* fo, MeshOutputs& mo) {
     psgpu::NcclApi& N = psgpu::nccl_api();
-    cudaStream_t st = ctx->stream;
+    cudaStream_t cs = ctx->commStream;  // (the host has read the scans' totals: everything the halo table is built from is complete)
     const int R = ctx->nranks, me = ctx->rank;
-    CK(cudaEventRecord(ctx->ev[8], st));
+    if (20 + 4 * R > psgpu_ctx::kHostScalars) { ctx->err = "too many ranks"; return PSGPU_PARAM_ERROR; }
+    CK(cudaEventRecord(ctx->ev[8], cs));
     CK(ctx->shardCounts.reserve((size_t)(2 + 2 * R) * 8));
     uint64_t* hsend = reinterpret_cast<uint64_t*>(&ctx->hostScalars[16]);
     hsend[0] = nV; hsend[1] = nT;
     uint64_t* dsend = ctx->shardCounts.as<uint64_t>();
     uint64_t* drecv = dsend + 2;
-    CK(cudaMemcpyAsync(dsend, hsend, 16, cudaMemcpyHostToDevice, st));
-    NK(N.AllGather(dsend, drecv, 2, psgpu::NcclApi::kUint64, ctx->comm, st));
-    ctx->rankCounts.assign((size_t)2 * R, 0);
-    CK(cudaMemcpyAsync(ctx->rankCounts.data(), drecv, (size_t)2 * R * 8, cudaMemcpyDeviceToHost, st));
-    CK(cudaStreamSynchronize(st));
-    uint64_t vOff = 0, tOff = 0, vTot = 0, tTot = 0;
-    for (int r = 0; r < R; r++) {
-        if (r < me) { vOff += ctx->rankCounts[2 * r]; tOff += ctx->rankCounts[2 * r + 1]; }
-        vTot += ctx->rankCounts[2 * r]; tTot += ctx->rankCounts[2 * r + 1];
-    }
-    if (vTot >= ((uint64_t)1 << 32)) { ctx->err = "stitched mesh exceeds 2^32 vertices"; return PSGPU_NOT_ENOUGH_MEM; }
-    G.vertexOffset = (uint32_t)vOff;
+    CK(cudaMemcpyAsync(dsend, hsend, 16, cudaMemcpyHostToDevice, cs));
+    NK(N.AllGather(dsend, drecv, 2, psgpu::NcclApi::kUint64, ctx->comm, cs));
+    CK(cudaMemcpyAsync(&ctx->hostScalars[20], drecv, (size_t)2 * R * 8, cudaMemcpyDeviceToHost, cs));  // pinned: does not block the host
     const int nx = G.hi[0] - G.lo[0], ny = G.hi[1] - G.lo[1];
     const size_t nxy = (size_t)nx * ny;
     const size_t bytes = nxy * (4 + 192 + 96);
@@ -460,16 +465,32 @@ int shard_exchange(psgpu_ctx* ctx, GridParams& G, uint32_t nV, uint32_t nT, cons
     if (me > 0) {
         CK(ctx->haloSend.reserve(bytes));
         carve(ctx->haloSend, sv, sm, sp);
-        if (fo) launch_halo_build(G, ctx->candOfMpu.as<int32_t>(), *fo, ctx->vbase.as<uint32_t>(), sv, sm, sp, (int)nxy, st);
-        else CK(cudaMemsetAsync(sv, 0xFF, nxy * 4, st));  // no candidates in this slab: no surface anywhere in the layer
+        if (fo) launch_halo_build(G, ctx->candOfMpu.as<int32_t>(), *fo, ctx->vbase.as<uint32_t>(), sv, sm, sp, (int)nxy, cs);
+        else CK(cudaMemsetAsync(sv, 0xFF, nxy * 4, cs));  // no candidates in this slab: no surface anywhere in the layer
     }
     if (me < R - 1) { CK(ctx->haloRecv.reserve(bytes)); carve(ctx->haloRecv, rv, rm, rp); }
     NK(N.GroupStart());
-    if (me > 0) NK(N.Send(sv, bytes, psgpu::NcclApi::kUint8, me - 1, ctx->comm, st));
-    if (me < R - 1) NK(N.Recv(rv, bytes, psgpu::NcclApi::kUint8, me + 1, ctx->comm, st));
+    if (me > 0) NK(N.Send(sv, bytes, psgpu::NcclApi::kUint8, me - 1, ctx->comm, cs));
+    if (me < R - 1) NK(N.Recv(rv, bytes, psgpu::NcclApi::kUint8, me + 1, ctx->comm, cs));
     NK(N.GroupEnd());
     mo.haloVbase = rv; mo.haloMask = rm; mo.haloPrefix = rp;
-    CK(cudaEventRecord(ctx->ev[9], st));
+    CK(cudaEventRecord(ctx->ev[9], cs));
+    return PSGPU_SUCCESS;
+}
+
+int shard_exchange_finish(psgpu_ctx* ctx, GridParams& G, psgpu_shard* info) {
+    const int R = ctx->nranks, me = ctx->rank;
+    CK(cudaStreamSynchronize(ctx->commStream));
+    const uint64_t* got = reinterpret_cast<const uint64_t*>(&ctx->hostScalars[20]);
+    ctx->rankCounts.assign(got, got + (size_t)2 * R);
+    uint64_t vOff = 0, tOff = 0, vTot = 0, tTot = 0;
+    for (int r = 0; r < R; r++) {
+        if (r < me) { vOff += ctx->rankCounts[2 * r]; tOff += ctx->rankCounts[2 * r + 1]; }
+        vTot += ctx->rankCounts[2 * r]; tTot += ctx->rankCounts[2 * r + 1];
+    }
+    if (vTot >= ((uint64_t)1 << 32)) { ctx->err = "stitched mesh exceeds 2^32 vertices"; return PSGPU_NOT_ENOUGH_MEM; }
+    G.vertexOffset = (uint32_t)vOff;
+    G.haloVertexOffset = (uint32_t)(vOff + ctx->rankCounts[2 * me]);  // = the vertex offset of the rank above
     if (info) {
         info->nranks = R; info->rank = me; info->z_begin = G.lo[2]; info->z_end = G.hi[2];
         info->vertex_offset = (int64_t)vOff; info->triangle_offset = (int64_t)tOff;
@@ -565,37 +586,59 @@ int polygonize_impl(psgpu_ctx* ctx, const psgpu_params* P, psgpu_mesh* out, bool
             CK(cudaMemcpyAsync(ctx->mpuVbase.as<uint32_t>() + nMixed, ctx->vbase.as<uint32_t>() + nCand, 4, cudaMemcpyDeviceToDevice, st));
             CK(cudaMemcpyAsync(ctx->mpuTbase.as<uint32_t>() + nMixed, ctx->tbase.as<uint32_t>() + nCand, 4, cudaMemcpyDeviceToDevice, st));
         }
-        if (stitch) {
-            rc = shard_exchange(ctx, G, nV, nT, &fo, mo, shard->info);
+        if (stitch) {  // enqueued on the communication stream; nothing on the compute stream waits for it before tri_kernel
+            rc = shard_exchange_begin(ctx, G, nV, nT, &fo, mo);
             if (rc != PSGPU_SUCCESS) return rc;
             launches++;
         }
         if (sink && ((int64_t)nV > sink->capV || (int64_t)nT > sink->capT)) {
+            if (stitch) shard_exchange_finish(ctx, G, shard->info);  // the other ranks are in the same collectives
             ctx->err = "host buffers too small";
             M.n_vertices = nV; M.n_triangles = nT;
             if (out) *out = M;
             return PSGPU_NOT_ENOUGH_MEM;
         }
         CK(cudaEventRecord(ctx->ev[3], st));
-        if (nMixed > 0) {
+        // A stitched run: vertex and colour kernels first (they need nothing from the other ranks), tri_kernel - global vertex
+        // offsets, halo table of the rank above - once the exchange is through; what a rank would wait for its neighbours is
+        // spent computing. Otherwise tri_kernel first: its output is ready soonest and leaves for the host while the others run.
+        const bool lateTri = stitch;
+        if (lateTri) {
+            if (nMixed > 0)
+                launch_emit_kernels(G, ctx->cands, ctx->pool.as<float4>(), ctx->colors.as<float>(), fo, mo, ctx->candOfMpu.as<int32_t>(), (int)nMixed,
+                                    maxLen, ctx->numSMs, st, nullptr, ctx->ev[6], PS_EMIT_VERTEX_COLOR);
+            CK(cudaEventRecord(ctx->ev[7], st));
+            rc = shard_exchange_finish(ctx, G, shard->info);
+            if (rc != PSGPU_SUCCESS) return rc;
+            CK(cudaStreamWaitEvent(st, ctx->ev[9], 0));
+            if (nMixed > 0)
+                launch_emit_kernels(G, ctx->cands, ctx->pool.as<float4>(), ctx->colors.as<float>(), fo, mo, ctx->candOfMpu.as<int32_t>(), (int)nMixed,
+                                    maxLen, ctx->numSMs, st, ctx->ev[5], nullptr, PS_EMIT_TRI);
+        } else if (nMixed > 0)
             launch_emit_kernels(G, ctx->cands, ctx->pool.as<float4>(), ctx->colors.as<float>(), fo, mo, ctx->candOfMpu.as<int32_t>(), (int)nMixed,
                                 maxLen, ctx->numSMs, st, ctx->ev[5], ctx->ev[6]);
-            launches += 2 + (G.wantColors ? 1 : 0);  // tri_kernel, vertex_kernel, color_kernel
-        }
+        if (nMixed > 0) launches += 2 + (G.wantColors ? 1 : 0);  // tri_kernel, vertex_kernel, color_kernel
         CK(cudaEventRecord(ctx->ev[4], st));
         if (sink && nMixed > 0 && P->output == PSGPU_OUT_INDEXED) {
             // each array leaves for the host as soon as the kernel that writes it is done: triangles behind tri_kernel (while
-            // vertex_kernel runs), positions + normals behind vertex_kernel (while color_kernel runs), colours last
+            // vertex_kernel runs), positions + normals behind vertex_kernel (while color_kernel runs), colours last; in a stitched
+            // run (tri_kernel last) the triangles go last
             cudaStream_t cs = ctx->copyStream;
-            CK(cudaStreamWaitEvent(cs, ctx->ev[5], 0));
-            if (sink->tri && nT) CK(cudaMemcpyAsync(sink->tri, ctx->tri.p, (size_t)nT * 12, cudaMemcpyDeviceToHost, cs));
+            const bool nrmLate = normals_in_color_pass(G);  // then the colour pass writes them
+            if (!lateTri) {
+                CK(cudaStreamWaitEvent(cs, ctx->ev[5], 0));
+                if (sink->tri && nT) CK(cudaMemcpyAsync(sink->tri, ctx->tri.p, (size_t)nT * 12, cudaMemcpyDeviceToHost, cs));
+            }
             CK(cudaStreamWaitEvent(cs, ctx->ev[6], 0));
             if (sink->pos && nV) CK(cudaMemcpyAsync(sink->pos, ctx->pos.p, (size_t)nV * 12, cudaMemcpyDeviceToHost, cs));
-            const bool nrmLate = normals_in_color_pass(G);  // then the colour pass writes them
             if (sink->nrm && nV && P->want_normals && !nrmLate) CK(cudaMemcpyAsync(sink->nrm, ctx->nrm.p, (size_t)nV * 12, cudaMemcpyDeviceToHost, cs));
-            CK(cudaStreamWaitEvent(cs, ctx->ev[4], 0));
+            CK(cudaStreamWaitEvent(cs, lateTri ? ctx->ev[7] : ctx->ev[4], 0));
             if (sink->nrm && nV && P->want_normals && nrmLate) CK(cudaMemcpyAsync(sink->nrm, ctx->nrm.p, (size_t)nV * 12, cudaMemcpyDeviceToHost, cs));
             if (sink->col && nV && P->want_colors) CK(cudaMemcpyAsync(sink->col, ctx->col.p, (size_t)nV * 12, cudaMemcpyDeviceToHost, cs));
+            if (lateTri) {
+                CK(cudaStreamWaitEvent(cs, ctx->ev[5], 0));
+                if (sink->tri && nT) CK(cudaMemcpyAsync(sink->tri, ctx->tri.p, (size_t)nT * 12, cudaMemcpyDeviceToHost, cs));
+            }
             streamed = true;
         }
         if (P->collect_stats) {
@@ -612,7 +655,9 @@ int polygonize_impl(psgpu_ctx* ctx, const psgpu_params* P, psgpu_mesh* out, bool
         CK(cudaEventRecord(ctx->ev[2], st));
         if (stitch) {  // an empty slab still takes part in the collectives
             MeshOutputs mo{};
-            rc = shard_exchange(ctx, G, 0u, 0u, nullptr, mo, shard->info);
+            CK(cudaEventRecord(ctx->ev[7], st));
+            rc = shard_exchange_begin(ctx, G, 0u, 0u, nullptr, mo);
+            if (rc == PSGPU_SUCCESS) rc = shard_exchange_finish(ctx, G, shard->info);
             if (rc != PSGPU_SUCCESS) return rc;
         }
         CK(cudaEventRecord(ctx->ev[3], st)); CK(cudaEventRecord(ctx->ev[4], st));
@@ -628,12 +673,23 @@ int polygonize_impl(psgpu_ctx* ctx, const psgpu_params* P, psgpu_mesh* out, bool
     cudaEventElapsedTime(&S.ms_scan, ctx->ev[2], ctx->ev[3]);
     cudaEventElapsedTime(&S.ms_emit, ctx->ev[3], ctx->ev[4]);
     cudaEventElapsedTime(&S.ms_total, ctx->ev[0], ctx->ev[4]);
-    if (nMixed > 0) {
+    if (stitch) {
+        // what the compute stream waited for the exchange: from the end of the colour kernel (ev[7]) to the end of the exchange on
+        // the communication stream (ev[9]), 0 when the exchange was through by then. ms_total - ms_exchange = the rank's own work.
+        float w = 0.f;
+        cudaEventElapsedTime(&w, ctx->ev[7], ctx->ev[9]);
+        S.ms_exchange = w > 0.f ? w : 0.f;
+    }
+    if (nMixed > 0 && stitch) {  // vertex, colour, then tri_kernel
+        cudaEventElapsedTime(&S.ms_vertex, ctx->ev[3], ctx->ev[6]);
+        cudaEventElapsedTime(&S.ms_color, ctx->ev[6], ctx->ev[7]);
+        cudaEventElapsedTime(&S.ms_tri, ctx->ev[7], ctx->ev[5]);
+        S.ms_tri = S.ms_tri > S.ms_exchange ? S.ms_tri - S.ms_exchange : 0.f;
+    } else if (nMixed > 0) {
         cudaEventElapsedTime(&S.ms_tri, ctx->ev[3], ctx->ev[5]);
         cudaEventElapsedTime(&S.ms_vertex, ctx->ev[5], ctx->ev[6]);
         cudaEventElapsedTime(&S.ms_color, ctx->ev[6], ctx->ev[4]);
     }
-    if (stitch) cudaEventElapsedTime(&S.ms_exchange, ctx->ev[8], ctx->ev[9]);
     if (shard && shard->info) shard->info->ms_exchange = S.ms_exchange;
     if (nMixed > 0 && P->output == PSGPU_OUT_INDEXED) {
         // edges whose owner did not report the crossing (tri_kernel): never expected, never silent

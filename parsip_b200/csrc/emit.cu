@@ -355,7 +355,7 @@ __global__ void __launch_bounds__(kThreads) tri_kernel(GridParams G, const Regio
                             if (hb != 0xFFFFFFFFu) {
                                 const uint32_t w = mo.haloMask[h * 48 + (eb >> 5)];
                                 found = (w & bit) != 0u;
-                                vid = hb + mo.haloPrefix[h * 48 + (eb >> 5)] + __popc(w & (bit - 1u));
+                                vid = G.haloVertexOffset + hb + mo.haloPrefix[h * 48 + (eb >> 5)] + __popc(w & (bit - 1u));
                             }
                         } else {
                             const int q = dI | (dJ << 1) | (dK << 2);
@@ -531,8 +531,9 @@ __global__ void __launch_bounds__(kThreads) color_kernel(GridParams G, const Reg
 
 }  // namespace
 
-// first-layer table this rank sends to the rank below (see tri_kernel): per (x, y) the GLOBAL vertex base of the MPU at the slab's
-// first z-layer and its crossing-edge mask / prefix, or 0xFFFFFFFF where that MPU has no surface
+// first-layer table this rank sends to the rank below (see tri_kernel): per (x, y) the vertex base of the MPU at the slab's first
+// z-layer WITHIN THIS RANK's arrays (the receiver adds this rank's global offset, GridParams.haloVertexOffset - so the table does not
+// wait for the count exchange) and its crossing-edge mask / prefix, or 0xFFFFFFFF where that MPU has no surface
 __global__ void halo_build_kernel(GridParams G, const int32_t* __restrict__ candOfMpu, FieldOutputs fo, const uint32_t* __restrict__ vbase,
                                   uint32_t* __restrict__ hVbase, uint32_t* __restrict__ hMask, uint16_t* __restrict__ hPrefix, int nxy) {
     const int h = blockIdx.x * (blockDim.x / 32) + (threadIdx.x >> 5), lane = threadIdx.x & 31;
@@ -540,7 +541,7 @@ __global__ void halo_build_kernel(GridParams G, const int32_t* __restrict__ cand
     const int nz = G.hi[2] - G.lo[2];
     const int32_t c = candOfMpu[(size_t)h * nz];
     const bool ok = c >= 0 && fo.tcount[c] != 0u;
-    if (lane == 0) hVbase[h] = ok ? G.vertexOffset + vbase[c] : 0xFFFFFFFFu;
+    if (lane == 0) hVbase[h] = ok ? vbase[c] : 0xFFFFFFFFu;
     for (int w = lane; w < 48; w += 32) {
         hMask[(size_t)h * 48 + w] = ok ? fo.edgeMask[(size_t)c * 48 + w] : 0u;
         hPrefix[(size_t)h * 48 + w] = ok ? fo.edgePrefix[(size_t)c * 48 + w] : (uint16_t)0;
@@ -577,9 +578,9 @@ bool normals_in_color_pass(const GridParams& G) {
 
 void launch_emit_kernels(const GridParams& G, const Region* cands, const float4* pool, const float* colorTab, const FieldOutputs& fo,
                          const MeshOutputs& mo, const int32_t* candOfMpu, int nMixed, uint32_t maxProgQuads, int numSMs, cudaStream_t st,
-                         cudaEvent_t evTriDone, cudaEvent_t evVertexDone) {
+                         cudaEvent_t evTriDone, cudaEvent_t evVertexDone, int phase) {
     if (nMixed <= 0) return;
-    {
+    if (phase != PS_EMIT_VERTEX_COLOR) {
         int perSM = 0;
         cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSM, tri_kernel, kThreads, 0);
         if (perSM < 1) perSM = 1;
@@ -589,6 +590,7 @@ void launch_emit_kernels(const GridParams& G, const Region* cands, const float4*
         tri_kernel<<<grid, kThreads, 0, st>>>(G, cands, fo, mo, candOfMpu, nMixed);
         if (evTriDone) cudaEventRecord(evTriDone, st);
     }
+    if (phase == PS_EMIT_TRI) return;
     const bool strict = (G.sem == PSGPU_SEM_SIMD);
     // per-warp staging slice = the longest list (multiple of 8 quads); up to 32 KB of dynamic shared memory per CTA
     uint32_t slice = (maxProgQuads + 7u) & ~7u;

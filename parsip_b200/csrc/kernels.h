@@ -44,6 +44,7 @@ struct GridParams {
     // closing plane and the others resolve those edges through the halo table of the rank above)
     int zOwnLast;
     uint32_t vertexOffset;  // added to every vertex id this rank writes into tri[] (global numbering across ranks)
+    uint32_t haloVertexOffset;  // the same of the rank above: added to the (rank-local) vertex bases of its halo table
 };
 
 // per-candidate outputs of the field kernel
@@ -66,7 +67,7 @@ struct MeshOutputs {
     int32_t* mpuIjk; uint32_t* mpuVbase; uint32_t* mpuTbase;
     uint16_t* vperm;           // PSGPU_OUT_MPU: [vertex base + edge rank] -> reference-order local vertex id
     // halo of the rank above (first MPU layer of its slab), indexed x * ny + y; null when this slab owns its closing plane
-    const uint32_t* haloVbase;   // GLOBAL vertex base of the MPU, 0xFFFFFFFF = no surface there
+    const uint32_t* haloVbase;   // vertex base of the MPU within ITS rank's arrays (+ GridParams.haloVertexOffset), 0xFFFFFFFF = no surface there
     const uint32_t* haloMask;    // [.][48]
     const uint16_t* haloPrefix;  // [.][48]
 };
@@ -111,9 +112,12 @@ void launch_cube_cases(const GridParams& G, const float* fv, uint8_t* case343, c
 void launch_halo_build(const GridParams& G, const int32_t* candOfMpu, const FieldOutputs& fo, const uint32_t* vbase, uint32_t* hVbase,
                        uint32_t* hMask, uint16_t* hPrefix, int nxy, cudaStream_t st);
 bool normals_in_color_pass(const GridParams& G);
+// phase: a stitched multi-rank run launches the vertex and colour kernels first (they need nothing from the other ranks) and
+// tri_kernel once the exchange with the neighbours is through (vertex offsets, halo table of the rank above)
+enum { PS_EMIT_ALL = 0, PS_EMIT_VERTEX_COLOR = 1, PS_EMIT_TRI = 2 };
 void launch_emit_kernels(const GridParams& G, const Region* cands, const float4* pool, const float* colorTab, const FieldOutputs& fo,
                          const MeshOutputs& mo, const int32_t* candOfMpu, int nMixed, uint32_t maxProgQuads, int numSMs, cudaStream_t st,
-                         cudaEvent_t evTriDone = nullptr, cudaEvent_t evVertexDone = nullptr);
+                         cudaEvent_t evTriDone = nullptr, cudaEvent_t evVertexDone = nullptr, int phase = PS_EMIT_ALL);
 
 }  // namespace psgpu
 #endif
