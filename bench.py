@@ -12,8 +12,8 @@ the job / device time of the step (field evals/s, triangles/s and ms per polygon
                the SAME job on more GPUs; `strong_scaling` in the line relates it to the same job timed on one GPU in the same run
 
 GPU arm: the scene is linearized on the host, uploaded once, and every step runs psgpu_polygonize_sharded (at N = 1 that is
-psgpu_polygonize): cull -> field -> scans -> [count all-gather + boundary halo exchange over NCCL] -> emit, all on the library's
-stream between its own CUDA events - the SAME clock at every N, max over ranks (`value`). Then, for `e2e`, upload of the
+psgpu_polygonize): cull -> field -> scans -> vertex + colour kernels [beside them, on a stream of its own: count all-gather +
+boundary halo exchange over NCCL] -> tri_kernel, between the library's own CUDA events on its compute stream - the SAME clock at every N, max over ranks (`value`). Then, for `e2e`, upload of the
 program from pinned host memory + polygonize + the rank's mesh share into pinned host buffers, timed by wall clock.
 Both arms run the SAME semantics (PS_SimdPoly: infinite lines, inside = f >= iso, 4-sample + lerp roots), so
 the meshes are comparable; `native` adds the numbers of the canonical mode (segments, bracketed root search).
@@ -410,7 +410,7 @@ def run_gpu(args):
         torch.cuda.synchronize()
 
     # ---- device-resident steps: `value`. One clock at every N: the library's CUDA events around cull .. emit on its own stream,
-    # which at N > 1 includes the NCCL count all-gather and the halo exchange (they run on that stream between the scans and emit).
+    # which at N > 1 includes the NCCL count all-gather and the halo exchange (they run on the library's communication stream beside the vertex / colour kernels; tri_kernel, which needs their results, waits for them).
     for _ in range(args.warmup):
         m = ctx.polygonize_sharded(prm)
     sampler = ClockSampler(local)
